@@ -1,0 +1,171 @@
+/* nr_sm100.h — C ABI of libnr_sm100.so: the B200 (sm_100a) kernels behind the
+ * NRMS/NAML train-and-eval hot path of patngnw/NewsRecommendation.
+ *
+ * Boundary contract:
+ *  - extern "C", plain pointers and sizes, no torch types.  Every pointer is a
+ *    DEVICE pointer unless its name ends in _host.  The caller (the PyTorch
+ *    host code in newsrecommendation_b200/) owns every buffer, including the
+ *    workspace; the library allocates nothing that outlives a call.
+ *  - All work is enqueued on `stream` (a cudaStream_t passed as void*); no
+ *    internal synchronisation.  Thread safe: no mutable globals except the
+ *    thread-local error string.
+ *  - Return 0 = ok; non-zero = error, text via nr_last_error().  Shapes
+ *    outside the compiled envelope are an ERROR, never a fallback.
+ *  - "reference" citations are file:line under /root/reference/ of the code
+ *    each entry point replaces.
+ *
+ * Row sources.  Several ops read an activation X of logical shape
+ * (n, S, D) through an `nr_rows_t`:
+ *   mode NR_ROWS_DENSE : X = dense (n*S, D) row-major fp32
+ *   mode NR_ROWS_TOKEN : X[i,s,:] = table[ids[i*ids_stride + s], :]      (A1:
+ *                        nn.Embedding word lookup, src/model/NRMS.py:28)
+ *   mode NR_ROWS_NEWS  : X[i,s,:] = table[ids[i*ids_stride], s*D:(s+1)*D] (A2:
+ *                        per-news title row, src/model/NAML.py:47-50)
+ * followed, when training with drop_p > 0, by inverted dropout whose keep mask
+ * is the counter-based stream (seed, stream id, element index i*S*D + s*D + d)
+ * exported by nr_dropout_keep_mask (F.dropout at NRMS.py:28-30, NAML.py:51-53).
+ */
+#ifndef NR_SM100_H
+#define NR_SM100_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NR_ABI_VERSION 1
+
+enum { NR_ROWS_DENSE = 0, NR_ROWS_TOKEN = 1, NR_ROWS_NEWS = 2 };
+/* arithmetic mode of the GEMM-shaped parts: fp32 SIMT (parity mode, rel 1e-5)
+ * or bf16 operands on tcgen05 tensor cores with fp32 TMEM accumulation. */
+enum { NR_PREC_FP32 = 0, NR_PREC_BF16 = 1 };
+/* dropout stream ids */
+enum { NR_STREAM_IN = 1, NR_STREAM_OUT = 2 };
+
+typedef struct nr_rows {
+    int32_t mode;          /* NR_ROWS_* */
+    int32_t ids_stride;    /* int32 elements between consecutive sequences in ids */
+    const float* dense;    /* NR_ROWS_DENSE */
+    const float* table;    /* NR_ROWS_TOKEN / NR_ROWS_NEWS */
+    const int32_t* ids;
+    int64_t table_rows;    /* bound check: ids must lie in [0, table_rows) */
+    float drop_p;          /* 0 => no dropout */
+    uint64_t seed;
+} nr_rows_t;
+
+/* ---- library ------------------------------------------------------------ */
+int nr_abi_version(void);
+const char* nr_last_error(void);
+/* sm count / compute capability of the current device */
+int nr_device_info(int32_t* sm_count, int32_t* cc_major, int32_t* cc_minor);
+
+/* keep[i] = 1 if element i of dropout stream (seed, stream_id) is kept at rate p */
+int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed,
+                         int32_t stream_id, void* stream);
+
+/* ---- A1/A2: embedding row gather (bit exact) ---------------------------------
+ * out[i,:] = table[ids[i],:], width fp32 elements per row (width % 4 == 0).
+ * reference: nn.Embedding lookups src/model/NRMS.py:28, src/model/NAML.py:48;
+ * eval gathers src/dataset.py:68,72. */
+int nr_gather_rows(const float* table, int64_t table_rows, const int32_t* ids,
+                   int64_t count, int32_t width, float* out, void* stream);
+
+/* ---- A6: AttentionPooling (src/model/model_utils.py:7-31) ----------------------
+ * x (n,S,H), mask (n,S) or NULL, w1 (Q,H), b1 (Q), w2 (Q), b2 (1) -> out (n,H).
+ * e_save (n,S,Q) and alpha_save (n,S) are written for backward. */
+size_t nr_attention_pooling_workspace(int64_t n, int32_t S, int32_t H, int32_t Q, int32_t prec);
+int nr_attention_pooling_fwd(const float* x, const float* mask, const float* w1, const float* b1,
+                             const float* w2, const float* b2, float* out, float* e_save,
+                             float* alpha_save, int64_t n, int32_t S, int32_t H, int32_t Q,
+                             int32_t prec, void* ws, size_t ws_bytes, void* stream);
+/* g (n,H) -> dx (n,S,H) written; dw1,db1,dw2,db2 ACCUMULATED (+=). dx may be NULL. */
+int nr_attention_pooling_bwd(const float* g, const float* x, const float* w1, const float* w2,
+                             const float* e_save, const float* alpha_save, float* dx, float* dw1,
+                             float* db1, float* dw2, float* db2, int64_t n, int32_t S, int32_t H,
+                             int32_t Q, int32_t prec, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- A4/A5: MultiHeadSelfAttention with Q=K=V=X (model_utils.py:34-95) ----------
+ * X through `rows` (n,S,Dm); key_mask (n,S) or NULL; w* (H,Dm), b* (H), H=heads*dk.
+ * ctx (n,S,H) = heads concatenated, after output dropout (stream NR_STREAM_OUT,
+ * rate out_drop_p; src/model/NRMS.py:32-34).  qkv_save (n,S,3H) kept for backward. */
+size_t nr_mhsa_workspace(int64_t n, int32_t S, int32_t Dm, int32_t H, int32_t prec);
+int nr_mhsa_fwd(const nr_rows_t* rows, const float* key_mask, const float* wq, const float* bq,
+                const float* wk, const float* bk, const float* wv, const float* bv, float* ctx,
+                float* qkv_save, int64_t n, int32_t S, int32_t Dm, int32_t heads, int32_t dk,
+                float out_drop_p, int32_t prec, void* ws, size_t ws_bytes, void* stream);
+/* dctx (n,S,H) -> weight and bias grads ACCUMULATED; dx_dense (n,S,Dm) written if non-NULL;
+ * dtable (same shape as rows.table) ACCUMULATED by scatter-add if non-NULL (token / news
+ * rows; row 0 = padding_idx gets no gradient, src/model/NRMS.py:73). */
+int nr_mhsa_bwd(const nr_rows_t* rows, const float* key_mask, const float* wq, const float* wk,
+                const float* wv, const float* qkv_save, const float* dctx, float* dwq, float* dbq,
+                float* dwk, float* dbk, float* dwv, float* dbv, float* dx_dense, float* dtable,
+                int64_t n, int32_t S, int32_t Dm, int32_t heads, int32_t dk, float out_drop_p,
+                int32_t prec, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- A7: Conv1d(k=3, pad=1) along tokens (src/model/NAML.py:27-32,54) ------------
+ * X through `rows` (n,L,D); w (H,D,3) as nn.Conv1d.weight, b (H) -> y (n,L,H). */
+size_t nr_conv1d_k3_workspace(int64_t n, int32_t L, int32_t D, int32_t H, int32_t prec);
+int nr_conv1d_k3_fwd(const nr_rows_t* rows, const float* w, const float* b, float* y, int64_t n,
+                     int32_t L, int32_t D, int32_t H, int32_t prec, void* ws, size_t ws_bytes,
+                     void* stream);
+/* dy -> dw, db ACCUMULATED; dx_dense (n,L,D) written if non-NULL (dense rows);
+ * dtable ACCUMULATED by scatter-add if non-NULL (token / news rows; row 0 skipped). */
+int nr_conv1d_k3_bwd(const nr_rows_t* rows, const float* w, const float* dy, float* dw, float* db,
+                     float* dx_dense, float* dtable, int64_t n, int32_t L, int32_t D, int32_t H,
+                     int32_t prec, void* ws, size_t ws_bytes, void* stream);
+
+/* ---- A8: NAML side view: dense(emb[ids]) (src/model/NAML.py:60-68) ---------------
+ * out[i*out_stride : +H] = w (H,E) . emb[ids[i*ids_stride]] + b. */
+int nr_embed_dense_fwd(const float* emb, int64_t emb_rows, const int32_t* ids, int32_t ids_stride,
+                       const float* w, const float* b, float* out, int64_t out_stride, int64_t n,
+                       int32_t E, int32_t H, void* stream);
+/* dout (row stride dout_stride) -> dw, db, demb ACCUMULATED (emb row 0 = padding_idx skipped) */
+int nr_embed_dense_bwd(const float* emb, int64_t emb_rows, const int32_t* ids, int32_t ids_stride,
+                       const float* w, const float* dout, int64_t dout_stride, float* dw, float* db,
+                       float* demb, int64_t n, int32_t E, int32_t H, void* ws, size_t ws_bytes,
+                       void* stream);
+
+/* ---- A9/A10: pad_doc blend (src/model/NRMS.py:59-60, src/model/NAML.py:94-95) ----
+ * out = v*m + pad*(1-m);  v (n,T,H), m (n,T), pad (H). */
+int nr_pad_blend_fwd(const float* v, const float* mask, const float* pad, float* out, int64_t n,
+                     int32_t T, int32_t H, void* stream);
+/* dv written (= dout*m); dpad ACCUMULATED (= sum dout*(1-m)) */
+int nr_pad_blend_bwd(const float* dout, const float* mask, float* dv, float* dpad, int64_t n,
+                     int32_t T, int32_t H, void* stream);
+
+/* ---- A11: candidate scoring + CrossEntropyLoss (NRMS.py:93-94, NAML.py:128-129) --
+ * cand (B,C,H), user (B,H), label (B) int64 -> score (B,C), loss (1) mean CE,
+ * hits (1) = #argmax==label (utils.acc, src/utils.py:36-40). */
+int nr_score_ce_fwd(const float* cand, const float* user, const int64_t* label, float* score,
+                    float* loss, float* hits, float* per_sample_ws, int64_t B, int32_t C,
+                    int32_t H, void* stream);
+/* gloss (1) upstream grad of loss -> dcand (B,C,H), duser (B,H) written */
+int nr_score_ce_bwd(const float* cand, const float* user, const int64_t* label, const float* score,
+                    const float* gloss, float* dcand, float* duser, int64_t B, int32_t C, int32_t H,
+                    void* stream);
+
+/* ---- A12: fused Adam over a flat fp32 bucket (torch.optim.Adam defaults, main.py:76)
+ * g is multiplied by grad_scale first (1/world_size folded in after the all-reduce). */
+int nr_adam_step(float* p, const float* g, float* m, float* v, int64_t count, float lr, float beta1,
+                 float beta2, float eps, int32_t step, float grad_scale, void* stream);
+
+/* ---- A14: eval impression scoring (src/dataset.py:64-74, src/main.py:253) ---------
+ * scores[j] = table[cand_idx[j],:] . user_vecs[imp(j),:], impressions as CSR offsets (I+1). */
+int nr_eval_score(const float* table, int64_t table_rows, const float* user_vecs,
+                  const int64_t* offsets, const int32_t* cand_idx, float* scores, int64_t I,
+                  int64_t total_cands, int32_t H, void* stream);
+/* ---- A15: ranking metrics (src/metrics.py:1-23, src/main.py:250-258) ---------------
+ * per impression i: metrics[i*4..] = AUC, MRR, nDCG@5, nDCG@10 (fp64); valid[i]=0 for the
+ * skipped impressions (labels all 0 or all 1).  Ties ranked higher-index-first. */
+int nr_eval_rank_metrics(const float* scores, const int8_t* labels, const int64_t* offsets,
+                         double* metrics, uint8_t* valid, int64_t I, void* stream);
+/* sums[0..3] = sum over valid impressions, sums[4] = #valid (deterministic order) */
+int nr_eval_reduce_metrics(const double* metrics, const uint8_t* valid, double* sums, int64_t I,
+                           void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NR_SM100_H */

@@ -1,0 +1,310 @@
+// nr_basic.cu — library plumbing and the HBM-bound elementwise/gather ops.
+#include <stdarg.h>
+#include "nr_common.cuh"
+
+namespace nr {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int check_last(const char* what) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        set_error("%s: kernel launch failed: %s", what, cudaGetErrorString(e));
+        return 3;
+    }
+    return 0;
+}
+
+RowsView make_rows_view(const nr_rows_t* r, int64_t n, int S, int D) {
+    RowsView v;
+    v.mode = r->mode;
+    v.dense = r->dense;
+    v.table = r->table;
+    v.ids = r->ids;
+    v.ids_stride = r->ids_stride;
+    v.S = S;
+    v.D = D;
+    v.rows = n * S;
+    v.thr = r->drop_p > 0.f ? drop_threshold(r->drop_p) : 0u;
+    v.scale = r->drop_p > 0.f ? 1.0f / (1.0f - r->drop_p) : 1.0f;
+    v.seed = r->seed;
+    return v;
+}
+
+int validate_rows(const nr_rows_t* r, const char* who) {
+    NR_REQUIRE(r != nullptr, "%s: rows is NULL", who);
+    NR_REQUIRE(r->mode >= NR_ROWS_DENSE && r->mode <= NR_ROWS_NEWS, "%s: bad rows.mode %d", who, r->mode);
+    if (r->mode == NR_ROWS_DENSE) {
+        NR_REQUIRE(r->dense != nullptr, "%s: rows.dense is NULL", who);
+    } else {
+        NR_REQUIRE(r->table != nullptr && r->ids != nullptr, "%s: rows.table/ids is NULL", who);
+        NR_REQUIRE(r->ids_stride >= 1, "%s: rows.ids_stride must be >= 1", who);
+    }
+    NR_REQUIRE(r->drop_p >= 0.f && r->drop_p < 1.f, "%s: drop_p %f outside [0,1)", who, r->drop_p);
+    return 0;
+}
+
+// ---- kernels -----------------------------------------------------------------------------
+// A1/A2 gather: one float4 per thread; consecutive threads walk one row -> 128-bit coalesced.
+__global__ void gather_rows_kernel(const float* __restrict__ table, const int32_t* __restrict__ ids,
+                                   float* __restrict__ out, int64_t total4, int w4) {
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total4;
+         t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / w4;
+        const int q = (int)(t - i * w4);
+        const int64_t id = __ldg(ids + i);
+        ((float4*)out)[t] = __ldg((const float4*)table + id * w4 + q);
+    }
+}
+
+__global__ void keep_mask_kernel(uint8_t* keep, int64_t count, uint32_t thr, uint64_t seed, uint32_t sid) {
+    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q * 4 < count;
+         q += (int64_t)gridDim.x * blockDim.x) {
+        const uint4 r = philox4(seed, sid, (uint64_t)q);
+        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+        for (int j = 0; j < 4; ++j)
+            if (q * 4 + j < count) keep[q * 4 + j] = w[j] >= thr ? 1 : 0;
+    }
+}
+
+__global__ void pad_blend_fwd_kernel(const float* __restrict__ v, const float* __restrict__ mask,
+                                     const float* __restrict__ pad, float* __restrict__ out,
+                                     int64_t rows, int h4) {
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < rows * h4;
+         t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = t / h4;
+        const int q = (int)(t - r * h4);
+        const float m = __ldg(mask + r);
+        const float4 a = __ldg((const float4*)v + t);
+        const float4 p = __ldg((const float4*)pad + q);
+        const float im = 1.f - m;   // v*m + pad*(1-m), same association as NRMS.py:60
+        ((float4*)out)[t] = make_float4(a.x * m + p.x * im, a.y * m + p.y * im, a.z * m + p.z * im,
+                                        a.w * m + p.w * im);
+    }
+}
+
+// dv = dout*m ; dpad += sum_r dout*(1-m).  grid.x blocks each own a strided set of rows.
+__global__ void pad_blend_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ mask,
+                                     float* __restrict__ dv, float* __restrict__ dpad, int64_t rows, int H) {
+    for (int c = threadIdx.x; c < H; c += blockDim.x) {
+        float acc = 0.f;
+        for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
+            const float m = __ldg(mask + r);
+            const float g = __ldg(dout + r * H + c);
+            dv[r * H + c] = g * m;
+            acc += g * (1.f - m);
+        }
+        atomicAdd(dpad + c, acc);
+    }
+}
+
+// score + CE: one warp per sample.
+__global__ void score_ce_fwd_kernel(const float* __restrict__ cand, const float* __restrict__ user,
+                                    const int64_t* __restrict__ label, float* __restrict__ score,
+                                    float* __restrict__ per_sample, int64_t B, int C, int H) {
+    const int lane = threadIdx.x & 31;
+    const int64_t b = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (b >= B) return;
+    const float* u = user + b * H;
+    float mx = -INFINITY, picked = 0.f;
+    int arg = 0;
+    const int lab = (int)label[b];
+    for (int k = 0; k < C; ++k) {
+        const float* c = cand + (b * C + k) * H;
+        float s = 0.f;
+        for (int h = lane; h < H; h += 32) s = fmaf(__ldg(c + h), __ldg(u + h), s);
+        s = warp_sum(s);
+        if (lane == 0) score[b * C + k] = s;
+        if (s > mx) { mx = s; arg = k; }    // first maximum, as torch.argmax
+        if (k == lab) picked = s;
+    }
+    float z = 0.f;
+    for (int k = 0; k < C; ++k) {
+        const float* c = cand + (b * C + k) * H;
+        float s = 0.f;
+        for (int h = lane; h < H; h += 32) s = fmaf(__ldg(c + h), __ldg(u + h), s);
+        s = warp_sum(s);
+        z += expf(s - mx);
+    }
+    if (lane == 0) {
+        per_sample[b * 2 + 0] = (mx + logf(z)) - picked;
+        per_sample[b * 2 + 1] = (arg == lab) ? 1.f : 0.f;
+    }
+}
+
+// fixed-order reduction of the per-sample losses -> mean loss, hit count (deterministic)
+__global__ void score_ce_reduce_kernel(const float* __restrict__ per_sample, float* loss, float* hits,
+                                       int64_t B) {
+    __shared__ double sl[256], sh[256];
+    double l = 0.0, h = 0.0;
+    for (int64_t b = threadIdx.x; b < B; b += blockDim.x) {
+        l += per_sample[b * 2];
+        h += per_sample[b * 2 + 1];
+    }
+    sl[threadIdx.x] = l;
+    sh[threadIdx.x] = h;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) { sl[threadIdx.x] += sl[threadIdx.x + o]; sh[threadIdx.x] += sh[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { *loss = (float)(sl[0] / (double)B); *hits = (float)sh[0]; }
+}
+
+// ds = (softmax(s) - onehot) * gloss / B ; dcand = ds*u ; duser = sum_k ds_k c_k.  block per sample.
+__global__ void score_ce_bwd_kernel(const float* __restrict__ cand, const float* __restrict__ user,
+                                    const int64_t* __restrict__ label, const float* __restrict__ score,
+                                    const float* __restrict__ gloss, float* __restrict__ dcand,
+                                    float* __restrict__ duser, int64_t B, int C, int H) {
+    extern __shared__ float ds[];
+    const int64_t b = blockIdx.x;
+    if (threadIdx.x == 0) {
+        float mx = -INFINITY;
+        for (int k = 0; k < C; ++k) mx = fmaxf(mx, score[b * C + k]);
+        float z = 0.f;
+        for (int k = 0; k < C; ++k) z += expf(score[b * C + k] - mx);
+        const float g = gloss[0] / (float)B;
+        const int lab = (int)label[b];
+        for (int k = 0; k < C; ++k)
+            ds[k] = (expf(score[b * C + k] - mx) / z - (k == lab ? 1.f : 0.f)) * g;
+    }
+    __syncthreads();
+    for (int h = threadIdx.x; h < H; h += blockDim.x) {
+        const float u = __ldg(user + b * H + h);
+        float du = 0.f;
+        for (int k = 0; k < C; ++k) {
+            const float d = ds[k];
+            dcand[(b * C + k) * H + h] = d * u;
+            du = fmaf(d, __ldg(cand + (b * C + k) * H + h), du);
+        }
+        duser[b * H + h] = du;
+    }
+}
+
+// torch.optim.Adam (amsgrad off, wd 0): same operation order as torch's single-tensor path.
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                            float* __restrict__ v, int64_t count, float lr_over_bc1, float beta1,
+                            float beta2, float eps, float inv_sqrt_bc2, float gscale) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const float gi = g[i] * gscale;
+        const float mi = m[i] * beta1 + gi * (1.f - beta1);
+        const float vi = v[i] * beta2 + (gi * gi) * (1.f - beta2);
+        m[i] = mi;
+        v[i] = vi;
+        const float denom = sqrtf(vi) * inv_sqrt_bc2 + eps;
+        p[i] = p[i] - lr_over_bc1 * (mi / denom);
+    }
+}
+
+static inline unsigned grid_for(int64_t work, int threads, int per_sm = 8) {
+    int64_t g = (work + threads - 1) / threads;
+    const int64_t cap = (int64_t)sm_count() * per_sm;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (unsigned)g;
+}
+
+}  // namespace nr
+
+using namespace nr;
+
+extern "C" {
+
+int nr_abi_version(void) { return NR_ABI_VERSION; }
+const char* nr_last_error(void) { return nr::g_err; }
+
+int nr_device_info(int32_t* sms, int32_t* major, int32_t* minor) {
+    int dev = 0;
+    NR_CUDA(cudaGetDevice(&dev));
+    int a = 0, b = 0, c = 0;
+    NR_CUDA(cudaDeviceGetAttribute(&a, cudaDevAttrMultiProcessorCount, dev));
+    NR_CUDA(cudaDeviceGetAttribute(&b, cudaDevAttrComputeCapabilityMajor, dev));
+    NR_CUDA(cudaDeviceGetAttribute(&c, cudaDevAttrComputeCapabilityMinor, dev));
+    if (sms) *sms = a;
+    if (major) *major = b;
+    if (minor) *minor = c;
+    return 0;
+}
+
+int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed, int32_t sid, void* stream) {
+    NR_REQUIRE(keep && count >= 0 && p >= 0.f && p < 1.f, "nr_dropout_keep_mask: bad arguments");
+    if (count == 0) return 0;
+    keep_mask_kernel<<<grid_for((count + 3) / 4, 256), 256, 0, (cudaStream_t)stream>>>(
+        keep, count, drop_threshold(p), seed, (uint32_t)sid);
+    return check_last("nr_dropout_keep_mask");
+}
+
+int nr_gather_rows(const float* table, int64_t table_rows, const int32_t* ids, int64_t count,
+                   int32_t width, float* out, void* stream) {
+    NR_REQUIRE(table && ids && out, "nr_gather_rows: NULL pointer");
+    NR_REQUIRE(width > 0 && (width & 3) == 0, "nr_gather_rows: width %d must be a positive multiple of 4", width);
+    NR_REQUIRE(table_rows > 0 && count >= 0, "nr_gather_rows: bad sizes");
+    if (count == 0) return 0;
+    const int64_t total4 = count * (width / 4);
+    gather_rows_kernel<<<grid_for(total4, 256, 16), 256, 0, (cudaStream_t)stream>>>(table, ids, out, total4,
+                                                                                    width / 4);
+    return check_last("nr_gather_rows");
+}
+
+int nr_pad_blend_fwd(const float* v, const float* mask, const float* pad, float* out, int64_t n,
+                     int32_t T, int32_t H, void* stream) {
+    NR_REQUIRE(v && mask && pad && out, "nr_pad_blend_fwd: NULL pointer");
+    NR_REQUIRE(H > 0 && (H & 3) == 0, "nr_pad_blend_fwd: H %d must be a multiple of 4", H);
+    if (n * T == 0) return 0;
+    pad_blend_fwd_kernel<<<grid_for(n * T * (H / 4), 256), 256, 0, (cudaStream_t)stream>>>(v, mask, pad, out,
+                                                                                         n * T, H / 4);
+    return check_last("nr_pad_blend_fwd");
+}
+
+int nr_pad_blend_bwd(const float* dout, const float* mask, float* dv, float* dpad, int64_t n, int32_t T,
+                     int32_t H, void* stream) {
+    NR_REQUIRE(dout && mask && dv && dpad, "nr_pad_blend_bwd: NULL pointer");
+    if (n * T == 0) return 0;
+    int64_t g = n * T < 2 * sm_count() ? n * T : 2 * sm_count();
+    pad_blend_bwd_kernel<<<(unsigned)g, 128, 0, (cudaStream_t)stream>>>(dout, mask, dv, dpad, n * T, H);
+    return check_last("nr_pad_blend_bwd");
+}
+
+int nr_score_ce_fwd(const float* cand, const float* user, const int64_t* label, float* score, float* loss,
+                    float* hits, float* per_sample_ws, int64_t B, int32_t C, int32_t H, void* stream) {
+    NR_REQUIRE(cand && user && label && score && loss && hits && per_sample_ws, "nr_score_ce_fwd: NULL pointer");
+    NR_REQUIRE(B > 0 && C > 0 && H > 0, "nr_score_ce_fwd: bad sizes");
+    const int threads = 128;
+    score_ce_fwd_kernel<<<(unsigned)((B * 32 + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
+        cand, user, label, score, per_sample_ws, B, C, H);
+    if (int e = check_last("nr_score_ce_fwd")) return e;
+    score_ce_reduce_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(per_sample_ws, loss, hits, B);
+    return check_last("nr_score_ce_fwd(reduce)");
+}
+
+int nr_score_ce_bwd(const float* cand, const float* user, const int64_t* label, const float* score,
+                    const float* gloss, float* dcand, float* duser, int64_t B, int32_t C, int32_t H,
+                    void* stream) {
+    NR_REQUIRE(cand && user && label && score && gloss && dcand && duser, "nr_score_ce_bwd: NULL pointer");
+    NR_REQUIRE(B > 0 && C > 0 && C <= 1024 && H > 0, "nr_score_ce_bwd: bad sizes");
+    score_ce_bwd_kernel<<<(unsigned)B, 128, C * sizeof(float), (cudaStream_t)stream>>>(
+        cand, user, label, score, gloss, dcand, duser, B, C, H);
+    return check_last("nr_score_ce_bwd");
+}
+
+int nr_adam_step(float* p, const float* g, float* m, float* v, int64_t count, float lr, float beta1,
+                 float beta2, float eps, int32_t step, float grad_scale, void* stream) {
+    NR_REQUIRE(p && g && m && v, "nr_adam_step: NULL pointer");
+    NR_REQUIRE(step >= 1, "nr_adam_step: step is 1-based");
+    if (count == 0) return 0;
+    const double bc1 = 1.0 - pow((double)beta1, (double)step);
+    const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    adam_kernel<<<grid_for(count, 256), 256, 0, (cudaStream_t)stream>>>(
+        p, g, m, v, count, (float)((double)lr / bc1), beta1, beta2, eps, (float)(1.0 / sqrt(bc2)), grad_scale);
+    return check_last("nr_adam_step");
+}
+
+}  // extern "C"

@@ -1,0 +1,215 @@
+// nr_common.cuh — shared device/host helpers for libnr_sm100.so
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include "../../include/nr_sm100.h"
+
+namespace nr {
+
+// ---- error plumbing -----------------------------------------------------------
+void set_error(const char* fmt, ...);
+int check_last(const char* what);   // cudaGetLastError -> error code + message
+
+#define NR_REQUIRE(cond, ...)                      \
+    do {                                           \
+        if (!(cond)) {                             \
+            nr::set_error(__VA_ARGS__);            \
+            return 1;                              \
+        }                                          \
+    } while (0)
+
+#define NR_CUDA(call)                                                               \
+    do {                                                                            \
+        cudaError_t e_ = (call);                                                    \
+        if (e_ != cudaSuccess) {                                                    \
+            nr::set_error("%s failed: %s", #call, cudaGetErrorString(e_));          \
+            return 2;                                                               \
+        }                                                                           \
+    } while (0)
+
+constexpr float kEps = 1e-8f;   // src/model/model_utils.py:29,53
+
+inline int sm_count() {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess)
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n;
+}
+
+// bump allocator over the caller-provided workspace
+struct Workspace {
+    char* base;
+    size_t bytes, used;
+    Workspace(void* p, size_t b) : base((char*)p), bytes(b), used(0) {}
+    template <typename T>
+    T* take(size_t count) {
+        size_t need = (count * sizeof(T) + 255) & ~size_t(255);
+        if (used + need > bytes) return nullptr;
+        T* r = (T*)(base + used);
+        used += need;
+        return r;
+    }
+    static size_t pad(size_t b) { return (b + 255) & ~size_t(255); }
+};
+
+// ---- Philox4x32-10 counter RNG: dropout keep masks ----------------------------
+// Element e of stream (seed, sid): word (e & 3) of philox(counter = e >> 2).
+__host__ __device__ __forceinline__ void philox_round(uint32_t& c0, uint32_t& c1, uint32_t& c2,
+                                                      uint32_t& c3, uint32_t k0, uint32_t k1) {
+    const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+    const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+    const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+    const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+    c1 = (uint32_t)p1;
+    c3 = (uint32_t)p0;
+    c0 = n0;
+    c2 = n2;
+}
+
+__host__ __device__ __forceinline__ uint4 philox4(uint64_t seed, uint32_t sid, uint64_t ctr) {
+    uint32_t c0 = (uint32_t)ctr, c1 = (uint32_t)(ctr >> 32), c2 = sid, c3 = 0x6e72u;
+    uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+#pragma unroll
+    for (int i = 0; i < 10; ++i) {
+        philox_round(c0, c1, c2, c3, k0, k1);
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    return make_uint4(c0, c1, c2, c3);
+}
+
+__host__ __device__ __forceinline__ uint32_t drop_threshold(float p) {
+    double t = (double)p * 4294967296.0;
+    if (t <= 0.0) return 0u;
+    if (t >= 4294967295.0) return 4294967295u;
+    return (uint32_t)t;
+}
+
+// Applies inverted dropout to 4 consecutive elements starting at element index e0 (e0 % 4 == 0).
+__device__ __forceinline__ float4 dropout4(float4 v, uint64_t e0, uint64_t seed, uint32_t sid,
+                                           uint32_t thr, float scale) {
+    const uint4 r = philox4(seed, sid, e0 >> 2);
+    v.x = (r.x >= thr) ? v.x * scale : 0.f;
+    v.y = (r.y >= thr) ? v.y * scale : 0.f;
+    v.z = (r.z >= thr) ? v.z * scale : 0.f;
+    v.w = (r.w >= thr) ? v.w * scale : 0.f;
+    return v;
+}
+
+// ---- warp / block reductions -------------------------------------------------------
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg((const float4*)p); }
+
+// ---- matrix views: row-major logical matrices read 4 columns at a time ------------------
+// Every view exposes   float4 load4(int64_t row, int col)   with zero fill outside
+// [0,rows) x [0,cols); col % 4 == 0 and cols % 4 == 0 always hold.
+
+struct DenseView {
+    const float* p;
+    int64_t ld;
+    int64_t rows;
+    int cols;
+    __device__ __forceinline__ float4 load4(int64_t r, int c) const {
+        if (r >= rows || c >= cols) return make_float4(0.f, 0.f, 0.f, 0.f);
+        return ldg4(p + r * ld + c);
+    }
+};
+
+// up to three stacked (rows_each x cols) matrices addressed as one (3*rows_each x cols):
+// W_Q / W_K / W_V are separate Parameters in the reference (model_utils.py:67-69).
+struct Stack3View {
+    const float* p0;
+    const float* p1;
+    const float* p2;
+    int rows_each;
+    int rows;
+    int cols;
+    __device__ __forceinline__ float4 load4(int64_t r, int c) const {
+        if (r >= rows || c >= cols) return make_float4(0.f, 0.f, 0.f, 0.f);
+        const int which = (int)r / rows_each;
+        const int rr = (int)r - which * rows_each;
+        const float* p = which == 0 ? p0 : (which == 1 ? p1 : p2);
+        return ldg4(p + (int64_t)rr * cols + c);
+    }
+};
+
+// Activation rows (n*S, D) behind an nr_rows_t, with optional input dropout.
+struct RowsView {
+    int mode;
+    const float* dense;
+    const float* table;
+    const int32_t* ids;
+    int ids_stride;
+    int S, D;
+    int64_t rows;   // n*S
+    uint32_t thr;   // 0 => no dropout
+    float scale;
+    uint64_t seed;
+    __device__ __forceinline__ int64_t id_of(int64_t seq, int s) const {
+        return mode == NR_ROWS_TOKEN ? (int64_t)__ldg(ids + seq * ids_stride + s)
+                                     : (int64_t)__ldg(ids + seq * ids_stride);
+    }
+    // element (row r = seq*S+s, col c)
+    __device__ __forceinline__ float4 load4(int64_t r, int c) const {
+        if (r >= rows || c >= D) return make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 v;
+        if (mode == NR_ROWS_DENSE) {
+            v = ldg4(dense + r * D + c);
+        } else {
+            const int64_t seq = r / S;
+            const int s = (int)(r - seq * S);
+            const int64_t id = id_of(seq, s);
+            v = mode == NR_ROWS_TOKEN ? ldg4(table + id * D + c)
+                                      : ldg4(table + id * ((int64_t)S * D) + (int64_t)s * D + c);
+        }
+        if (thr) v = dropout4(v, (uint64_t)(r * D + c), seed, NR_STREAM_IN, thr, scale);
+        return v;
+    }
+};
+
+// im2col view of a RowsView for Conv1d(k=3,pad=1): (n*L, 3*D), col = t*D + c -> X[l+t-1, c]
+struct ConvView {
+    RowsView x;
+    int64_t rows;
+    int cols;   // 3*D
+    __device__ __forceinline__ float4 load4(int64_t r, int c) const {
+        if (r >= rows || c >= cols) return make_float4(0.f, 0.f, 0.f, 0.f);
+        const int t = c / x.D;
+        const int cc = c - t * x.D;
+        const int64_t seq = r / x.S;
+        const int l = (int)(r - seq * x.S) + t - 1;
+        if (l < 0 || l >= x.S) return make_float4(0.f, 0.f, 0.f, 0.f);
+        return x.load4(seq * x.S + l, cc);
+    }
+};
+
+// rows of a small embedding table gathered by one id column: (n, E)
+struct EmbedView {
+    const float* emb;
+    const int32_t* ids;
+    int ids_stride;
+    int64_t rows;
+    int cols;
+    __device__ __forceinline__ float4 load4(int64_t r, int c) const {
+        if (r >= rows || c >= cols) return make_float4(0.f, 0.f, 0.f, 0.f);
+        const int64_t id = __ldg(ids + r * ids_stride);
+        return ldg4(emb + id * cols + c);
+    }
+};
+
+RowsView make_rows_view(const nr_rows_t* r, int64_t n, int S, int D);
+int validate_rows(const nr_rows_t* r, const char* who);
+
+}  // namespace nr
