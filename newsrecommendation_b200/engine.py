@@ -1,0 +1,163 @@
+"""Runtime around the model plugin: the train step of src/main.py:98-110 and the eval
+path of src/main.py:185-277, both device-resident.
+
+Train: parameters and gradients are re-homed into two flat fp32 buckets; one NCCL
+all-reduce of the gradient bucket per step (DDP semantics, main.py:82,109) and one fused
+Adam launch (torch.optim.Adam defaults, main.py:76) with the 1/world_size mean folded in.
+`model.parameters()` remain ordinary leaf Parameters (views into the bucket), so the
+reference's own `optim.Adam(model.parameters())` + DDP loop keeps working unchanged.
+
+Eval: news-vector cache encoded in row shards + all-gather (reference: every rank encodes
+everything, main.py:190-196); impressions as CSR, scored by gather+dot from the device
+table; AUC/MRR/nDCG@5/10 per impression on device; 5-scalar all-reduce.
+"""
+import ctypes as C
+
+import torch
+import torch.distributed as dist
+
+from . import _lib as L
+from . import ops
+
+
+def _dist_on():
+    return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+
+
+class FlatAdam:
+    """Flat-bucket Adam == torch.optim.Adam(params, lr) (betas .9/.999, eps 1e-8, wd 0)."""
+
+    def __init__(self, model, lr, betas=(0.9, 0.999), eps=1e-8):
+        self.params = [p for p in model.parameters() if p.requires_grad]
+        if not self.params:
+            raise ValueError('no trainable parameters')
+        dev = self.params[0].device
+        if dev.type != 'cuda':
+            raise RuntimeError('FlatAdam: move the model to a CUDA device first (no CPU path exists)')
+        self.count = sum(p.numel() for p in self.params)
+        self.flat_p = torch.empty(self.count, dtype=torch.float32, device=dev)
+        self.flat_g = torch.zeros(self.count, dtype=torch.float32, device=dev)
+        self.m = torch.zeros_like(self.flat_p)
+        self.v = torch.zeros_like(self.flat_p)
+        off = 0
+        for p in self.params:
+            n = p.numel()
+            self.flat_p[off:off + n].copy_(p.data.reshape(-1))
+            p.data = self.flat_p[off:off + n].view(p.shape)          # Parameter object unchanged
+            p.grad = self.flat_g[off:off + n].view(p.shape)
+            off += n
+        self.lr, self.betas, self.eps = lr, betas, eps
+        self.step_count = 0
+
+    def zero_grad(self):
+        self.flat_g.zero_()
+        off = 0
+        for p in self.params:      # re-attach in case autograd replaced .grad
+            n = p.numel()
+            g = self.flat_g[off:off + n].view(p.shape)
+            if p.grad is None or p.grad.data_ptr() != g.data_ptr():
+                p.grad = g
+            off += n
+
+    def broadcast_params(self):
+        """DDP constructor semantics (main.py:82): rank 0's weights everywhere."""
+        if _dist_on():
+            dist.broadcast(self.flat_p, src=0)
+
+    def step(self):
+        scale = 1.0
+        if _dist_on():
+            dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM)
+            scale = 1.0 / dist.get_world_size()
+        self.step_count += 1
+        L.call('nr_adam_step', L.ptr(self.flat_p), L.ptr(self.flat_g), L.ptr(self.m), L.ptr(self.v), self.count,
+               self.lr, self.betas[0], self.betas[1], self.eps, self.step_count, scale, L.stream())
+
+
+def train_step(model, opt, history, history_mask, candidate, label):
+    """One iteration of src/main.py:105-110.  Returns (loss, hits) device scalars."""
+    opt.zero_grad()
+    loss, _score = model(history, history_mask, candidate, label)
+    loss.backward()
+    opt.step()
+    return loss.detach(), model.last_hits
+
+
+# --------------------------------------------------------------------------------------
+# eval path
+# --------------------------------------------------------------------------------------
+@torch.no_grad()
+def build_news_cache(model, news_combined, batch=1024, shard=True):
+    """src/main.py:185-198: news_encoder over EVERY row of news_combined (row 0 = the pad
+    news included) -> device table (N+1, news_dim) fp32.  With a process group, rank r
+    encodes the contiguous row range [r*per, (r+1)*per) and the shards are all-gathered
+    in place."""
+    was_training = model.training
+    model.eval()
+    rows = news_combined.shape[0]
+    dev = news_combined.device
+    H = model.args.news_dim
+    W = dist.get_world_size() if (shard and _dist_on()) else 1
+    r = dist.get_rank() if W > 1 else 0
+    per = (rows + W - 1) // W
+    table = torch.empty(per * W, H, dtype=torch.float32, device=dev)
+    lo, hi = min(rows, r * per), min(rows, (r + 1) * per)
+    for b0 in range(lo, hi, batch):
+        b1 = min(hi, b0 + batch)
+        table[b0:b1] = model.news_encoder(news_combined[b0:b1])
+    if hi < (r + 1) * per:
+        table[hi:(r + 1) * per].zero_()
+    if W > 1:
+        dist.all_gather_into_tensor(table, table[r * per:(r + 1) * per].clone())
+    if was_training:
+        model.train()
+    return table[:rows]
+
+
+@torch.no_grad()
+def score_impressions(model, table, hist_idx, hist_mask, offsets, cand_idx, labels, batch=1024):
+    """src/main.py:240-263 + src/dataset.py:64-74 on device.
+    Impressions as CSR (offsets int64 (I+1), cand_idx int32, labels int8) with front-padded
+    history indices hist_idx int32 (I,T) and hist_mask fp32 (I,T).
+    Returns (scores fp32 flat, metrics fp64 (I,4), valid uint8 (I), sums fp64 (5):
+    sum AUC, MRR, nDCG@5, nDCG@10 over scored impressions and their count)."""
+    was_training = model.training
+    model.eval()
+    I, T = hist_idx.shape
+    dev = table.device
+    H = table.shape[1]
+    total = cand_idx.numel()
+    table = L.f32(table)
+    user = torch.empty(I, H, dtype=torch.float32, device=dev)
+    for b0 in range(0, I, batch):
+        b1 = min(I, b0 + batch)
+        log_vecs = ops.gather_rows(table, hist_idx[b0:b1])                 # dataset.py:67-68
+        user[b0:b1] = model.user_encoder(log_vecs, hist_mask[b0:b1])       # main.py:247
+    scores = torch.empty(total, dtype=torch.float32, device=dev)
+    metrics = torch.empty(I, 4, dtype=torch.float64, device=dev)
+    valid = torch.empty(I, dtype=torch.uint8, device=dev)
+    sums = torch.zeros(5, dtype=torch.float64, device=dev)
+    offsets = offsets.contiguous().to(torch.int64)
+    cand_idx = cand_idx.contiguous().to(torch.int32)
+    labels = labels.contiguous().to(torch.int8)
+    st = L.stream()
+    L.call('nr_eval_score', L.ptr(table), table.shape[0], L.ptr(user), L.ptr(offsets), L.ptr(cand_idx),
+           L.ptr(scores), I, total, H, st)                                  # main.py:253
+    L.call('nr_eval_rank_metrics', L.ptr(scores), L.ptr(labels), L.ptr(offsets), L.ptr(metrics), L.ptr(valid),
+           I, st)                                                           # main.py:250-258
+    L.call('nr_eval_reduce_metrics', L.ptr(metrics), L.ptr(valid), L.ptr(sums), I, st)
+    if was_training:
+        model.train()
+    return scores, metrics, valid, sums
+
+
+def reduce_eval_sums(sums, n_impressions):
+    """src/main.py:268-277: SUM over ranks of the 4 metric sums, the scored count and the
+    total impression count.  Returns dict with both denominators."""
+    t = torch.cat([sums, torch.tensor([float(n_impressions)], dtype=torch.float64, device=sums.device)])
+    if _dist_on():
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    t = t.cpu()
+    scored, total = float(t[4]), float(t[5])
+    return {'sums': t[:4].numpy(), 'scored': int(scored), 'total': int(total),
+            'mean_scored': (t[:4] / max(1.0, scored)).numpy(), 'mean_total': (t[:4] / max(1.0, total)).numpy()}

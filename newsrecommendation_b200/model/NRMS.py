@@ -1,0 +1,82 @@
+"""NRMS plugin (drop-in for src/model/NRMS.py): Model(args, embedding_matrix, ...),
+model(history, history_mask, candidate, label) -> (loss, score), .news_encoder(ids),
+.user_encoder(vecs, mask); 22 state_dict keys as the reference."""
+import torch
+from torch import nn
+
+from newsrecommendation_b200 import ops
+from newsrecommendation_b200 import _lib as L
+from .model_utils import AttentionPooling, MultiHeadSelfAttention, precision_of
+
+
+def _heads(args):
+    dk = args.news_dim // args.num_attention_heads
+    if dk * args.num_attention_heads != args.news_dim:
+        raise ValueError('news_dim must equal num_attention_heads * dim_per_head')
+    return dk
+
+
+class NewsEncoder(nn.Module):
+    """word gather -> dropout -> MHSA -> dropout -> additive pooling (NRMS.py:8-36).
+    The gather and both dropouts run inside the MHSA kernels."""
+
+    def __init__(self, args, embedding_matrix):
+        super().__init__()
+        prec = precision_of(args)
+        self.embedding_matrix = embedding_matrix
+        self.drop_rate = args.drop_rate
+        self.dim_per_head = _heads(args)
+        self.multi_head_self_attn = MultiHeadSelfAttention(args.word_embedding_dim, args.num_attention_heads,
+                                                           self.dim_per_head, self.dim_per_head, prec)
+        self.attn = AttentionPooling(args.news_dim, args.news_query_vector_dim, prec)
+
+    def forward(self, x, mask=None):
+        if mask is not None:
+            raise RuntimeError('title masks are never used by the reference (NRMS.py:87,90); not built')
+        p = self.drop_rate if self.training else 0.0
+        h = self.multi_head_self_attn.forward_rows(self.embedding_matrix.weight, x.reshape(-1, x.shape[-1]),
+                                                   L.ROWS_TOKEN, x.shape[-1], p, p, ops.next_seed() if p else 0)
+        return self.attn(h)
+
+
+class UserEncoder(nn.Module):
+    """NRMS.py:39-63: masked MHSA + masked pooling, or pad_doc blend + unmasked."""
+
+    def __init__(self, args):
+        super().__init__()
+        prec = precision_of(args)
+        self.args = args
+        self.dim_per_head = _heads(args)
+        self.multi_head_self_attn = MultiHeadSelfAttention(args.news_dim, args.num_attention_heads,
+                                                           self.dim_per_head, self.dim_per_head, prec)
+        self.attn = AttentionPooling(args.news_dim, args.user_query_vector_dim, prec)
+        self.pad_doc = nn.Parameter(torch.empty(1, args.news_dim).uniform_(-1, 1))
+
+    def forward(self, news_vecs, log_mask=None):
+        if self.args.user_log_mask:
+            h = self.multi_head_self_attn(news_vecs, mask=log_mask)
+            return self.attn(h, log_mask)
+        v = ops.pad_blend(news_vecs, log_mask, self.pad_doc)
+        return self.attn(self.multi_head_self_attn(v))
+
+
+class Model(nn.Module):
+    def __init__(self, args, embedding_matrix, num_category=None, num_subcategory=None, **kwargs):
+        # two extra positionals tolerated: main.py:64 passes them to every model
+        super().__init__()
+        self.args = args
+        table = torch.as_tensor(embedding_matrix).float()
+        emb = nn.Embedding.from_pretrained(table, freeze=args.freeze_embedding, padding_idx=0)
+        self.news_encoder = NewsEncoder(args, emb)
+        self.user_encoder = UserEncoder(args)
+        self.last_hits = None
+
+    def forward(self, history, history_mask, candidate, label):
+        a = self.args
+        Lw = a.num_words_title
+        cv = self.news_encoder(candidate.reshape(-1, Lw)).reshape(-1, 1 + a.npratio, a.news_dim)
+        hv = self.news_encoder(history.reshape(-1, Lw)).reshape(-1, a.user_log_length, a.news_dim)
+        u = self.user_encoder(hv, history_mask)
+        loss, score, hits = ops.score_ce(cv, u, label)
+        self.last_hits = hits      # #argmax==label of this batch (utils.acc numerator), device scalar
+        return loss, score

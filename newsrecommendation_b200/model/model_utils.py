@@ -1,0 +1,82 @@
+"""Operator modules of the hot path, mirroring src/model/model_utils.py.
+
+Parameters live in the same nn.Linear containers as the reference (so the
+state_dict keys and default initialisation match); forward() hands the raw
+parameter tensors to the CUDA library through newsrecommendation_b200.ops.
+"""
+import os
+
+import torch
+from torch import nn
+
+from newsrecommendation_b200 import ops
+from newsrecommendation_b200 import _lib as L
+
+
+def precision_of(args):
+    """fp32 (parity mode, rel 1e-5) or bf16 tensor-core mode (rel 1e-2).  Taken from
+    `args.precision` when the caller's parser defines it, else $NR_PRECISION, else fp32."""
+    p = getattr(args, 'precision', None) or os.environ.get('NR_PRECISION', 'fp32')
+    if p not in ('fp32', 'bf16'):
+        raise ValueError(f'precision must be fp32 or bf16, got {p!r}')
+    return L.PREC_BF16 if p == 'bf16' else L.PREC_FP32
+
+
+class AttentionPooling(nn.Module):
+    """src/model/model_utils.py:7-31."""
+
+    def __init__(self, emb_size, hidden_size, prec=L.PREC_FP32):
+        super().__init__()
+        self.att_fc1 = nn.Linear(emb_size, hidden_size)
+        self.att_fc2 = nn.Linear(hidden_size, 1)
+        self.prec = prec
+
+    def forward(self, x, attn_mask=None):
+        return ops.attention_pooling(x, attn_mask, self.att_fc1.weight, self.att_fc1.bias,
+                                     self.att_fc2.weight, self.att_fc2.bias, self.prec)
+
+
+class ScaledDotProductAttention(nn.Module):
+    """src/model/model_utils.py:34-55.  The reference only ever reaches this through
+    MultiHeadSelfAttention with Q=K=V; the library fuses it there (nr_mhsa_fwd), so this
+    class exists for import compatibility and records d_k."""
+
+    def __init__(self, d_k):
+        super().__init__()
+        self.d_k = d_k
+
+    def forward(self, Q, K, V, attn_mask=None):
+        raise RuntimeError('ScaledDotProductAttention is fused into MultiHeadSelfAttention '
+                           '(nr_mhsa_fwd); call that module instead')
+
+
+class MultiHeadSelfAttention(nn.Module):
+    """src/model/model_utils.py:58-95 (xavier-uniform weights, :73-76)."""
+
+    def __init__(self, d_model, n_heads, d_k, d_v, prec=L.PREC_FP32):
+        super().__init__()
+        if d_k != d_v:
+            raise ValueError('d_k != d_v is outside the compiled envelope')
+        self.d_model, self.n_heads, self.d_k, self.d_v = d_model, n_heads, d_k, d_v
+        self.W_Q = nn.Linear(d_model, d_k * n_heads)
+        self.W_K = nn.Linear(d_model, d_k * n_heads)
+        self.W_V = nn.Linear(d_model, d_v * n_heads)
+        self.scaled_dot_product_attn = ScaledDotProductAttention(d_k)
+        self.prec = prec
+        for m in (self.W_Q, self.W_K, self.W_V):
+            nn.init.xavier_uniform_(m.weight, gain=1)
+
+    def _w(self):
+        return (self.W_Q.weight, self.W_Q.bias, self.W_K.weight, self.W_K.bias, self.W_V.weight, self.W_V.bias)
+
+    def forward(self, Q, K=None, V=None, mask=None):
+        if (K is not None and K is not Q) or (V is not None and V is not Q):
+            raise RuntimeError('only self-attention (Q is K is V) is built, as at every reference call site')
+        return ops.mhsa(Q, None, mask, *self._w(), mode=L.ROWS_DENSE, S=Q.shape[1], Dm=self.d_model,
+                        heads=self.n_heads, prec=self.prec)
+
+    def forward_rows(self, table, ids, mode, S, in_drop, out_drop, seed):
+        """Self-attention over rows gathered from an embedding table (gather + both
+        dropouts fused; NRMS.py:28-34)."""
+        return ops.mhsa(table, ids, None, *self._w(), mode=mode, S=S, Dm=self.d_model, heads=self.n_heads,
+                        in_drop=in_drop, out_drop=out_drop, seed=seed, prec=self.prec)

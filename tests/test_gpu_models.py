@@ -1,0 +1,174 @@
+"""GPU parity, model level: the drop-in `model.NRMS` / `model.NAML` plugin, the train step
+(flat Adam) and the eval path vs the CPU oracle and the reference-generated fixtures."""
+import argparse
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from oracle import nr_oracle as O
+from test_gpu_ops import T, close, gclose
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(__file__), 'golden')
+
+
+def ref_args(**kw):
+    a = argparse.Namespace(
+        drop_rate=0.0, news_dim=400, num_attention_heads=20, word_embedding_dim=300,
+        news_query_vector_dim=200, user_query_vector_dim=200, user_log_mask=False,
+        user_log_length=50, num_words_title=30, npratio=4, freeze_embedding=False,
+        use_category=False, use_subcategory=False, category_emb_dim=100)
+    for k, v in kw.items():
+        setattr(a, k, v)
+    return a
+
+
+def build_model(tag, **extra):
+    from newsrecommendation_b200.model import NRMS, NAML
+    kind, kw, P, bt = synth.case_inputs(tag)
+    if kind == 'nrms':
+        a = ref_args(user_log_mask=kw['user_log_mask'], num_words_title=kw['L'], **extra)
+        model = NRMS.Model(a, P['news_encoder.embedding_matrix.weight'], 0, 0)   # 4 positionals (F3)
+    else:
+        a = ref_args(user_log_mask=kw['user_log_mask'], num_words_title=kw['L'], use_category=kw['use_cat'],
+                     use_subcategory=kw['use_sub'], freeze_embedding=True, **extra)
+        model = NAML.Model(a, P['news_encoder.title_embeddings.weight'], synth.NCAT, synth.NSUB)
+    assert list(model.state_dict().keys()) == list(P.keys())          # key contract
+    model.load_state_dict({k: T(v) for k, v in P.items()})            # strict
+    return kind, kw, P, bt, model.cuda()
+
+
+@pytest.mark.parametrize('tag', sorted(synth.MODEL_CASES))
+def test_model_vs_reference_golden(tag):
+    g = np.load(os.path.join(G, tag + '.npz'))
+    kind, kw, P, bt, model = build_model(tag)
+    hist, mask, cand, label = [T(a).cuda() for a in bt]
+    model.train()
+    loss, score = model(hist, mask, cand, label)
+    np.testing.assert_allclose(loss.item(), g['loss'], rtol=1e-5)
+    close(score, g['score'], rtol=1e-5, atol=2e-5)
+    from newsrecommendation_b200 import ops   # noqa: F401
+    assert abs(model.last_hits.item() - (score.argmax(-1) == label).sum().item()) == 0
+    loss.backward()
+    for k, p in model.named_parameters():
+        if 'gs:' + k not in g.files:
+            continue
+        gr = torch.zeros_like(p) if p.grad is None else p.grad
+        s, st = synth.grad_digest(gr.cpu().numpy())
+        scale = max(1e-12, float(np.abs(g['gs:' + k]).max()))
+        np.testing.assert_allclose(s, g['gs:' + k], rtol=1e-4, atol=2e-5 * scale + 1e-6, err_msg=k)
+        np.testing.assert_allclose(st[1], g['gt:' + k][1], rtol=1e-4, atol=1e-6, err_msg=k)
+    if kind == 'nrms':
+        assert (model.news_encoder.embedding_matrix.weight.grad[0] == 0).all()
+    model.eval()
+    F = hist.shape[-1]
+    with torch.no_grad():
+        nv = model.news_encoder(hist.reshape(-1, F))
+        uv = model.user_encoder(nv.reshape(hist.shape[0], hist.shape[1], -1), mask)
+        pv = model.news_encoder(torch.zeros(1, F, dtype=torch.int32, device='cuda'))
+    close(nv, g['hist_vecs'], atol=3e-6)
+    close(uv, g['user_vec'], atol=3e-6)
+    close(pv, g['pad_news_vec'], atol=3e-6)
+    if kw['user_log_mask']:
+        assert (uv[0] == 0).all()              # empty history -> exact zero (B1)
+    else:
+        assert uv[0].abs().max() > 0           # pad_doc-only user (B3)
+
+
+def test_state_dict_roundtrip_and_ragged_last_batch():
+    kind, kw, P, bt, model = build_model('nrms_ulm0')
+    sd = {k: v.cpu() for k, v in model.state_dict().items()}
+    for k in P:
+        assert torch.equal(sd[k], T(P[k])), k
+    hist, mask, cand, label = [T(a).cuda() for a in bt]
+    loss, score = model(hist[:1], mask[:1], cand[:1], label[:1])       # B=1 (no drop_last, B13)
+    assert score.shape == (1, 5) and torch.isfinite(loss)
+
+
+def test_train_steps_match_oracle_adam():
+    """3 optimisation steps (main.py:105-110) == oracle forward/backward + torch-semantics Adam."""
+    from newsrecommendation_b200 import engine
+    kind, kw, Pn, bt, model = build_model('naml_ulm0_c11')
+    opt = engine.FlatAdam(model, lr=3e-4)
+    P = {k: T(v).clone() for k, v in Pn.items()}
+    train_keys = [k for k, p in model.named_parameters() if p.requires_grad]
+    st = {k: (torch.zeros_like(P[k]), torch.zeros_like(P[k])) for k in train_keys}
+    hist, mask, cand, label = [T(a) for a in bt]
+    model.train()
+    for step in range(1, 4):
+        loss_d, hits = engine.train_step(model, opt, hist.cuda(), mask.cuda(), cand.cuda(), label.cuda())
+        for k in train_keys:
+            P[k].requires_grad_(True)
+        loss_o, _ = O.naml_forward(hist, mask, cand, label, P, kw['L'], synth.D, True, True, False)
+        loss_o.backward()
+        np.testing.assert_allclose(loss_d.item(), loss_o.item(), rtol=2e-5)
+        with torch.no_grad():
+            for k in train_keys:
+                gk = P[k].grad if P[k].grad is not None else torch.zeros_like(P[k])
+                P[k].requires_grad_(False)
+                O.adam_step(P[k], gk, st[k][0], st[k][1], step, 3e-4)
+                P[k].grad = None
+    sd = model.state_dict()
+    for k in train_keys:
+        # Adam's first steps move every weight by ~lr regardless of gradient size, so
+        # compare the UPDATE (p - p0) rather than p
+        d_dev = sd[k].cpu() - T(Pn[k]); d_or = P[k] - T(Pn[k])
+        np.testing.assert_allclose(d_dev.numpy(), d_or.numpy(), rtol=0, atol=3e-5, err_msg=k)
+        assert d_or.abs().max() > 1e-4
+
+
+def test_adam_vs_torch_golden():
+    from newsrecommendation_b200 import _lib as L
+    g = np.load(os.path.join(G, 'adam.npz'))
+    ra = np.random.RandomState(8)
+    p = T(ra.standard_normal(1000).astype(np.float32)).cuda()
+    m = torch.zeros_like(p); v = torch.zeros_like(p)
+    for s in range(3):
+        gr = T(ra.standard_normal(1000).astype(np.float32)).cuda()
+        L.call('nr_adam_step', L.ptr(p), L.ptr(gr), L.ptr(m), L.ptr(v), 1000, 3e-4, 0.9, 0.999, 1e-8, s + 1, 1.0,
+               L.stream())
+        close(p, g[f'p{s + 1}'], rtol=1e-6, atol=1e-7)
+
+
+def test_score_ce_and_small_ops():
+    from newsrecommendation_b200 import ops
+    rs = np.random.RandomState(40)
+    B, C, H = 37, 5, 400
+    cand = T(rs.standard_normal((B, C, H)).astype(np.float32) * 0.2)
+    user = T(rs.standard_normal((B, H)).astype(np.float32) * 0.2)
+    label = T(rs.randint(0, C, size=(B,)).astype(np.int64))
+    cd, ud = cand.cuda().requires_grad_(True), user.cuda().requires_grad_(True)
+    loss, score, hits = ops.score_ce(cd, ud, label.cuda())
+    co, uo = cand.clone().requires_grad_(True), user.clone().requires_grad_(True)
+    lo, so = O.score_and_loss(co, uo, label)
+    close(score, so, atol=1e-6); np.testing.assert_allclose(loss.item(), lo.item(), rtol=1e-5)
+    assert hits.item() == (so.argmax(-1) == label).sum().item()
+    (loss * 1.7).backward(); (lo * 1.7).backward()
+    gclose(cd.grad, co.grad); gclose(ud.grad, uo.grad)
+    # pad_doc blend
+    v = T(rs.standard_normal((4, 50, H)).astype(np.float32)); m = T((rs.rand(4, 50) > 0.4).astype(np.float32))
+    pad = T(rs.uniform(-1, 1, (1, H)).astype(np.float32))
+    vd, pd = v.cuda().requires_grad_(True), pad.cuda().requires_grad_(True)
+    out = ops.pad_blend(vd, m.cuda(), pd)
+    vo, po = v.clone().requires_grad_(True), pad.clone().requires_grad_(True)
+    ref = O.pad_doc_blend(vo, m, po)
+    assert torch.equal(out.cpu(), ref.detach())
+    gup = T(rs.standard_normal((4, 50, H)).astype(np.float32))
+    out.backward(gup.cuda()); ref.backward(gup)
+    gclose(vd.grad, vo.grad); gclose(pd.grad, po.grad)
+    # category view: dense(emb[ids[:,col]])
+    emb = T(rs.standard_normal((18, 100)).astype(np.float32)); emb[0] = 0
+    w = T(rs.uniform(-.1, .1, (H, 100)).astype(np.float32)); b = T(rs.uniform(-.1, .1, (H,)).astype(np.float32))
+    ids = T(rs.randint(0, 18, size=(23, 3)).astype(np.int32))
+    ed, wd, bd = emb.cuda().requires_grad_(True), w.cuda().requires_grad_(True), b.cuda().requires_grad_(True)
+    out = ops.embed_dense(ed, ids.cuda(), 1, wd, bd)
+    eo, wo, bo = emb.clone().requires_grad_(True), w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    ref = O.embedding_lookup(eo, ids[:, 1]) @ wo.t() + bo
+    close(out, ref)
+    gup = T(rs.standard_normal((23, H)).astype(np.float32))
+    out.backward(gup.cuda()); ref.backward(gup)
+    gclose(ed.grad, eo.grad); gclose(wd.grad, wo.grad); gclose(bd.grad, bo.grad)
+    assert (ed.grad[0] == 0).all()
