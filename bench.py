@@ -1,0 +1,376 @@
+#!/usr/bin/env python
+"""bench.py — NRMS/NAML train samples/s (+ eval impressions/s) on N B200s, one JSON line.
+
+A "step" is one optimisation step of src/main.py:105-110 (forward, backward, gradient
+all-reduce, Adam) over one batch of synthetic MIND-shaped samples.
+
+  value        device-timed whole-job samples/s, batches resident in HBM, CUDA events, max over ranks
+  e2e          same metric through the public plugin API with HOST (pinned) batches: H2D of the
+               four input tensors + D2H of the loss inside the timed region, every step
+  roofline     dominant kernel of the step: algorithmic FLOPs (or bytes) / CUDA-event time on the
+               launch stream (library-side event pairs, separate profiled pass) vs MEASURED_PEAKS.json
+  cpu_baseline the oracle port of the reference's CPU path, timed on this box's host cores
+  --impl reference   the same CPU path as its own arm (all host threads)
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+V_SMALL, N_SMALL, L_TITLE, T_HIST, K_NEG = 12508, 65238, 30, 50, 4
+METRIC = 'NRMS/NAML train samples/s & eval impressions/s at 1/2/4/8 B200 vs CPU ref'
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=20)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--model', default='NRMS', choices=['NRMS', 'NAML'])
+    ap.add_argument('--precision', default=os.environ.get('NR_PRECISION', 'fp32'), choices=['fp32', 'bf16'])
+    ap.add_argument('--batch', type=int, default=128, help='samples per GPU per step (weak scaling)')
+    ap.add_argument('--eval-impressions', type=int, default=73152)
+    ap.add_argument('--no-eval', action='store_true')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--cpu-batch', type=int, default=32)
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, 'MEASURED_PEAKS.json')
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {'hbm': d['hbm_gbs'], 'tensor_burst': d['bf16_tflops'],
+                'tensor': d.get('bf16_tflops_sustained', d['bf16_tflops']), 'src': 'measured'}
+    return {'hbm': 6650.0, 'tensor_burst': 1590.0, 'tensor': 1400.0, 'src': 'fallback'}
+
+
+# ----------------------------------------------------------------------------------------
+# workload
+# ----------------------------------------------------------------------------------------
+def make_workload(a, rank):
+    from newsrecommendation_b200 import synthetic as S
+    if a.model == 'NRMS':
+        args = S.default_args(num_words_title=L_TITLE, drop_rate=0.2, batch_size=a.batch, precision=a.precision)
+        table = S.word_table(V_SMALL)
+        news = S.news_titles(N_SMALL, L_TITLE, V_SMALL)
+        ctor = (table, 0, 0)
+    else:
+        args = S.default_args(num_words_title=L_TITLE, drop_rate=0.2, batch_size=a.batch, precision=a.precision,
+                              use_category=True, use_subcategory=True, freeze_embedding=True)
+        table = S.title_table(N_SMALL, L_TITLE)
+        news = S.naml_features(N_SMALL)
+        ctor = (table, 17, 264)
+    return args, ctor, news
+
+
+def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20):
+    """Algorithmic FLOPs per step for each named kernel of the step."""
+    n = B * (T + 1 + K_NEG)
+    M, Mu = n * L, B * T
+    f = {}
+    if model == 'NRMS':
+        f['mhsa.qkv'] = 2.0 * M * D * 3 * H + 2.0 * Mu * H * 3 * H
+        f['attn_fwd'] = 4.0 * n * L * L * H + 4.0 * B * T * T * H
+        f['attn_bwd'] = 2.5 * f['attn_fwd']
+        f['mhsa.dw'] = f['mhsa.qkv']
+        f['mhsa.dtable'] = 2.0 * M * D * 3 * H
+        f['mhsa.dx'] = 2.0 * Mu * H * 3 * H
+        f['pool.fc1'] = 2.0 * (M + Mu) * H * Q
+        f['nrms.encoder_fwd'] = 2.0 * M * D * 3 * H + 4.0 * n * L * L * H + 2.0 * M * H * Q
+    else:
+        f['conv.fwd'] = 2.0 * M * 3 * D * H
+        f['conv.dw'] = f['conv.fwd']
+        f['pool.fc1'] = 2.0 * (M + Mu + 3 * n) * H * Q
+        f['naml.encoder_fwd'] = 2.0 * M * 3 * D * H + 2.0 * M * H * Q
+    f['pool.dx'] = f['pool.fc1']
+    f['pool.dw1'] = f['pool.fc1']
+    return f
+
+
+class ClockSampler:
+    Q = ('index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,'
+         'clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
+         'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, idx):
+        self.f = tempfile.NamedTemporaryFile('w+', suffix='.csv', delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(['nvidia-smi', '-i', str(idx), '--query-gpu=' + self.Q,
+                                       '--format=csv,noheader,nounits', '-lms', '100'], stdout=self.f,
+                                      stderr=subprocess.DEVNULL)
+        except OSError:
+            pass
+
+    def stop(self):
+        if self.p is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        self.p.terminate()
+        self.p.wait()
+        self.f.flush()
+        sm, mx, reasons = [], 0, set()
+        for line in open(self.f.name):
+            c = [x.strip() for x in line.split(',')]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx = max(mx, float(c[2]))
+            except ValueError:
+                continue
+            for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), c[5:9]):
+                if v.lower().startswith('active'):
+                    reasons.add(name)
+        os.unlink(self.f.name)
+        # under load = upper half of the samples (the sampler also sees the idle edges)
+        sm.sort()
+        load = sm[len(sm) // 2:] if sm else []
+        return {'sm_mhz': float(np.median(load)) if load else None, 'sm_max_mhz': mx or None,
+                'reasons': sorted(reasons), 'samples': len(sm)}
+
+
+def timed(fn, steps, world):
+    """K calls of fn(i) between barrier+sync, CUDA events on the current stream, max over ranks."""
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(steps):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device='cuda', dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item())
+
+
+# ----------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's train step (src/main.py:105-110), all host threads
+# ----------------------------------------------------------------------------------------
+def cpu_train_samples_per_s(a, budget_s=25.0, max_steps=6):
+    from oracle import nr_oracle as O
+    from newsrecommendation_b200 import synthetic as S
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    B, p = a.cpu_batch, 0.2
+    if a.model == 'NRMS':
+        table = S.word_table(V_SMALL)
+        news = S.news_titles(2000, L_TITLE, V_SMALL)
+        sys.path.insert(0, os.path.join(ROOT, 'tests', 'golden'))
+        import synth
+        P = synth.nrms_weights(0, 8)
+        P['news_encoder.embedding_matrix.weight'] = table
+    else:
+        sys.path.insert(0, os.path.join(ROOT, 'tests', 'golden'))
+        import synth
+        P = synth.naml_weights(0, 2000, L_TITLE, True, True)
+        news = S.naml_features(2000)
+    P = {k: torch.from_numpy(v).clone() for k, v in P.items()}
+    train = [k for k in P if not (a.model == 'NAML' and k.endswith('title_embeddings.weight'))]
+    for k in train:
+        P[k].requires_grad_(True)
+    st = {k: (torch.zeros_like(P[k]), torch.zeros_like(P[k])) for k in train}
+    batches = S.train_batches(news, 2, B)
+    n = B * (T_HIST + 1 + K_NEG)
+
+    def step(i, s):
+        h, m, c, y = [torch.from_numpy(x) for x in batches[i % 2]]
+        # F.dropout's Bernoulli draws are part of the reference step (39.6 % of its CPU time)
+        keep = {}
+        nc, nh = B * (1 + K_NEG), B * T_HIST
+        for tag, cnt in (('cand', nc), ('hist', nh)):
+            keep[tag + '1'] = torch.empty(cnt, L_TITLE, 300).bernoulli_(1 - p)
+            if a.model == 'NRMS':
+                keep[tag + '2'] = torch.empty(cnt, L_TITLE, 400).bernoulli_(1 - p)
+        if a.model == 'NRMS':
+            loss, _ = O.nrms_forward(h, m, c, y, P, 20, False, p, keep)
+        else:
+            loss, _ = O.naml_forward(h, m, c, y, P, L_TITLE, 300, True, True, False, p, keep)
+        for k in train:
+            P[k].grad = None
+        loss.backward()
+        with torch.no_grad():
+            for k in train:
+                g = P[k].grad if P[k].grad is not None else torch.zeros_like(P[k])
+                O.adam_step(P[k], g, st[k][0], st[k][1], s, 3e-4)
+        return float(loss)
+
+    step(0, 1)                                   # warm-up
+    t0 = time.perf_counter()
+    done = 0
+    while done < max_steps and (time.perf_counter() - t0 < budget_s or done < 2):
+        step(done + 1, done + 2)
+        done += 1
+    dt = time.perf_counter() - t0
+    return {'value': done * B / dt, 'unit': 'samples/s', 'cores': cores, 'kind': 'port',
+            'sample': f'{done} train steps of batch {B} ({a.model}, L={L_TITLE}, T={T_HIST}, drop 0.2, '
+                      f'Adam) through oracle/nr_oracle.py on torch-CPU, {cores} threads',
+            'ms_per_step': dt / done * 1e3, 'batch': B}
+
+
+def run_reference(a):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    r = cpu_train_samples_per_s(a, budget_s=20.0 * max(1, a.steps) / 4, max_steps=max(2, a.steps))
+    line = {'metric': METRIC, 'impl': 'reference', 'value': r['value'], 'unit': 'samples/s', 'n_gpus': a.gpus,
+            'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': r['ms_per_step'], 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+            'config': {'workload': f'{a.model} train step, MIND-small shape (L=30, T=50, npratio=4, D=300, '
+                                   f'20x20 heads), CPU batch {r["batch"]}', 'model_family': a.model},
+            'cpu_baseline': {k: r[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')},
+            'e2e': {'value': r['value'], 'unit': 'samples/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+    print(json.dumps(line))
+
+
+# ----------------------------------------------------------------------------------------
+# GPU arm
+# ----------------------------------------------------------------------------------------
+def run_ours(a):
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    from newsrecommendation_b200 import _lib as L, engine, synthetic as S
+    from newsrecommendation_b200 import model as model_pkg  # noqa: F401
+    import importlib
+    mod = importlib.import_module(f'newsrecommendation_b200.model.{a.model}')   # main.py:63
+    torch.manual_seed(0)
+    args, ctor, news = make_workload(a, rank)
+    model = mod.Model(args, *ctor).cuda()
+    model.train()
+    opt = engine.FlatAdam(model, lr=3e-4)
+    opt.broadcast_params()
+    R = 8
+    host = S.train_batches(news, R, a.batch, seed=100 + rank)
+    pinned = [[torch.from_numpy(x).pin_memory() for x in b] for b in host]
+    dev = [[t.cuda() for t in b] for b in pinned]
+    h2d = sum(t.numel() * t.element_size() for t in pinned[0])
+
+    def step_dev(i):
+        engine.train_step(model, opt, *dev[i % R])
+
+    losses = []
+
+    def step_e2e(i):
+        h, m, c, y = [t.cuda(non_blocking=True) for t in pinned[i % R]]      # main.py:99-103
+        opt.zero_grad()
+        loss, score = model(h, m, c, y)                                       # main.py:105
+        loss.backward()                                                       # main.py:109
+        opt.step()                                                            # main.py:110 (+ all-reduce)
+        losses.append(loss.item())                                            # D2H of the step's result
+
+    for i in range(max(3, a.warmup)):
+        step_dev(i)
+    sampler = ClockSampler(local) if rank == 0 else None
+    n0 = L.lib.nr_launch_count()
+    ms = timed(step_dev, a.steps, world)
+    launches = L.lib.nr_launch_count() - n0
+    clocks = sampler.stop() if sampler else None
+    for i in range(2):
+        step_e2e(i)
+    ms_e2e = timed(step_e2e, a.steps, world)
+    # profiled pass: library-side CUDA-event pairs around every kernel, on the launch stream
+    L.lib.nr_prof_enable(1)
+    for i in range(a.steps):
+        step_dev(i)
+    prof = L.prof_report()
+    L.lib.nr_prof_enable(0)
+
+    ev = None
+    if not a.no_eval:
+        ev = run_eval(a, model, news, rank, world, engine, S)
+
+    if rank == 0:
+        pk = peaks()
+        ft = flops_table(a.model, a.batch)
+        tot = sum(v[1] for v in prof.values()) or 1.0
+        kern = {k: {'ms_per_step': v[1] / a.steps, 'launches_per_step': v[0] / a.steps, 'share': v[1] / tot}
+                for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
+        for k in kern:
+            if k in ft:
+                kern[k]['tflops'] = ft[k] / (kern[k]['ms_per_step'] * 1e-3) / 1e12
+        top = next((k for k in kern if k in ft), None)
+        roof = None
+        if top:
+            ach = kern[top]['tflops']
+            roof = {'kernel': top, 'bound': 'tensor', 'achieved': ach, 'peak': pk['tensor'], 'unit': 'TFLOP/s',
+                    'frac': ach / pk['tensor'], 'traffic': None, 'peak_source': pk['src'] + ' (sustained bf16)',
+                    'share_of_step': kern[top]['share'], 'flops_per_step': ft[top],
+                    'avg_launch_ms': kern[top]['ms_per_step'] / max(1e-9, kern[top]['launches_per_step'])}
+        B = a.batch
+        line = {
+            'metric': METRIC, 'value': world * B * a.steps / (ms * 1e-3), 'unit': 'samples/s', 'n_gpus': world,
+            'steps': a.steps, 'warmup': max(3, a.warmup), 'ms_per_step': ms / a.steps, 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16' if a.precision == 'bf16' else 'f32',
+            'data': 'synthetic',
+            'config': {'workload': f'{a.model} train step (fwd+bwd+allreduce+Adam), MIND-small shape: batch {B}/GPU, '
+                                   f'title len {L_TITLE}, history {T_HIST}, npratio {K_NEG}, 300-d emb, 20x20 heads, '
+                                   f'drop 0.2, V={V_SMALL}', 'model_family': a.model, 'per_gpu_batch': B,
+                       'global_batch': B * world, 'precision': a.precision, 'parallelism': f'dp{world}',
+                       'l2_policy': f'{R} distinct resident batches rotated; per-step activations '
+                                    f'(>1 GB fp32) exceed the 126 MB L2'},
+            'e2e': {'value': world * B * a.steps / (ms_e2e * 1e-3), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d,
+                    'd2h_bytes_per_step': 4, 'ms_per_step': ms_e2e / a.steps},
+            'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roof, 'kernels': kern,
+            'final_loss': losses[-1] if losses else None,
+        }
+        if ev:
+            line['eval'] = ev
+        if world == 1 and not a.no_cpu_baseline:
+            r = cpu_train_samples_per_s(a)
+            line['cpu_baseline'] = {k: r[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_eval(a, model, news, rank, world, engine, S):
+    """Config 4: news-vector cache (sharded encode + all-gather), impressions sharded i % world."""
+    I = a.eval_impressions // world
+    hidx, hmask, off, cand, labels = [torch.from_numpy(x).cuda() for x in
+                                      S.eval_impressions(news.shape[0] - 1, I, seed=500 + rank)]
+    news_d = torch.from_numpy(news).cuda()
+    out = {}
+
+    def cache(_):
+        out['table'] = engine.build_news_cache(model, news_d, batch=4096)
+
+    def score(_):
+        out['res'] = engine.score_impressions(model, out['table'], hidx, hmask, off, cand, labels, batch=4096)
+
+    cache(0)
+    ms_cache = timed(cache, 1, world)
+    score(0)
+    ms_score = timed(score, 2, world) / 2
+    res = engine.reduce_eval_sums(out['res'][3], I)
+    model.train()
+    return {'news': int(news.shape[0]), 'news_per_s': news.shape[0] / (ms_cache * 1e-3),
+            'impressions': I * world, 'impressions_per_s': I * world / (ms_score * 1e-3),
+            'impressions_per_s_incl_cache': I * world / ((ms_score + ms_cache) * 1e-3),
+            'metrics_mean_scored': [float(x) for x in res['mean_scored']], 'scored': res['scored']}
+
+
+if __name__ == '__main__':
+    a = parse()
+    if a.impl == 'reference':
+        run_reference(a)
+    else:
+        run_ours(a)

@@ -61,6 +61,13 @@ const char* nr_last_error(void);
 /* sm count / compute capability of the current device */
 int nr_device_info(int32_t* sm_count, int32_t* cc_major, int32_t* cc_minor);
 
+/* number of kernels this library has launched in this process (bench.py: gpu_launches) */
+long long nr_launch_count(void);
+/* per-kernel CUDA-event timing on the launch stream: enable, run, then report.  The report
+ * synchronises the device and writes "name launches total_ms" lines; returns bytes needed. */
+int nr_prof_enable(int on);
+size_t nr_prof_report(char* buf, size_t cap);
+
 /* keep[i] = 1 if element i of dropout stream (seed, stream_id) is kept at rate p */
 int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed,
                          int32_t stream_id, void* stream);

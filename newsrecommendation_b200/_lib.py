@@ -37,6 +37,9 @@ _SIGS = {
     'nr_abi_version': (C.c_int, []),
     'nr_last_error': (C.c_char_p, []),
     'nr_device_info': (C.c_int, [_P, _P, _P]),
+    'nr_launch_count': (C.c_longlong, []),
+    'nr_prof_enable': (C.c_int, [C.c_int]),
+    'nr_prof_report': (_SZ, [C.c_char_p, _SZ]),
     'nr_dropout_keep_mask': (C.c_int, [_P, _I64, _F, _U64, _I32, _P]),
     'nr_gather_rows': (C.c_int, [_P, _I64, _P, _I64, _I32, _P, _P]),
     'nr_attention_pooling_workspace': (_SZ, [_I64, _I32, _I32, _I32, _I32]),
@@ -114,6 +117,17 @@ def make_rows(mode, *, dense=None, table=None, ids=None, ids_stride=0, drop_p=0.
     r.drop_p = float(drop_p)
     r.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
     return r
+
+
+def prof_report():
+    """{kernel name: (launches, total_ms)} recorded since nr_prof_enable(1); clears the log."""
+    buf = C.create_string_buffer(1 << 16)
+    lib.nr_prof_report(buf, len(buf))
+    out = {}
+    for line in buf.value.decode().splitlines():
+        name, n, ms = line.rsplit(' ', 2)
+        out[name] = (int(n), float(ms))
+    return out
 
 
 def workspace(nbytes, device):

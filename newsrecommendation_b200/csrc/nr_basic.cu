@@ -1,5 +1,10 @@
 // nr_basic.cu — library plumbing and the HBM-bound elementwise/gather ops.
 #include <stdarg.h>
+#include <atomic>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
 #include "nr_common.cuh"
 
 namespace nr {
@@ -20,6 +25,30 @@ int check_last(const char* what) {
         return 3;
     }
     return 0;
+}
+
+// ---- launch counter + optional per-kernel event timing ------------------------------------
+static std::atomic<long long> g_launches{0};
+static std::atomic<int> g_prof_on{0};
+struct ProfRec { const char* name; cudaEvent_t a, b; };
+static std::mutex g_prof_mu;
+static std::vector<ProfRec*> g_prof_recs;
+
+ProfScope::ProfScope(const char* n, cudaStream_t s) : name(n), st(s), slot(nullptr) {
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    if (!g_prof_on.load(std::memory_order_relaxed)) return;
+    ProfRec* r = new ProfRec{n, nullptr, nullptr};
+    cudaEventCreate(&r->a);
+    cudaEventCreate(&r->b);
+    cudaEventRecord(r->a, s);
+    slot = r;
+}
+ProfScope::~ProfScope() {
+    if (!slot) return;
+    ProfRec* r = (ProfRec*)slot;
+    cudaEventRecord(r->b, st);
+    std::lock_guard<std::mutex> lk(g_prof_mu);
+    g_prof_recs.push_back(r);
 }
 
 RowsView make_rows_view(const nr_rows_t* r, int64_t n, int S, int D) {
@@ -219,6 +248,48 @@ using namespace nr;
 extern "C" {
 
 int nr_abi_version(void) { return NR_ABI_VERSION; }
+
+long long nr_launch_count(void) { return nr::g_launches.load(); }
+
+int nr_prof_enable(int on) {
+    nr::g_prof_on.store(on ? 1 : 0);
+    return 0;
+}
+
+// Synchronises the device, sums the recorded event pairs by kernel name and clears them.
+// Writes lines "name launches total_ms\n" into buf (NUL terminated); returns bytes needed.
+size_t nr_prof_report(char* buf, size_t cap) {
+    cudaDeviceSynchronize();
+    std::vector<nr::ProfRec*> recs;
+    {
+        std::lock_guard<std::mutex> lk(nr::g_prof_mu);
+        recs.swap(nr::g_prof_recs);
+    }
+    std::map<std::string, std::pair<long long, double>> agg;
+    for (nr::ProfRec* r : recs) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, r->a, r->b) == cudaSuccess) {
+            auto& e = agg[r->name];
+            e.first += 1;
+            e.second += ms;
+        }
+        cudaEventDestroy(r->a);
+        cudaEventDestroy(r->b);
+        delete r;
+    }
+    std::string out;
+    char line[256];
+    for (auto& kv : agg) {
+        snprintf(line, sizeof(line), "%s %lld %.6f\n", kv.first.c_str(), kv.second.first, kv.second.second);
+        out += line;
+    }
+    if (buf && cap) {
+        size_t n = out.size() < cap - 1 ? out.size() : cap - 1;
+        memcpy(buf, out.data(), n);
+        buf[n] = 0;
+    }
+    return out.size() + 1;
+}
 const char* nr_last_error(void) { return nr::g_err; }
 
 int nr_device_info(int32_t* sms, int32_t* major, int32_t* minor) {
@@ -237,6 +308,7 @@ int nr_device_info(int32_t* sms, int32_t* major, int32_t* minor) {
 int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed, int32_t sid, void* stream) {
     NR_REQUIRE(keep && count >= 0 && p >= 0.f && p < 1.f, "nr_dropout_keep_mask: bad arguments");
     if (count == 0) return 0;
+    ProfScope ps_keep_mask("keep_mask", (cudaStream_t)stream);
     keep_mask_kernel<<<grid_for((count + 3) / 4, 256), 256, 0, (cudaStream_t)stream>>>(
         keep, count, drop_threshold(p), seed, (uint32_t)sid);
     return check_last("nr_dropout_keep_mask");
@@ -244,11 +316,13 @@ int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed, i
 
 int nr_gather_rows(const float* table, int64_t table_rows, const int32_t* ids, int64_t count,
                    int32_t width, float* out, void* stream) {
+    if (count == 0) return 0;
     NR_REQUIRE(table && ids && out, "nr_gather_rows: NULL pointer");
     NR_REQUIRE(width > 0 && (width & 3) == 0, "nr_gather_rows: width %d must be a positive multiple of 4", width);
     NR_REQUIRE(table_rows > 0 && count >= 0, "nr_gather_rows: bad sizes");
     if (count == 0) return 0;
     const int64_t total4 = count * (width / 4);
+    ProfScope ps_gather_rows("gather_rows", (cudaStream_t)stream);
     gather_rows_kernel<<<grid_for(total4, 256, 16), 256, 0, (cudaStream_t)stream>>>(table, ids, out, total4,
                                                                                     width / 4);
     return check_last("nr_gather_rows");
@@ -259,6 +333,7 @@ int nr_pad_blend_fwd(const float* v, const float* mask, const float* pad, float*
     NR_REQUIRE(v && mask && pad && out, "nr_pad_blend_fwd: NULL pointer");
     NR_REQUIRE(H > 0 && (H & 3) == 0, "nr_pad_blend_fwd: H %d must be a multiple of 4", H);
     if (n * T == 0) return 0;
+    ProfScope ps_pad_blend_fwd("pad_blend_fwd", (cudaStream_t)stream);
     pad_blend_fwd_kernel<<<grid_for(n * T * (H / 4), 256), 256, 0, (cudaStream_t)stream>>>(v, mask, pad, out,
                                                                                          n * T, H / 4);
     return check_last("nr_pad_blend_fwd");
@@ -269,6 +344,7 @@ int nr_pad_blend_bwd(const float* dout, const float* mask, float* dv, float* dpa
     NR_REQUIRE(dout && mask && dv && dpad, "nr_pad_blend_bwd: NULL pointer");
     if (n * T == 0) return 0;
     int64_t g = n * T < 2 * sm_count() ? n * T : 2 * sm_count();
+    ProfScope ps_pad_blend_bwd("pad_blend_bwd", (cudaStream_t)stream);
     pad_blend_bwd_kernel<<<(unsigned)g, 128, 0, (cudaStream_t)stream>>>(dout, mask, dv, dpad, n * T, H);
     return check_last("nr_pad_blend_bwd");
 }
@@ -278,9 +354,11 @@ int nr_score_ce_fwd(const float* cand, const float* user, const int64_t* label, 
     NR_REQUIRE(cand && user && label && score && loss && hits && per_sample_ws, "nr_score_ce_fwd: NULL pointer");
     NR_REQUIRE(B > 0 && C > 0 && H > 0, "nr_score_ce_fwd: bad sizes");
     const int threads = 128;
+    ProfScope ps_score_ce_fwd("score_ce_fwd", (cudaStream_t)stream);
     score_ce_fwd_kernel<<<(unsigned)((B * 32 + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
         cand, user, label, score, per_sample_ws, B, C, H);
     if (int e = check_last("nr_score_ce_fwd")) return e;
+    ProfScope ps_score_ce_reduce("score_ce_reduce", (cudaStream_t)stream);
     score_ce_reduce_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(per_sample_ws, loss, hits, B);
     return check_last("nr_score_ce_fwd(reduce)");
 }
@@ -290,6 +368,7 @@ int nr_score_ce_bwd(const float* cand, const float* user, const int64_t* label, 
                     void* stream) {
     NR_REQUIRE(cand && user && label && score && gloss && dcand && duser, "nr_score_ce_bwd: NULL pointer");
     NR_REQUIRE(B > 0 && C > 0 && C <= 1024 && H > 0, "nr_score_ce_bwd: bad sizes");
+    ProfScope ps_score_ce_bwd("score_ce_bwd", (cudaStream_t)stream);
     score_ce_bwd_kernel<<<(unsigned)B, 128, C * sizeof(float), (cudaStream_t)stream>>>(
         cand, user, label, score, gloss, dcand, duser, B, C, H);
     return check_last("nr_score_ce_bwd");
@@ -302,6 +381,7 @@ int nr_adam_step(float* p, const float* g, float* m, float* v, int64_t count, fl
     if (count == 0) return 0;
     const double bc1 = 1.0 - pow((double)beta1, (double)step);
     const double bc2 = 1.0 - pow((double)beta2, (double)step);
+    ProfScope ps_adam("adam", (cudaStream_t)stream);
     adam_kernel<<<grid_for(count, 256), 256, 0, (cudaStream_t)stream>>>(
         p, g, m, v, count, (float)((double)lr / bc1), beta1, beta2, eps, (float)(1.0 / sqrt(bc2)), grad_scale);
     return check_last("nr_adam_step");

@@ -12,6 +12,17 @@ namespace nr {
 void set_error(const char* fmt, ...);
 int check_last(const char* what);   // cudaGetLastError -> error code + message
 
+// Per-kernel CUDA-event timing (off by default; bench.py turns it on for one profiled pass).
+// A ProfScope placed around a launch records start/stop events on the launch stream and
+// counts the launch; nr_prof_report sums the event pairs by name.
+struct ProfScope {
+    const char* name;
+    cudaStream_t st;
+    void* slot;
+    ProfScope(const char* name, cudaStream_t st);
+    ~ProfScope();
+};
+
 #define NR_REQUIRE(cond, ...)                      \
     do {                                           \
         if (!(cond)) {                             \

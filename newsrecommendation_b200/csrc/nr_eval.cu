@@ -138,6 +138,7 @@ int nr_eval_score(const float* table, int64_t table_rows, const float* user_vecs
     int64_t blocks = (total_cands * 32 + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 16;
     if (blocks > cap) blocks = cap;
+    ProfScope ps("eval_score", (cudaStream_t)stream);
     eval_score_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(table, user_vecs, offsets, cand_idx,
                                                                          scores, I, total_cands, H);
     return check_last("nr_eval_score");
@@ -148,6 +149,7 @@ int nr_eval_rank_metrics(const float* scores, const int8_t* labels, const int64_
     NR_REQUIRE(scores && labels && offsets && metrics && valid, "nr_eval_rank_metrics: NULL pointer");
     if (I == 0) return 0;
     int64_t blocks = I < (int64_t)sm_count() * 16 ? I : (int64_t)sm_count() * 16;
+    ProfScope ps("rank_metrics", (cudaStream_t)stream);
     rank_metrics_kernel<<<(unsigned)blocks, 128, 0, (cudaStream_t)stream>>>(scores, labels, offsets, metrics,
                                                                            valid, I);
     return check_last("nr_eval_rank_metrics");
@@ -155,6 +157,7 @@ int nr_eval_rank_metrics(const float* scores, const int8_t* labels, const int64_
 
 int nr_eval_reduce_metrics(const double* metrics, const uint8_t* valid, double* sums, int64_t I, void* stream) {
     NR_REQUIRE(metrics && valid && sums, "nr_eval_reduce_metrics: NULL pointer");
+    ProfScope ps("reduce_metrics", (cudaStream_t)stream);
     reduce_metrics_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(metrics, valid, sums, I);
     return check_last("nr_eval_reduce_metrics");
 }

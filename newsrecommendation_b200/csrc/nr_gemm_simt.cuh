@@ -269,6 +269,7 @@ int gemm_nt(const AV& a, const BV& b, const Epi& e, int64_t M, int N, int K, cud
     if (M == 0 || N == 0) return 0;
     if ((N & 3) || (K & 3)) { set_error("%s: N=%d K=%d must be multiples of 4", what, N, K); return 1; }
     dim3 grid((unsigned)((M + GBM - 1) / GBM), (unsigned)((N + GBN - 1) / GBN), 1);
+    ProfScope ps(what, st);
     gemm_simt_kernel<true, true, AV, BV, Epi><<<grid, GTHREADS, 0, st>>>(a, b, e, M, N, K, K);
     return check_last(what);
 }
@@ -289,6 +290,7 @@ int gemm_tn(const AV& a, const BV& b, const Epi& e, int M, int N, int64_t K, cud
     k_chunk = (k_chunk + GBK - 1) / GBK * GBK;
     splits = (K + k_chunk - 1) / k_chunk;
     dim3 grid((unsigned)((M + GBM - 1) / GBM), (unsigned)((N + GBN - 1) / GBN), (unsigned)splits);
+    ProfScope ps(what, st);
     gemm_simt_kernel<false, false, AV, BV, Epi><<<grid, GTHREADS, 0, st>>>(a, b, e, M, N, K, k_chunk);
     return check_last(what);
 }

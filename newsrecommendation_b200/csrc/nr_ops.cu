@@ -13,6 +13,7 @@ int launch_attn_fwd(const float* qkv, const float* mask, float* ctx, int64_t n, 
     const size_t smem = attn_fwd_smem(S, DK);
     NR_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int groups = (heads + 3) / 4;
+    ProfScope ps("attn_fwd", st);
     attn_fwd_kernel<DK><<<(unsigned)(n * groups), 128, smem, st>>>(
         qkv, mask, ctx, S, heads, 1.0f / sqrtf((float)DK), p > 0.f ? drop_threshold(p) : 0u,
         p > 0.f ? 1.f / (1.f - p) : 1.f, seed);
@@ -24,6 +25,7 @@ int launch_attn_bwd(const float* qkv, const float* mask, const float* dctx, floa
     const size_t smem = attn_bwd_smem(S, DK);
     NR_CUDA(cudaFuncSetAttribute(attn_bwd_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int groups = (heads + 3) / 4;
+    ProfScope ps("attn_bwd", st);
     attn_bwd_kernel<DK><<<(unsigned)(n * groups), 128, smem, st>>>(
         qkv, mask, dctx, dqkv, S, heads, 1.0f / sqrtf((float)DK), p > 0.f ? drop_threshold(p) : 0u,
         p > 0.f ? 1.f / (1.f - p) : 1.f, seed);
@@ -79,6 +81,7 @@ int nr_attention_pooling_fwd(const float* x, const float* mask, const float* w1,
     if (int e = gemm_nt(DenseView{x, H, M, H}, DenseView{w1, H, Q, H}, EpiBiasTanh{e_save, Q, b1}, M, Q, H, st,
                         "pool.fc1"))
         return e;
+    ProfScope ps("pool_tail_fwd", st);
     pool_tail_fwd_kernel<<<(unsigned)n, 128, S * sizeof(float), st>>>(x, e_save, mask, w2, b2, out, alpha_save,
                                                                       S, H, Q);
     return check_last("pool_tail_fwd");
@@ -99,6 +102,7 @@ int nr_attention_pooling_bwd(const float* g, const float* x, const float* w1, co
     float* dz = W.take<float>((size_t)M * Q);
     NR_REQUIRE(dz, "nr_attention_pooling_bwd: workspace too small (%zu bytes)", ws_bytes);
     int64_t grid = n < 4 * (int64_t)sm_count() ? n : 4 * (int64_t)sm_count();
+    ProfScope ps("pool_tail_bwd", st);
     pool_tail_bwd_kernel<<<(unsigned)grid, 256, (S + Q) * sizeof(float), st>>>(g, x, e_save, alpha_save, w2, dz,
                                                                                dx, dw2, db2, n, S, H, Q);
     if (int e = check_last("pool_tail_bwd")) return e;

@@ -135,6 +135,7 @@ inline int colsum(const float* Y, int64_t rows, int64_t ld, int cols, float* o0,
     int64_t gy = (4 * (int64_t)sm_count() + gx - 1) / gx;
     if (gy > rows) gy = rows;
     if (gy > 65535) gy = 65535;
+    ProfScope ps("colsum", st);
     colsum_kernel<<<dim3(gx, (unsigned)gy), 128, 0, st>>>(Y, rows, ld, cols, o0, o1, o2, each);
     return check_last("colsum");
 }

@@ -34,30 +34,30 @@ class FlatAdam:
         dev = self.params[0].device
         if dev.type != 'cuda':
             raise RuntimeError('FlatAdam: move the model to a CUDA device first (no CPU path exists)')
-        self.count = sum(p.numel() for p in self.params)
-        self.flat_p = torch.empty(self.count, dtype=torch.float32, device=dev)
+        # every parameter starts on a 256-byte boundary (kernels use 128-bit loads on them)
+        self.offsets, off = [], 0
+        for p in self.params:
+            self.offsets.append(off)
+            off += (p.numel() + 63) // 64 * 64
+        self.count = off
+        self.flat_p = torch.zeros(self.count, dtype=torch.float32, device=dev)
         self.flat_g = torch.zeros(self.count, dtype=torch.float32, device=dev)
         self.m = torch.zeros_like(self.flat_p)
         self.v = torch.zeros_like(self.flat_p)
-        off = 0
-        for p in self.params:
+        for p, off in zip(self.params, self.offsets):
             n = p.numel()
             self.flat_p[off:off + n].copy_(p.data.reshape(-1))
             p.data = self.flat_p[off:off + n].view(p.shape)          # Parameter object unchanged
             p.grad = self.flat_g[off:off + n].view(p.shape)
-            off += n
         self.lr, self.betas, self.eps = lr, betas, eps
         self.step_count = 0
 
     def zero_grad(self):
         self.flat_g.zero_()
-        off = 0
-        for p in self.params:      # re-attach in case autograd replaced .grad
-            n = p.numel()
-            g = self.flat_g[off:off + n].view(p.shape)
+        for p, off in zip(self.params, self.offsets):      # re-attach in case autograd replaced .grad
+            g = self.flat_g[off:off + p.numel()].view(p.shape)
             if p.grad is None or p.grad.data_ptr() != g.data_ptr():
                 p.grad = g
-            off += n
 
     def broadcast_params(self):
         """DDP constructor semantics (main.py:82): rank 0's weights everywhere."""

@@ -83,9 +83,10 @@ def test_eval_pipeline_vs_oracle(tag):
         k = 0 if i == 0 else int(rs.randint(1, 70))
         h, m = O.pad_history(rs.randint(1, N + 1, size=k).tolist(), Tn)     # dataset.py:17-24
         hist[i], hmask[i] = h, m
-    cs = rs.randint(2, 60, size=I); cs[1] = 300
+    cs = rs.randint(2, min(60, N), size=I); cs[1] = min(300, N)
     off = np.zeros(I + 1, np.int64); off[1:] = np.cumsum(cs)
-    cand = rs.randint(0, N + 1, size=off[-1]).astype(np.int32)
+    # candidates without repeats inside an impression (repeats = exactly tied scores)
+    cand = np.concatenate([rs.permutation(N + 1)[:c] for c in cs]).astype(np.int32)
     labels = (rs.rand(off[-1]) < 0.15).astype(np.int8)
     for i in range(I):
         labels[off[i]] = 1; labels[off[i] + 1] = 0
@@ -119,7 +120,7 @@ def test_eval_pipeline_vs_oracle(tag):
     # given the same cached table, device scoring must rank identically wherever scores are untied
     md = mets_d.cpu().numpy()
     untied = np.array([len(np.unique(scores_o[off[i]:off[i + 1]])) == off[i + 1] - off[i] and
-                       np.min(np.diff(np.sort(scores_o[off[i]:off[i + 1]]))) > 1e-5 for i in range(I)])
+                       np.min(np.diff(np.sort(scores_o[off[i]:off[i + 1]]))) > 2e-6 for i in range(I)])
     sel = valid_o & untied
-    assert sel.sum() > I // 2
+    assert sel.sum() > I // 3
     np.testing.assert_allclose(md[sel], mets_o[sel], rtol=0, atol=1e-12)

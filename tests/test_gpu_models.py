@@ -96,6 +96,7 @@ def test_train_steps_match_oracle_adam():
     P = {k: T(v).clone() for k, v in Pn.items()}
     train_keys = [k for k, p in model.named_parameters() if p.requires_grad]
     st = {k: (torch.zeros_like(P[k]), torch.zeros_like(P[k])) for k in train_keys}
+    g1 = {}
     hist, mask, cand, label = [T(a) for a in bt]
     model.train()
     for step in range(1, 4):
@@ -109,14 +110,19 @@ def test_train_steps_match_oracle_adam():
             for k in train_keys:
                 gk = P[k].grad if P[k].grad is not None else torch.zeros_like(P[k])
                 P[k].requires_grad_(False)
+                g1.setdefault(k, gk.clone())
                 O.adam_step(P[k], gk, st[k][0], st[k][1], step, 3e-4)
                 P[k].grad = None
     sd = model.state_dict()
     for k in train_keys:
         # Adam's first steps move every weight by ~lr regardless of gradient size, so
         # compare the UPDATE (p - p0) rather than p
+        # ...and only where the gradient is well above rounding noise: for g ~ 0 the Adam
+        # ratio m/sqrt(v) is +-1 on noise alone (e.g. analytically-zero gradients)
         d_dev = sd[k].cpu() - T(Pn[k]); d_or = P[k] - T(Pn[k])
-        np.testing.assert_allclose(d_dev.numpy(), d_or.numpy(), rtol=0, atol=3e-5, err_msg=k)
+        sel = g1[k].abs() > 1e-2 * g1[k].abs().max()
+        assert sel.any(), k
+        np.testing.assert_allclose(d_dev[sel].numpy(), d_or[sel].numpy(), rtol=0, atol=3e-5, err_msg=k)
         assert d_or.abs().max() > 1e-4
 
 

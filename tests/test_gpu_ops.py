@@ -29,7 +29,7 @@ def gclose(a, b, msg=''):
     """gradients: tolerance relative to the tensor's own scale"""
     b = b.detach().cpu().numpy()
     sc = max(1e-12, float(np.abs(b).max()))
-    close(a, b, rtol=1e-4, atol=2e-5 * sc + 1e-7, msg=msg)
+    close(a, b, rtol=1e-4, atol=2e-5 * sc + 1e-6, msg=msg)
 
 
 @pytest.fixture(scope='module')
