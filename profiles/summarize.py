@@ -1,0 +1,59 @@
+"""Summarise ncu outputs brought back in gpurun_out/ into small committed text files.
+  python profiles/summarize.py launches gpurun_out/X_launches.csv profiles/X_launches.txt
+  python profiles/summarize.py full gpurun_out/X.ncu-rep profiles/X_full.txt
+"""
+import csv
+import io
+import re
+import subprocess
+import sys
+from collections import defaultdict
+
+
+def launches(src, dst):
+    rows = [l for l in open(src, errors='replace') if l.startswith('"')]
+    rd = csv.DictReader(io.StringIO(''.join(rows)))
+    agg = defaultdict(lambda: [0, 0.0])
+    total = 0.0
+    for r in rd:
+        if r.get('Metric Name') != 'gpu__time_duration.sum':
+            continue
+        v = float(r['Metric Value'].replace(',', ''))
+        unit = r.get('Metric Unit', 'ns')
+        ns = v * {'ns': 1, 'us': 1e3, 'usecond': 1e3, 'ms': 1e6, 'msecond': 1e6, 'nsecond': 1}.get(unit, 1)
+        name = re.sub(r'\(.*', '', r['Kernel Name'])[:110]
+        agg[name][0] += 1
+        agg[name][1] += ns
+        total += ns
+    with open(dst, 'w') as f:
+        f.write(f'# ncu --metrics gpu__time_duration.sum --clock-control none ; source {src}\n')
+        f.write(f'# per-launch times are cold-cache and serialised: compare SHARES\n')
+        f.write(f'{"kernel":110s} {"launches":>8s} {"total_us":>12s} {"avg_us":>10s} {"share":>7s}\n')
+        for k, (n, ns) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            f.write(f'{k:110s} {n:8d} {ns / 1e3:12.1f} {ns / 1e3 / n:10.2f} {ns / total:7.3f}\n')
+        f.write(f'{"TOTAL":110s} {sum(v[0] for v in agg.values()):8d} {total / 1e3:12.1f}\n')
+
+
+KEYS = ('dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__time_duration.sum', 'gpu__dram_throughput',
+        'dram__cycles_active', 'sm__pipe_tensor', 'sm__warps_active.avg.pct', 'launch__registers_per_thread',
+        'launch__grid_size', 'launch__block_size', 'sm__throughput.avg.pct', 'smsp__inst_executed.sum',
+        'launch__occupancy_limit', 'sm__inst_executed_pipe_tensor', 'lts__t_bytes.sum', 'l1tex__t_bytes.sum',
+        'smsp__cycles_active.avg', 'sm__cycles_elapsed.max', 'launch__shared_mem_per_block')
+
+
+def full(src, dst):
+    out = subprocess.run(['ncu', '-i', src, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+    rd = list(csv.reader(io.StringIO(out)))
+    hdr, units = rd[0], rd[1]
+    with open(dst, 'w') as f:
+        f.write(f'# ncu --set full --clock-control none ; source {src}\n')
+        for row in rd[2:]:
+            d = dict(zip(hdr, row))
+            f.write(f'\n== {d.get("Kernel Name", "?")[:150]}  grid {d.get("Grid Size")} block {d.get("Block Size")}\n')
+            for h, u, v in zip(hdr, units, row):
+                if any(k in h for k in KEYS):
+                    f.write(f'  {h:70s} {v:>18s} {u}\n')
+
+
+if __name__ == '__main__':
+    {'launches': launches, 'full': full}[sys.argv[1]](sys.argv[2], sys.argv[3])

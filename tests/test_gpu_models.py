@@ -114,16 +114,21 @@ def test_train_steps_match_oracle_adam():
                 O.adam_step(P[k], gk, st[k][0], st[k][1], step, 3e-4)
                 P[k].grad = None
     sd = model.state_dict()
+    gmax = max(g.abs().max().item() for g in g1.values())
+    checked = 0
     for k in train_keys:
         # Adam's first steps move every weight by ~lr regardless of gradient size, so
         # compare the UPDATE (p - p0) rather than p
         # ...and only where the gradient is well above rounding noise: for g ~ 0 the Adam
         # ratio m/sqrt(v) is +-1 on noise alone (e.g. analytically-zero gradients)
         d_dev = sd[k].cpu() - T(Pn[k]); d_or = P[k] - T(Pn[k])
-        sel = g1[k].abs() > 1e-2 * g1[k].abs().max()
-        assert sel.any(), k
+        sel = g1[k].abs() > max(1e-2 * g1[k].abs().max().item(), 1e-5 * gmax)
+        if not sel.any():
+            continue          # e.g. att_fc2.bias: gradient analytically 0 (softmax shift invariance)
+        checked += 1
         np.testing.assert_allclose(d_dev[sel].numpy(), d_or[sel].numpy(), rtol=0, atol=3e-5, err_msg=k)
         assert d_or.abs().max() > 1e-4
+    assert checked >= len(train_keys) - 4
 
 
 def test_adam_vs_torch_golden():
