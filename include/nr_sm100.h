@@ -172,6 +172,16 @@ int nr_eval_rank_metrics(const float* scores, const int8_t* labels, const int64_
 int nr_eval_reduce_metrics(const double* metrics, const uint8_t* valid, double* sums, int64_t I,
                            void* stream);
 
+/* ---- bf16 tensor-core building block (tcgen05.mma, TMA-fed, fp32 accumulation in TMEM) ------
+ * C[m,n] = bias[n] + sum_{t<taps} sum_{k<K} A[m + shifts[t], k] * B[n, t*Kpad + k],  Kpad = ceil64(K)
+ * A (a_rows x K, leading dim lda) and B (N x taps*Kpad, leading dim ldb) are bf16, K contiguous;
+ * rows of A outside [0,a_rows) read as zero.  taps=1: plain x.W^T GEMM (nn.Linear, model_utils.py:21,
+ * 89-91); taps=3, shifts {-1,0,1}: Conv1d(k=3,pad=1) (NAML.py:27-32).  C is bf16 (c_bf16=1) or fp32.
+ * shifts_host is a HOST pointer. */
+int nr_tc_gemm_nt(const void* A, int64_t a_rows, int32_t K, int64_t lda, const void* B, int32_t N,
+                  int64_t ldb, const float* bias, void* C, int64_t ldc, int32_t c_bf16, int64_t M,
+                  int32_t taps, const int32_t* shifts_host, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
