@@ -9,15 +9,29 @@ int make_tmap_bf16_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_
     cuuint64_t gstride[1] = {ld_elems * 2};
     cuuint32_t box[2] = {box_cols, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = cuTensorMapEncodeTiled(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim,
+    // libcuda is reached through the runtime (cudaGetDriverEntryPoint), not linked: the library must
+    // load on a box without a driver (build check, symbol tests) and fail only when a kernel is asked for.
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t ce = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (ce != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) {
+            set_error("cuTensorMapEncodeTiled not available from the driver (%s)", cudaGetErrorString(ce));
+            return 4;
+        }
+        encode = (EncodeFn)fn;
+    }
+    CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim,
                                         gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                                         CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
-        const char* msg = nullptr;
-        cuGetErrorString(r, &msg);
-        set_error("cuTensorMapEncodeTiled failed (%d: %s) rows=%llu cols=%llu ld=%llu box=%ux%u", (int)r,
-                  msg ? msg : "?", (unsigned long long)rows, (unsigned long long)cols,
+        set_error("cuTensorMapEncodeTiled failed (CUresult %d) rows=%llu cols=%llu ld=%llu box=%ux%u", (int)r,
+                  (unsigned long long)rows, (unsigned long long)cols,
                   (unsigned long long)ld_elems, box_rows, box_cols);
         return 4;
     }
