@@ -38,7 +38,7 @@ def parse():
     ap.add_argument('--warmup', type=int, default=5)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--model', default='NRMS', choices=['NRMS', 'NAML'])
-    ap.add_argument('--precision', default=os.environ.get('NR_PRECISION', 'fp32'), choices=['fp32', 'bf16'])
+    ap.add_argument('--precision', default=os.environ.get('NR_PRECISION', 'bf16'), choices=['fp32', 'bf16'])
     ap.add_argument('--batch', type=int, default=128, help='samples per GPU per step (weak scaling)')
     ap.add_argument('--eval-impressions', type=int, default=73152)
     ap.add_argument('--no-eval', action='store_true')
@@ -96,6 +96,15 @@ def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20):
         f['naml.encoder_fwd'] = 2.0 * M * 3 * D * H + 2.0 * M * H * Q
     f['pool.dx'] = f['pool.fc1']
     f['pool.dw1'] = f['pool.fc1']
+    # bf16 tensor-core title encoder (nr_encoder.cu)
+    if model == 'NRMS':
+        f['enc.qkv'] = f['enc.dwqkv'] = f['enc.dx'] = 2.0 * M * D * 3 * H + 2.0 * Mu * H * 3 * H
+        f['enc.attn_fwd'] = f['attn_fwd']
+        f['enc.attn_bwd'] = f['attn_bwd']
+        f['enc.fc1'] = f['enc.pool_dx'] = f['enc.dw1'] = 2.0 * (M + Mu) * H * Q
+    else:
+        f['enc.conv'] = f['enc.dwconv'] = 2.0 * M * 3 * D * H
+        f['enc.fc1'] = f['enc.pool_dx'] = f['enc.dw1'] = 2.0 * M * H * Q
     return f
 
 

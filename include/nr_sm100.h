@@ -182,6 +182,50 @@ int nr_tc_gemm_nt(const void* A, int64_t a_rows, int32_t K, int64_t lda, const v
                   int64_t ldb, const float* bias, void* C, int64_t ldc, int32_t c_bf16, int64_t M,
                   int32_t taps, const int32_t* shifts_host, void* stream);
 
+/* C[tap][i,j] (fp32, Mo x ldc, taps stacked tap_stride apart) += sum_r A[r,i] * B[r + shifts[tap], j]
+ * A (rows x Mo, lda), B (rows x No, ldb) bf16 row-major: the split-K weight-gradient GEMM
+ * (dW = dY^T X of nn.Linear / nn.Conv1d backward; autograd of model_utils.py:21,89-91, NAML.py:54). */
+int nr_tc_gemm_tn(const void* A, int32_t Mo, int64_t lda, const void* B, int32_t No, int64_t ldb,
+                  int64_t rows, int32_t taps, const int32_t* shifts_host, float* C, int64_t ldc,
+                  int64_t tap_stride, void* stream);
+
+/* ---- bf16 title encoder: the whole NewsEncoder title path / NRMS UserEncoder in one call ------
+ *   NR_ENC_MHSA: rows -> [dropout] -> MultiHeadSelfAttention -> [dropout] -> AttentionPooling
+ *                (src/model/NRMS.py:27-35 news encoder; NRMS.py:55-62 user encoder with rows dense)
+ *   NR_ENC_CONV: rows -> [dropout] -> Conv1d(k=3,pad=1) -> AttentionPooling   (src/model/NAML.py:47-56)
+ * GEMMs run on tcgen05 tensor cores (bf16 operands, fp32 accumulation in TMEM); softmax-like
+ * normalisations, tanh and all reductions are fp32.  `mask` (n,S) or NULL is used both as the MHSA
+ * key mask and as the pooling mask (NRMS.py:56-57).  `save` keeps the bf16 activations for backward
+ * (opaque, caller owned, nr_title_encoder_save_bytes); `ws` is scratch. */
+enum { NR_ENC_MHSA = 0, NR_ENC_CONV = 1 };
+typedef struct nr_title_encoder {
+    int32_t kind, S, Dm, H, Q, heads;
+    const float* w[3];      /* MHSA: W_Q, W_K, W_V (H,Dm);  CONV: w[0] = Conv1d.weight (H,Dm,3) */
+    const float* b[3];      /* matching biases (H) */
+    const float* p_w1;      /* AttentionPooling att_fc1.weight (Q,H) */
+    const float* p_b1;      /* (Q) */
+    const float* p_w2;      /* att_fc2.weight (Q) */
+    const float* p_b2;      /* (1) */
+    const float* mask;      /* (n,S) fp32 or NULL */
+    float out_drop_p;       /* MHSA output dropout (NRMS.py:32-34); 0 otherwise */
+} nr_title_encoder_t;
+typedef struct nr_title_encoder_grads {   /* all ACCUMULATED (+=); any pointer may be NULL = not wanted */
+    float* dw[3];
+    float* db[3];
+    float* dp_w1; float* dp_b1; float* dp_w2; float* dp_b2;
+    float* dtable;          /* token / news rows: dense embedding-table gradient (row 0 skipped) */
+    float* dx_dense;        /* dense rows: (n,S,Dm) gradient, WRITTEN */
+} nr_title_encoder_grads_t;
+size_t nr_title_encoder_save_bytes(const nr_title_encoder_t* enc, int64_t n);
+size_t nr_title_encoder_workspace(const nr_title_encoder_t* enc, int64_t n);
+/* out (n,H) fp32 */
+int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, float* out,
+                         void* save, size_t save_bytes, void* ws, size_t ws_bytes, void* stream);
+/* g (n,H) fp32 = dL/dout */
+int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, const float* g,
+                         const void* save, size_t save_bytes, const nr_title_encoder_grads_t* grads,
+                         void* ws, size_t ws_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -30,8 +30,24 @@ class NrRows(C.Structure):
                 ('drop_p', C.c_float), ('seed', C.c_uint64)]
 
 
+class NrTitleEncoder(C.Structure):
+    _fields_ = [('kind', C.c_int32), ('S', C.c_int32), ('Dm', C.c_int32), ('H', C.c_int32), ('Q', C.c_int32),
+                ('heads', C.c_int32), ('w', C.c_void_p * 3), ('b', C.c_void_p * 3), ('p_w1', C.c_void_p),
+                ('p_b1', C.c_void_p), ('p_w2', C.c_void_p), ('p_b2', C.c_void_p), ('mask', C.c_void_p),
+                ('out_drop_p', C.c_float)]
+
+
+class NrTitleEncoderGrads(C.Structure):
+    _fields_ = [('dw', C.c_void_p * 3), ('db', C.c_void_p * 3), ('dp_w1', C.c_void_p), ('dp_b1', C.c_void_p),
+                ('dp_w2', C.c_void_p), ('dp_b2', C.c_void_p), ('dtable', C.c_void_p), ('dx_dense', C.c_void_p)]
+
+
+ENC_MHSA, ENC_CONV = 0, 1
+
 _P, _I32, _I64, _F, _U64, _SZ = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_uint64, C.c_size_t
 _R = C.POINTER(NrRows)
+_E = C.POINTER(NrTitleEncoder)
+_G = C.POINTER(NrTitleEncoderGrads)
 
 _SIGS = {
     'nr_abi_version': (C.c_int, []),
@@ -59,6 +75,11 @@ _SIGS = {
     'nr_score_ce_bwd': (C.c_int, [_P] * 7 + [_I64, _I32, _I32, _P]),
     'nr_adam_step': (C.c_int, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _I32, _F, _P]),
     'nr_tc_gemm_nt': (C.c_int, [_P, _I64, _I32, _I64, _P, _I32, _I64, _P, _P, _I64, _I32, _I64, _I32, _P, _P]),
+    'nr_tc_gemm_tn': (C.c_int, [_P, _I32, _I64, _P, _I32, _I64, _I64, _I32, _P, _P, _I64, _I64, _P]),
+    'nr_title_encoder_save_bytes': (_SZ, [_E, _I64]),
+    'nr_title_encoder_workspace': (_SZ, [_E, _I64]),
+    'nr_title_encoder_fwd': (C.c_int, [_E, _R, _I64, _P, _P, _SZ, _P, _SZ, _P]),
+    'nr_title_encoder_bwd': (C.c_int, [_E, _R, _I64, _P, _P, _SZ, _G, _P, _SZ, _P]),
     'nr_eval_score': (C.c_int, [_P, _I64, _P, _P, _P, _P, _I64, _I64, _I32, _P]),
     'nr_eval_rank_metrics': (C.c_int, [_P, _P, _P, _P, _P, _I64, _P]),
     'nr_eval_reduce_metrics': (C.c_int, [_P, _P, _P, _I64, _P]),

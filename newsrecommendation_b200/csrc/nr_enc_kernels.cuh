@@ -1,0 +1,374 @@
+// nr_enc_kernels.cuh — SIMT kernels of the bf16 title-encoder pipeline (nr_encoder.cu):
+// row staging (gather + dropout + bf16 pack), weight packing, per-head exp-attention and the
+// additive-attention tails, all over the PADDED token layout:
+//
+//   activation row of (sequence i, position s) = i*SP + s,  SP = pitch >= S+1 (multiple of 32);
+//   rows s >= S are zero ("pad rows").  Zero pad rows make the Conv1d taps of NAML.py:27-32 read
+//   zeros across title edges and contribute nothing to any weight gradient, and the 32-row pitch
+//   aligns every title with one epilogue warp of the tcgen05 GEMMs.
+//
+// Arithmetic is fp32 in registers; only the HBM representation is bf16.
+#pragma once
+#include "nr_common.cuh"
+#include "nr_tc.cuh"
+
+namespace nr {
+
+typedef __nv_bfloat16 bf16;
+
+__device__ __forceinline__ float2 bf2_to_f2(uint32_t w) {
+    return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xFFFF0000u));
+}
+__device__ __forceinline__ float4 ld_bf4(const bf16* p) {   // 8-byte aligned
+    const uint2 w = __ldg((const uint2*)p);
+    const float2 a = bf2_to_f2(w.x), b = bf2_to_f2(w.y);
+    return make_float4(a.x, a.y, b.x, b.y);
+}
+__device__ __forceinline__ void st_bf4(bf16* p, float4 v) {
+    *(uint2*)p = make_uint2(tc::pack_bf16(v.x, v.y), tc::pack_bf16(v.z, v.w));
+}
+
+// ---- staging: X (fp32, through a RowsView incl. input dropout) -> Xb (n*SP, ldx) bf16 ------------
+// column Dm holds 1.0 on real rows (the "ones column": dW GEMMs then yield the bias gradient as
+// output column Dm); columns (Dm, ldx) and pad rows are zero.  One thread = 8 output columns.
+static __global__ void __launch_bounds__(256)
+stage_rows_kernel(RowsView x, bf16* __restrict__ xb, int64_t n, int SP, int ldx) {
+    const int c8 = ldx >> 3;
+    const int64_t total = n * SP * c8;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = t / c8;
+        const int c = (int)(t - row * c8) * 8;
+        const int64_t seq = row / SP;
+        const int s = (int)(row - seq * SP);
+        uint4 o = make_uint4(0u, 0u, 0u, 0u);
+        if (s < x.S) {
+            const int64_t r = seq * x.S + s;
+            float4 a = x.load4(r, c), b = x.load4(r, c + 4);    // zero beyond D
+            if (c <= x.D && x.D < c + 8) {
+                float* f = x.D < c + 4 ? &a.x : &b.x;
+                f[(x.D - c) & 3] = 1.0f;
+            }
+            o = make_uint4(tc::pack_bf16(a.x, a.y), tc::pack_bf16(a.z, a.w), tc::pack_bf16(b.x, b.y),
+                           tc::pack_bf16(b.z, b.w));
+        }
+        *(uint4*)(xb + row * ldx + c) = o;
+    }
+}
+
+// ---- weight packing (fp32 Parameters -> bf16 GEMM operands, zero padded) ---------------------------
+// mode 0: out[j][k]          = W_{j / H}[j % H][k]          (3 stacked (H,Dm) matrices -> (3H, ldo))
+// mode 1: out[c][j]          = W_{j / H}[j % H][c]          (their transpose (Dm, ldo), ldo >= 3H)
+// mode 2: out[o][t*ldt + c]  = w[o][c][t]                   (Conv1d weight (H,Dm,3) -> (H, 3*ldt))
+// mode 3: out[c][u*ldt + o]  = w[o][c][u]                   (conv dX operand (Dm, 3*ldt), ldt >= H)
+struct PackArgs {
+    const float* w0; const float* w1; const float* w2;
+    int mode, H, Dm, ldt, rows, ldo, nmat;
+};
+static __global__ void pack_weights_kernel(PackArgs a, bf16* __restrict__ out) {
+    const int64_t total = (int64_t)a.rows * a.ldo;
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
+         t += (int64_t)gridDim.x * blockDim.x) {
+        const int r = (int)(t / a.ldo), c = (int)(t - (int64_t)r * a.ldo);
+        float v = 0.f;
+        if (a.mode == 0) {
+            if (c < a.Dm) {
+                const int w = r / a.H;
+                const float* p = w == 0 ? a.w0 : (w == 1 ? a.w1 : a.w2);
+                v = __ldg(p + (int64_t)(r - w * a.H) * a.Dm + c);
+            }
+        } else if (a.mode == 1) {
+            if (c < a.nmat * a.H) {
+                const int w = c / a.H;
+                const float* p = w == 0 ? a.w0 : (w == 1 ? a.w1 : a.w2);
+                v = __ldg(p + (int64_t)(c - w * a.H) * a.Dm + r);
+            }
+        } else if (a.mode == 2) {
+            const int tp = c / a.ldt, cc = c - tp * a.ldt;
+            if (cc < a.Dm) v = __ldg(a.w0 + ((int64_t)r * a.Dm + cc) * 3 + tp);
+        } else {
+            const int u = c / a.ldt, o = c - u * a.ldt;
+            if (o < a.H) v = __ldg(a.w0 + ((int64_t)o * a.Dm + r) * 3 + u);
+        }
+        out[t] = __float2bfloat16(v);
+    }
+}
+
+// ---- per-head exp-attention over bf16 qkv (model_utils.py:39-55; F8: no max subtraction) -------------
+// qkv (n*SP, 3H): q at col h*DK, k at H + h*DK, v at 2H + h*DK.  One warp per (sequence, head), four
+// heads per block; K and V of the head in shared memory (fp32); lane i owns query rows i, i+32, ...
+// ctx (n*SP, H) = heads concatenated, output dropout (stream NR_STREAM_OUT, element index
+// (seq*S+i)*H + col) applied; pad rows written as zero.
+template <int DK>
+static __global__ void __launch_bounds__(128)
+attn_fwd_bf16_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
+                     int S, int SP, int heads, float scale, uint32_t thr, float dscale, uint64_t seed) {
+    extern __shared__ __align__(16) float smem[];
+    const int H = heads * DK;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int groups = (heads + 3) / 4;
+    const int64_t seq = blockIdx.x / groups;
+    const int head = (blockIdx.x % groups) * 4 + warp;
+    if (head >= heads) return;
+    float* Ks = smem + warp * (2 * S * DK);
+    float* Vs = Ks + S * DK;
+    const bf16* base = qkv + seq * SP * 3 * H + head * DK;
+    for (int idx = lane; idx < S * (DK / 4); idx += 32) {
+        const int s = idx / (DK / 4), q4 = idx % (DK / 4);
+        const bf16* row = base + (int64_t)s * 3 * H + q4 * 4;
+        *(float4*)(Ks + s * DK + q4 * 4) = ld_bf4(row + H);
+        *(float4*)(Vs + s * DK + q4 * 4) = ld_bf4(row + 2 * H);
+    }
+    __syncwarp();
+    for (int i = lane; i < SP; i += 32) {
+        bf16* out = ctx + (seq * SP + i) * H + head * DK;
+        if (i >= S) {
+#pragma unroll
+            for (int d = 0; d < DK; d += 4) *(uint2*)(out + d) = make_uint2(0u, 0u);
+            continue;
+        }
+        float q[DK], o[DK];
+        const bf16* qr = base + (int64_t)i * 3 * H;
+#pragma unroll
+        for (int d = 0; d < DK; d += 4) {
+            const float4 t = ld_bf4(qr + d);
+            q[d] = t.x * scale; q[d + 1] = t.y * scale; q[d + 2] = t.z * scale; q[d + 3] = t.w * scale;
+        }
+#pragma unroll
+        for (int d = 0; d < DK; ++d) o[d] = 0.f;
+        float z = 0.f;
+        for (int j = 0; j < S; ++j) {
+            float dot = 0.f;
+#pragma unroll
+            for (int d = 0; d < DK; ++d) dot = fmaf(q[d], Ks[j * DK + d], dot);
+            float p = __expf(dot);
+            if (key_mask) p *= __ldg(key_mask + seq * S + j);
+            z += p;
+#pragma unroll
+            for (int d = 0; d < DK; ++d) o[d] = fmaf(p, Vs[j * DK + d], o[d]);
+        }
+        const float inv = 1.f / (z + kEps);
+#pragma unroll
+        for (int d = 0; d < DK; d += 4) {
+            float4 t = make_float4(o[d] * inv, o[d + 1] * inv, o[d + 2] * inv, o[d + 3] * inv);
+            if (thr) t = dropout4(t, (uint64_t)((seq * S + i) * H + head * DK + d), seed, NR_STREAM_OUT, thr, dscale);
+            st_bf4(out + d, t);
+        }
+    }
+}
+
+// backward: dctx here is the gradient w.r.t. the PRE-dropout context (the output
+// dropout mask is applied by the producer of dctx).  Pass 1 (lane = query row): dQ, Z_i, rd_i;
+// pass 2 (lane = key row): dK, dV.  dqkv pad rows are written as zero.
+template <int DK>
+static __global__ void __launch_bounds__(128)
+attn_bwd_bf16_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask,
+                     const bf16* __restrict__ dctx, bf16* __restrict__ dqkv, int S, int SP, int heads,
+                     float scale) {
+    extern __shared__ __align__(16) float smem[];
+    const int H = heads * DK;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int groups = (heads + 3) / 4;
+    const int64_t seq = blockIdx.x / groups;
+    const int head = (blockIdx.x % groups) * 4 + warp;
+    if (head >= heads) return;
+    const int per_warp = 4 * S * DK + 2 * S + ((2 * S) & 3 ? 4 - ((2 * S) & 3) : 0);
+    float* Qs = smem + warp * per_warp;
+    float* Ks = Qs + S * DK;
+    float* Vs = Ks + S * DK;
+    float* Gs = Vs + S * DK;
+    float* Zs = Gs + S * DK;
+    float* Rs = Zs + S;
+    const bf16* base = qkv + seq * SP * 3 * H + head * DK;
+    const bf16* gbase = dctx + seq * SP * H + head * DK;
+    for (int idx = lane; idx < S * (DK / 4); idx += 32) {
+        const int s = idx / (DK / 4), q4 = idx % (DK / 4);
+        const bf16* row = base + (int64_t)s * 3 * H + q4 * 4;
+        *(float4*)(Qs + s * DK + q4 * 4) = ld_bf4(row);
+        *(float4*)(Ks + s * DK + q4 * 4) = ld_bf4(row + H);
+        *(float4*)(Vs + s * DK + q4 * 4) = ld_bf4(row + 2 * H);
+        *(float4*)(Gs + s * DK + q4 * 4) = ld_bf4(gbase + (int64_t)s * H + q4 * 4);
+    }
+    __syncwarp();
+    bf16* dbase = dqkv + seq * SP * 3 * H + head * DK;
+    for (int i = lane; i < SP; i += 32) {
+        bf16* dq = dbase + (int64_t)i * 3 * H;
+        if (i >= S) {
+#pragma unroll
+            for (int d = 0; d < DK; d += 4) {
+                *(uint2*)(dq + d) = make_uint2(0u, 0u);
+                *(uint2*)(dq + H + d) = make_uint2(0u, 0u);
+                *(uint2*)(dq + 2 * H + d) = make_uint2(0u, 0u);
+            }
+            continue;
+        }
+        float q[DK], go[DK], t1[DK], t2[DK];
+#pragma unroll
+        for (int d = 0; d < DK; ++d) { q[d] = Qs[i * DK + d]; go[d] = Gs[i * DK + d]; t1[d] = 0.f; t2[d] = 0.f; }
+        float z = 0.f, rd = 0.f;
+        for (int j = 0; j < S; ++j) {
+            float dot = 0.f, dA = 0.f;
+#pragma unroll
+            for (int d = 0; d < DK; ++d) { dot = fmaf(q[d], Ks[j * DK + d], dot); dA = fmaf(go[d], Vs[j * DK + d], dA); }
+            float p = __expf(dot * scale);
+            if (key_mask) p *= __ldg(key_mask + seq * S + j);
+            z += p;
+            const float pd = p * dA;
+            rd += pd;
+#pragma unroll
+            for (int d = 0; d < DK; ++d) { const float kv = Ks[j * DK + d]; t1[d] = fmaf(pd, kv, t1[d]); t2[d] = fmaf(p, kv, t2[d]); }
+        }
+        z += kEps;
+        const float inv = 1.f / z;
+        rd *= inv;
+        Zs[i] = inv;
+        Rs[i] = rd;
+#pragma unroll
+        for (int d = 0; d < DK; d += 4)
+            st_bf4(dq + d, make_float4((t1[d] - rd * t2[d]) * inv * scale, (t1[d + 1] - rd * t2[d + 1]) * inv * scale,
+                                       (t1[d + 2] - rd * t2[d + 2]) * inv * scale, (t1[d + 3] - rd * t2[d + 3]) * inv * scale));
+    }
+    __syncwarp();
+    for (int j = lane; j < S; j += 32) {
+        float k[DK], v[DK], dk[DK], dv[DK];
+#pragma unroll
+        for (int d = 0; d < DK; ++d) { k[d] = Ks[j * DK + d]; v[d] = Vs[j * DK + d]; dk[d] = 0.f; dv[d] = 0.f; }
+        const float mj = key_mask ? __ldg(key_mask + seq * S + j) : 1.f;
+        for (int i = 0; i < S; ++i) {
+            float dot = 0.f, dA = 0.f;
+#pragma unroll
+            for (int d = 0; d < DK; ++d) { dot = fmaf(Qs[i * DK + d], k[d], dot); dA = fmaf(Gs[i * DK + d], v[d], dA); }
+            const float a = __expf(dot * scale) * mj * Zs[i];
+            const float dS = a * (dA - Rs[i]);
+#pragma unroll
+            for (int d = 0; d < DK; ++d) { dk[d] = fmaf(dS, Qs[i * DK + d], dk[d]); dv[d] = fmaf(a, Gs[i * DK + d], dv[d]); }
+        }
+        bf16* dkr = dbase + (int64_t)j * 3 * H + H;
+        bf16* dvr = dkr + H;
+#pragma unroll
+        for (int d = 0; d < DK; d += 4) {
+            st_bf4(dkr + d, make_float4(dk[d] * scale, dk[d + 1] * scale, dk[d + 2] * scale, dk[d + 3] * scale));
+            st_bf4(dvr + d, make_float4(dv[d], dv[d + 1], dv[d + 2], dv[d + 3]));
+        }
+    }
+}
+
+inline size_t attn_bf16_fwd_smem(int S, int DK) { return (size_t)4 * 2 * S * DK * sizeof(float); }
+inline size_t attn_bf16_bwd_smem(int S, int DK) {
+    const int per_warp = 4 * S * DK + 2 * S + ((2 * S) & 3 ? 4 - ((2 * S) & 3) : 0);
+    return (size_t)4 * per_warp * sizeof(float);
+}
+
+// ---- AttentionPooling tails over bf16 (model_utils.py:23-30) -----------------------------------------
+// logits (n*SP) fp32 come from the fc1 GEMM epilogue (tanh, dot w2, + b2).  p = exp(a)*m;
+// alpha = p/(sum p + eps); out = sum_s alpha_s y_s.  One block (128 threads) per sequence.
+static __global__ void __launch_bounds__(128)
+pool_tail_fwd_bf16_kernel(const bf16* __restrict__ y, const float* __restrict__ logits,
+                          const float* __restrict__ mask, float* __restrict__ out,
+                          float* __restrict__ alpha_save, int S, int SP, int H) {
+    extern __shared__ float sp[];   // SP
+    const int64_t seq = blockIdx.x;
+    for (int s = threadIdx.x; s < SP; s += blockDim.x) {
+        float p = 0.f;
+        if (s < S) {
+            p = expf(__ldg(logits + seq * SP + s));
+            if (mask) p *= __ldg(mask + seq * S + s);
+        }
+        sp[s] = p;
+    }
+    __syncthreads();
+    float z = 0.f;
+    for (int s = 0; s < S; ++s) z += sp[s];
+    const float inv = 1.f / (z + kEps);          // model_utils.py:29
+    __syncthreads();
+    for (int s = threadIdx.x; s < SP; s += blockDim.x) {
+        const float a = sp[s] * inv;
+        sp[s] = a;
+        alpha_save[seq * SP + s] = a;
+    }
+    __syncthreads();
+    for (int h = threadIdx.x * 4; h < H; h += blockDim.x * 4) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        const bf16* yr = y + seq * SP * H + h;
+        for (int s = 0; s < S; ++s) {
+            const float4 v = ld_bf4(yr + (int64_t)s * H);
+            const float a = sp[s];
+            acc.x = fmaf(a, v.x, acc.x); acc.y = fmaf(a, v.y, acc.y); acc.z = fmaf(a, v.z, acc.z); acc.w = fmaf(a, v.w, acc.w);
+        }
+        *(float4*)(out + seq * H + h) = acc;
+    }
+}
+
+// backward tail: dalpha_s = g.y_s ; da_s = alpha_s (dalpha_s - sum_t alpha_t dalpha_t) ;
+// dz[s,q] = da_s w2[q] (1 - e[s,q]^2) (bf16, pad rows zero) ; dw2 += sum da_s e_s ; db2 += sum da_s ;
+// db1 += sum_s dz[s,:].  Blocks stride over sequences; one atomic per block and column at the end.
+static __global__ void __launch_bounds__(256)
+pool_tail_bwd_bf16_kernel(const float* __restrict__ g, const bf16* __restrict__ y, const bf16* __restrict__ e,
+                          const float* __restrict__ alpha, const float* __restrict__ w2, bf16* __restrict__ dz,
+                          float* __restrict__ dw2, float* __restrict__ db2, float* __restrict__ db1, int64_t n,
+                          int S, int SP, int H, int Q) {
+    extern __shared__ float sm[];   // da[SP] | dw2_acc[Q] | db1_acc[Q]
+    float* da = sm;
+    float* dw2_acc = sm + SP;
+    float* db1_acc = dw2_acc + Q;
+    __shared__ float s_c;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    for (int q = threadIdx.x; q < 2 * Q; q += blockDim.x) dw2_acc[q] = 0.f;
+    float db2_acc = 0.f;
+    for (int64_t seq = blockIdx.x; seq < n; seq += gridDim.x) {
+        __syncthreads();
+        const float* gr = g + seq * H;
+        for (int s = warp; s < S; s += nw) {
+            const bf16* yr = y + (seq * SP + s) * H;
+            float d = 0.f;
+            for (int h = lane * 4; h < H; h += 128) {
+                const float4 a = ldg4(gr + h), b = ld_bf4(yr + h);
+                d = fmaf(a.x, b.x, d); d = fmaf(a.y, b.y, d); d = fmaf(a.z, b.z, d); d = fmaf(a.w, b.w, d);
+            }
+            d = warp_sum(d);
+            if (lane == 0) da[s] = d;
+        }
+        __syncthreads();
+        if (warp == 0) {
+            float c = 0.f;
+            for (int s = lane; s < S; s += 32) c = fmaf(__ldg(alpha + seq * SP + s), da[s], c);
+            c = warp_sum(c);
+            if (lane == 0) s_c = c;
+        }
+        __syncthreads();
+        const float c = s_c;
+        __syncthreads();
+        for (int s = threadIdx.x; s < S; s += blockDim.x) da[s] = __ldg(alpha + seq * SP + s) * (da[s] - c);
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            float t = 0.f;
+            for (int s = 0; s < S; ++s) t += da[s];
+            db2_acc += t;
+        }
+        for (int q = threadIdx.x * 4; q < Q; q += blockDim.x * 4) {
+            const float4 w = ldg4(w2 + q);
+            float4 a2 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a2;
+            for (int s = 0; s < SP; ++s) {
+                bf16* zr = dz + (seq * SP + s) * Q + q;
+                if (s >= S) { *(uint2*)zr = make_uint2(0u, 0u); continue; }
+                const float4 ev = ld_bf4(e + (seq * SP + s) * Q + q);
+                const float d = da[s];
+                const float4 z = make_float4(d * w.x * (1.f - ev.x * ev.x), d * w.y * (1.f - ev.y * ev.y),
+                                             d * w.z * (1.f - ev.z * ev.z), d * w.w * (1.f - ev.w * ev.w));
+                st_bf4(zr, z);
+                a2.x = fmaf(d, ev.x, a2.x); a2.y = fmaf(d, ev.y, a2.y); a2.z = fmaf(d, ev.z, a2.z); a2.w = fmaf(d, ev.w, a2.w);
+                a1.x += z.x; a1.y += z.y; a1.z += z.z; a1.w += z.w;
+            }
+            dw2_acc[q] += a2.x; dw2_acc[q + 1] += a2.y; dw2_acc[q + 2] += a2.z; dw2_acc[q + 3] += a2.w;
+            db1_acc[q] += a1.x; db1_acc[q + 1] += a1.y; db1_acc[q + 2] += a1.z; db1_acc[q + 3] += a1.w;
+        }
+    }
+    __syncthreads();
+    for (int q = threadIdx.x; q < Q; q += blockDim.x) {
+        atomicAdd(dw2 + q, dw2_acc[q]);
+        atomicAdd(db1 + q, db1_acc[q]);
+    }
+    if (threadIdx.x == 0) atomicAdd(db2, db2_acc);
+}
+
+}  // namespace nr

@@ -1,0 +1,428 @@
+// nr_encoder.cu — bf16 tensor-core title encoder (nr_title_encoder_fwd / _bwd): the NewsEncoder title
+// path of NRMS (gather -> dropout -> MHSA -> dropout -> additive pooling, src/model/NRMS.py:27-35), of
+// NAML (gather -> dropout -> Conv1d(k=3) -> additive pooling, src/model/NAML.py:47-56) and the NRMS
+// UserEncoder (NRMS.py:55-62) as one pipeline of tcgen05 GEMMs (nr_tc_gemm.cuh, nr_tc_gemm_tn.cuh)
+// with fused epilogues and fp32 SIMT tails (nr_enc_kernels.cuh).  Gradient math: SURVEY Appendix C.
+#include "nr_enc_kernels.cuh"
+#include "nr_tc_gemm.cuh"
+#include "nr_tc_gemm_tn.cuh"
+
+using namespace nr;
+
+namespace {
+
+inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
+
+// ---- NT epilogues (protocol of nr_tc_gemm.cuh: one thread = one output row) --------------------------
+// qkv (bf16) = acc + [b_Q | b_K | b_V]
+struct EpiQkvBias {
+    bf16* C; int64_t ldc; const float* b0; const float* b1; const float* b2; int each;
+    __device__ __forceinline__ void begin(int64_t) {}
+    __device__ __forceinline__ void end(int64_t) {}
+    __device__ __forceinline__ float bias(int col) const {
+        return col < each ? __ldg(b0 + col) : (col < 2 * each ? __ldg(b1 + col - each) : __ldg(b2 + col - 2 * each));
+    }
+    __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
+        bf16* out = C + row * ldc + col0;
+        if (nc == 32) {
+            uint32_t w[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) w[j] = tc::pack_bf16(v[2 * j] + bias(col0 + 2 * j), v[2 * j + 1] + bias(col0 + 2 * j + 1));
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ((uint4*)out)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+        } else {
+            for (int j = 0; j < nc; ++j) out[j] = __float2bfloat16(v[j] + bias(col0 + j));
+        }
+    }
+};
+
+// AttentionPooling fc1 + tanh + fc2 (model_utils.py:21-23): e (bf16) = tanh(acc + b1);
+// logits[row] = e . w2 + b2 (fp32, from the unrounded tanh).  Needs the whole row in one n tile.
+struct EpiTanhLogit {
+    bf16* E; int64_t lde; const float* b1; const float* w2; const float* b2; float* logits;
+    float acc;
+    __device__ __forceinline__ void begin(int64_t) { acc = 0.f; }
+    __device__ __forceinline__ void end(int64_t row) { logits[row] = acc + __ldg(b2); }
+    __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
+        bf16* out = E + row * lde + col0;
+        if (nc == 32) {
+            uint32_t w[16];
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+                const float t0 = tanhf(v[2 * j] + __ldg(b1 + col0 + 2 * j));
+                const float t1 = tanhf(v[2 * j + 1] + __ldg(b1 + col0 + 2 * j + 1));
+                acc = fmaf(t0, __ldg(w2 + col0 + 2 * j), acc);
+                acc = fmaf(t1, __ldg(w2 + col0 + 2 * j + 1), acc);
+                w[j] = tc::pack_bf16(t0, t1);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) ((uint4*)out)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+        } else {
+            for (int j = 0; j < nc; ++j) {
+                const float t = tanhf(v[j] + __ldg(b1 + col0 + j));
+                acc = fmaf(t, __ldg(w2 + col0 + j), acc);
+                out[j] = __float2bfloat16(t);
+            }
+        }
+    }
+};
+
+// dY (bf16) = (dz . W1 + alpha_s g) [* output-dropout mask]; pad rows zero.
+struct EpiPoolDx {
+    bf16* dY; int64_t ld; const float* alpha; const float* g; int S, SP, H;
+    uint32_t thr; float dscale; uint64_t seed;
+    int64_t seq; int s; float a;
+    __device__ __forceinline__ void begin(int64_t row) {
+        seq = row / SP; s = (int)(row - seq * SP);
+        a = s < S ? __ldg(alpha + row) : 0.f;
+    }
+    __device__ __forceinline__ void end(int64_t) {}
+    __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
+        bf16* out = dY + row * ld + col0;
+        if (s >= S) {
+            for (int j = 0; j < nc; j += 4) *(uint2*)(out + j) = make_uint2(0u, 0u);
+            return;
+        }
+        const float* gr = g + seq * H + col0;
+        for (int j = 0; j < nc; j += 4) {      // nc % 4 == 0 (H % 8 == 0)
+            const float4 gv = ldg4(gr + j);
+            float4 t = make_float4(fmaf(a, gv.x, v[j]), fmaf(a, gv.y, v[j + 1]), fmaf(a, gv.z, v[j + 2]), fmaf(a, gv.w, v[j + 3]));
+            if (thr) t = dropout4(t, (uint64_t)((seq * S + s) * H + col0 + j), seed, NR_STREAM_OUT, thr, dscale);
+            st_bf4(out + j, t);
+        }
+    }
+};
+
+// dX of the encoder input: input-dropout mask re-applied, then either a dense fp32 store (n,S,Dm) or a
+// scatter-add into the embedding-table gradient (id 0 = padding_idx skipped; NRMS.py:73, B7).
+struct EpiDx {
+    float* dx_dense; float* dtable; RowsView x; int SP;
+    int64_t seq; int s; int64_t id;
+    __device__ __forceinline__ void begin(int64_t row) {
+        seq = row / SP; s = (int)(row - seq * SP);
+        id = -1;
+        if (s < x.S && x.mode != NR_ROWS_DENSE) id = x.id_of(seq, s);
+    }
+    __device__ __forceinline__ void end(int64_t) {}
+    __device__ __forceinline__ void chunk(int64_t, int col0, const float* v, int nc) {
+        if (s >= x.S) return;
+        if (x.mode != NR_ROWS_DENSE && id == 0) return;
+        const int64_t r = seq * x.S + s;
+        float* dst = x.mode == NR_ROWS_DENSE ? dx_dense + r * x.D
+                   : (x.mode == NR_ROWS_TOKEN ? dtable + id * x.D : dtable + id * ((int64_t)x.S * x.D) + (int64_t)s * x.D);
+        for (int j = 0; j < nc; j += 4) {      // nc % 4 == 0 (Dm % 4 == 0)
+            float4 t = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            if (x.thr) t = dropout4(t, (uint64_t)(r * x.D + col0 + j), x.seed, NR_STREAM_IN, x.thr, x.scale);
+            float* p = dst + col0 + j;
+            if (x.mode == NR_ROWS_DENSE) *(float4*)p = t;
+            else atomicAdd((float4*)p, t);
+        }
+    }
+};
+
+// ---- TN epilogues ----------------------------------------------------------------------------------------
+// rows i of [dW_Q; dW_K; dW_V] (3H x Dm); column Dm of the product (ones column of Xb) = bias gradient
+struct TnEpiQkv {
+    float* dw0; float* dw1; float* dw2; float* db0; float* db1; float* db2; int H, Dm;
+    __device__ __forceinline__ void operator()(int i, int, int j, const float* v, int nc) const {
+        const int w = i / H, ii = i - w * H;
+        float* dw = w == 0 ? dw0 : (w == 1 ? dw1 : dw2);
+        float* db = w == 0 ? db0 : (w == 1 ? db1 : db2);
+        for (int t = 0; t < nc; ++t) {
+            const int c = j + t;
+            if (c < Dm) { if (dw) atomicAdd(dw + (int64_t)ii * Dm + c, v[t]); }
+            else if (c == Dm) { if (db) atomicAdd(db + ii, v[t]); }
+        }
+    }
+};
+// nn.Conv1d.weight gradient layout dw[o][c][t]; bias gradient = ones column of the unshifted tap
+struct TnEpiConv {
+    float* dw; float* db; int Dm;
+    __device__ __forceinline__ void operator()(int o, int tap, int j, const float* v, int nc) const {
+        for (int t = 0; t < nc; ++t) {
+            const int c = j + t;
+            if (c < Dm) { if (dw) atomicAdd(dw + ((int64_t)o * Dm + c) * 3 + tap, v[t]); }
+            else if (c == Dm && tap == 1) { if (db) atomicAdd(db + o, v[t]); }
+        }
+    }
+};
+
+// ---- buffer plan ---------------------------------------------------------------------------------------------
+struct Plan {
+    int SP, ldx, Kp, HK, QK, K3, Nw;
+    int64_t R;
+    // save
+    size_t o_wb, o_w1b, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
+    // backward workspace
+    size_t o_dz, o_dy, o_dqkv, o_w1t, o_wt, ws_bytes;
+};
+
+Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
+    Plan p;
+    p.SP = round_up(e->S + 1, 32);
+    p.ldx = round_up(e->Dm + 1, 64);
+    p.Kp = round_up(e->Dm, 64);
+    p.HK = round_up(e->H, 64);
+    p.QK = round_up(e->Q, 64);
+    p.K3 = round_up(3 * e->H, 64);
+    p.Nw = e->kind == NR_ENC_MHSA ? 3 * e->H : e->H;
+    p.R = n * p.SP;
+    const int taps = e->kind == NR_ENC_MHSA ? 1 : 3;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o += (bytes + 1023) & ~size_t(1023); return r; };
+    p.o_wb = take((size_t)p.Nw * taps * p.Kp * 2);
+    p.o_w1b = take((size_t)e->Q * p.HK * 2);
+    p.o_xb = take((size_t)p.R * p.ldx * 2);
+    p.o_qkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
+    p.o_y = take((size_t)p.R * e->H * 2);
+    p.o_e = take((size_t)p.R * e->Q * 2);
+    p.o_alpha = take((size_t)p.R * 4);
+    p.o_logits = take((size_t)p.R * 4);
+    p.save_bytes = o;
+    o = 0;
+    p.o_dz = take((size_t)p.R * e->Q * 2);
+    p.o_dy = take((size_t)p.R * e->H * 2);
+    p.o_dqkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
+    p.o_w1t = take((size_t)e->H * p.QK * 2);
+    p.o_wt = take(e->kind == NR_ENC_MHSA ? (size_t)e->Dm * p.K3 * 2 : (size_t)e->Dm * 3 * p.HK * 2);
+    p.ws_bytes = o;
+    return p;
+}
+
+int validate(const nr_title_encoder_t* e, const char* who) {
+    NR_REQUIRE(e != nullptr, "%s: enc is NULL", who);
+    NR_REQUIRE(e->kind == NR_ENC_MHSA || e->kind == NR_ENC_CONV, "%s: bad kind %d", who, e->kind);
+    NR_REQUIRE(e->S >= 1 && e->S <= 64, "%s: S=%d outside [1,64]", who, e->S);
+    NR_REQUIRE(e->Dm >= 4 && (e->Dm & 3) == 0, "%s: Dm=%d must be a positive multiple of 4", who, e->Dm);
+    NR_REQUIRE(e->H >= 8 && (e->H & 7) == 0, "%s: H=%d must be a positive multiple of 8", who, e->H);
+    NR_REQUIRE(e->Q >= 8 && (e->Q & 7) == 0 && e->Q <= 256, "%s: Q=%d must be a multiple of 8 in [8,256]", who, e->Q);
+    NR_REQUIRE(e->p_w1 && e->p_b1 && e->p_w2 && e->p_b2, "%s: pooling parameter is NULL", who);
+    NR_REQUIRE(e->out_drop_p >= 0.f && e->out_drop_p < 1.f, "%s: out_drop_p outside [0,1)", who);
+    if (e->kind == NR_ENC_MHSA) {
+        NR_REQUIRE(e->heads >= 1 && e->H % e->heads == 0, "%s: H=%d not divisible by heads=%d", who, e->H, e->heads);
+        for (int i = 0; i < 3; ++i) NR_REQUIRE(e->w[i] && e->b[i], "%s: W_Q/W_K/W_V parameter is NULL", who);
+    } else {
+        NR_REQUIRE(e->w[0] && e->b[0], "%s: Conv1d parameter is NULL", who);
+        NR_REQUIRE(e->out_drop_p == 0.f, "%s: CONV encoder has no output dropout", who);
+    }
+    return 0;
+}
+
+int pack(const PackArgs& a, bf16* out, cudaStream_t st) {
+    const int64_t total = (int64_t)a.rows * a.ldo;
+    const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
+    ProfScope ps("enc.pack_w", st);
+    pack_weights_kernel<<<blocks, 256, 0, st>>>(a, out);
+    return check_last("enc.pack_w");
+}
+
+template <int DK>
+int launch_attn_fwd(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int SP, int heads, float p,
+                    uint64_t seed, cudaStream_t st) {
+    const size_t smem = attn_bf16_fwd_smem(S, DK);
+    NR_CUDA(cudaFuncSetAttribute(attn_fwd_bf16_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ProfScope ps("enc.attn_fwd", st);
+    attn_fwd_bf16_kernel<DK><<<(unsigned)(n * ((heads + 3) / 4)), 128, smem, st>>>(
+        qkv, mask, ctx, S, SP, heads, 1.0f / sqrtf((float)DK), p > 0.f ? drop_threshold(p) : 0u,
+        p > 0.f ? 1.f / (1.f - p) : 1.f, seed);
+    return check_last("enc.attn_fwd");
+}
+template <int DK>
+int launch_attn_bwd(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int SP,
+                    int heads, cudaStream_t st) {
+    const size_t smem = attn_bf16_bwd_smem(S, DK);
+    NR_CUDA(cudaFuncSetAttribute(attn_bwd_bf16_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    ProfScope ps("enc.attn_bwd", st);
+    attn_bwd_bf16_kernel<DK><<<(unsigned)(n * ((heads + 3) / 4)), 128, smem, st>>>(qkv, mask, dctx, dqkv, S, SP, heads,
+                                                                                  1.0f / sqrtf((float)DK));
+    return check_last("enc.attn_bwd");
+}
+#define NR_ENC_DISPATCH_DK(dk, CALL)                                                   \
+    switch (dk) {                                                                      \
+        case 8: { constexpr int DK = 8; return CALL; }                                 \
+        case 16: { constexpr int DK = 16; return CALL; }                               \
+        case 20: { constexpr int DK = 20; return CALL; }                               \
+        case 32: { constexpr int DK = 32; return CALL; }                               \
+        case 40: { constexpr int DK = 40; return CALL; }                               \
+        default: set_error("title encoder: head dim %d not in compiled set {8,16,20,32,40}", dk); return 1; \
+    }
+int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int SP, int heads, int dk, float p,
+               uint64_t seed, cudaStream_t st) {
+    NR_ENC_DISPATCH_DK(dk, launch_attn_fwd<DK>(qkv, mask, ctx, n, S, SP, heads, p, seed, st));
+}
+int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int SP, int heads,
+               int dk, cudaStream_t st) {
+    NR_ENC_DISPATCH_DK(dk, launch_attn_bwd<DK>(qkv, mask, dctx, dqkv, n, S, SP, heads, st));
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t nr_title_encoder_save_bytes(const nr_title_encoder_t* enc, int64_t n) {
+    if (!enc || n <= 0) return 256;
+    return make_plan(enc, n).save_bytes + 1024;
+}
+size_t nr_title_encoder_workspace(const nr_title_encoder_t* enc, int64_t n) {
+    if (!enc || n <= 0) return 256;
+    return make_plan(enc, n).ws_bytes + 1024;
+}
+
+int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, float* out, void* save,
+                         size_t save_bytes, void* ws, size_t ws_bytes, void* stream) {
+    (void)ws; (void)ws_bytes;
+    const char* who = "nr_title_encoder_fwd";
+    if (int e = validate(enc, who)) return e;
+    if (int e = validate_rows(rows, who)) return e;
+    NR_REQUIRE(out && save, "%s: NULL pointer", who);
+    NR_REQUIRE(n >= 0, "%s: n < 0", who);
+    if (n == 0) return 0;
+    const Plan p = make_plan(enc, n);
+    char* sv = (char*)(((uintptr_t)save + 1023) & ~(uintptr_t)1023);
+    NR_REQUIRE((size_t)(sv - (char*)save) + p.save_bytes <= save_bytes, "%s: save buffer too small (%zu < %zu)", who,
+               save_bytes, p.save_bytes + 1024);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int S = enc->S, Dm = enc->Dm, H = enc->H, Q = enc->Q;
+    bf16* wb = (bf16*)(sv + p.o_wb);
+    bf16* w1b = (bf16*)(sv + p.o_w1b);
+    bf16* xb = (bf16*)(sv + p.o_xb);
+    bf16* qkv = (bf16*)(sv + p.o_qkv);
+    bf16* y = (bf16*)(sv + p.o_y);
+    bf16* eb = (bf16*)(sv + p.o_e);
+    float* alpha = (float*)(sv + p.o_alpha);
+    float* logits = (float*)(sv + p.o_logits);
+
+    // 1. weights -> bf16 GEMM operands
+    if (enc->kind == NR_ENC_MHSA) {
+        if (int e = pack(PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3}, wb, st)) return e;
+    } else {
+        if (int e = pack(PackArgs{enc->w[0], nullptr, nullptr, 2, H, Dm, p.Kp, H, 3 * p.Kp, 1}, wb, st)) return e;
+    }
+    if (int e = pack(PackArgs{enc->p_w1, nullptr, nullptr, 0, Q, H, 0, Q, p.HK, 1}, w1b, st)) return e;
+    // 2. stage rows: gather + input dropout + bf16, padded pitch
+    {
+        const RowsView xv = make_rows_view(rows, n, S, Dm);
+        const int64_t total = p.R * (p.ldx >> 3);
+        const int blocks = (int)((total + 255) / 256 < (int64_t)sm_count() * 16 ? (total + 255) / 256 : (int64_t)sm_count() * 16);
+        ProfScope ps("enc.stage", st);
+        stage_rows_kernel<<<blocks, 256, 0, st>>>(xv, xb, n, p.SP, p.ldx);
+        if (int e = check_last("enc.stage")) return e;
+    }
+    // 3. token mixer
+    const int one = 0;
+    if (enc->kind == NR_ENC_MHSA) {
+        if (int e = gemm_tc(xb, p.R, Dm, p.ldx, wb, 3 * H, p.Kp, 1, &one, p.R,
+                            EpiQkvBias{qkv, 3 * H, enc->b[0], enc->b[1], enc->b[2], H}, st, "enc.qkv"))
+            return e;
+        if (int e = attn_fwd_b(qkv, enc->mask, y, n, S, p.SP, enc->heads, H / enc->heads, enc->out_drop_p, rows->seed, st))
+            return e;
+    } else {
+        const int sh[3] = {-1, 0, 1};
+        if (int e = gemm_tc(xb, p.R, Dm, p.ldx, wb, H, 3 * p.Kp, 3, sh, p.R, TcEpiBiasBf16{y, H, enc->b[0], H}, st,
+                            "enc.conv"))
+            return e;
+    }
+    // 4. additive attention: fc1 + tanh + fc2 in the GEMM epilogue, then the softmax-like tail
+    if (int e = gemm_tc(y, p.R, H, H, w1b, Q, p.HK, 1, &one, p.R,
+                        EpiTanhLogit{eb, Q, enc->p_b1, enc->p_w2, enc->p_b2, logits, 0.f}, st, "enc.fc1"))
+        return e;
+    ProfScope ps("enc.pool_fwd", st);
+    pool_tail_fwd_bf16_kernel<<<(unsigned)n, 128, p.SP * sizeof(float), st>>>(y, logits, enc->mask, out, alpha, S, p.SP, H);
+    return check_last("enc.pool_fwd");
+}
+
+int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, const float* g,
+                         const void* save, size_t save_bytes, const nr_title_encoder_grads_t* gr, void* ws,
+                         size_t ws_bytes, void* stream) {
+    const char* who = "nr_title_encoder_bwd";
+    if (int e = validate(enc, who)) return e;
+    if (int e = validate_rows(rows, who)) return e;
+    NR_REQUIRE(g && save && gr && ws, "%s: NULL pointer", who);
+    NR_REQUIRE(gr->dp_w1 && gr->dp_b1 && gr->dp_w2 && gr->dp_b2, "%s: pooling gradient pointer is NULL", who);
+    NR_REQUIRE(!(gr->dtable && rows->mode == NR_ROWS_DENSE), "%s: dtable given for dense rows", who);
+    NR_REQUIRE(!(gr->dx_dense && rows->mode != NR_ROWS_DENSE), "%s: dx_dense given for gathered rows", who);
+    if (n == 0) return 0;
+    const Plan p = make_plan(enc, n);
+    const char* sv = (const char*)(((uintptr_t)save + 1023) & ~(uintptr_t)1023);
+    NR_REQUIRE((size_t)(sv - (const char*)save) + p.save_bytes <= save_bytes, "%s: save buffer too small", who);
+    char* wsb = (char*)(((uintptr_t)ws + 1023) & ~(uintptr_t)1023);
+    NR_REQUIRE((size_t)(wsb - (char*)ws) + p.ws_bytes <= ws_bytes, "%s: workspace too small (%zu < %zu)", who, ws_bytes,
+               p.ws_bytes + 1024);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int S = enc->S, Dm = enc->Dm, H = enc->H, Q = enc->Q;
+    const bf16* xb = (const bf16*)(sv + p.o_xb);
+    const bf16* qkv = (const bf16*)(sv + p.o_qkv);
+    const bf16* y = (const bf16*)(sv + p.o_y);
+    const bf16* eb = (const bf16*)(sv + p.o_e);
+    const float* alpha = (const float*)(sv + p.o_alpha);
+    bf16* dz = (bf16*)(wsb + p.o_dz);
+    bf16* dy = (bf16*)(wsb + p.o_dy);
+    bf16* dqkv = (bf16*)(wsb + p.o_dqkv);
+    bf16* w1t = (bf16*)(wsb + p.o_w1t);
+    bf16* wt = (bf16*)(wsb + p.o_wt);
+    const bool want_dx = gr->dtable || gr->dx_dense;
+    const int one = 0;
+
+    // transposed weights for the dX GEMMs
+    if (int e = pack(PackArgs{enc->p_w1, nullptr, nullptr, 1, Q, H, 0, H, p.QK, 1}, w1t, st)) return e;
+    if (want_dx) {
+        if (enc->kind == NR_ENC_MHSA) {
+            if (int e = pack(PackArgs{enc->w[0], enc->w[1], enc->w[2], 1, H, Dm, 0, Dm, p.K3, 3}, wt, st)) return e;
+        } else {
+            if (int e = pack(PackArgs{enc->w[0], nullptr, nullptr, 3, H, Dm, p.HK, Dm, 3 * p.HK, 1}, wt, st)) return e;
+        }
+    }
+    // 1. pooling tail backward: dz, dw2, db2, db1
+    {
+        int64_t grid = n < 4 * (int64_t)sm_count() ? n : 4 * (int64_t)sm_count();
+        ProfScope ps("enc.pool_bwd", st);
+        pool_tail_bwd_bf16_kernel<<<(unsigned)grid, 256, (p.SP + 2 * Q) * sizeof(float), st>>>(
+            g, y, eb, alpha, enc->p_w2, dz, gr->dp_w2, gr->dp_b2, gr->dp_b1, n, S, p.SP, H, Q);
+        if (int e = check_last("enc.pool_bwd")) return e;
+    }
+    // 2. dW1 (Q,H) += dz^T . y
+    if (int e = gemm_tc_tn(dz, Q, Q, y, H, H, p.R, 1, &one, TnEpiPlain{gr->dp_w1, H, 0}, st, "enc.dw1")) return e;
+    // 3. dY = dz . W1 + alpha g   (output-dropout mask re-applied for MHSA)
+    {
+        EpiPoolDx ep{dy, H, alpha, g, S, p.SP, H,
+                     enc->out_drop_p > 0.f ? drop_threshold(enc->out_drop_p) : 0u,
+                     enc->out_drop_p > 0.f ? 1.f / (1.f - enc->out_drop_p) : 1.f, rows->seed, 0, 0, 0.f};
+        if (int e = gemm_tc(dz, p.R, Q, Q, w1t, H, p.QK, 1, &one, p.R, ep, st, "enc.pool_dx")) return e;
+    }
+    const RowsView xv = make_rows_view(rows, n, S, Dm);
+    if (enc->kind == NR_ENC_MHSA) {
+        if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st)) return e;
+        if (int e = gemm_tc_tn(dqkv, 3 * H, 3 * H, xb, Dm + 1, p.ldx, p.R, 1, &one,
+                               TnEpiQkv{gr->dw[0], gr->dw[1], gr->dw[2], gr->db[0], gr->db[1], gr->db[2], H, Dm}, st,
+                               "enc.dwqkv"))
+            return e;
+        if (want_dx)
+            if (int e = gemm_tc(dqkv, p.R, 3 * H, 3 * H, wt, Dm, p.K3, 1, &one, p.R,
+                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, 0, 0, 0}, st, "enc.dx"))
+                return e;
+    } else {
+        const int sh[3] = {-1, 0, 1};
+        if (int e = gemm_tc_tn(dy, H, H, xb, Dm + 1, p.ldx, p.R, 3, sh, TnEpiConv{gr->dw[0], gr->db[0], Dm}, st,
+                               "enc.dwconv"))
+            return e;
+        if (want_dx) {
+            const int shx[3] = {1, 0, -1};
+            if (int e = gemm_tc(dy, p.R, H, H, wt, Dm, 3 * p.HK, 3, shx, p.R,
+                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, 0, 0, 0}, st, "enc.dx"))
+                return e;
+        }
+    }
+    return 0;
+}
+
+int nr_tc_gemm_tn(const void* A, int32_t Mo, int64_t lda, const void* B, int32_t No, int64_t ldb, int64_t rows,
+                  int32_t taps, const int32_t* shifts_host, float* C, int64_t ldc, int64_t tap_stride, void* stream) {
+    NR_REQUIRE(A && B && C, "nr_tc_gemm_tn: NULL pointer");
+    NR_REQUIRE(Mo > 0 && No > 0 && rows >= 0, "nr_tc_gemm_tn: bad sizes");
+    int sh[3] = {0, 0, 0};
+    for (int t = 0; t < taps && t < 3; ++t) sh[t] = shifts_host ? shifts_host[t] : 0;
+    return gemm_tc_tn((const bf16*)A, Mo, lda, (const bf16*)B, No, ldb, rows, taps, sh, TnEpiPlain{C, ldc, tap_stride},
+                      (cudaStream_t)stream, "tc.gemm_tn");
+}
+
+}  // extern "C"

@@ -8,7 +8,7 @@ from torch import nn
 
 from newsrecommendation_b200 import ops
 from newsrecommendation_b200 import _lib as L
-from .model_utils import AttentionPooling, precision_of
+from .model_utils import AttentionPooling, encode_both, precision_of
 
 
 class NewsEncoder(nn.Module):
@@ -43,9 +43,15 @@ class NewsEncoder(nn.Module):
         Lw, D = self.num_words_title, self.word_embedding_dim
         p = self.drop_rate if self.training else 0.0
         mode = L.ROWS_TOKEN if self.word_ids else L.ROWS_NEWS
-        c = ops.conv1d_k3(self.title_embeddings.weight, x, self.cnn.weight, self.cnn.bias, mode=mode, L_=Lw, D=D,
-                          in_drop=p, seed=ops.next_seed() if p else 0, prec=self.prec)
-        views = [self.attn(c)]
+        if self.prec == L.PREC_BF16:
+            title = ops.title_encoder(L.ENC_CONV, self.title_embeddings.weight, x, None,
+                                      (self.cnn.weight, self.cnn.bias), self.attn._p(), mode=mode, S=Lw, Dm=D,
+                                      in_drop=p, seed=ops.next_seed() if p else 0)
+        else:
+            c = ops.conv1d_k3(self.title_embeddings.weight, x, self.cnn.weight, self.cnn.bias, mode=mode, L_=Lw,
+                              D=D, in_drop=p, seed=ops.next_seed() if p else 0, prec=self.prec)
+            title = self.attn(c)
+        views = [title]
         col = Lw if self.word_ids else 1
         if self.use_category:
             views.append(ops.embed_dense(self.category_emb.weight, x, col, self.category_dense.weight,
@@ -87,8 +93,9 @@ class Model(nn.Module):
     def forward(self, history, history_mask, candidate, label):
         a = self.args
         F = history.shape[-1]
-        cv = self.news_encoder(candidate.reshape(-1, F)).reshape(-1, 1 + a.npratio, a.news_dim)
-        hv = self.news_encoder(history.reshape(-1, F)).reshape(-1, a.user_log_length, a.news_dim)
+        cv, hv = encode_both(self.news_encoder, candidate.reshape(-1, F), history.reshape(-1, F))
+        cv = cv.reshape(-1, 1 + a.npratio, a.news_dim)
+        hv = hv.reshape(-1, a.user_log_length, a.news_dim)
         u = self.user_encoder(hv, history_mask)
         loss, score, hits = ops.score_ce(cv, u, label)
         self.last_hits = hits

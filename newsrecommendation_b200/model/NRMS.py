@@ -6,7 +6,7 @@ from torch import nn
 
 from newsrecommendation_b200 import ops
 from newsrecommendation_b200 import _lib as L
-from .model_utils import AttentionPooling, MultiHeadSelfAttention, precision_of
+from .model_utils import AttentionPooling, MultiHeadSelfAttention, encode_both, precision_of
 
 
 def _heads(args):
@@ -23,6 +23,7 @@ class NewsEncoder(nn.Module):
     def __init__(self, args, embedding_matrix):
         super().__init__()
         prec = precision_of(args)
+        self.prec = prec
         self.embedding_matrix = embedding_matrix
         self.drop_rate = args.drop_rate
         self.dim_per_head = _heads(args)
@@ -34,6 +35,11 @@ class NewsEncoder(nn.Module):
         if mask is not None:
             raise RuntimeError('title masks are never used by the reference (NRMS.py:87,90); not built')
         p = self.drop_rate if self.training else 0.0
+        if self.prec == L.PREC_BF16:
+            m = self.multi_head_self_attn
+            return ops.title_encoder(L.ENC_MHSA, self.embedding_matrix.weight, x.reshape(-1, x.shape[-1]), None,
+                                     m._w(), self.attn._p(), mode=L.ROWS_TOKEN, S=x.shape[-1], Dm=m.d_model,
+                                     heads=m.n_heads, in_drop=p, out_drop=p, seed=ops.next_seed() if p else 0)
         h = self.multi_head_self_attn.forward_rows(self.embedding_matrix.weight, x.reshape(-1, x.shape[-1]),
                                                    L.ROWS_TOKEN, x.shape[-1], p, p, ops.next_seed() if p else 0)
         return self.attn(h)
@@ -45,6 +51,7 @@ class UserEncoder(nn.Module):
     def __init__(self, args):
         super().__init__()
         prec = precision_of(args)
+        self.prec = prec
         self.args = args
         self.dim_per_head = _heads(args)
         self.multi_head_self_attn = MultiHeadSelfAttention(args.news_dim, args.num_attention_heads,
@@ -53,6 +60,14 @@ class UserEncoder(nn.Module):
         self.pad_doc = nn.Parameter(torch.empty(1, args.news_dim).uniform_(-1, 1))
 
     def forward(self, news_vecs, log_mask=None):
+        if self.prec == L.PREC_BF16:
+            m = self.multi_head_self_attn
+            if self.args.user_log_mask:
+                v, mask = news_vecs, log_mask
+            else:
+                v, mask = ops.pad_blend(news_vecs, log_mask, self.pad_doc), None
+            return ops.title_encoder(L.ENC_MHSA, v, None, mask, m._w(), self.attn._p(), mode=L.ROWS_DENSE,
+                                     S=v.shape[1], Dm=m.d_model, heads=m.n_heads)
         if self.args.user_log_mask:
             h = self.multi_head_self_attn(news_vecs, mask=log_mask)
             return self.attn(h, log_mask)
@@ -74,8 +89,9 @@ class Model(nn.Module):
     def forward(self, history, history_mask, candidate, label):
         a = self.args
         Lw = a.num_words_title
-        cv = self.news_encoder(candidate.reshape(-1, Lw)).reshape(-1, 1 + a.npratio, a.news_dim)
-        hv = self.news_encoder(history.reshape(-1, Lw)).reshape(-1, a.user_log_length, a.news_dim)
+        cv, hv = encode_both(self.news_encoder, candidate.reshape(-1, Lw), history.reshape(-1, Lw))
+        cv = cv.reshape(-1, 1 + a.npratio, a.news_dim)
+        hv = hv.reshape(-1, a.user_log_length, a.news_dim)
         u = self.user_encoder(hv, history_mask)
         loss, score, hits = ops.score_ce(cv, u, label)
         self.last_hits = hits      # #argmax==label of this batch (utils.acc numerator), device scalar

@@ -32,8 +32,13 @@ class AttentionPooling(nn.Module):
         self.prec = prec
 
     def forward(self, x, attn_mask=None):
+        # stand-alone pooling (NAML view / user pooling: a few thousand rows) always runs the fp32 kernels;
+        # in bf16 mode the title-level pooling is part of the fused title encoder (ops.title_encoder)
         return ops.attention_pooling(x, attn_mask, self.att_fc1.weight, self.att_fc1.bias,
-                                     self.att_fc2.weight, self.att_fc2.bias, self.prec)
+                                     self.att_fc2.weight, self.att_fc2.bias, L.PREC_FP32)
+
+    def _p(self):
+        return (self.att_fc1.weight, self.att_fc1.bias, self.att_fc2.weight, self.att_fc2.bias)
 
 
 class ScaledDotProductAttention(nn.Module):
@@ -80,3 +85,11 @@ class MultiHeadSelfAttention(nn.Module):
         dropouts fused; NRMS.py:28-34)."""
         return ops.mhsa(table, ids, None, *self._w(), mode=mode, S=S, Dm=self.d_model, heads=self.n_heads,
                         in_drop=in_drop, out_drop=out_drop, seed=seed, prec=self.prec)
+
+
+def encode_both(news_encoder, cand_rows, hist_rows):
+    """The reference encodes candidates and history in two calls (NRMS.py:87,90 / NAML.py:122,125);
+    one call over the concatenated rows gives the same vectors with half the launches."""
+    nc = cand_rows.shape[0]
+    v = news_encoder(torch.cat([cand_rows, hist_rows], dim=0))
+    return v[:nc], v[nc:]

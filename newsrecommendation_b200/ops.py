@@ -314,3 +314,73 @@ class ScoreCEFn(torch.autograd.Function):
 
 def score_ce(cand, user, label):
     return ScoreCEFn.apply(cand, user, label)
+
+
+class TitleEncoderFn(torch.autograd.Function):
+    """bf16 tensor-core title encoder (nr_title_encoder_fwd/_bwd): the whole
+    gather -> dropout -> {MHSA -> dropout | Conv1d(k=3)} -> AttentionPooling chain of
+    NRMS.py:27-35 / NAML.py:47-56, and the NRMS user encoder (NRMS.py:55-62) over dense rows."""
+
+    @staticmethod
+    def forward(ctx, src, ids, mask, w0, b0, w1, b1, w2, b2, p_w1, p_b1, p_w2, p_b2, cfg):
+        kind, mode, S, Dm, heads, in_drop, out_drop, seed = cfg
+        rows = _make_rows(src, ids, mode, S, Dm, in_drop, seed)
+        n = rows.n
+        ws_ = [None if t is None else L.f32(t) for t in (w0, b0, w1, b1, w2, b2)]
+        pool = [L.f32(t) for t in (p_w1, p_b1, p_w2, p_b2)]
+        H, Q = ws_[0].shape[0], pool[0].shape[0]
+        mask = None if mask is None else L.f32(mask)
+        dev = pool[0].device
+        enc = L.NrTitleEncoder()
+        enc.kind, enc.S, enc.Dm, enc.H, enc.Q, enc.heads = kind, S, Dm, H, Q, heads
+        for i in range(3):
+            enc.w[i] = L.ptr(ws_[2 * i])
+            enc.b[i] = L.ptr(ws_[2 * i + 1])
+        enc.p_w1, enc.p_b1, enc.p_w2, enc.p_b2 = [L.ptr(t) for t in pool]
+        enc.mask = L.ptr(mask)
+        enc.out_drop_p = float(out_drop)
+        save = torch.empty(L.lib.nr_title_encoder_save_bytes(C.byref(enc), n), dtype=torch.uint8, device=dev)
+        out = torch.empty(n, H, dtype=torch.float32, device=dev)
+        ws = L.workspace(0, dev)
+        r = rows.c()
+        L.call('nr_title_encoder_fwd', C.byref(enc), C.byref(r), n, L.ptr(out), L.ptr(save), save.numel(),
+               L.ptr(ws), ws.numel(), L.stream())
+        ctx.enc, ctx.rows, ctx.keep = enc, rows, (ws_, pool, mask, save)
+        ctx.src_shape = src.shape
+        ctx.n = n
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        enc, rows, (ws_, pool, mask, save) = ctx.enc, ctx.rows, ctx.keep
+        n = ctx.n
+        dev = save.device
+        g = L.f32(g)
+        gr = L.NrTitleEncoderGrads()
+        dws = [None if t is None else torch.zeros_like(t) for t in ws_]
+        dpool = [torch.zeros_like(t) for t in pool]
+        for i in range(3):
+            gr.dw[i] = L.ptr(dws[2 * i])
+            gr.db[i] = L.ptr(dws[2 * i + 1])
+        gr.dp_w1, gr.dp_b1, gr.dp_w2, gr.dp_b2 = [L.ptr(t) for t in dpool]
+        dsrc = None
+        if ctx.needs_input_grad[0]:
+            if rows.mode == L.ROWS_DENSE:
+                dsrc = torch.empty(ctx.src_shape, dtype=torch.float32, device=dev)
+                gr.dx_dense = L.ptr(dsrc)
+            else:
+                dsrc = torch.zeros(ctx.src_shape, dtype=torch.float32, device=dev)
+                gr.dtable = L.ptr(dsrc)
+        ws = L.workspace(L.lib.nr_title_encoder_workspace(C.byref(enc), n), dev)
+        r = rows.c()
+        L.call('nr_title_encoder_bwd', C.byref(enc), C.byref(r), n, L.ptr(g), L.ptr(save), save.numel(), C.byref(gr),
+               L.ptr(ws), ws.numel(), L.stream())
+        ctx.keep = None
+        return (dsrc, None, None, *dws, *dpool, None)
+
+
+def title_encoder(kind, src, ids, mask, weights, pool, *, mode, S, Dm, heads=1, in_drop=0.0, out_drop=0.0, seed=0):
+    """weights: MHSA (W_Q, b_Q, W_K, b_K, W_V, b_V); CONV (conv.weight, conv.bias).
+    pool: (att_fc1.weight, att_fc1.bias, att_fc2.weight, att_fc2.bias)."""
+    w = list(weights) + [None] * (6 - len(weights))
+    return TitleEncoderFn.apply(src, ids, mask, *w, *pool, (kind, mode, S, Dm, heads, in_drop, out_drop, seed))

@@ -1,0 +1,165 @@
+"""GPU parity of the bf16 tensor-core mode (tcgen05 GEMMs, fp32 accumulation) against the
+reference-generated golden fixtures and the CPU oracle.
+
+Tolerance (BASELINE.json north_star): scores and loss rel 1e-2 in bf16 mode.  Gradients: every
+entry within 6e-2 of the tensor's largest reference entry AND cosine similarity >= 0.998 per tensor.
+(bf16 activations carry 2^-9 relative rounding; the softmax-like backward da = alpha (dalpha - sum
+alpha dalpha) subtracts nearly equal numbers, which amplifies it to a few percent on the smallest
+gradient tensors.)  Tensors whose reference gradient is below 1e-3 of the largest gradient in the
+model (analytically zero ones: W_K.bias and att_fc2.bias cancel in the normalisation) are only
+required to stay below that floor."""
+import ctypes as C
+import itertools
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from oracle import nr_oracle as O
+from test_gpu_ops import T
+from test_gpu_models import build_model, G
+
+pytestmark = pytest.mark.gpu
+
+
+def tc_gemm_tn(A, B, taps=1, shifts=(0,)):
+    from newsrecommendation_b200 import _lib as L
+    rows, Mo = A.shape
+    No = B.shape[1]
+    out = torch.zeros(taps, Mo, No, dtype=torch.float32, device='cuda')
+    sh = (C.c_int32 * 3)(*(list(shifts) + [0, 0, 0])[:3])
+    L.call('nr_tc_gemm_tn', A.data_ptr(), Mo, A.stride(0), B.data_ptr(), No, B.stride(0), rows, taps,
+           C.cast(sh, C.c_void_p), out.data_ptr(), No, Mo * No, L.stream())
+    return out
+
+
+@pytest.mark.parametrize('rows,Mo,No', [(64, 128, 64), (1000, 200, 400), (4096 + 77, 1200, 301), (333, 16, 16),
+                                         (20000, 400, 320), (130, 130, 520)])
+def test_tc_gemm_tn(rows, Mo, No):
+    g = torch.Generator(device='cpu').manual_seed(rows + Mo + No)
+    lda, ldb = (Mo + 7) // 8 * 8, (No + 7) // 8 * 8
+    A = torch.zeros(rows, lda); A[:, :Mo] = torch.randn(rows, Mo, generator=g) * 0.5
+    B = torch.zeros(rows, ldb); B[:, :No] = torch.randn(rows, No, generator=g) * 0.3
+    Ab, Bb = A.to(torch.bfloat16).cuda(), B.to(torch.bfloat16).cuda()
+    ref = (Ab[:, :Mo].double().t() @ Bb[:, :No].double()).cpu()
+    out = tc_gemm_tn(Ab[:, :Mo], Bb[:, :No])[0].cpu()
+    scale = ref.abs().max().item()
+    np.testing.assert_allclose(out.numpy(), ref.numpy(), rtol=1e-4, atol=3e-6 * scale * np.sqrt(rows))
+
+
+def test_tc_gemm_tn_taps():
+    # conv weight gradient: C[t] = A^T . shift(B, t-1), rows shifted past either end read as zero
+    rows, Mo, No = 1500, 400, 304
+    g = torch.Generator(device='cpu').manual_seed(3)
+    Ab = (torch.randn(rows, Mo, generator=g) * 0.5).to(torch.bfloat16).cuda()
+    Bb = (torch.randn(rows, No, generator=g) * 0.3).to(torch.bfloat16).cuda()
+    out = tc_gemm_tn(Ab, Bb, taps=3, shifts=(-1, 0, 1)).cpu()
+    Ad, Bd = Ab.double().cpu(), Bb.double().cpu()
+    for t, sh in enumerate((-1, 0, 1)):
+        Bs = torch.zeros_like(Bd)
+        if sh < 0:
+            Bs[-sh:] = Bd[:sh]
+        elif sh > 0:
+            Bs[:-sh] = Bd[sh:]
+        else:
+            Bs = Bd
+        ref = Ad.t() @ Bs
+        np.testing.assert_allclose(out[t].numpy(), ref.numpy(), rtol=1e-4, atol=3e-6 * ref.abs().max().item() * 40)
+
+
+def _cmp_grad(name, got, ref, tol=6e-2, floor=0.0, errs=None):
+    """|got - ref| <= tol * max|ref| elementwise; `floor` = smallest scale taken seriously (gradients
+    that are analytically zero, e.g. att_fc2.bias under the shift-invariant normalisation, are noise)."""
+    got, ref = got.detach().float().cpu().numpy(), np.asarray(ref, dtype=np.float32)
+    scale = max(floor, float(np.abs(ref).max()), 1e-12)
+    if float(np.abs(ref).max()) <= floor:      # analytically ~zero gradient: only has to stay noise
+        if float(np.abs(got).max()) > 2 * floor:
+            (errs if errs is not None else []).append(f'{name}: noise {np.abs(got).max():.3e} above floor {floor:.3e}')
+        return
+    bad = float(np.abs(got - ref).max()) / scale
+    cos = 1.0
+    if float(np.abs(ref).max()) > floor:
+        cos = float((got.astype(np.float64) * ref).sum() /
+                    max(1e-300, np.linalg.norm(got.astype(np.float64)) * np.linalg.norm(ref.astype(np.float64))))
+    if bad > tol or cos < 0.998:
+        msg = f'{name}: max|diff|/scale = {bad:.4f} (tol {tol}), cosine {cos:.5f} (scale {scale:.3e})'
+        if errs is None:
+            raise AssertionError(msg)
+        errs.append(msg)
+
+
+@pytest.mark.parametrize('tag', sorted(synth.MODEL_CASES))
+def test_bf16_model_vs_reference_golden(tag):
+    g = np.load(os.path.join(G, tag + '.npz'))
+    kind, kw, P, bt, model = build_model(tag, precision='bf16')
+    hist, mask, cand, label = [T(a).cuda() for a in bt]
+    model.train()
+    loss, score = model(hist, mask, cand, label)
+    np.testing.assert_allclose(loss.item(), g['loss'], rtol=1e-2)
+    sscale = float(np.abs(g['score']).max())
+    np.testing.assert_allclose(score.detach().cpu().numpy(), g["score"], rtol=1e-2, atol=1e-2 * sscale)
+    loss.backward()
+    errs = []
+    gmax = max(float(np.abs(g[f]).max()) for f in g.files if f.startswith('gs:'))
+    for k, p in model.named_parameters():
+        if 'gs:' + k not in g.files:
+            continue
+        gr = torch.zeros_like(p) if p.grad is None else p.grad
+        s, st = synth.grad_digest(gr.cpu().numpy())
+        _cmp_grad(k, torch.from_numpy(s), g['gs:' + k], floor=1e-3 * gmax, errs=errs)
+        if abs(st[1] - g['gt:' + k][1]) > 3e-2 * g['gt:' + k][1] + 1e-2 * gmax:
+            errs.append(f'{k}: L2 norm {st[1]:.5e} vs {g["gt:" + k][1]:.5e}')
+    assert not errs, '\n'.join(errs)
+    if kind == 'nrms':
+        assert (model.news_encoder.embedding_matrix.weight.grad[0] == 0).all()      # padding_idx (B7)
+    model.eval()
+    F = hist.shape[-1]
+    with torch.no_grad():
+        nv = model.news_encoder(hist.reshape(-1, F))
+        uv = model.user_encoder(nv.reshape(hist.shape[0], hist.shape[1], -1), mask)
+        pv = model.news_encoder(torch.zeros(1, F, dtype=torch.int32, device='cuda'))
+    vs = float(np.abs(g['hist_vecs']).max())
+    np.testing.assert_allclose(nv.cpu().numpy(), g['hist_vecs'], rtol=1e-2, atol=1e-2 * vs)
+    np.testing.assert_allclose(uv.cpu().numpy(), g['user_vec'], rtol=1e-2, atol=1e-2 * float(np.abs(g['user_vec']).max()))
+    np.testing.assert_allclose(pv.cpu().numpy(), g['pad_news_vec'], rtol=1e-2, atol=1e-2 * vs)
+    if kw['user_log_mask']:
+        assert (uv[0] == 0).all()              # empty history -> exact zero (B1)
+
+
+@pytest.mark.parametrize('kind', ['nrms', 'naml'])
+def test_bf16_matches_fp32_path_with_dropout(kind):
+    """Both precision modes draw the same counter-based dropout masks, so a train-mode forward/backward
+    with drop_rate=0.2 must agree between them to bf16 tolerance (B=16, MIND-small shapes)."""
+    from newsrecommendation_b200 import ops, synthetic as S
+    from newsrecommendation_b200.model import NRMS, NAML
+    outs = {}
+    for prec in ('fp32', 'bf16'):
+        torch.manual_seed(0)
+        ops._seed_counter = itertools.count(1)
+        if kind == 'nrms':
+            a = S.default_args(num_words_title=30, drop_rate=0.2, precision=prec)
+            model = NRMS.Model(a, S.word_table(500))
+            news = S.news_titles(300, 30, 500)
+        else:
+            a = S.default_args(num_words_title=30, drop_rate=0.2, precision=prec, use_category=True,
+                               use_subcategory=True, freeze_embedding=True)
+            model = NAML.Model(a, S.title_table(300, 30), 17, 264)
+            news = S.naml_features(300)
+        model.cuda().train()
+        h, m, c, y = [torch.from_numpy(x).cuda() for x in S.train_batches(news, 1, 16, seed=5)[0]]
+        loss, score = model(h, m, c, y)
+        loss.backward()
+        outs[prec] = (loss.item(), score.detach().cpu(), {k: p.grad.detach().cpu() for k, p in model.named_parameters()
+                                                          if p.grad is not None})
+    l32, s32, g32 = outs['fp32']
+    l16, s16, g16 = outs['bf16']
+    np.testing.assert_allclose(l16, l32, rtol=1e-2)
+    np.testing.assert_allclose(s16.numpy(), s32.numpy(), rtol=1e-2, atol=1e-2 * s32.abs().max().item())
+    assert set(g16) == set(g32)
+    errs = []
+    gmax = max(v.abs().max().item() for v in g32.values())
+    for k in g32:
+        _cmp_grad(k, g16[k], g32[k].numpy(), floor=1e-3 * gmax, errs=errs)
+    assert not errs, '\n'.join(errs)
