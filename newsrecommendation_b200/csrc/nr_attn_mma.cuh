@@ -1,0 +1,418 @@
+// nr_attn_mma.cuh — per-head exp-attention of the title encoder on warp-level tensor-core MMAs
+// (model_utils.py:39-55; SURVEY Appendix C for the gradients).
+//
+// One title is S <= 31 tokens and a head is DK <= 32 wide: the whole (32 x 32) score tile of one
+// (title, head) lives in ONE warp's registers, so each product is a handful of
+// mma.sync.m16n8k16 (bf16 in, fp32 accumulate) instead of ~10^3 scalar FMAs per lane.  tcgen05 is
+// the wrong tool at this size: its smallest tile is 128 x N x 16 out of shared memory into TMEM, four
+// titles per instruction with 3/4 of the tile wasted on cross-title blocks, and a TMEM round trip per
+// product; the warp-level path keeps P, dS and all intermediates in registers.
+//
+//   forward : S = Q K^T,  P = exp(S/sqrt(dk)) * keymask,  O = (P / (rowsum P + eps)) V   [+ dropout]
+//   backward: both orientations are computed (S and S^T, dA and dA^T) so that every operand of the
+//             five gradient products is already in MMA fragment layout: dQ = dS K, dK = dS^T Q, dV = A^T dO.
+//
+// Layout: qkv (n*32, 3H) bf16 with q | k | v column blocks, head h at columns h*DK; pitch SP = 32.
+#pragma once
+#include "nr_enc_kernels.cuh"
+
+namespace nr {
+namespace amma {
+
+constexpr int PITCH = 40;                 // bf16 elements per shared-memory row (80 B: conflict-free ldmatrix)
+constexpr int TILE = 32 * PITCH;          // one 32-row operand tile
+
+__device__ __forceinline__ void ldsm_x4(const bf16* p, uint32_t* r) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(tc::smem_u32(p)));
+}
+__device__ __forceinline__ void ldsm_x2_trans(const bf16* p, uint32_t* r) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];"
+                 : "=r"(r[0]), "=r"(r[1]) : "r"(tc::smem_u32(p)));
+}
+__device__ __forceinline__ void mma16816(float* c, const uint32_t* a, const uint32_t* b) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
+}
+
+// A fragments (row-major 32 x 16*KS tile in smem): a[mt][ks][4]
+template <int KS>
+__device__ __forceinline__ void load_a(const bf16* tile, int lane, uint32_t (&a)[2][KS][4]) {
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks)
+            ldsm_x4(tile + (mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * PITCH + ks * 16 + (lane >> 4) * 8, a[mt][ks]);
+}
+// B fragments of X^T for a row-major X (rows = n, cols = k): b[nt][ks][2], nt < 4
+template <int KS>
+__device__ __forceinline__ void load_b_rows(const bf16* tile, int lane, uint32_t (&b)[4][KS][2]) {
+#pragma unroll
+    for (int np = 0; np < 2; ++np)
+#pragma unroll
+        for (int ks = 0; ks < KS; ++ks) {
+            uint32_t r[4];
+            ldsm_x4(tile + (np * 16 + (lane & 7) + (lane >> 4) * 8) * PITCH + ks * 16 + ((lane >> 3) & 1) * 8, r);
+            b[2 * np][ks][0] = r[0]; b[2 * np][ks][1] = r[1];
+            b[2 * np + 1][ks][0] = r[2]; b[2 * np + 1][ks][1] = r[3];
+        }
+}
+// B fragments of X for a row-major X (rows = k (32), cols = n): b[nt][ks][2], nt < NT, ks < 2
+template <int NT>
+__device__ __forceinline__ void load_b_cols(const bf16* tile, int lane, uint32_t (&b)[NT][2][2]) {
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks)
+            ldsm_x2_trans(tile + (ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * PITCH + nt * 8, b[nt][ks]);
+}
+// (32 x 32) accumulator tile (C layout) -> A fragments of the same matrix, bf16
+__device__ __forceinline__ void c_to_a(const float (&c)[2][4][4], uint32_t (&a)[2][2][4]) {
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks) {
+            a[mt][ks][0] = tc::pack_bf16(c[mt][2 * ks][0], c[mt][2 * ks][1]);
+            a[mt][ks][1] = tc::pack_bf16(c[mt][2 * ks][2], c[mt][2 * ks][3]);
+            a[mt][ks][2] = tc::pack_bf16(c[mt][2 * ks + 1][0], c[mt][2 * ks + 1][1]);
+            a[mt][ks][3] = tc::pack_bf16(c[mt][2 * ks + 1][2], c[mt][2 * ks + 1][3]);
+        }
+}
+__device__ __forceinline__ void zero_c(float (&c)[2][4][4]) {
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) c[mt][nt][e] = 0.f;
+}
+// C (32 x 32) = A (32 x 16KS) . B^T-fragments
+template <int KS>
+__device__ __forceinline__ void mm_32x32(float (&c)[2][4][4], const uint32_t (&a)[2][KS][4], const uint32_t (&b)[4][KS][2]) {
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int ks = 0; ks < KS; ++ks) mma16816(c[mt][nt], a[mt][ks], b[nt][ks]);
+}
+// C (32 x 8NT) = A (32 x 32) . B
+template <int NT>
+__device__ __forceinline__ void mm_32xn(float (&c)[2][NT][4], const uint32_t (&a)[2][2][4], const uint32_t (&b)[NT][2][2]) {
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) c[mt][nt][e] = 0.f;
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks) mma16816(c[mt][nt], a[mt][ks], b[nt][ks]);
+        }
+}
+// quad reduction: lanes 4g..4g+3 hold partial sums of the same rows
+__device__ __forceinline__ float quad_sum(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    return v;
+}
+// accumulator (32 x 8NT, C layout) * mul -> fp32 staging tile os[32][DK]
+template <int NT, int DK>
+__device__ __forceinline__ void stage_out(const float (&c)[2][NT][4], float* os, int lane, float m00, float m01, float m10,
+                                          float m11) {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            const int col = nt * 8 + 2 * t;
+            if (col < DK) {
+                const float lo = mt == 0 ? m00 : m10, hi = mt == 0 ? m01 : m11;
+                *(float2*)(os + (mt * 16 + g) * DK + col) = make_float2(c[mt][nt][0] * lo, c[mt][nt][1] * lo);
+                *(float2*)(os + (mt * 16 + g + 8) * DK + col) = make_float2(c[mt][nt][2] * hi, c[mt][nt][3] * hi);
+            }
+        }
+}
+// asynchronous copy of the (32 x DK) head slice of one operand into a shared tile (columns >= DK stay
+// zero).  cp.async: the copies of item i+1 are in flight while item i is computed (double buffer).
+template <int DK>
+__device__ __forceinline__ void prefetch_tile(bf16* tile, const bf16* src, int64_t ld, int lane) {
+#pragma unroll
+    for (int it = 0; it < DK / 4; ++it) {
+        const int idx = it * 32 + lane;
+        const int s = idx / (DK / 4), q4 = idx % (DK / 4);
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(tc::smem_u32(tile + s * PITCH + q4 * 4)),
+                     "l"(src + (int64_t)s * ld + q4 * 4) : "memory");
+    }
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+// fp32 staging tile -> bf16 rows of dst (rows >= S written as zero)
+template <int DK>
+__device__ __forceinline__ void store_tile(bf16* dst, int64_t ld, const float* os, int S, int lane) {
+    for (int idx = lane; idx < 32 * (DK / 4); idx += 32) {
+        const int s = idx / (DK / 4), q4 = idx % (DK / 4);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (s < S) v = *(const float4*)(os + s * DK + q4 * 4);
+        st_bf4(dst + (int64_t)s * ld + q4 * 4, v);
+    }
+}
+
+template <int DK>
+struct Cfg {
+    static constexpr int KS = (DK + 15) / 16;   // k-steps of Q K^T
+    static constexpr int NT = (DK + 7) / 8;     // n-tiles of the (32 x DK) outputs
+};
+
+__host__ __device__ constexpr size_t fwd_smem_per_warp(int DK) { return (size_t)2 * 3 * TILE * 2 + (size_t)32 * DK * 4; }
+__host__ __device__ constexpr size_t bwd_smem_per_warp(int DK) { return (size_t)2 * 4 * TILE * 2 + (size_t)32 * DK * 4 + 64 * 4; }
+
+template <int DK>
+static __global__ void __launch_bounds__(128)
+attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
+                    int64_t items, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed) {
+    constexpr int KS = Cfg<DK>::KS, NT = Cfg<DK>::NT;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t = lane & 3;
+    const int H = heads * DK;
+    uint8_t* base = smem_raw + warp * fwd_smem_per_warp(DK);
+    bf16* buf = (bf16*)base;                       // 2 stages x (Q | K | V)
+    float* Os = (float*)(buf + 6 * TILE);
+    for (int i = lane; i < 6 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncwarp();
+    const int64_t stride = (int64_t)gridDim.x * 4;
+    int64_t item = (int64_t)blockIdx.x * 4 + warp;
+    auto issue = [&](int64_t it, int stage) {
+        const int64_t sq = it / heads;
+        const bf16* src = qkv + sq * 32 * 3 * H + (int)(it - sq * heads) * DK;
+        bf16* b = buf + stage * 3 * TILE;
+        prefetch_tile<DK>(b, src, 3 * H, lane);
+        prefetch_tile<DK>(b + TILE, src + H, 3 * H, lane);
+        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, 3 * H, lane);
+        cp_async_commit();
+    };
+    if (item < items) issue(item, 0);
+    for (int stage = 0; item < items; item += stride, stage ^= 1) {
+        const int64_t seq = item / heads;
+        const int head = (int)(item - seq * heads);
+        if (item + stride < items) issue(item + stride, stage ^ 1); else cp_async_commit();
+        const bf16* Qs = buf + stage * 3 * TILE;
+        const bf16* Ks = Qs + TILE;
+        const bf16* Vs = Ks + TILE;
+        float mk[4][2];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int col = nt * 8 + 2 * t + e;
+                mk[nt][e] = col < S ? (key_mask ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
+            }
+        cp_async_wait<1>();
+        __syncwarp();
+        float acc[2][4][4];
+        zero_c(acc);
+        {
+            uint32_t aq[2][KS][4], bk[4][KS][2];
+            load_a<KS>(Qs, lane, aq);
+            load_b_rows<KS>(Ks, lane, bk);
+            mm_32x32<KS>(acc, aq, bk);
+        }
+        float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float m = mk[nt][e & 1];
+                    const float p = m != 0.f ? __expf(acc[mt][nt][e] * scale) * m : 0.f;
+                    acc[mt][nt][e] = p;
+                    z[mt][e >> 1] += p;
+                }
+        float inv[2][2];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) inv[mt][h] = 1.f / (quad_sum(z[mt][h]) + kEps);    // model_utils.py:53
+        uint32_t ap[2][2][4], bv[NT][2][2];
+        c_to_a(acc, ap);
+        load_b_cols<NT>(Vs, lane, bv);
+        float o[2][NT][4];
+        mm_32xn<NT>(o, ap, bv);
+        stage_out<NT, DK>(o, Os, lane, inv[0][0], inv[0][1], inv[1][0], inv[1][1]);
+        __syncwarp();
+        bf16* dst = ctx + seq * 32 * H + head * DK;
+        for (int idx = lane; idx < 32 * (DK / 4); idx += 32) {
+            const int s = idx / (DK / 4), q4 = idx % (DK / 4);
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (s < S) {
+                v = *(const float4*)(Os + s * DK + q4 * 4);
+                if (thr) v = dropout4(v, (uint64_t)((seq * S + s) * H + head * DK + q4 * 4), seed, NR_STREAM_OUT, thr, dscale);
+            }
+            st_bf4(dst + (int64_t)s * H + q4 * 4, v);
+        }
+        __syncwarp();
+    }
+}
+
+template <int DK>
+static __global__ void __launch_bounds__(128)
+attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
+                    bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale) {
+    constexpr int KS = Cfg<DK>::KS, NT = Cfg<DK>::NT;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int H = heads * DK;
+    uint8_t* base = smem_raw + warp * bwd_smem_per_warp(DK);
+    bf16* buf = (bf16*)base;                       // 2 stages x (Q | K | V | dO)
+    float* Os = (float*)(buf + 8 * TILE);
+    float* zinv = Os + 32 * DK;
+    float* rds = zinv + 32;
+    for (int i = lane; i < 8 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncwarp();
+    const int64_t stride = (int64_t)gridDim.x * 4;
+    int64_t item = (int64_t)blockIdx.x * 4 + warp;
+    auto issue = [&](int64_t it, int stage) {
+        const int64_t sq = it / heads;
+        const int hd = (int)(it - sq * heads);
+        const bf16* src = qkv + sq * 32 * 3 * H + hd * DK;
+        bf16* b = buf + stage * 4 * TILE;
+        prefetch_tile<DK>(b, src, 3 * H, lane);
+        prefetch_tile<DK>(b + TILE, src + H, 3 * H, lane);
+        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, 3 * H, lane);
+        prefetch_tile<DK>(b + 3 * TILE, dctx + sq * 32 * H + hd * DK, H, lane);
+        cp_async_commit();
+    };
+    if (item < items) issue(item, 0);
+    for (int stage = 0; item < items; item += stride, stage ^= 1) {
+        const int64_t seq = item / heads;
+        const int head = (int)(item - seq * heads);
+        if (item + stride < items) issue(item + stride, stage ^ 1); else cp_async_commit();
+        const bf16* Qs = buf + stage * 4 * TILE;
+        const bf16* Ks = Qs + TILE;
+        const bf16* Vs = Ks + TILE;
+        const bf16* Gs = Vs + TILE;
+        float mcol[4][2], mrow[2][2];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int col = nt * 8 + 2 * t + e;
+                mcol[nt][e] = col < S ? (key_mask ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
+            }
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int row = mt * 16 + g + 8 * h;
+                mrow[mt][h] = row < S ? (key_mask ? __ldg(key_mask + seq * S + row) : 1.f) : 0.f;
+            }
+        cp_async_wait<1>();
+        __syncwarp();
+        bf16* dst = dqkv + seq * 32 * 3 * H + head * DK;
+        // ---- query-major pass: A = P/Z, dA = dO V^T, dS = A (dA - rd), dQ = dS K / sqrt(dk)
+        {
+            float s[2][4][4], da[2][4][4];
+            zero_c(s); zero_c(da);
+            {
+                uint32_t a[2][KS][4], b[4][KS][2];
+                load_a<KS>(Qs, lane, a); load_b_rows<KS>(Ks, lane, b);
+                mm_32x32<KS>(s, a, b);
+                load_a<KS>(Gs, lane, a); load_b_rows<KS>(Vs, lane, b);
+                mm_32x32<KS>(da, a, b);
+            }
+            float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, rd[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float m = mcol[nt][e & 1];
+                        const float p = m != 0.f ? __expf(s[mt][nt][e] * scale) * m : 0.f;
+                        s[mt][nt][e] = p;
+                        z[mt][e >> 1] += p;
+                        rd[mt][e >> 1] = fmaf(p, da[mt][nt][e], rd[mt][e >> 1]);
+                    }
+            float inv[2][2];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int row = mt * 16 + g + 8 * h;
+                    const float zs = quad_sum(z[mt][h]), rs = quad_sum(rd[mt][h]);   // shuffles: all lanes, no branch
+                    inv[mt][h] = row < S ? 1.f / (zs + kEps) : 0.f;
+                    rd[mt][h] = rs * inv[mt][h];
+                    if (t == 0) { zinv[row] = inv[mt][h]; rds[row] = rd[mt][h]; }
+                }
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        s[mt][nt][e] = s[mt][nt][e] * inv[mt][e >> 1] * (da[mt][nt][e] - rd[mt][e >> 1]);
+            uint32_t ads[2][2][4], bk[NT][2][2];
+            c_to_a(s, ads);
+            load_b_cols<NT>(Ks, lane, bk);
+            float dq[2][NT][4];
+            mm_32xn<NT>(dq, ads, bk);
+            stage_out<NT, DK>(dq, Os, lane, scale, scale, scale, scale);
+        }
+        __syncwarp();
+        store_tile<DK>(dst, 3 * H, Os, S, lane);
+        __syncwarp();
+        // ---- key-major pass: S^T = K Q^T, dA^T = V dO^T; dK = dS^T Q / sqrt(dk), dV = A^T dO
+        {
+            float s[2][4][4], da[2][4][4];
+            zero_c(s); zero_c(da);
+            {
+                uint32_t a[2][KS][4], b[4][KS][2];
+                load_a<KS>(Ks, lane, a); load_b_rows<KS>(Qs, lane, b);
+                mm_32x32<KS>(s, a, b);
+                load_a<KS>(Vs, lane, a); load_b_rows<KS>(Gs, lane, b);
+                mm_32x32<KS>(da, a, b);
+            }
+            float zi[4][2], ri[4][2];
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) { zi[nt][e] = zinv[nt * 8 + 2 * t + e]; ri[nt][e] = rds[nt * 8 + 2 * t + e]; }
+            // s <- A^T, da <- dS^T
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float m = mrow[mt][e >> 1];
+                        const float zv = zi[nt][e & 1];
+                        const float a = (m != 0.f && zv != 0.f) ? __expf(s[mt][nt][e] * scale) * m * zv : 0.f;
+                        s[mt][nt][e] = a;
+                        da[mt][nt][e] = a * (da[mt][nt][e] - ri[nt][e & 1]);
+                    }
+            uint32_t af[2][2][4], bf[NT][2][2];
+            float out[2][NT][4];
+            c_to_a(da, af);
+            load_b_cols<NT>(Qs, lane, bf);
+            mm_32xn<NT>(out, af, bf);
+            stage_out<NT, DK>(out, Os, lane, scale, scale, scale, scale);
+            __syncwarp();
+            store_tile<DK>(dst + H, 3 * H, Os, S, lane);
+            __syncwarp();
+            c_to_a(s, af);
+            load_b_cols<NT>(Gs, lane, bf);
+            mm_32xn<NT>(out, af, bf);
+            stage_out<NT, DK>(out, Os, lane, 1.f, 1.f, 1.f, 1.f);
+        }
+        __syncwarp();
+        store_tile<DK>(dst + 2 * H, 3 * H, Os, S, lane);
+        __syncwarp();
+    }
+}
+
+}  // namespace amma
+}  // namespace nr

@@ -4,6 +4,7 @@
 // UserEncoder (NRMS.py:55-62) as one pipeline of tcgen05 GEMMs (nr_tc_gemm.cuh, nr_tc_gemm_tn.cuh)
 // with fused epilogues and fp32 SIMT tails (nr_enc_kernels.cuh).  Gradient math: SURVEY Appendix C.
 #include "nr_enc_kernels.cuh"
+#include "nr_attn_mma.cuh"
 #include "nr_tc_gemm.cuh"
 #include "nr_tc_gemm_tn.cuh"
 
@@ -13,28 +14,13 @@ namespace {
 
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }
 
-// ---- NT epilogues (protocol of nr_tc_gemm.cuh: one thread = one output row) --------------------------
-// qkv (bf16) = acc + [b_Q | b_K | b_V]
-struct EpiQkvBias {
-    bf16* C; int64_t ldc; const float* b0; const float* b1; const float* b2; int each;
-    __device__ __forceinline__ void begin(int64_t) {}
-    __device__ __forceinline__ void end(int64_t) {}
-    __device__ __forceinline__ float bias(int col) const {
-        return col < each ? __ldg(b0 + col) : (col < 2 * each ? __ldg(b1 + col - each) : __ldg(b2 + col - 2 * each));
-    }
-    __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
-        bf16* out = C + row * ldc + col0;
-        if (nc == 32) {
-            uint32_t w[16];
-#pragma unroll
-            for (int j = 0; j < 16; ++j) w[j] = tc::pack_bf16(v[2 * j] + bias(col0 + 2 * j), v[2 * j + 1] + bias(col0 + 2 * j + 1));
-#pragma unroll
-            for (int j = 0; j < 4; ++j) ((uint4*)out)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-        } else {
-            for (int j = 0; j < nc; ++j) out[j] = __float2bfloat16(v[j] + bias(col0 + j));
-        }
-    }
-};
+// ---- NT epilogues (protocol of nr_tc_gemm.cuh: one thread = one output row; register arrays are
+// indexed at compile time only) -----------------------------------------------------------------------
+__device__ __forceinline__ float tanh_fast(float x) {      // MUFU.TANH, rel. error ~2^-11 (< bf16 rounding)
+    float y;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
 
 // AttentionPooling fc1 + tanh + fc2 (model_utils.py:21-23): e (bf16) = tanh(acc + b1);
 // logits[row] = e . w2 + b2 (fp32, from the unrounded tanh).  Needs the whole row in one n tile.
@@ -44,30 +30,19 @@ struct EpiTanhLogit {
     __device__ __forceinline__ void begin(int64_t) { acc = 0.f; }
     __device__ __forceinline__ void end(int64_t row) { logits[row] = acc + __ldg(b2); }
     __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
-        bf16* out = E + row * lde + col0;
-        if (nc == 32) {
-            uint32_t w[16];
+        float b[32], w[32], o[32];
+        load_bias32(b1, col0, nc, b);
+        load_bias32(w2, col0, nc, w);      // zero beyond nc: padded columns add nothing to the logit
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const float t0 = tanhf(v[2 * j] + __ldg(b1 + col0 + 2 * j));
-                const float t1 = tanhf(v[2 * j + 1] + __ldg(b1 + col0 + 2 * j + 1));
-                acc = fmaf(t0, __ldg(w2 + col0 + 2 * j), acc);
-                acc = fmaf(t1, __ldg(w2 + col0 + 2 * j + 1), acc);
-                w[j] = tc::pack_bf16(t0, t1);
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) ((uint4*)out)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-        } else {
-            for (int j = 0; j < nc; ++j) {
-                const float t = tanhf(v[j] + __ldg(b1 + col0 + j));
-                acc = fmaf(t, __ldg(w2 + col0 + j), acc);
-                out[j] = __float2bfloat16(t);
-            }
+        for (int j = 0; j < 32; ++j) {
+            o[j] = tanh_fast(v[j] + b[j]);
+            acc = fmaf(o[j], w[j], acc);
         }
+        store_bf16_32(E + row * lde + col0, o, nc);
     }
 };
 
-// dY (bf16) = (dz . W1 + alpha_s g) [* output-dropout mask]; pad rows zero.
+// dY (bf16) = (dz . W1 + alpha_s g) [* output-dropout mask]; pad rows zero.  nc % 4 == 0 (H % 8 == 0).
 struct EpiPoolDx {
     bf16* dY; int64_t ld; const float* alpha; const float* g; int S, SP, H;
     uint32_t thr; float dscale; uint64_t seed;
@@ -79,16 +54,21 @@ struct EpiPoolDx {
     __device__ __forceinline__ void end(int64_t) {}
     __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
         bf16* out = dY + row * ld + col0;
-        if (s >= S) {
-            for (int j = 0; j < nc; j += 4) *(uint2*)(out + j) = make_uint2(0u, 0u);
-            return;
-        }
+        const bool real = s < S;
         const float* gr = g + seq * H + col0;
-        for (int j = 0; j < nc; j += 4) {      // nc % 4 == 0 (H % 8 == 0)
-            const float4 gv = ldg4(gr + j);
-            float4 t = make_float4(fmaf(a, gv.x, v[j]), fmaf(a, gv.y, v[j + 1]), fmaf(a, gv.z, v[j + 2]), fmaf(a, gv.w, v[j + 3]));
-            if (thr) t = dropout4(t, (uint64_t)((seq * S + s) * H + col0 + j), seed, NR_STREAM_OUT, thr, dscale);
-            st_bf4(out + j, t);
+        const uint64_t e0 = (uint64_t)((seq * S + s) * H + col0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            if (4 * j < nc) {
+                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (real) {
+                    const float4 gv = ldg4(gr + 4 * j);
+                    t = make_float4(fmaf(a, gv.x, v[4 * j]), fmaf(a, gv.y, v[4 * j + 1]), fmaf(a, gv.z, v[4 * j + 2]),
+                                    fmaf(a, gv.w, v[4 * j + 3]));
+                    if (thr) t = dropout4(t, e0 + 4 * j, seed, NR_STREAM_OUT, thr, dscale);
+                }
+                st_bf4(out + 4 * j, t);
+            }
         }
     }
 };
@@ -108,14 +88,18 @@ struct EpiDx {
         if (s >= x.S) return;
         if (x.mode != NR_ROWS_DENSE && id == 0) return;
         const int64_t r = seq * x.S + s;
-        float* dst = x.mode == NR_ROWS_DENSE ? dx_dense + r * x.D
-                   : (x.mode == NR_ROWS_TOKEN ? dtable + id * x.D : dtable + id * ((int64_t)x.S * x.D) + (int64_t)s * x.D);
-        for (int j = 0; j < nc; j += 4) {      // nc % 4 == 0 (Dm % 4 == 0)
-            float4 t = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            if (x.thr) t = dropout4(t, (uint64_t)(r * x.D + col0 + j), x.seed, NR_STREAM_IN, x.thr, x.scale);
-            float* p = dst + col0 + j;
-            if (x.mode == NR_ROWS_DENSE) *(float4*)p = t;
-            else atomicAdd((float4*)p, t);
+        float* dst = (x.mode == NR_ROWS_DENSE ? dx_dense + r * x.D
+                   : (x.mode == NR_ROWS_TOKEN ? dtable + id * x.D : dtable + id * ((int64_t)x.S * x.D) + (int64_t)s * x.D))
+                     + col0;
+        const uint64_t e0 = (uint64_t)(r * x.D + col0);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {      // nc % 4 == 0 (Dm % 4 == 0)
+            if (4 * j < nc) {
+                float4 t = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                if (x.thr) t = dropout4(t, e0 + 4 * j, x.seed, NR_STREAM_IN, x.thr, x.scale);
+                if (x.mode == NR_ROWS_DENSE) *(float4*)(dst + 4 * j) = t;
+                else atomicAdd((float4*)(dst + 4 * j), t);
+            }
         }
     }
 };
@@ -128,10 +112,14 @@ struct TnEpiQkv {
         const int w = i / H, ii = i - w * H;
         float* dw = w == 0 ? dw0 : (w == 1 ? dw1 : dw2);
         float* db = w == 0 ? db0 : (w == 1 ? db1 : db2);
-        for (int t = 0; t < nc; ++t) {
+        float* row = dw ? dw + (int64_t)ii * Dm : nullptr;
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
             const int c = j + t;
-            if (c < Dm) { if (dw) atomicAdd(dw + (int64_t)ii * Dm + c, v[t]); }
-            else if (c == Dm) { if (db) atomicAdd(db + ii, v[t]); }
+            if (t < nc) {
+                if (c < Dm) { if (row) atomicAdd(row + c, v[t]); }
+                else if (c == Dm) { if (db) atomicAdd(db + ii, v[t]); }
+            }
         }
     }
 };
@@ -139,10 +127,13 @@ struct TnEpiQkv {
 struct TnEpiConv {
     float* dw; float* db; int Dm;
     __device__ __forceinline__ void operator()(int o, int tap, int j, const float* v, int nc) const {
-        for (int t = 0; t < nc; ++t) {
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
             const int c = j + t;
-            if (c < Dm) { if (dw) atomicAdd(dw + ((int64_t)o * Dm + c) * 3 + tap, v[t]); }
-            else if (c == Dm && tap == 1) { if (db) atomicAdd(db + o, v[t]); }
+            if (t < nc) {
+                if (c < Dm) { if (dw) atomicAdd(dw + ((int64_t)o * Dm + c) * 3 + tap, v[t]); }
+                else if (c == Dm && tap == 1) { if (db) atomicAdd(db + o, v[t]); }
+            }
         }
     }
 };
@@ -152,7 +143,7 @@ struct Plan {
     int SP, ldx, Kp, HK, QK, K3, Nw;
     int64_t R;
     // save
-    size_t o_wb, o_w1b, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
+    size_t o_wb, o_w1b, o_bias, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
     // backward workspace
     size_t o_dz, o_dy, o_dqkv, o_w1t, o_wt, ws_bytes;
 };
@@ -172,6 +163,7 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     auto take = [&](size_t bytes) { size_t r = o; o += (bytes + 1023) & ~size_t(1023); return r; };
     p.o_wb = take((size_t)p.Nw * taps * p.Kp * 2);
     p.o_w1b = take((size_t)e->Q * p.HK * 2);
+    p.o_bias = take((size_t)3 * e->H * 4);
     p.o_xb = take((size_t)p.R * p.ldx * 2);
     p.o_qkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
     p.o_y = take((size_t)p.R * e->H * 2);
@@ -237,6 +229,41 @@ int launch_attn_bwd(const bf16* qkv, const float* mask, const bf16* dctx, bf16* 
                                                                                   1.0f / sqrtf((float)DK));
     return check_last("enc.attn_bwd");
 }
+// warp-level tensor-core attention (S <= 31 => pitch 32, head dim <= 32)
+template <int DK>
+int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
+                        uint64_t seed, cudaStream_t st) {
+    const size_t smem = 4 * amma::fwd_smem_per_warp(DK);
+    NR_CUDA(cudaFuncSetAttribute(amma::attn_fwd_mma_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t items = n * heads;
+    int64_t grid = (items + 3) / 4;
+    int per_sm = 1;
+    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, amma::attn_fwd_mma_kernel<DK>, 128, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;    // persistent: one wave
+    ProfScope ps("enc.attn_fwd", st);
+    amma::attn_fwd_mma_kernel<DK><<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads,
+                                                                    1.0f / sqrtf((float)DK), p > 0.f ? drop_threshold(p) : 0u,
+                                                                    p > 0.f ? 1.f / (1.f - p) : 1.f, seed);
+    return check_last("enc.attn_fwd");
+}
+template <int DK>
+int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
+                        cudaStream_t st) {
+    const size_t smem = 4 * amma::bwd_smem_per_warp(DK);
+    NR_CUDA(cudaFuncSetAttribute(amma::attn_bwd_mma_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t items = n * heads;
+    int64_t grid = (items + 3) / 4;
+    int per_sm = 1;
+    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, amma::attn_bwd_mma_kernel<DK>, 128, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
+    ProfScope ps("enc.attn_bwd", st);
+    amma::attn_bwd_mma_kernel<DK><<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads,
+                                                                    1.0f / sqrtf((float)DK));
+    return check_last("enc.attn_bwd");
+}
+
 #define NR_ENC_DISPATCH_DK(dk, CALL)                                                   \
     switch (dk) {                                                                      \
         case 8: { constexpr int DK = 8; return CALL; }                                 \
@@ -248,10 +275,28 @@ int launch_attn_bwd(const bf16* qkv, const float* mask, const bf16* dctx, bf16* 
     }
 int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int SP, int heads, int dk, float p,
                uint64_t seed, cudaStream_t st) {
+    if (SP == 32) {
+        switch (dk) {
+            case 8: return launch_attn_fwd_mma<8>(qkv, mask, ctx, n, S, heads, p, seed, st);
+            case 16: return launch_attn_fwd_mma<16>(qkv, mask, ctx, n, S, heads, p, seed, st);
+            case 20: return launch_attn_fwd_mma<20>(qkv, mask, ctx, n, S, heads, p, seed, st);
+            case 32: return launch_attn_fwd_mma<32>(qkv, mask, ctx, n, S, heads, p, seed, st);
+            default: break;
+        }
+    }
     NR_ENC_DISPATCH_DK(dk, launch_attn_fwd<DK>(qkv, mask, ctx, n, S, SP, heads, p, seed, st));
 }
 int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int SP, int heads,
                int dk, cudaStream_t st) {
+    if (SP == 32) {
+        switch (dk) {
+            case 8: return launch_attn_bwd_mma<8>(qkv, mask, dctx, dqkv, n, S, heads, st);
+            case 16: return launch_attn_bwd_mma<16>(qkv, mask, dctx, dqkv, n, S, heads, st);
+            case 20: return launch_attn_bwd_mma<20>(qkv, mask, dctx, dqkv, n, S, heads, st);
+            case 32: return launch_attn_bwd_mma<32>(qkv, mask, dctx, dqkv, n, S, heads, st);
+            default: break;
+        }
+    }
     NR_ENC_DISPATCH_DK(dk, launch_attn_bwd<DK>(qkv, mask, dctx, dqkv, n, S, SP, heads, st));
 }
 
@@ -285,6 +330,7 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     const int S = enc->S, Dm = enc->Dm, H = enc->H, Q = enc->Q;
     bf16* wb = (bf16*)(sv + p.o_wb);
     bf16* w1b = (bf16*)(sv + p.o_w1b);
+    float* bias_cat = (float*)(sv + p.o_bias);
     bf16* xb = (bf16*)(sv + p.o_xb);
     bf16* qkv = (bf16*)(sv + p.o_qkv);
     bf16* y = (bf16*)(sv + p.o_y);
@@ -295,6 +341,8 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     // 1. weights -> bf16 GEMM operands
     if (enc->kind == NR_ENC_MHSA) {
         if (int e = pack(PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3}, wb, st)) return e;
+        for (int i = 0; i < 3; ++i)
+            NR_CUDA(cudaMemcpyAsync(bias_cat + (size_t)i * H, enc->b[i], (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
     } else {
         if (int e = pack(PackArgs{enc->w[0], nullptr, nullptr, 2, H, Dm, p.Kp, H, 3 * p.Kp, 1}, wb, st)) return e;
     }
@@ -312,7 +360,7 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     const int one = 0;
     if (enc->kind == NR_ENC_MHSA) {
         if (int e = gemm_tc(xb, p.R, Dm, p.ldx, wb, 3 * H, p.Kp, 1, &one, p.R,
-                            EpiQkvBias{qkv, 3 * H, enc->b[0], enc->b[1], enc->b[2], H}, st, "enc.qkv"))
+                            TcEpiBiasBf16{qkv, 3 * H, bias_cat, 3 * H}, st, "enc.qkv"))
             return e;
         if (int e = attn_fwd_b(qkv, enc->mask, y, n, S, p.SP, enc->heads, H / enc->heads, enc->out_drop_p, rows->seed, st))
             return e;

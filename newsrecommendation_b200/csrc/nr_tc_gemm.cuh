@@ -7,9 +7,11 @@
 // Conv1d(k=3,pad=1) implicit GEMM over a token-major activation whose titles are separated by a
 // zero row (TMA zero-fills rows outside the tensor).
 //
-// CTA = 192 threads: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane; owns TMEM),
-// warps 2..5 = epilogue (TMEM -> registers -> functor).  Tile 128 x BN (BN <= 256, BN % 16 == 0),
-// two TMEM accumulators (2 x 256 columns) so the epilogue of tile i overlaps the MMAs of tile i+1.
+// CTA = 320 threads: warp 0 = TMA producer, warp 1 = MMA issuer (one elected lane; owns TMEM),
+// warps 2..5 = epilogue group 0, warps 6..9 = epilogue group 1 (TMEM -> registers -> functor).
+// Tile 128 x BN (BN <= 256, BN % 16 == 0), two TMEM accumulators (2 x 256 columns): accumulator a is
+// drained by epilogue group a, so two tile epilogues and the MMAs of a third tile overlap (the
+// epilogue of these K <= 1200 GEMMs costs more cycles than their MMAs).
 // Persistent: grid = #SMs, tiles assigned round-robin with n fastest (A tile reuse through L2).
 #pragma once
 #include "nr_common.cuh"
@@ -17,7 +19,7 @@
 
 namespace nr {
 
-constexpr int TC_BM = 128, TC_BK = 64, TC_THREADS = 192, TC_MAX_BN = 256;
+constexpr int TC_BM = 128, TC_BK = 64, TC_THREADS = 320, TC_MAX_BN = 256;
 
 struct TcGemmParams {
     int64_t M;        // output rows
@@ -115,17 +117,20 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (++acc == 2) { acc = 0; aph ^= 1; }
         }
     } else {
-        // ===== epilogue: warps 2..5; warp w may touch TMEM lanes [32*(w%4), +32) =====
+        // ===== epilogue: group g = warps 2+4g .. 5+4g drains accumulator g; warp w may touch TMEM
+        // lanes [32*(w%4), +32) =====
         Epi epi = epi_in;
         const int q = warp & 3;
-        int acc = 0; uint32_t aph = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const int64_t m0 = (int64_t)(tile / p.n_tiles) * TC_BM;
-            const int n0 = (tile % p.n_tiles) * p.BN;
+        const int grp = (warp - 2) >> 2;
+        for (int it = grp;; it += 2) {
+            const int64_t tile = (int64_t)blockIdx.x + (int64_t)it * gridDim.x;
+            if (tile >= total_tiles) break;
+            const int64_t m0 = (tile / p.n_tiles) * TC_BM;
+            const int n0 = (int)(tile % p.n_tiles) * p.BN;
             const int64_t row = m0 + q * 32 + lane;
-            tc::mbar_wait(tfull + acc, aph);
+            tc::mbar_wait(tfull + grp, (uint32_t)(it >> 1) & 1u);
             tc::tc_fence_after();
-            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * TC_MAX_BN;
+            const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * TC_MAX_BN;
             const int ncols = (p.N - n0 < p.BN) ? p.N - n0 : p.BN;
             const bool live = row < p.M;
             if (live) epi.begin(row);
@@ -138,8 +143,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (live) epi.end(row);
             tc::tc_fence_before();
             __syncwarp();
-            if (lane == 0) tc::mbar_arrive(tempty + acc);
-            if (++acc == 2) { acc = 0; aph ^= 1; }
+            if (lane == 0) tc::mbar_arrive(tempty + grp);
         }
     }
     tc::tc_fence_before();
@@ -191,42 +195,69 @@ int gemm_tc(const __nv_bfloat16* A, int64_t a_rows, int Kt_real, int64_t lda, co
 }
 
 // ---- epilogues -----------------------------------------------------------------------------------
-// C (bf16, leading dimension ldc) = acc + bias[col]
+// All register-array indexing is compile-time (fully unrolled, predicated tails) so v[] never
+// spills to local memory.  bias pointers must be 16-byte aligned (col0 is a multiple of 16).
+__device__ __forceinline__ void load_bias32(const float* bias, int col0, int nc, float* b) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (bias && 4 * j < nc) {
+            if (4 * j + 4 <= nc) t = ldg4(bias + col0 + 4 * j);
+            else {
+                t.x = __ldg(bias + col0 + 4 * j);
+                if (4 * j + 1 < nc) t.y = __ldg(bias + col0 + 4 * j + 1);
+                if (4 * j + 2 < nc) t.z = __ldg(bias + col0 + 4 * j + 2);
+            }
+        }
+        b[4 * j] = t.x; b[4 * j + 1] = t.y; b[4 * j + 2] = t.z; b[4 * j + 3] = t.w;
+    }
+}
+// 32 fp32 values -> bf16 row segment (16-byte stores where the tail allows)
+__device__ __forceinline__ void store_bf16_32(__nv_bfloat16* out, const float* v, int nc) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        if (8 * j + 8 <= nc) {
+            *(uint4*)(out + 8 * j) = make_uint4(tc::pack_bf16(v[8 * j], v[8 * j + 1]), tc::pack_bf16(v[8 * j + 2], v[8 * j + 3]),
+                                                tc::pack_bf16(v[8 * j + 4], v[8 * j + 5]), tc::pack_bf16(v[8 * j + 6], v[8 * j + 7]));
+        } else {
+#pragma unroll
+            for (int t = 0; t < 8; ++t)
+                if (8 * j + t < nc) out[8 * j + t] = __float2bfloat16(v[8 * j + t]);
+        }
+    }
+}
+// C (bf16, leading dimension ldc, ldc % 8 == 0) = acc + bias[col]
 struct TcEpiBiasBf16 {
     __nv_bfloat16* C; int64_t ldc; const float* bias; int N;
     __device__ __forceinline__ void begin(int64_t) {}
     __device__ __forceinline__ void end(int64_t) {}
     __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
-        __nv_bfloat16* out = C + row * ldc + col0;
-        if (nc == 32) {
-            uint32_t w[16];
+        float b[32], o[32];
+        load_bias32(bias, col0, nc, b);
 #pragma unroll
-            for (int j = 0; j < 16; ++j) {
-                const float b0 = bias ? __ldg(bias + col0 + 2 * j) : 0.f, b1 = bias ? __ldg(bias + col0 + 2 * j + 1) : 0.f;
-                w[j] = tc::pack_bf16(v[2 * j] + b0, v[2 * j + 1] + b1);
-            }
-#pragma unroll
-            for (int j = 0; j < 4; ++j) ((uint4*)out)[j] = make_uint4(w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
-        } else {
-            for (int j = 0; j < nc; ++j) out[j] = __float2bfloat16(v[j] + (bias ? __ldg(bias + col0 + j) : 0.f));
-        }
+        for (int j = 0; j < 32; ++j) o[j] = v[j] + b[j];
+        store_bf16_32(C + row * ldc + col0, o, nc);
     }
 };
-// C (fp32) = acc + bias[col]
+// C (fp32, ldc % 4 == 0) = acc + bias[col]
 struct TcEpiBiasF32 {
     float* C; int64_t ldc; const float* bias; int N;
     __device__ __forceinline__ void begin(int64_t) {}
     __device__ __forceinline__ void end(int64_t) {}
     __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
+        float b[32];
+        load_bias32(bias, col0, nc, b);
         float* out = C + row * ldc + col0;
-        if (nc == 32) {
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                float4 b = bias ? ldg4(bias + col0 + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
-                ((float4*)out)[j] = make_float4(v[4 * j] + b.x, v[4 * j + 1] + b.y, v[4 * j + 2] + b.z, v[4 * j + 3] + b.w);
+        for (int j = 0; j < 8; ++j) {
+            if (4 * j + 4 <= nc) {
+                *(float4*)(out + 4 * j) = make_float4(v[4 * j] + b[4 * j], v[4 * j + 1] + b[4 * j + 1],
+                                                      v[4 * j + 2] + b[4 * j + 2], v[4 * j + 3] + b[4 * j + 3]);
+            } else {
+#pragma unroll
+                for (int t = 0; t < 4; ++t)
+                    if (4 * j + t < nc) out[4 * j + t] = v[4 * j + t] + b[4 * j + t];
             }
-        } else {
-            for (int j = 0; j < nc; ++j) out[j] = v[j] + (bias ? __ldg(bias + col0 + j) : 0.f);
         }
     }
 };

@@ -180,7 +180,9 @@ struct TnEpiPlain {       // C[tap] (Mo x ldc) fp32 += acc
     float* C; int64_t ldc; int64_t tap_stride;
     __device__ __forceinline__ void operator()(int i, int tap, int j, const float* v, int nc) const {
         float* p = C + tap * tap_stride + (int64_t)i * ldc + j;
-        for (int t = 0; t < nc; ++t) atomicAdd(p + t, v[t]);
+#pragma unroll
+        for (int t = 0; t < 32; ++t)
+            if (t < nc) atomicAdd(p + t, v[t]);
     }
 };
 
