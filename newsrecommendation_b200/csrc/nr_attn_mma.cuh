@@ -182,11 +182,11 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     float* Os = (float*)(buf + 6 * TILE);
     for (int i = lane; i < 6 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
-    const int64_t stride = (int64_t)gridDim.x * 4;
-    int64_t item = (int64_t)blockIdx.x * 4 + warp;
-    auto issue = [&](int64_t it, int stage) {
-        const int64_t sq = it / heads;
-        const bf16* src = qkv + sq * 32 * 3 * H + (int)(it - sq * heads) * DK;
+    const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
+    int item = (int)blockIdx.x * 4 + warp;
+    auto issue = [&](int it, int stage) {
+        const int sq = it / heads;
+        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + (it - sq * heads) * DK;
         bf16* b = buf + stage * 3 * TILE;
         prefetch_tile<DK>(b, src, 3 * H, lane);
         prefetch_tile<DK>(b + TILE, src + H, 3 * H, lane);
@@ -196,8 +196,8 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     if (item < items) issue(item, 0);
     for (int stage = 0; item < items; item += stride, stage ^= 1) {
         const int64_t seq = item / heads;
-        const int head = (int)(item - seq * heads);
-        if (item + stride < items) issue(item + stride, stage ^ 1); else cp_async_commit();
+        const int head = item - (int)seq * heads;
+        if ((int64_t)item + stride < items) issue(item + stride, stage ^ 1); else cp_async_commit();
         const bf16* Qs = buf + stage * 3 * TILE;
         const bf16* Ks = Qs + TILE;
         const bf16* Vs = Ks + TILE;
@@ -227,7 +227,8 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const float m = mk[nt][e & 1];
-                    const float p = m != 0.f ? __expf(acc[mt][nt][e] * scale) * m : 0.f;
+                    float p = __expf(acc[mt][nt][e] * scale) * m;
+                    p = m != 0.f ? p : 0.f;                 // select, not a branch (inf * 0 guard for pad columns)
                     acc[mt][nt][e] = p;
                     z[mt][e >> 1] += p;
                 }
@@ -273,24 +274,24 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     float* rds = zinv + 32;
     for (int i = lane; i < 8 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
-    const int64_t stride = (int64_t)gridDim.x * 4;
-    int64_t item = (int64_t)blockIdx.x * 4 + warp;
-    auto issue = [&](int64_t it, int stage) {
-        const int64_t sq = it / heads;
-        const int hd = (int)(it - sq * heads);
-        const bf16* src = qkv + sq * 32 * 3 * H + hd * DK;
+    const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
+    int item = (int)blockIdx.x * 4 + warp;
+    auto issue = [&](int it, int stage) {
+        const int sq = it / heads;
+        const int hd = it - sq * heads;
+        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + hd * DK;
         bf16* b = buf + stage * 4 * TILE;
         prefetch_tile<DK>(b, src, 3 * H, lane);
         prefetch_tile<DK>(b + TILE, src + H, 3 * H, lane);
         prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, 3 * H, lane);
-        prefetch_tile<DK>(b + 3 * TILE, dctx + sq * 32 * H + hd * DK, H, lane);
+        prefetch_tile<DK>(b + 3 * TILE, dctx + (int64_t)sq * 32 * H + hd * DK, H, lane);
         cp_async_commit();
     };
     if (item < items) issue(item, 0);
     for (int stage = 0; item < items; item += stride, stage ^= 1) {
         const int64_t seq = item / heads;
-        const int head = (int)(item - seq * heads);
-        if (item + stride < items) issue(item + stride, stage ^ 1); else cp_async_commit();
+        const int head = item - (int)seq * heads;
+        if ((int64_t)item + stride < items) issue(item + stride, stage ^ 1); else cp_async_commit();
         const bf16* Qs = buf + stage * 4 * TILE;
         const bf16* Ks = Qs + TILE;
         const bf16* Vs = Ks + TILE;
@@ -332,7 +333,8 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         const float m = mcol[nt][e & 1];
-                        const float p = m != 0.f ? __expf(s[mt][nt][e] * scale) * m : 0.f;
+                        float p = __expf(s[mt][nt][e] * scale) * m;
+                        p = m != 0.f ? p : 0.f;
                         s[mt][nt][e] = p;
                         z[mt][e >> 1] += p;
                         rd[mt][e >> 1] = fmaf(p, da[mt][nt][e], rd[mt][e >> 1]);
@@ -390,7 +392,8 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
                     for (int e = 0; e < 4; ++e) {
                         const float m = mrow[mt][e >> 1];
                         const float zv = zi[nt][e & 1];
-                        const float a = (m != 0.f && zv != 0.f) ? __expf(s[mt][nt][e] * scale) * m * zv : 0.f;
+                        float a = __expf(s[mt][nt][e] * scale) * (m * zv);
+                        a = (m * zv != 0.f) ? a : 0.f;
                         s[mt][nt][e] = a;
                         da[mt][nt][e] = a * (da[mt][nt][e] - ri[nt][e & 1]);
                     }

@@ -236,6 +236,7 @@ int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n
     const size_t smem = 4 * amma::fwd_smem_per_warp(DK);
     NR_CUDA(cudaFuncSetAttribute(amma::attn_fwd_mma_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t items = n * heads;
+    NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
     int64_t grid = (items + 3) / 4;
     int per_sm = 1;
     NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, amma::attn_fwd_mma_kernel<DK>, 128, smem));
@@ -253,6 +254,7 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     const size_t smem = 4 * amma::bwd_smem_per_warp(DK);
     NR_CUDA(cudaFuncSetAttribute(amma::attn_bwd_mma_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t items = n * heads;
+    NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
     int64_t grid = (items + 3) / 4;
     int per_sm = 1;
     NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, amma::attn_bwd_mma_kernel<DK>, 128, smem));
