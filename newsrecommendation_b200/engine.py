@@ -24,6 +24,27 @@ def _dist_on():
     return dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
 
 
+def shard_rows(rows, world, rank):
+    """Contiguous row range [lo, hi) of rank `rank` when `rows` rows are split over `world` ranks in
+    equal slabs of `per` rows (the last slab may be short or empty)."""
+    per = (rows + world - 1) // world
+    return min(rows, rank * per), min(rows, (rank + 1) * per), per
+
+
+def impression_shard(n_impressions, world, rank):
+    """Impression i belongs to rank i % world (src/prepare_data.py:57-58)."""
+    return range(rank, n_impressions, world)
+
+
+def allreduce_gradients(flat_g):
+    """DDP semantics (main.py:82,109): SUM all-reduce of the flat gradient bucket; returns the scale
+    (1/world) the optimizer folds into its update so that the applied gradient is the rank mean."""
+    if _dist_on():
+        dist.all_reduce(flat_g, op=dist.ReduceOp.SUM)
+        return 1.0 / dist.get_world_size()
+    return 1.0
+
+
 class FlatAdam:
     """Flat-bucket Adam == torch.optim.Adam(params, lr) (betas .9/.999, eps 1e-8, wd 0)."""
 
@@ -65,10 +86,7 @@ class FlatAdam:
             dist.broadcast(self.flat_p, src=0)
 
     def step(self):
-        scale = 1.0
-        if _dist_on():
-            dist.all_reduce(self.flat_g, op=dist.ReduceOp.SUM)
-            scale = 1.0 / dist.get_world_size()
+        scale = allreduce_gradients(self.flat_g)
         self.step_count += 1
         L.call('nr_adam_step', L.ptr(self.flat_p), L.ptr(self.flat_g), L.ptr(self.m), L.ptr(self.v), self.count,
                self.lr, self.betas[0], self.betas[1], self.eps, self.step_count, scale, L.stream())
@@ -99,9 +117,8 @@ def build_news_cache(model, news_combined, batch=1024, shard=True):
     H = model.args.news_dim
     W = dist.get_world_size() if (shard and _dist_on()) else 1
     r = dist.get_rank() if W > 1 else 0
-    per = (rows + W - 1) // W
+    lo, hi, per = shard_rows(rows, W, r)
     table = torch.empty(per * W, H, dtype=torch.float32, device=dev)
-    lo, hi = min(rows, r * per), min(rows, (r + 1) * per)
     for b0 in range(lo, hi, batch):
         b1 = min(hi, b0 + batch)
         table[b0:b1] = model.news_encoder(news_combined[b0:b1])
