@@ -31,28 +31,35 @@ __device__ __forceinline__ void st_bf4(bf16* p, float4 v) {
 // ---- staging: X (fp32, through a RowsView incl. input dropout) -> Xb (n*SP, ldx) bf16 ------------
 // column Dm holds 1.0 on real rows (the "ones column": dW GEMMs then yield the bias gradient as
 // output column Dm); columns (Dm, ldx) and pad rows are zero.  One thread = 8 output columns.
+// blockDim = (ldx/8, rows per block): threadIdx.x = 8-column chunk, threadIdx.y = row slot, so no
+// per-thread division by the row width and one id lookup (broadcast) per row.
 static __global__ void __launch_bounds__(256)
-stage_rows_kernel(RowsView x, bf16* __restrict__ xb, int64_t n, int SP, int ldx) {
-    const int c8 = ldx >> 3;
-    const int64_t total = n * SP * c8;
-    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
-         t += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t row = t / c8;
-        const int c = (int)(t - row * c8) * 8;
-        const int64_t seq = row / SP;
-        const int s = (int)(row - seq * SP);
+stage_rows_kernel(RowsView x, bf16* __restrict__ xb, int R, int SP, int ldx) {
+    const int c = threadIdx.x * 8;
+    for (int row = blockIdx.x * blockDim.y + threadIdx.y; row < R; row += gridDim.x * blockDim.y) {
+        const int seq = row / SP;
+        const int s = row - seq * SP;
         uint4 o = make_uint4(0u, 0u, 0u, 0u);
         if (s < x.S) {
-            const int64_t r = seq * x.S + s;
-            float4 a = x.load4(r, c), b = x.load4(r, c + 4);    // zero beyond D
-            if (c <= x.D && x.D < c + 8) {
-                float* f = x.D < c + 4 ? &a.x : &b.x;
-                f[(x.D - c) & 3] = 1.0f;
+            const int64_t r = (int64_t)seq * x.S + s;
+            const float* src;
+            if (x.mode == NR_ROWS_DENSE) src = x.dense + r * x.D;
+            else if (x.mode == NR_ROWS_TOKEN) src = x.table + (int64_t)__ldg(x.ids + (int64_t)seq * x.ids_stride + s) * x.D;
+            else src = x.table + (int64_t)__ldg(x.ids + (int64_t)seq * x.ids_stride) * ((int64_t)x.S * x.D) + (int64_t)s * x.D;
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
+            if (c < x.D) a = ldg4(src + c);
+            if (c + 4 < x.D) b = ldg4(src + c + 4);
+            if (x.thr) {
+                if (c < x.D) a = dropout4(a, (uint64_t)(r * x.D + c), x.seed, NR_STREAM_IN, x.thr, x.scale);
+                if (c + 4 < x.D) b = dropout4(b, (uint64_t)(r * x.D + c + 4), x.seed, NR_STREAM_IN, x.thr, x.scale);
+            }
+            if (c <= x.D && x.D < c + 8) {           // the ones column
+                if (x.D < c + 4) a.x = 1.0f; else b.x = 1.0f;    // D % 4 == 0
             }
             o = make_uint4(tc::pack_bf16(a.x, a.y), tc::pack_bf16(a.z, a.w), tc::pack_bf16(b.x, b.y),
                            tc::pack_bf16(b.z, b.w));
         }
-        *(uint4*)(xb + row * ldx + c) = o;
+        *(uint4*)(xb + (int64_t)row * ldx + c) = o;
     }
 }
 
@@ -301,29 +308,45 @@ pool_tail_fwd_bf16_kernel(const bf16* __restrict__ y, const float* __restrict__ 
 
 // backward tail: dalpha_s = g.y_s ; da_s = alpha_s (dalpha_s - sum_t alpha_t dalpha_t) ;
 // dz[s,q] = da_s w2[q] (1 - e[s,q]^2) (bf16, pad rows zero) ; dw2 += sum da_s e_s ; db2 += sum da_s ;
-// db1 += sum_s dz[s,:].  Blocks stride over sequences; one atomic per block and column at the end.
+// db1 += sum_s dz[s,:].
+// 256 threads per block, blocks stride over sequences.  Phase 1: warp w takes rows w, w+8, ... and reads
+// them with 16-byte loads (coalesced) against g held in shared memory.  Phase 2: thread t owns the
+// 4-column group q4 = t % (Q/4) and the rows rg, rg+RG, ... (RG = 256 / (Q/4) row groups), so the E read
+// and the dz write are coalesced and spread over all threads; the column sums for dw2 / db1 stay in
+// registers across sequences and are flushed once per block.
 static __global__ void __launch_bounds__(256)
 pool_tail_bwd_bf16_kernel(const float* __restrict__ g, const bf16* __restrict__ y, const bf16* __restrict__ e,
                           const float* __restrict__ alpha, const float* __restrict__ w2, bf16* __restrict__ dz,
                           float* __restrict__ dw2, float* __restrict__ db2, float* __restrict__ db1, int64_t n,
                           int S, int SP, int H, int Q) {
-    extern __shared__ float sm[];   // da[SP] | dw2_acc[Q] | db1_acc[Q]
-    float* da = sm;
-    float* dw2_acc = sm + SP;
-    float* db1_acc = dw2_acc + Q;
+    extern __shared__ __align__(16) float sm[];   // gs[H] | da[SP] | red[2*Q]
+    float* gs = sm;
+    float* da = gs + H;
+    float* red = da + SP;
     __shared__ float s_c;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-    for (int q = threadIdx.x; q < 2 * Q; q += blockDim.x) dw2_acc[q] = 0.f;
+    const int QC = Q >> 2;                       // 4-column groups
+    const int RG = blockDim.x / QC;              // row groups (>= 1: Q <= 1024)
+    const int q4 = (threadIdx.x % QC) * 4, rg = threadIdx.x / QC;
+    const bool worker = rg < RG;
+    float4 wv = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (worker) wv = ldg4(w2 + q4);
+    float4 a2 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a2;
     float db2_acc = 0.f;
+    for (int q = threadIdx.x; q < 2 * Q; q += blockDim.x) red[q] = 0.f;
     for (int64_t seq = blockIdx.x; seq < n; seq += gridDim.x) {
         __syncthreads();
-        const float* gr = g + seq * H;
+        for (int h = threadIdx.x * 4; h < H; h += blockDim.x * 4) *(float4*)(gs + h) = ldg4(g + seq * H + h);
+        __syncthreads();
         for (int s = warp; s < S; s += nw) {
             const bf16* yr = y + (seq * SP + s) * H;
             float d = 0.f;
-            for (int h = lane * 4; h < H; h += 128) {
-                const float4 a = ldg4(gr + h), b = ld_bf4(yr + h);
-                d = fmaf(a.x, b.x, d); d = fmaf(a.y, b.y, d); d = fmaf(a.z, b.z, d); d = fmaf(a.w, b.w, d);
+            for (int h = lane * 8; h < H; h += 256) {
+                const uint4 w = __ldg((const uint4*)(yr + h));
+                const float2 y0 = bf2_to_f2(w.x), y1 = bf2_to_f2(w.y), y2 = bf2_to_f2(w.z), y3 = bf2_to_f2(w.w);
+                const float4 g0 = *(const float4*)(gs + h), g1 = *(const float4*)(gs + h + 4);
+                d = fmaf(g0.x, y0.x, d); d = fmaf(g0.y, y0.y, d); d = fmaf(g0.z, y1.x, d); d = fmaf(g0.w, y1.y, d);
+                d = fmaf(g1.x, y2.x, d); d = fmaf(g1.y, y2.y, d); d = fmaf(g1.z, y3.x, d); d = fmaf(g1.w, y3.y, d);
             }
             d = warp_sum(d);
             if (lane == 0) da[s] = d;
@@ -345,28 +368,30 @@ pool_tail_bwd_bf16_kernel(const float* __restrict__ g, const bf16* __restrict__ 
             for (int s = 0; s < S; ++s) t += da[s];
             db2_acc += t;
         }
-        for (int q = threadIdx.x * 4; q < Q; q += blockDim.x * 4) {
-            const float4 w = ldg4(w2 + q);
-            float4 a2 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a2;
-            for (int s = 0; s < SP; ++s) {
-                bf16* zr = dz + (seq * SP + s) * Q + q;
+        if (worker) {
+            for (int s = rg; s < SP; s += RG) {
+                bf16* zr = dz + (seq * SP + s) * Q + q4;
                 if (s >= S) { *(uint2*)zr = make_uint2(0u, 0u); continue; }
-                const float4 ev = ld_bf4(e + (seq * SP + s) * Q + q);
+                const float4 ev = ld_bf4(e + (seq * SP + s) * Q + q4);
                 const float d = da[s];
-                const float4 z = make_float4(d * w.x * (1.f - ev.x * ev.x), d * w.y * (1.f - ev.y * ev.y),
-                                             d * w.z * (1.f - ev.z * ev.z), d * w.w * (1.f - ev.w * ev.w));
+                const float4 z = make_float4(d * wv.x * (1.f - ev.x * ev.x), d * wv.y * (1.f - ev.y * ev.y),
+                                             d * wv.z * (1.f - ev.z * ev.z), d * wv.w * (1.f - ev.w * ev.w));
                 st_bf4(zr, z);
                 a2.x = fmaf(d, ev.x, a2.x); a2.y = fmaf(d, ev.y, a2.y); a2.z = fmaf(d, ev.z, a2.z); a2.w = fmaf(d, ev.w, a2.w);
                 a1.x += z.x; a1.y += z.y; a1.z += z.z; a1.w += z.w;
             }
-            dw2_acc[q] += a2.x; dw2_acc[q + 1] += a2.y; dw2_acc[q + 2] += a2.z; dw2_acc[q + 3] += a2.w;
-            db1_acc[q] += a1.x; db1_acc[q + 1] += a1.y; db1_acc[q + 2] += a1.z; db1_acc[q + 3] += a1.w;
         }
     }
     __syncthreads();
+    if (worker) {
+        atomicAdd(red + q4, a2.x); atomicAdd(red + q4 + 1, a2.y); atomicAdd(red + q4 + 2, a2.z); atomicAdd(red + q4 + 3, a2.w);
+        atomicAdd(red + Q + q4, a1.x); atomicAdd(red + Q + q4 + 1, a1.y); atomicAdd(red + Q + q4 + 2, a1.z);
+        atomicAdd(red + Q + q4 + 3, a1.w);
+    }
+    __syncthreads();
     for (int q = threadIdx.x; q < Q; q += blockDim.x) {
-        atomicAdd(dw2 + q, dw2_acc[q]);
-        atomicAdd(db1 + q, db1_acc[q]);
+        atomicAdd(dw2 + q, red[q]);
+        atomicAdd(db1 + q, red[Q + q]);
     }
     if (threadIdx.x == 0) atomicAdd(db2, db2_acc);
 }

@@ -352,10 +352,14 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     // 2. stage rows: gather + input dropout + bf16, padded pitch
     {
         const RowsView xv = make_rows_view(rows, n, S, Dm);
-        const int64_t total = p.R * (p.ldx >> 3);
-        const int blocks = (int)((total + 255) / 256 < (int64_t)sm_count() * 16 ? (total + 255) / 256 : (int64_t)sm_count() * 16);
+        NR_REQUIRE(p.R < ((int64_t)1 << 31) && p.ldx <= 2048, "%s: n*pitch = %lld rows / ldx %d outside the staging envelope",
+                   who, (long long)p.R, p.ldx);
+        const int cx = p.ldx >> 3;
+        const int ry = 256 / cx > 0 ? 256 / cx : 1;
+        int64_t blocks = (p.R + ry - 1) / ry;
+        if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
         ProfScope ps("enc.stage", st);
-        stage_rows_kernel<<<blocks, 256, 0, st>>>(xv, xb, n, p.SP, p.ldx);
+        stage_rows_kernel<<<(unsigned)blocks, dim3(cx, ry), 0, st>>>(xv, xb, (int)p.R, p.SP, p.ldx);
         if (int e = check_last("enc.stage")) return e;
     }
     // 3. token mixer
@@ -424,9 +428,9 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     }
     // 1. pooling tail backward: dz, dw2, db2, db1
     {
-        int64_t grid = n < 4 * (int64_t)sm_count() ? n : 4 * (int64_t)sm_count();
+        int64_t grid = n < 8 * (int64_t)sm_count() ? n : 8 * (int64_t)sm_count();
         ProfScope ps("enc.pool_bwd", st);
-        pool_tail_bwd_bf16_kernel<<<(unsigned)grid, 256, (p.SP + 2 * Q) * sizeof(float), st>>>(
+        pool_tail_bwd_bf16_kernel<<<(unsigned)grid, 256, (H + p.SP + 2 * Q) * sizeof(float), st>>>(
             g, y, eb, alpha, enc->p_w2, dz, gr->dp_w2, gr->dp_b2, gr->dp_b1, n, S, p.SP, H, Q);
         if (int e = check_last("enc.pool_bwd")) return e;
     }
