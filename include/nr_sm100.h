@@ -196,8 +196,10 @@ int nr_tc_gemm_tn(const void* A, int32_t Mo, int64_t lda, const void* B, int32_t
  * GEMMs run on tcgen05 tensor cores (bf16 operands, fp32 accumulation in TMEM); softmax-like
  * normalisations, tanh and all reductions are fp32.  `mask` (n,S) or NULL is used both as the MHSA
  * key mask and as the pooling mask (NRMS.py:56-57).  `save` keeps the bf16 activations for backward
- * (opaque, caller owned, nr_title_encoder_save_bytes); `ws` is scratch. */
-enum { NR_ENC_MHSA = 0, NR_ENC_CONV = 1 };
+ * (opaque, caller owned, nr_title_encoder_save_bytes); `ws` is scratch.
+ *   NR_ENC_POOL: dense rows (n,S,H) -> AttentionPooling only (model_utils.py:7-31): NAML's view
+ *                attention (NAML.py:74) and user pooling (NAML.py:91-96); Dm must equal H. */
+enum { NR_ENC_MHSA = 0, NR_ENC_CONV = 1, NR_ENC_POOL = 2 };
 typedef struct nr_title_encoder {
     int32_t kind, S, Dm, H, Q, heads;
     const float* w[3];      /* MHSA: W_Q, W_K, W_V (H,Dm);  CONV: w[0] = Conv1d.weight (H,Dm,3) */

@@ -42,7 +42,7 @@ class NrTitleEncoderGrads(C.Structure):
                 ('dp_w2', C.c_void_p), ('dp_b2', C.c_void_p), ('dtable', C.c_void_p), ('dx_dense', C.c_void_p)]
 
 
-ENC_MHSA, ENC_CONV = 0, 1
+ENC_MHSA, ENC_CONV, ENC_POOL = 0, 1, 2
 
 _P, _I32, _I64, _F, _U64, _SZ = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_uint64, C.c_size_t
 _R = C.POINTER(NrRows)

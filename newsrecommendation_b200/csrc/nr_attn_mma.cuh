@@ -110,6 +110,13 @@ __device__ __forceinline__ void mm_32xn(float (&c)[2][NT][4], const uint32_t (&a
             for (int ks = 0; ks < 2; ++ks) mma16816(c[mt][nt], a[mt][ks], b[nt][ks]);
         }
 }
+// exp(x * scale) as one FMUL + MUFU.EX2: the caller passes c = scale * log2(e)
+__device__ __forceinline__ float exp2_fast(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // quad reduction: lanes 4g..4g+3 hold partial sums of the same rows
 __device__ __forceinline__ float quad_sum(float v) {
     v += __shfl_xor_sync(0xffffffffu, v, 1);
@@ -168,7 +175,7 @@ struct Cfg {
 __host__ __device__ constexpr size_t fwd_smem_per_warp(int DK) { return (size_t)2 * 3 * TILE * 2 + (size_t)32 * DK * 4; }
 __host__ __device__ constexpr size_t bwd_smem_per_warp(int DK) { return (size_t)2 * 4 * TILE * 2 + (size_t)32 * DK * 4 + 64 * 4; }
 
-template <int DK>
+template <int DK, bool MASK>
 static __global__ void __launch_bounds__(128)
 attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
                     int64_t items, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed) {
@@ -177,6 +184,7 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int t = lane & 3;
     const int H = heads * DK;
+    const float sl2 = scale * 1.4426950408889634f;
     uint8_t* base = smem_raw + warp * fwd_smem_per_warp(DK);
     bf16* buf = (bf16*)base;                       // 2 stages x (Q | K | V)
     float* Os = (float*)(buf + 6 * TILE);
@@ -207,7 +215,7 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 const int col = nt * 8 + 2 * t + e;
-                mk[nt][e] = col < S ? (key_mask ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
+                mk[nt][e] = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
             }
         cp_async_wait<1>();
         __syncwarp();
@@ -227,7 +235,8 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 #pragma unroll
                 for (int e = 0; e < 4; ++e) {
                     const float m = mk[nt][e & 1];
-                    float p = __expf(acc[mt][nt][e] * scale) * m;
+                    float p = exp2_fast(acc[mt][nt][e] * sl2);
+                    if (MASK) p *= m;
                     p = m != 0.f ? p : 0.f;                 // select, not a branch (inf * 0 guard for pad columns)
                     acc[mt][nt][e] = p;
                     z[mt][e >> 1] += p;
@@ -258,7 +267,7 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     }
 }
 
-template <int DK>
+template <int DK, bool MASK>
 static __global__ void __launch_bounds__(128)
 attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
                     bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale) {
@@ -267,6 +276,7 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
     const int H = heads * DK;
+    const float sl2 = scale * 1.4426950408889634f;
     uint8_t* base = smem_raw + warp * bwd_smem_per_warp(DK);
     bf16* buf = (bf16*)base;                       // 2 stages x (Q | K | V | dO)
     float* Os = (float*)(buf + 8 * TILE);
@@ -302,14 +312,14 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 const int col = nt * 8 + 2 * t + e;
-                mcol[nt][e] = col < S ? (key_mask ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
+                mcol[nt][e] = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
             }
 #pragma unroll
         for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int row = mt * 16 + g + 8 * h;
-                mrow[mt][h] = row < S ? (key_mask ? __ldg(key_mask + seq * S + row) : 1.f) : 0.f;
+                mrow[mt][h] = row < S ? (MASK ? __ldg(key_mask + seq * S + row) : 1.f) : 0.f;
             }
         cp_async_wait<1>();
         __syncwarp();
@@ -333,7 +343,8 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 #pragma unroll
                     for (int e = 0; e < 4; ++e) {
                         const float m = mcol[nt][e & 1];
-                        float p = __expf(s[mt][nt][e] * scale) * m;
+                        float p = exp2_fast(s[mt][nt][e] * sl2);
+                        if (MASK) p *= m;
                         p = m != 0.f ? p : 0.f;
                         s[mt][nt][e] = p;
                         z[mt][e >> 1] += p;
@@ -392,8 +403,9 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
                     for (int e = 0; e < 4; ++e) {
                         const float m = mrow[mt][e >> 1];
                         const float zv = zi[nt][e & 1];
-                        float a = __expf(s[mt][nt][e] * scale) * (m * zv);
-                        a = (m * zv != 0.f) ? a : 0.f;
+                        const float mz = MASK ? m * zv : (m != 0.f ? zv : 0.f);
+                        float a = exp2_fast(s[mt][nt][e] * sl2) * mz;
+                        a = mz != 0.f ? a : 0.f;
                         s[mt][nt][e] = a;
                         da[mt][nt][e] = a * (da[mt][nt][e] - ri[nt][e & 1]);
                     }

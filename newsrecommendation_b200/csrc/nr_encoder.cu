@@ -44,7 +44,7 @@ struct EpiTanhLogit {
 
 // dY (bf16) = (dz . W1 + alpha_s g) [* output-dropout mask]; pad rows zero.  nc % 4 == 0 (H % 8 == 0).
 struct EpiPoolDx {
-    bf16* dY; int64_t ld; const float* alpha; const float* g; int S, SP, H;
+    bf16* dY; float* dx32; int64_t ld; const float* alpha; const float* g; int S, SP, H;
     uint32_t thr; float dscale; uint64_t seed;
     int64_t seq; int s; float a;
     __device__ __forceinline__ void begin(int64_t row) {
@@ -54,6 +54,7 @@ struct EpiPoolDx {
     __device__ __forceinline__ void end(int64_t) {}
     __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
         bf16* out = dY + row * ld + col0;
+        float* out32 = dx32 ? dx32 + (seq * S + s) * ld + col0 : nullptr;   // POOL kind: fp32 (n,S,H), no pad rows
         const bool real = s < S;
         const float* gr = g + seq * H + col0;
         const uint64_t e0 = (uint64_t)((seq * S + s) * H + col0);
@@ -67,7 +68,8 @@ struct EpiPoolDx {
                                     fmaf(a, gv.w, v[4 * j + 3]));
                     if (thr) t = dropout4(t, e0 + 4 * j, seed, NR_STREAM_OUT, thr, dscale);
                 }
-                st_bf4(out + 4 * j, t);
+                if (out32) { if (real) *(float4*)(out32 + 4 * j) = t; }
+                else st_bf4(out + 4 * j, t);
             }
         }
     }
@@ -150,8 +152,9 @@ struct Plan {
 
 Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     Plan p;
-    p.SP = round_up(e->S + 1, 32);
-    p.ldx = round_up(e->Dm + 1, 64);
+    const bool pool = e->kind == NR_ENC_POOL;
+    p.SP = pool ? e->S : round_up(e->S + 1, 32);
+    p.ldx = pool ? e->H : round_up(e->Dm + 1, 64);
     p.Kp = round_up(e->Dm, 64);
     p.HK = round_up(e->H, 64);
     p.QK = round_up(e->Q, 64);
@@ -161,10 +164,10 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     const int taps = e->kind == NR_ENC_MHSA ? 1 : 3;
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o += (bytes + 1023) & ~size_t(1023); return r; };
-    p.o_wb = take((size_t)p.Nw * taps * p.Kp * 2);
+    p.o_wb = take(pool ? 0 : (size_t)p.Nw * taps * p.Kp * 2);
     p.o_w1b = take((size_t)e->Q * p.HK * 2);
     p.o_bias = take((size_t)3 * e->H * 4);
-    p.o_xb = take((size_t)p.R * p.ldx * 2);
+    p.o_xb = take(pool ? 0 : (size_t)p.R * p.ldx * 2);
     p.o_qkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
     p.o_y = take((size_t)p.R * e->H * 2);
     p.o_e = take((size_t)p.R * e->Q * 2);
@@ -173,18 +176,18 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     p.save_bytes = o;
     o = 0;
     p.o_dz = take((size_t)p.R * e->Q * 2);
-    p.o_dy = take((size_t)p.R * e->H * 2);
+    p.o_dy = take(pool ? 0 : (size_t)p.R * e->H * 2);
     p.o_dqkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
     p.o_w1t = take((size_t)e->H * p.QK * 2);
-    p.o_wt = take(e->kind == NR_ENC_MHSA ? (size_t)e->Dm * p.K3 * 2 : (size_t)e->Dm * 3 * p.HK * 2);
+    p.o_wt = take(pool ? 0 : (e->kind == NR_ENC_MHSA ? (size_t)e->Dm * p.K3 * 2 : (size_t)e->Dm * 3 * p.HK * 2));
     p.ws_bytes = o;
     return p;
 }
 
 int validate(const nr_title_encoder_t* e, const char* who) {
     NR_REQUIRE(e != nullptr, "%s: enc is NULL", who);
-    NR_REQUIRE(e->kind == NR_ENC_MHSA || e->kind == NR_ENC_CONV, "%s: bad kind %d", who, e->kind);
-    NR_REQUIRE(e->S >= 1 && e->S <= 64, "%s: S=%d outside [1,64]", who, e->S);
+    NR_REQUIRE(e->kind >= NR_ENC_MHSA && e->kind <= NR_ENC_POOL, "%s: bad kind %d", who, e->kind);
+    NR_REQUIRE(e->S >= 1 && (e->S <= 64 || e->kind == NR_ENC_POOL) && e->S <= 4096, "%s: S=%d outside the envelope", who, e->S);
     NR_REQUIRE(e->Dm >= 4 && (e->Dm & 3) == 0, "%s: Dm=%d must be a positive multiple of 4", who, e->Dm);
     NR_REQUIRE(e->H >= 8 && (e->H & 7) == 0, "%s: H=%d must be a positive multiple of 8", who, e->H);
     NR_REQUIRE(e->Q >= 8 && (e->Q & 7) == 0 && e->Q <= 256, "%s: Q=%d must be a multiple of 8 in [8,256]", who, e->Q);
@@ -193,9 +196,12 @@ int validate(const nr_title_encoder_t* e, const char* who) {
     if (e->kind == NR_ENC_MHSA) {
         NR_REQUIRE(e->heads >= 1 && e->H % e->heads == 0, "%s: H=%d not divisible by heads=%d", who, e->H, e->heads);
         for (int i = 0; i < 3; ++i) NR_REQUIRE(e->w[i] && e->b[i], "%s: W_Q/W_K/W_V parameter is NULL", who);
-    } else {
+    } else if (e->kind == NR_ENC_CONV) {
         NR_REQUIRE(e->w[0] && e->b[0], "%s: Conv1d parameter is NULL", who);
         NR_REQUIRE(e->out_drop_p == 0.f, "%s: CONV encoder has no output dropout", who);
+    } else {
+        NR_REQUIRE(e->Dm == e->H, "%s: POOL kind needs Dm == H (got %d, %d)", who, e->Dm, e->H);
+        NR_REQUIRE(e->out_drop_p == 0.f, "%s: POOL kind has no output dropout", who);
     }
     return 0;
 }
@@ -230,41 +236,45 @@ int launch_attn_bwd(const bf16* qkv, const float* mask, const bf16* dctx, bf16* 
     return check_last("enc.attn_bwd");
 }
 // warp-level tensor-core attention (S <= 31 => pitch 32, head dim <= 32)
-template <int DK>
+template <int DK, bool MASK>
 int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
                         uint64_t seed, cudaStream_t st) {
     const size_t smem = 4 * amma::fwd_smem_per_warp(DK);
-    NR_CUDA(cudaFuncSetAttribute(amma::attn_fwd_mma_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    auto kern = amma::attn_fwd_mma_kernel<DK, MASK>;
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t items = n * heads;
     NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
     int64_t grid = (items + 3) / 4;
     int per_sm = 1;
-    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, amma::attn_fwd_mma_kernel<DK>, 128, smem));
+    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
     if (per_sm < 1) per_sm = 1;
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;    // persistent: one wave
     ProfScope ps("enc.attn_fwd", st);
-    amma::attn_fwd_mma_kernel<DK><<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads,
-                                                                    1.0f / sqrtf((float)DK), p > 0.f ? drop_threshold(p) : 0u,
-                                                                    p > 0.f ? 1.f / (1.f - p) : 1.f, seed);
+    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads, 1.0f / sqrtf((float)DK),
+                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed);
     return check_last("enc.attn_fwd");
 }
-template <int DK>
+template <int DK, bool MASK>
 int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
                         cudaStream_t st) {
     const size_t smem = 4 * amma::bwd_smem_per_warp(DK);
-    NR_CUDA(cudaFuncSetAttribute(amma::attn_bwd_mma_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    auto kern = amma::attn_bwd_mma_kernel<DK, MASK>;
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t items = n * heads;
     NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
     int64_t grid = (items + 3) / 4;
     int per_sm = 1;
-    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, amma::attn_bwd_mma_kernel<DK>, 128, smem));
+    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
     if (per_sm < 1) per_sm = 1;
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
     ProfScope ps("enc.attn_bwd", st);
-    amma::attn_bwd_mma_kernel<DK><<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads,
-                                                                    1.0f / sqrtf((float)DK));
+    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
     return check_last("enc.attn_bwd");
 }
+#define NR_MMA_FWD(DKV) (mask ? launch_attn_fwd_mma<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, st) \
+                              : launch_attn_fwd_mma<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, st))
+#define NR_MMA_BWD(DKV) (mask ? launch_attn_bwd_mma<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st) \
+                              : launch_attn_bwd_mma<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))
 
 #define NR_ENC_DISPATCH_DK(dk, CALL)                                                   \
     switch (dk) {                                                                      \
@@ -279,10 +289,10 @@ int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, 
                uint64_t seed, cudaStream_t st) {
     if (SP == 32) {
         switch (dk) {
-            case 8: return launch_attn_fwd_mma<8>(qkv, mask, ctx, n, S, heads, p, seed, st);
-            case 16: return launch_attn_fwd_mma<16>(qkv, mask, ctx, n, S, heads, p, seed, st);
-            case 20: return launch_attn_fwd_mma<20>(qkv, mask, ctx, n, S, heads, p, seed, st);
-            case 32: return launch_attn_fwd_mma<32>(qkv, mask, ctx, n, S, heads, p, seed, st);
+            case 8: return NR_MMA_FWD(8);
+            case 16: return NR_MMA_FWD(16);
+            case 20: return NR_MMA_FWD(20);
+            case 32: return NR_MMA_FWD(32);
             default: break;
         }
     }
@@ -292,10 +302,10 @@ int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv,
                int dk, cudaStream_t st) {
     if (SP == 32) {
         switch (dk) {
-            case 8: return launch_attn_bwd_mma<8>(qkv, mask, dctx, dqkv, n, S, heads, st);
-            case 16: return launch_attn_bwd_mma<16>(qkv, mask, dctx, dqkv, n, S, heads, st);
-            case 20: return launch_attn_bwd_mma<20>(qkv, mask, dctx, dqkv, n, S, heads, st);
-            case 32: return launch_attn_bwd_mma<32>(qkv, mask, dctx, dqkv, n, S, heads, st);
+            case 8: return NR_MMA_BWD(8);
+            case 16: return NR_MMA_BWD(16);
+            case 20: return NR_MMA_BWD(20);
+            case 32: return NR_MMA_BWD(32);
             default: break;
         }
     }
@@ -340,8 +350,14 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     float* alpha = (float*)(sv + p.o_alpha);
     float* logits = (float*)(sv + p.o_logits);
 
+    const bool pool = enc->kind == NR_ENC_POOL;
+    if (pool) {
+        NR_REQUIRE(rows->mode == NR_ROWS_DENSE && rows->drop_p == 0.f, "%s: POOL kind takes dense rows without dropout", who);
+        xb = y;                     // the staged input IS the pooling input
+    }
     // 1. weights -> bf16 GEMM operands
-    if (enc->kind == NR_ENC_MHSA) {
+    if (pool) {
+    } else if (enc->kind == NR_ENC_MHSA) {
         if (int e = pack(PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3}, wb, st)) return e;
         for (int i = 0; i < 3; ++i)
             NR_CUDA(cudaMemcpyAsync(bias_cat + (size_t)i * H, enc->b[i], (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
@@ -364,7 +380,8 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     }
     // 3. token mixer
     const int one = 0;
-    if (enc->kind == NR_ENC_MHSA) {
+    if (pool) {
+    } else if (enc->kind == NR_ENC_MHSA) {
         if (int e = gemm_tc(xb, p.R, Dm, p.ldx, wb, 3 * H, p.Kp, 1, &one, p.R,
                             TcEpiBiasBf16{qkv, 3 * H, bias_cat, 3 * H}, st, "enc.qkv"))
             return e;
@@ -414,12 +431,13 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     bf16* dqkv = (bf16*)(wsb + p.o_dqkv);
     bf16* w1t = (bf16*)(wsb + p.o_w1t);
     bf16* wt = (bf16*)(wsb + p.o_wt);
+    const bool pool = enc->kind == NR_ENC_POOL;
     const bool want_dx = gr->dtable || gr->dx_dense;
     const int one = 0;
 
     // transposed weights for the dX GEMMs
     if (int e = pack(PackArgs{enc->p_w1, nullptr, nullptr, 1, Q, H, 0, H, p.QK, 1}, w1t, st)) return e;
-    if (want_dx) {
+    if (want_dx && !pool) {
         if (enc->kind == NR_ENC_MHSA) {
             if (int e = pack(PackArgs{enc->w[0], enc->w[1], enc->w[2], 1, H, Dm, 0, Dm, p.K3, 3}, wt, st)) return e;
         } else {
@@ -437,12 +455,13 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     // 2. dW1 (Q,H) += dz^T . y
     if (int e = gemm_tc_tn(dz, Q, Q, y, H, H, p.R, 1, &one, TnEpiPlain{gr->dp_w1, H, 0}, st, "enc.dw1")) return e;
     // 3. dY = dz . W1 + alpha g   (output-dropout mask re-applied for MHSA)
-    {
-        EpiPoolDx ep{dy, H, alpha, g, S, p.SP, H,
+    if (!pool || want_dx) {
+        EpiPoolDx ep{dy, pool ? gr->dx_dense : nullptr, H, alpha, g, S, p.SP, H,
                      enc->out_drop_p > 0.f ? drop_threshold(enc->out_drop_p) : 0u,
                      enc->out_drop_p > 0.f ? 1.f / (1.f - enc->out_drop_p) : 1.f, rows->seed, 0, 0, 0.f};
         if (int e = gemm_tc(dz, p.R, Q, Q, w1t, H, p.QK, 1, &one, p.R, ep, st, "enc.pool_dx")) return e;
     }
+    if (pool) return 0;
     const RowsView xv = make_rows_view(rows, n, S, Dm);
     if (enc->kind == NR_ENC_MHSA) {
         if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st)) return e;

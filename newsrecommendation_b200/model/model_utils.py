@@ -32,8 +32,9 @@ class AttentionPooling(nn.Module):
         self.prec = prec
 
     def forward(self, x, attn_mask=None):
-        # stand-alone pooling (NAML view / user pooling: a few thousand rows) always runs the fp32 kernels;
-        # in bf16 mode the title-level pooling is part of the fused title encoder (ops.title_encoder)
+        if self.prec == L.PREC_BF16:      # tensor-core path (title-level pooling is fused into ops.title_encoder)
+            return ops.title_encoder(L.ENC_POOL, x, None, attn_mask, (), self._p(), mode=L.ROWS_DENSE,
+                                     S=x.shape[1], Dm=x.shape[2])
         return ops.attention_pooling(x, attn_mask, self.att_fc1.weight, self.att_fc1.bias,
                                      self.att_fc2.weight, self.att_fc2.bias, L.PREC_FP32)
 

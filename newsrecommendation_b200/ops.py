@@ -328,7 +328,7 @@ class TitleEncoderFn(torch.autograd.Function):
         n = rows.n
         ws_ = [None if t is None else L.f32(t) for t in (w0, b0, w1, b1, w2, b2)]
         pool = [L.f32(t) for t in (p_w1, p_b1, p_w2, p_b2)]
-        H, Q = ws_[0].shape[0], pool[0].shape[0]
+        H, Q = (ws_[0].shape[0] if ws_[0] is not None else Dm), pool[0].shape[0]
         mask = None if mask is None else L.f32(mask)
         dev = pool[0].device
         enc = L.NrTitleEncoder()
