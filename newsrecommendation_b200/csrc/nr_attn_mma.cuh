@@ -3,28 +3,43 @@
 //
 // One title is S <= 31 tokens and a head is DK <= 32 wide: the whole (32 x 32) score tile of one
 // (title, head) lives in ONE warp's registers, so each product is a handful of
-// mma.sync.m16n8k16 (bf16 in, fp32 accumulate) instead of ~10^3 scalar FMAs per lane.  tcgen05 is
-// the wrong tool at this size: its smallest tile is 128 x N x 16 out of shared memory into TMEM, four
-// titles per instruction with 3/4 of the tile wasted on cross-title blocks, and a TMEM round trip per
-// product; the warp-level path keeps P, dS and all intermediates in registers.
+// mma.sync.m16n8k16 / m16n8k8 (bf16 in, fp32 accumulate) instead of ~10^3 scalar FMAs per lane.
+// tcgen05 is the wrong tool at this size: its smallest tile is 128 x N x 16 out of shared memory into
+// TMEM, four titles per instruction with 3/4 of the tile wasted on cross-title blocks, and a TMEM round
+// trip per product; the warp-level path keeps P, dS and all intermediates in registers.
 //
 //   forward : S = Q K^T,  P = exp(S/sqrt(dk)) * keymask,  O = (P / (rowsum P + eps)) V   [+ dropout]
 //   backward: both orientations are computed (S and S^T, dA and dA^T) so that every operand of the
 //             five gradient products is already in MMA fragment layout: dQ = dS K, dK = dS^T Q, dV = A^T dO.
 //
 // Layout: qkv (n*32, 3H) bf16 with q | k | v column blocks, head h at columns h*DK; pitch SP = 32.
+// Shared tiles are [32 rows][PITCH] bf16 with PITCH chosen per head width so that ldmatrix is bank
+// conflict free (48-byte rows for DK = 16/20, 80-byte rows for DK = 32, 16-byte rows for DK = 8) and the
+// k extent is covered by DK/16 full k-steps plus one 8-wide half step (m16n8k8) when DK % 16 != 0.
 #pragma once
 #include "nr_enc_kernels.cuh"
 
 namespace nr {
 namespace amma {
 
-constexpr int PITCH = 40;                 // bf16 elements per shared-memory row (80 B: conflict-free ldmatrix)
-constexpr int TILE = 32 * PITCH;          // one 32-row operand tile
+template <int DK>
+struct Cfg {
+    static_assert(DK == 8 || DK == 16 || DK == 20 || DK == 32, "head width outside the compiled set");
+    static constexpr int KF = DK / 16;                      // full 16-wide k-steps of Q K^T
+    static constexpr int KH = (DK % 16) ? 1 : 0;            // one 8-wide half step (DK % 16 <= 8)
+    static constexpr int NT = (DK + 7) / 8;                 // n-tiles of the (32 x DK) outputs
+    static constexpr int PITCH = DK == 32 ? 40 : (DK == 8 ? 8 : 24);
+    static constexpr int TILE = 32 * PITCH;
+    static constexpr int SLOTS = DK / 4;                    // 8-byte chunks per lane per tile
+};
 
 __device__ __forceinline__ void ldsm_x4(const bf16* p, uint32_t* r) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(tc::smem_u32(p)));
+}
+__device__ __forceinline__ void ldsm_x2(const bf16* p, uint32_t* r) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x2.shared.b16 {%0,%1}, [%2];"
+                 : "=r"(r[0]), "=r"(r[1]) : "r"(tc::smem_u32(p)));
 }
 __device__ __forceinline__ void ldsm_x2_trans(const bf16* p, uint32_t* r) {
     asm volatile("ldmatrix.sync.aligned.m8n8.x2.trans.shared.b16 {%0,%1}, [%2];"
@@ -35,37 +50,71 @@ __device__ __forceinline__ void mma16816(float* c, const uint32_t* a, const uint
                  : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                  : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]));
 }
+__device__ __forceinline__ void mma1688(float* c, const uint32_t* a, uint32_t b) {
+    asm volatile("mma.sync.aligned.m16n8k8.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(b));
+}
 
-// A fragments (row-major 32 x 16*KS tile in smem): a[mt][ks][4]
-template <int KS>
-__device__ __forceinline__ void load_a(const bf16* tile, int lane, uint32_t (&a)[2][KS][4]) {
+// Fragments of a row-major (32 x DK) shared tile X used as the A operand (rows = m, cols = k) and as the
+// "row" B operand (B = X^T: rows = n, cols = k).  Full k-steps + optional half step.
+template <int DK>
+struct Frag {
+    uint32_t a[2][Cfg<DK>::KF + 1][4];      // [mt][ks]: ks == KF is the half step (2 registers used)
+    uint32_t b[4][Cfg<DK>::KF + 1][2];      // [nt][ks]: half step uses b[..][KF][0]
+};
+template <int DK>
+__device__ __forceinline__ void load_a(const bf16* tile, int lane, Frag<DK>& f) {
+    constexpr int P = Cfg<DK>::PITCH, KF = Cfg<DK>::KF, KH = Cfg<DK>::KH;
+    const int row = (lane & 7) + ((lane >> 3) & 1) * 8;
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt) {
+#pragma unroll
+        for (int ks = 0; ks < KF; ++ks) ldsm_x4(tile + (mt * 16 + row) * P + ks * 16 + (lane >> 4) * 8, f.a[mt][ks]);
+        if (KH) ldsm_x2(tile + (mt * 16 + row) * P + KF * 16, f.a[mt][KF]);
+    }
+}
+template <int DK>
+__device__ __forceinline__ void load_b_rows(const bf16* tile, int lane, Frag<DK>& f) {
+    constexpr int P = Cfg<DK>::PITCH, KF = Cfg<DK>::KF, KH = Cfg<DK>::KH;
+#pragma unroll
+    for (int np = 0; np < 2; ++np) {
+#pragma unroll
+        for (int ks = 0; ks < KF; ++ks) {
+            uint32_t r[4];
+            ldsm_x4(tile + (np * 16 + (lane & 7) + (lane >> 4) * 8) * P + ks * 16 + ((lane >> 3) & 1) * 8, r);
+            f.b[2 * np][ks][0] = r[0]; f.b[2 * np][ks][1] = r[1];
+            f.b[2 * np + 1][ks][0] = r[2]; f.b[2 * np + 1][ks][1] = r[3];
+        }
+        if (KH) {
+            uint32_t r[2];
+            ldsm_x2(tile + (np * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * P + KF * 16, r);
+            f.b[2 * np][KF][0] = r[0];
+            f.b[2 * np + 1][KF][0] = r[1];
+        }
+    }
+}
+// C (32 x 32) += A-fragments . B-row-fragments^T over the DK-wide contraction
+template <int DK>
+__device__ __forceinline__ void mm_32x32(float (&c)[2][4][4], const Frag<DK>& fa, const Frag<DK>& fb) {
+    constexpr int KF = Cfg<DK>::KF, KH = Cfg<DK>::KH;
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
-        for (int ks = 0; ks < KS; ++ks)
-            ldsm_x4(tile + (mt * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * PITCH + ks * 16 + (lane >> 4) * 8, a[mt][ks]);
-}
-// B fragments of X^T for a row-major X (rows = n, cols = k): b[nt][ks][2], nt < 4
-template <int KS>
-__device__ __forceinline__ void load_b_rows(const bf16* tile, int lane, uint32_t (&b)[4][KS][2]) {
+        for (int nt = 0; nt < 4; ++nt) {
 #pragma unroll
-    for (int np = 0; np < 2; ++np)
-#pragma unroll
-        for (int ks = 0; ks < KS; ++ks) {
-            uint32_t r[4];
-            ldsm_x4(tile + (np * 16 + (lane & 7) + (lane >> 4) * 8) * PITCH + ks * 16 + ((lane >> 3) & 1) * 8, r);
-            b[2 * np][ks][0] = r[0]; b[2 * np][ks][1] = r[1];
-            b[2 * np + 1][ks][0] = r[2]; b[2 * np + 1][ks][1] = r[3];
+            for (int ks = 0; ks < KF; ++ks) mma16816(c[mt][nt], fa.a[mt][ks], fb.b[nt][ks]);
+            if (KH) mma1688(c[mt][nt], fa.a[mt][KF], fb.b[nt][KF][0]);
         }
 }
 // B fragments of X for a row-major X (rows = k (32), cols = n): b[nt][ks][2], nt < NT, ks < 2
-template <int NT>
-__device__ __forceinline__ void load_b_cols(const bf16* tile, int lane, uint32_t (&b)[NT][2][2]) {
+template <int DK>
+__device__ __forceinline__ void load_b_cols(const bf16* tile, int lane, uint32_t (&b)[Cfg<DK>::NT][2][2]) {
+    constexpr int P = Cfg<DK>::PITCH;
 #pragma unroll
-    for (int nt = 0; nt < NT; ++nt)
+    for (int nt = 0; nt < Cfg<DK>::NT; ++nt)
 #pragma unroll
         for (int ks = 0; ks < 2; ++ks)
-            ldsm_x2_trans(tile + (ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * PITCH + nt * 8, b[nt][ks]);
+            ldsm_x2_trans(tile + (ks * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * P + nt * 8, b[nt][ks]);
 }
 // (32 x 32) accumulator tile (C layout) -> A fragments of the same matrix, bf16
 __device__ __forceinline__ void c_to_a(const float (&c)[2][4][4], uint32_t (&a)[2][2][4]) {
@@ -87,16 +136,6 @@ __device__ __forceinline__ void zero_c(float (&c)[2][4][4]) {
 #pragma unroll
             for (int e = 0; e < 4; ++e) c[mt][nt][e] = 0.f;
 }
-// C (32 x 32) = A (32 x 16KS) . B^T-fragments
-template <int KS>
-__device__ __forceinline__ void mm_32x32(float (&c)[2][4][4], const uint32_t (&a)[2][KS][4], const uint32_t (&b)[4][KS][2]) {
-#pragma unroll
-    for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-        for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-            for (int ks = 0; ks < KS; ++ks) mma16816(c[mt][nt], a[mt][ks], b[nt][ks]);
-}
 // C (32 x 8NT) = A (32 x 32) . B
 template <int NT>
 __device__ __forceinline__ void mm_32xn(float (&c)[2][NT][4], const uint32_t (&a)[2][2][4], const uint32_t (&b)[NT][2][2]) {
@@ -116,7 +155,6 @@ __device__ __forceinline__ float exp2_fast(float x) {
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
 }
-
 // quad reduction: lanes 4g..4g+3 hold partial sums of the same rows
 __device__ __forceinline__ float quad_sum(float v) {
     v += __shfl_xor_sync(0xffffffffu, v, 1);
@@ -140,46 +178,61 @@ __device__ __forceinline__ void stage_out(const float (&c)[2][NT][4], float* os,
             }
         }
 }
-// asynchronous copy of the (32 x DK) head slice of one operand into a shared tile (columns >= DK stay
-// zero).  cp.async: the copies of item i+1 are in flight while item i is computed (double buffer).
+
+// Per-lane copy slots: a (32 x DK) bf16 head slice is 32*DK/4 8-byte chunks = DK/4 chunks per lane.
+// Slot i of lane l is chunk idx = 32 i + l: row s = idx / (DK/4), 4-column group q4 = idx % (DK/4).
+// The row and the shared/global element offsets are computed ONCE per kernel (no divisions in the loop).
 template <int DK>
-__device__ __forceinline__ void prefetch_tile(bf16* tile, const bf16* src, int64_t ld, int lane) {
+struct Slots {
+    int s[Cfg<DK>::SLOTS];          // row
+    int so[Cfg<DK>::SLOTS];         // element offset in a shared tile
+    int c[Cfg<DK>::SLOTS];          // column (q4*4)
+    __device__ __forceinline__ void init(int lane) {
 #pragma unroll
-    for (int it = 0; it < DK / 4; ++it) {
-        const int idx = it * 32 + lane;
-        const int s = idx / (DK / 4), q4 = idx % (DK / 4);
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(tc::smem_u32(tile + s * PITCH + q4 * 4)),
-                     "l"(src + (int64_t)s * ld + q4 * 4) : "memory");
+        for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
+            const int idx = i * 32 + lane;
+            s[i] = idx / Cfg<DK>::SLOTS;
+            c[i] = (idx - s[i] * Cfg<DK>::SLOTS) * 4;
+            so[i] = s[i] * Cfg<DK>::PITCH + c[i];
+        }
     }
+};
+// asynchronous copy of a head slice into a shared tile (columns >= DK stay zero): the copies of item
+// i+1 are in flight while item i is computed (double buffer)
+template <int DK>
+__device__ __forceinline__ void prefetch_tile(bf16* tile, const bf16* src, int ld, const Slots<DK>& sl) {
+#pragma unroll
+    for (int i = 0; i < Cfg<DK>::SLOTS; ++i)
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(tc::smem_u32(tile + sl.so[i])),
+                     "l"(src + sl.s[i] * ld + sl.c[i]) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 // fp32 staging tile -> bf16 rows of dst (rows >= S written as zero)
 template <int DK>
-__device__ __forceinline__ void store_tile(bf16* dst, int64_t ld, const float* os, int S, int lane) {
-    for (int idx = lane; idx < 32 * (DK / 4); idx += 32) {
-        const int s = idx / (DK / 4), q4 = idx % (DK / 4);
+__device__ __forceinline__ void store_tile(bf16* dst, int ld, const float* os, int S, const Slots<DK>& sl) {
+#pragma unroll
+    for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (s < S) v = *(const float4*)(os + s * DK + q4 * 4);
-        st_bf4(dst + (int64_t)s * ld + q4 * 4, v);
+        if (sl.s[i] < S) v = *(const float4*)(os + sl.s[i] * DK + sl.c[i]);
+        st_bf4(dst + sl.s[i] * ld + sl.c[i], v);
     }
 }
 
-template <int DK>
-struct Cfg {
-    static constexpr int KS = (DK + 15) / 16;   // k-steps of Q K^T
-    static constexpr int NT = (DK + 7) / 8;     // n-tiles of the (32 x DK) outputs
-};
-
-__host__ __device__ constexpr size_t fwd_smem_per_warp(int DK) { return (size_t)2 * 3 * TILE * 2 + (size_t)32 * DK * 4; }
-__host__ __device__ constexpr size_t bwd_smem_per_warp(int DK) { return (size_t)2 * 4 * TILE * 2 + (size_t)32 * DK * 4 + 64 * 4; }
+__host__ __device__ constexpr int pitch_of(int DK) { return DK == 32 ? 40 : (DK == 8 ? 8 : 24); }
+__host__ __device__ constexpr size_t fwd_smem_per_warp(int DK) {
+    return (size_t)2 * 3 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 4;
+}
+__host__ __device__ constexpr size_t bwd_smem_per_warp(int DK) {
+    return (size_t)2 * 4 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 4 + 64 * 4;
+}
 
 template <int DK, bool MASK>
 static __global__ void __launch_bounds__(128)
 attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
                     int64_t items, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed) {
-    constexpr int KS = Cfg<DK>::KS, NT = Cfg<DK>::NT;
+    constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int t = lane & 3;
@@ -190,15 +243,17 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     float* Os = (float*)(buf + 6 * TILE);
     for (int i = lane; i < 6 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
+    Slots<DK> sl;
+    sl.init(lane);
     const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
     int item = (int)blockIdx.x * 4 + warp;
     auto issue = [&](int it, int stage) {
         const int sq = it / heads;
         const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + (it - sq * heads) * DK;
         bf16* b = buf + stage * 3 * TILE;
-        prefetch_tile<DK>(b, src, 3 * H, lane);
-        prefetch_tile<DK>(b + TILE, src + H, 3 * H, lane);
-        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, 3 * H, lane);
+        prefetch_tile<DK>(b, src, 3 * H, sl);
+        prefetch_tile<DK>(b + TILE, src + H, 3 * H, sl);
+        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, 3 * H, sl);
         cp_async_commit();
     };
     if (item < items) issue(item, 0);
@@ -222,10 +277,10 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         float acc[2][4][4];
         zero_c(acc);
         {
-            uint32_t aq[2][KS][4], bk[4][KS][2];
-            load_a<KS>(Qs, lane, aq);
-            load_b_rows<KS>(Ks, lane, bk);
-            mm_32x32<KS>(acc, aq, bk);
+            Frag<DK> fq, fk;
+            load_a<DK>(Qs, lane, fq);
+            load_b_rows<DK>(Ks, lane, fk);
+            mm_32x32<DK>(acc, fq, fk);
         }
         float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
 #pragma unroll
@@ -248,20 +303,21 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             for (int h = 0; h < 2; ++h) inv[mt][h] = 1.f / (quad_sum(z[mt][h]) + kEps);    // model_utils.py:53
         uint32_t ap[2][2][4], bv[NT][2][2];
         c_to_a(acc, ap);
-        load_b_cols<NT>(Vs, lane, bv);
+        load_b_cols<DK>(Vs, lane, bv);
         float o[2][NT][4];
         mm_32xn<NT>(o, ap, bv);
         stage_out<NT, DK>(o, Os, lane, inv[0][0], inv[0][1], inv[1][0], inv[1][1]);
         __syncwarp();
         bf16* dst = ctx + seq * 32 * H + head * DK;
-        for (int idx = lane; idx < 32 * (DK / 4); idx += 32) {
-            const int s = idx / (DK / 4), q4 = idx % (DK / 4);
+#pragma unroll
+        for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
+            const int s = sl.s[i], c = sl.c[i];
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (s < S) {
-                v = *(const float4*)(Os + s * DK + q4 * 4);
-                if (thr) v = dropout4(v, (uint64_t)((seq * S + s) * H + head * DK + q4 * 4), seed, NR_STREAM_OUT, thr, dscale);
+                v = *(const float4*)(Os + s * DK + c);
+                if (thr) v = dropout4(v, (uint64_t)((seq * S + s) * H + head * DK + c), seed, NR_STREAM_OUT, thr, dscale);
             }
-            st_bf4(dst + (int64_t)s * H + q4 * 4, v);
+            st_bf4(dst + s * H + c, v);
         }
         __syncwarp();
     }
@@ -271,7 +327,7 @@ template <int DK, bool MASK>
 static __global__ void __launch_bounds__(128)
 attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
                     bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale) {
-    constexpr int KS = Cfg<DK>::KS, NT = Cfg<DK>::NT;
+    constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, t = lane & 3;
@@ -284,6 +340,8 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     float* rds = zinv + 32;
     for (int i = lane; i < 8 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
+    Slots<DK> sl;
+    sl.init(lane);
     const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
     int item = (int)blockIdx.x * 4 + warp;
     auto issue = [&](int it, int stage) {
@@ -291,10 +349,10 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         const int hd = it - sq * heads;
         const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + hd * DK;
         bf16* b = buf + stage * 4 * TILE;
-        prefetch_tile<DK>(b, src, 3 * H, lane);
-        prefetch_tile<DK>(b + TILE, src + H, 3 * H, lane);
-        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, 3 * H, lane);
-        prefetch_tile<DK>(b + 3 * TILE, dctx + (int64_t)sq * 32 * H + hd * DK, H, lane);
+        prefetch_tile<DK>(b, src, 3 * H, sl);
+        prefetch_tile<DK>(b + TILE, src + H, 3 * H, sl);
+        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, 3 * H, sl);
+        prefetch_tile<DK>(b + 3 * TILE, dctx + (int64_t)sq * 32 * H + hd * DK, H, sl);
         cp_async_commit();
     };
     if (item < items) issue(item, 0);
@@ -329,11 +387,11 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             float s[2][4][4], da[2][4][4];
             zero_c(s); zero_c(da);
             {
-                uint32_t a[2][KS][4], b[4][KS][2];
-                load_a<KS>(Qs, lane, a); load_b_rows<KS>(Ks, lane, b);
-                mm_32x32<KS>(s, a, b);
-                load_a<KS>(Gs, lane, a); load_b_rows<KS>(Vs, lane, b);
-                mm_32x32<KS>(da, a, b);
+                Frag<DK> fa, fb;
+                load_a<DK>(Qs, lane, fa); load_b_rows<DK>(Ks, lane, fb);
+                mm_32x32<DK>(s, fa, fb);
+                load_a<DK>(Gs, lane, fa); load_b_rows<DK>(Vs, lane, fb);
+                mm_32x32<DK>(da, fa, fb);
             }
             float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, rd[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
 #pragma unroll
@@ -370,24 +428,24 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
                         s[mt][nt][e] = s[mt][nt][e] * inv[mt][e >> 1] * (da[mt][nt][e] - rd[mt][e >> 1]);
             uint32_t ads[2][2][4], bk[NT][2][2];
             c_to_a(s, ads);
-            load_b_cols<NT>(Ks, lane, bk);
+            load_b_cols<DK>(Ks, lane, bk);
             float dq[2][NT][4];
             mm_32xn<NT>(dq, ads, bk);
             stage_out<NT, DK>(dq, Os, lane, scale, scale, scale, scale);
         }
         __syncwarp();
-        store_tile<DK>(dst, 3 * H, Os, S, lane);
+        store_tile<DK>(dst, 3 * H, Os, S, sl);
         __syncwarp();
         // ---- key-major pass: S^T = K Q^T, dA^T = V dO^T; dK = dS^T Q / sqrt(dk), dV = A^T dO
         {
             float s[2][4][4], da[2][4][4];
             zero_c(s); zero_c(da);
             {
-                uint32_t a[2][KS][4], b[4][KS][2];
-                load_a<KS>(Ks, lane, a); load_b_rows<KS>(Qs, lane, b);
-                mm_32x32<KS>(s, a, b);
-                load_a<KS>(Vs, lane, a); load_b_rows<KS>(Gs, lane, b);
-                mm_32x32<KS>(da, a, b);
+                Frag<DK> fa, fb;
+                load_a<DK>(Ks, lane, fa); load_b_rows<DK>(Qs, lane, fb);
+                mm_32x32<DK>(s, fa, fb);
+                load_a<DK>(Vs, lane, fa); load_b_rows<DK>(Gs, lane, fb);
+                mm_32x32<DK>(da, fa, fb);
             }
             float zi[4][2], ri[4][2];
 #pragma unroll
@@ -412,19 +470,19 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             uint32_t af[2][2][4], bf[NT][2][2];
             float out[2][NT][4];
             c_to_a(da, af);
-            load_b_cols<NT>(Qs, lane, bf);
+            load_b_cols<DK>(Qs, lane, bf);
             mm_32xn<NT>(out, af, bf);
             stage_out<NT, DK>(out, Os, lane, scale, scale, scale, scale);
             __syncwarp();
-            store_tile<DK>(dst + H, 3 * H, Os, S, lane);
+            store_tile<DK>(dst + H, 3 * H, Os, S, sl);
             __syncwarp();
             c_to_a(s, af);
-            load_b_cols<NT>(Gs, lane, bf);
+            load_b_cols<DK>(Gs, lane, bf);
             mm_32xn<NT>(out, af, bf);
             stage_out<NT, DK>(out, Os, lane, 1.f, 1.f, 1.f, 1.f);
         }
         __syncwarp();
-        store_tile<DK>(dst + 2 * H, 3 * H, Os, S, lane);
+        store_tile<DK>(dst + 2 * H, 3 * H, Os, S, sl);
         __syncwarp();
     }
 }
