@@ -64,13 +64,17 @@ stage_rows_kernel(RowsView x, bf16* __restrict__ xb, int R, int SP, int ldx) {
 }
 
 // ---- weight packing (fp32 Parameters -> bf16 GEMM operands, zero padded) ---------------------------
-// mode 0: out[j][k]          = W_{j / H}[j % H][k]          (3 stacked (H,Dm) matrices -> (3H, ldo))
+// mode 0: out[j][k]          = W_{j / H}[j % H][k]          (3 stacked (H,Dm) matrices -> (3H, ldo));
+//         with biases given, out[j][Dm] = b_{j / H}[j % H]: the product with the ones column of Xb
+//         adds the bias inside the GEMM
+// (mode 2 likewise puts the Conv1d bias at column Dm of the unshifted tap)
 // mode 1: out[c][j]          = W_{j / H}[j % H][c]          (their transpose (Dm, ldo), ldo >= 3H)
 // mode 2: out[o][t*ldt + c]  = w[o][c][t]                   (Conv1d weight (H,Dm,3) -> (H, 3*ldt))
 // mode 3: out[c][u*ldt + o]  = w[o][c][u]                   (conv dX operand (Dm, 3*ldt), ldt >= H)
 struct PackArgs {
     const float* w0; const float* w1; const float* w2;
     int mode, H, Dm, ldt, rows, ldo, nmat;
+    const float* b0; const float* b1; const float* b2;     // optional biases (modes 0 and 2)
 };
 static __global__ void pack_weights_kernel(PackArgs a, bf16* __restrict__ out) {
     const int64_t total = (int64_t)a.rows * a.ldo;
@@ -79,10 +83,13 @@ static __global__ void pack_weights_kernel(PackArgs a, bf16* __restrict__ out) {
         const int r = (int)(t / a.ldo), c = (int)(t - (int64_t)r * a.ldo);
         float v = 0.f;
         if (a.mode == 0) {
+            const int w = r / a.H;
             if (c < a.Dm) {
-                const int w = r / a.H;
                 const float* p = w == 0 ? a.w0 : (w == 1 ? a.w1 : a.w2);
                 v = __ldg(p + (int64_t)(r - w * a.H) * a.Dm + c);
+            } else if (c == a.Dm && a.b0) {
+                const float* p = w == 0 ? a.b0 : (w == 1 ? a.b1 : a.b2);
+                v = __ldg(p + (r - w * a.H));
             }
         } else if (a.mode == 1) {
             if (c < a.nmat * a.H) {
@@ -93,6 +100,7 @@ static __global__ void pack_weights_kernel(PackArgs a, bf16* __restrict__ out) {
         } else if (a.mode == 2) {
             const int tp = c / a.ldt, cc = c - tp * a.ldt;
             if (cc < a.Dm) v = __ldg(a.w0 + ((int64_t)r * a.Dm + cc) * 3 + tp);
+            else if (cc == a.Dm && tp == 1 && a.b0) v = __ldg(a.b0 + r);
         } else {
             const int u = c / a.ldt, o = c - u * a.ldt;
             if (o < a.H) v = __ldg(a.w0 + ((int64_t)o * a.Dm + r) * 3 + u);

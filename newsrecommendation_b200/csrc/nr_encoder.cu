@@ -27,9 +27,9 @@ __device__ __forceinline__ float tanh_fast(float x) {      // MUFU.TANH, rel. er
 struct EpiTanhLogit {
     bf16* E; int64_t lde; const float* b1; const float* w2; const float* b2; float* logits;
     float acc;
-    __device__ __forceinline__ void begin(int64_t) { acc = 0.f; }
-    __device__ __forceinline__ void end(int64_t row) { logits[row] = acc + __ldg(b2); }
-    __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
+    __device__ __forceinline__ void begin(const EpiCtx&, int64_t) { acc = 0.f; }
+    __device__ __forceinline__ void end(const EpiCtx& cx, int64_t row) { if (cx.live) logits[row] = acc + __ldg(b2); }
+    __device__ __forceinline__ void chunk(const EpiCtx& cx, int64_t, int col0, const float* v, int nc) {
         float b[32], w[32], o[32];
         load_bias32(b1, col0, nc, b);
         load_bias32(w2, col0, nc, w);      // zero beyond nc: padded columns add nothing to the logit
@@ -38,7 +38,7 @@ struct EpiTanhLogit {
             o[j] = tanh_fast(v[j] + b[j]);
             acc = fmaf(o[j], w[j], acc);
         }
-        store_bf16_32(E + row * lde + col0, o, nc);
+        store_rows_bf16(cx, E, lde, col0, o, nc);
     }
 };
 
@@ -47,30 +47,36 @@ struct EpiPoolDx {
     bf16* dY; float* dx32; int64_t ld; const float* alpha; const float* g; int S, SP, H;
     uint32_t thr; float dscale; uint64_t seed;
     int64_t seq; int s; float a;
-    __device__ __forceinline__ void begin(int64_t row) {
+    __device__ __forceinline__ void begin(const EpiCtx& cx, int64_t row) {
         seq = row / SP; s = (int)(row - seq * SP);
-        a = s < S ? __ldg(alpha + row) : 0.f;
+        a = (cx.live && s < S) ? __ldg(alpha + row) : 0.f;
     }
-    __device__ __forceinline__ void end(int64_t) {}
-    __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
-        bf16* out = dY + row * ld + col0;
-        float* out32 = dx32 ? dx32 + (seq * S + s) * ld + col0 : nullptr;   // POOL kind: fp32 (n,S,H), no pad rows
-        const bool real = s < S;
+    __device__ __forceinline__ void end(const EpiCtx&, int64_t) {}
+    __device__ __forceinline__ void chunk(const EpiCtx& cx, int64_t, int col0, const float* v, int nc) {
+        const bool real = cx.live && s < S;
         const float* gr = g + seq * H + col0;
         const uint64_t e0 = (uint64_t)((seq * S + s) * H + col0);
+        float o[32];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            if (4 * j < nc) {
-                float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (real) {
-                    const float4 gv = ldg4(gr + 4 * j);
-                    t = make_float4(fmaf(a, gv.x, v[4 * j]), fmaf(a, gv.y, v[4 * j + 1]), fmaf(a, gv.z, v[4 * j + 2]),
-                                    fmaf(a, gv.w, v[4 * j + 3]));
-                    if (thr) t = dropout4(t, e0 + 4 * j, seed, NR_STREAM_OUT, thr, dscale);
-                }
-                if (out32) { if (real) *(float4*)(out32 + 4 * j) = t; }
-                else st_bf4(out + 4 * j, t);
+            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (real && 4 * j < nc) {
+                const float4 gv = ldg4(gr + 4 * j);
+                t = make_float4(fmaf(a, gv.x, v[4 * j]), fmaf(a, gv.y, v[4 * j + 1]), fmaf(a, gv.z, v[4 * j + 2]),
+                                fmaf(a, gv.w, v[4 * j + 3]));
+                if (thr) t = dropout4(t, e0 + 4 * j, seed, NR_STREAM_OUT, thr, dscale);
             }
+            o[4 * j] = t.x; o[4 * j + 1] = t.y; o[4 * j + 2] = t.z; o[4 * j + 3] = t.w;
+        }
+        if (dx32) {                 // POOL kind: fp32 (n,S,H) gradient, no pad rows
+            if (real) {
+                float* out32 = dx32 + (seq * S + s) * ld + col0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (4 * j < nc) *(float4*)(out32 + 4 * j) = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
+            }
+        } else {
+            store_rows_bf16(cx, dY, ld, col0, o, nc);     // pad rows are written as zero
         }
     }
 };
@@ -80,13 +86,14 @@ struct EpiPoolDx {
 struct EpiDx {
     float* dx_dense; float* dtable; RowsView x; int SP;
     int64_t seq; int s; int64_t id;
-    __device__ __forceinline__ void begin(int64_t row) {
+    __device__ __forceinline__ void begin(const EpiCtx& cx, int64_t row) {
         seq = row / SP; s = (int)(row - seq * SP);
         id = -1;
+        if (!cx.live) s = x.S;          // rows past the end behave like pad rows
         if (s < x.S && x.mode != NR_ROWS_DENSE) id = x.id_of(seq, s);
     }
-    __device__ __forceinline__ void end(int64_t) {}
-    __device__ __forceinline__ void chunk(int64_t, int col0, const float* v, int nc) {
+    __device__ __forceinline__ void end(const EpiCtx&, int64_t) {}
+    __device__ __forceinline__ void chunk(const EpiCtx&, int64_t, int col0, const float* v, int nc) {
         if (s >= x.S) return;
         if (x.mode != NR_ROWS_DENSE && id == 0) return;
         const int64_t r = seq * x.S + s;
@@ -155,7 +162,7 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     const bool pool = e->kind == NR_ENC_POOL;
     p.SP = pool ? e->S : round_up(e->S + 1, 32);
     p.ldx = pool ? e->H : round_up(e->Dm + 1, 64);
-    p.Kp = round_up(e->Dm, 64);
+    p.Kp = pool ? round_up(e->Dm, 64) : round_up(e->Dm + 1, 64);   // room for the bias column at Dm
     p.HK = round_up(e->H, 64);
     p.QK = round_up(e->Q, 64);
     p.K3 = round_up(3 * e->H, 64);
@@ -342,7 +349,6 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     const int S = enc->S, Dm = enc->Dm, H = enc->H, Q = enc->Q;
     bf16* wb = (bf16*)(sv + p.o_wb);
     bf16* w1b = (bf16*)(sv + p.o_w1b);
-    float* bias_cat = (float*)(sv + p.o_bias);
     bf16* xb = (bf16*)(sv + p.o_xb);
     bf16* qkv = (bf16*)(sv + p.o_qkv);
     bf16* y = (bf16*)(sv + p.o_y);
@@ -358,11 +364,13 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     // 1. weights -> bf16 GEMM operands
     if (pool) {
     } else if (enc->kind == NR_ENC_MHSA) {
-        if (int e = pack(PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3}, wb, st)) return e;
-        for (int i = 0; i < 3; ++i)
-            NR_CUDA(cudaMemcpyAsync(bias_cat + (size_t)i * H, enc->b[i], (size_t)H * 4, cudaMemcpyDeviceToDevice, st));
+        if (int e = pack(PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3, enc->b[0], enc->b[1],
+                                  enc->b[2]}, wb, st))
+            return e;
     } else {
-        if (int e = pack(PackArgs{enc->w[0], nullptr, nullptr, 2, H, Dm, p.Kp, H, 3 * p.Kp, 1}, wb, st)) return e;
+        if (int e = pack(PackArgs{enc->w[0], nullptr, nullptr, 2, H, Dm, p.Kp, H, 3 * p.Kp, 1, enc->b[0], nullptr, nullptr},
+                         wb, st))
+            return e;
     }
     if (int e = pack(PackArgs{enc->p_w1, nullptr, nullptr, 0, Q, H, 0, Q, p.HK, 1}, w1b, st)) return e;
     // 2. stage rows: gather + input dropout + bf16, padded pitch
@@ -382,15 +390,14 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     const int one = 0;
     if (pool) {
     } else if (enc->kind == NR_ENC_MHSA) {
-        if (int e = gemm_tc(xb, p.R, Dm, p.ldx, wb, 3 * H, p.Kp, 1, &one, p.R,
-                            TcEpiBiasBf16{qkv, 3 * H, bias_cat, 3 * H}, st, "enc.qkv"))
+        // K = Dm + 1: the ones column of Xb times the bias column of the packed weights
+        if (int e = gemm_tc(xb, p.R, Dm + 1, p.ldx, wb, 3 * H, p.Kp, 1, &one, p.R, TcEpiStoreBf16{qkv, 3 * H}, st, "enc.qkv"))
             return e;
         if (int e = attn_fwd_b(qkv, enc->mask, y, n, S, p.SP, enc->heads, H / enc->heads, enc->out_drop_p, rows->seed, st))
             return e;
     } else {
         const int sh[3] = {-1, 0, 1};
-        if (int e = gemm_tc(xb, p.R, Dm, p.ldx, wb, H, 3 * p.Kp, 3, sh, p.R, TcEpiBiasBf16{y, H, enc->b[0], H}, st,
-                            "enc.conv"))
+        if (int e = gemm_tc(xb, p.R, Dm + 1, p.ldx, wb, H, 3 * p.Kp, 3, sh, p.R, TcEpiStoreBf16{y, H}, st, "enc.conv"))
             return e;
     }
     // 4. additive attention: fc1 + tanh + fc2 in the GEMM epilogue, then the softmax-like tail

@@ -13,13 +13,19 @@
 // drained by epilogue group a, so two tile epilogues and the MMAs of a third tile overlap (the
 // epilogue of these K <= 1200 GEMMs costs more cycles than their MMAs).
 // Persistent: grid = #SMs, tiles assigned round-robin with n fastest (A tile reuse through L2).
+// Optional "B-resident" mode (NR_TC_BRES=1; short-K GEMMs whose (BN x K) weight slice fits shared
+// memory): every CTA loads its n tile's slice of B ONCE and streams only A tiles.  It cuts the L2 -> SM
+// traffic of the QKV GEMM from 2.1 GB to 0.7 GB per launch but was not faster on B200 (see tc_disable_bres).
 #pragma once
+#include <stdlib.h>
 #include "nr_common.cuh"
 #include "nr_tc.cuh"
 
 namespace nr {
 
 constexpr int TC_BM = 128, TC_BK = 64, TC_THREADS = 320, TC_MAX_BN = 256;
+constexpr int TC_STAGE_PITCH = 40;                                  // epilogue staging: 80-byte rows (conflict-free 16-byte accesses)
+constexpr int TC_STAGE_BYTES = 8 * 32 * TC_STAGE_PITCH * 2;         // 8 epilogue warps
 
 struct TcGemmParams {
     int64_t M;        // output rows
@@ -30,13 +36,69 @@ struct TcGemmParams {
     int shift[3];     // A row shift per tap
     int stages;
     int m_tiles, n_tiles;
+    int b_res;        // 1: the whole (BN x K) slice of B stays in shared memory, CTA c owns n tile c % n_tiles
+    int groups;       // b_res: CTAs per n tile (grid = groups * n_tiles); CTA c takes m tiles c / n_tiles + i * groups
 };
 
 inline size_t tc_stage_bytes(int BN) { return (size_t)TC_BM * TC_BK * 2 + (size_t)BN * TC_BK * 2; }
-inline size_t tc_smem_bytes(int BN, int stages) { return 1024 + stages * tc_stage_bytes(BN) + 256; }
+inline size_t tc_smem_bytes(int BN, int stages) { return 1024 + stages * tc_stage_bytes(BN) + 256 + TC_STAGE_BYTES; }
+inline bool tc_debug() {
+    static const bool on = [] { const char* e = getenv("NR_TC_DEBUG"); return e && e[0] == '1'; }();
+    return on;
+}
+// The B-resident mode is OFF unless NR_TC_BRES=1: measured on B200 it does not pay (QKV 0.228 ms resident
+// vs 0.206 ms streaming) — once the epilogue was thinned the kernels were no longer L2-feed bound, and the
+// resident slice costs one pipeline stage and 3 CTAs of the grid.  Kept for A/B measurements.
+inline bool tc_disable_bres() {
+    static const bool on = [] { const char* e = getenv("NR_TC_BRES"); return e && e[0] == '1'; }();
+    return !on;
+}
 
-// Epilogue functor protocol (one thread owns one output row of the tile):
-//   begin(row) ; chunk(row, col0, v[32], ncols) for col0 = n0, n0+32, ... ; end(row)
+// Epilogue functor protocol (one thread owns one output row of the tile; ALL 32 lanes of the warp call
+// every hook, `cx.live` says whether this lane's row exists):
+//   begin(cx, row) ; chunk(cx, row, col0, v[32], ncols) for col0 = n0, n0+32, ... ; end(cx, row)
+struct EpiCtx {
+    __nv_bfloat16* stage;   // this warp's [32][TC_STAGE_PITCH] bf16 staging tile in shared memory
+    int lane;
+    int64_t row0;           // first row of the warp (lane l owns row0 + l)
+    int64_t M;              // rows that exist
+    bool live;
+};
+
+// A thread-per-row epilogue writes 16 bytes per lane into 32 DIFFERENT rows per store instruction (32
+// L1 wavefronts, half-filled sectors).  This helper transposes the warp's 32 x 32 bf16 chunk through
+// shared memory so that every store instruction covers 8 rows x 64 contiguous bytes instead.
+__device__ __forceinline__ void store_rows_bf16(const EpiCtx& cx, __nv_bfloat16* C, int64_t ldc, int col0, const float* o,
+                                                int nc) {
+    uint4* srow = (uint4*)(cx.stage + cx.lane * TC_STAGE_PITCH);
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        srow[j] = make_uint4(tc::pack_bf16(o[8 * j], o[8 * j + 1]), tc::pack_bf16(o[8 * j + 2], o[8 * j + 3]),
+                             tc::pack_bf16(o[8 * j + 4], o[8 * j + 5]), tc::pack_bf16(o[8 * j + 6], o[8 * j + 7]));
+    __syncwarp();
+    const int c = (cx.lane & 3) * 8;
+    if (nc == 32 && cx.row0 + 32 <= cx.M) {          // full chunk: straight-line code
+        const __nv_bfloat16* src = cx.stage + (cx.lane >> 2) * TC_STAGE_PITCH + c;
+        __nv_bfloat16* dst = C + (cx.row0 + (cx.lane >> 2)) * ldc + col0 + c;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) *(uint4*)(dst + (int64_t)8 * j * ldc) = *(const uint4*)(src + 8 * j * TC_STAGE_PITCH);
+        __syncwarp();
+        return;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const int r = 8 * j + (cx.lane >> 2);
+        if (cx.row0 + r < cx.M && c < nc) {
+            const __nv_bfloat16* src = cx.stage + r * TC_STAGE_PITCH + c;
+            __nv_bfloat16* dst = C + (cx.row0 + r) * ldc + col0 + c;
+            if (c + 8 <= nc) *(uint4*)dst = *(const uint4*)src;
+            else
+                for (int t = 0; t < nc - c; ++t) dst[t] = src[t];
+        }
+    }
+    __syncwarp();
+}
+
 template <class Epi>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
@@ -46,24 +108,44 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     const int stages = p.stages;
     const uint32_t a_bytes = TC_BM * TC_BK * 2, b_bytes = (uint32_t)p.BN * TC_BK * 2;
-    const uint32_t stage_bytes = a_bytes + b_bytes;
-    uint64_t* bars = (uint64_t*)(smem + (size_t)stages * stage_bytes);
-    uint64_t* full = bars;                  // [stages]   TMA -> MMA
-    uint64_t* empty = bars + stages;        // [stages]   MMA -> TMA
-    uint64_t* tfull = bars + 2 * stages;    // [2]        MMA -> epilogue
-    uint64_t* tempty = tfull + 2;           // [2]        epilogue -> MMA
-    uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
-
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int total_tiles = p.m_tiles * p.n_tiles;
     const int kc = p.Kt / TC_BK;
     const int k_iters = p.taps * kc;
+    const bool bres = p.b_res != 0;
+    const uint32_t stage_bytes = bres ? a_bytes : a_bytes + b_bytes;
+    uint8_t* sB = smem;                                            // resident B: k_iters tiles of b_bytes
+    uint8_t* ring = smem + (bres ? (size_t)k_iters * b_bytes : 0); // operand ring
+    uint64_t* bars = (uint64_t*)(ring + (size_t)stages * stage_bytes);
+    uint64_t* full = bars;                  // [stages]   TMA -> MMA
+    uint64_t* empty = bars + stages;        // [stages]   MMA -> TMA
+    uint64_t* tfull = bars + 2 * stages;    // [2]        MMA -> epilogue
+    uint64_t* tempty = tfull + 2;           // [2]        epilogue -> MMA
+    uint64_t* bfull = tempty + 2;           // [1]        resident B landed
+    uint32_t* tmem_slot = (uint32_t*)(bfull + 1);
+    __nv_bfloat16* epi_stage = (__nv_bfloat16*)((uint8_t*)bars + 256);      // 8 x [32][TC_STAGE_PITCH]
+    // tile sequence of this CTA: it-th tile -> (m tile, n tile)
+    const int my_nt = bres ? (int)blockIdx.x % p.n_tiles : 0;
+    const int my_j = bres ? (int)blockIdx.x / p.n_tiles : 0;
+    auto tile_of = [&](int it, int& mt, int& nt) -> bool {
+        if (bres) {
+            nt = my_nt;
+            mt = my_j + it * p.groups;
+            return mt < p.m_tiles;
+        }
+        const int64_t tile = (int64_t)blockIdx.x + (int64_t)it * gridDim.x;
+        if (tile >= total_tiles) return false;
+        mt = (int)(tile / p.n_tiles);
+        nt = (int)(tile % p.n_tiles);
+        return true;
+    };
 
     if (warp == 0 && lane == 0) {
         tc::prefetch_tmap(&tmA);
         tc::prefetch_tmap(&tmB);
         for (int s = 0; s < stages; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); }
         for (int a = 0; a < 2; ++a) { tc::mbar_init(tfull + a, 1); tc::mbar_init(tempty + a, 4); }
+        tc::mbar_init(bfull, 1);
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
@@ -76,15 +158,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // ===== TMA producer =====
         if (lane == 0) {
             int s = 0; uint32_t ph = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int m0 = (tile / p.n_tiles) * TC_BM, n0 = (tile % p.n_tiles) * p.BN;
+            int mt, nt;
+            if (bres && tile_of(0, mt, nt)) {
+                tc::mbar_arrive_expect_tx(bfull, (uint32_t)k_iters * b_bytes);
+                for (int i = 0; i < k_iters; ++i)
+                    tc::tma_load_2d(sB + (size_t)i * b_bytes, &tmB, bfull, i * TC_BK, nt * p.BN);
+            }
+            for (int it = 0; tile_of(it, mt, nt); ++it) {
+                const int m0 = mt * TC_BM, n0 = nt * p.BN;
                 for (int i = 0; i < k_iters; ++i) {
                     const int tap = i / kc, kk = (i - tap * kc) * TC_BK;
                     tc::mbar_wait(empty + s, ph ^ 1);
-                    uint8_t* sa = smem + (size_t)s * stage_bytes;
+                    uint8_t* sa = ring + (size_t)s * stage_bytes;
                     tc::mbar_arrive_expect_tx(full + s, stage_bytes);
                     tc::tma_load_2d(sa, &tmA, full + s, kk, m0 + p.shift[tap]);
-                    tc::tma_load_2d(sa + a_bytes, &tmB, full + s, i * TC_BK, n0);
+                    if (!bres) tc::tma_load_2d(sa + a_bytes, &tmB, full + s, i * TC_BK, n0);
                     if (++s == stages) { s = 0; ph ^= 1; }
                 }
             }
@@ -94,7 +182,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const uint32_t idesc = tc::umma_idesc_bf16(TC_BM, p.BN, 0, 0);
         int s = 0; uint32_t ph = 0;
         int acc = 0; uint32_t aph = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int mt, nt;
+        if (bres && tile_of(0, mt, nt)) tc::mbar_wait(bfull, 0);
+        for (int it = 0; tile_of(it, mt, nt); ++it) {
             tc::mbar_wait(tempty + acc, aph ^ 1);
             tc::tc_fence_after();
             const uint32_t d_tmem = tmem_base + (uint32_t)acc * TC_MAX_BN;
@@ -102,9 +192,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 tc::mbar_wait(full + s, ph);
                 tc::tc_fence_after();
                 if (lane == 0) {
-                    const uint32_t sa = tc::smem_u32(smem + (size_t)s * stage_bytes);
+                    const uint32_t sa = tc::smem_u32(ring + (size_t)s * stage_bytes);
                     const uint64_t da = tc::umma_desc_sw128(sa, 16, 1024);
-                    const uint64_t db = tc::umma_desc_sw128(sa + a_bytes, 16, 1024);
+                    const uint64_t db = tc::umma_desc_sw128(bres ? tc::smem_u32(sB + (size_t)i * b_bytes) : sa + a_bytes, 16, 1024);
 #pragma unroll
                     for (int k = 0; k < TC_BK / 16; ++k)   // +32 B per 16-element k step (>>4 => +2)
                         tc::umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (i | k) ? 1u : 0u);
@@ -122,25 +212,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         Epi epi = epi_in;
         const int q = warp & 3;
         const int grp = (warp - 2) >> 2;
-        for (int it = grp;; it += 2) {
-            const int64_t tile = (int64_t)blockIdx.x + (int64_t)it * gridDim.x;
-            if (tile >= total_tiles) break;
-            const int64_t m0 = (tile / p.n_tiles) * TC_BM;
-            const int n0 = (int)(tile % p.n_tiles) * p.BN;
+        int mt, nt;
+        for (int it = grp; tile_of(it, mt, nt); it += 2) {
+            const int64_t m0 = (int64_t)mt * TC_BM;
+            const int n0 = nt * p.BN;
             const int64_t row = m0 + q * 32 + lane;
             tc::mbar_wait(tfull + grp, (uint32_t)(it >> 1) & 1u);
             tc::tc_fence_after();
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * TC_MAX_BN;
             const int ncols = (p.N - n0 < p.BN) ? p.N - n0 : p.BN;
-            const bool live = row < p.M;
-            if (live) epi.begin(row);
-            for (int c = 0; c < ncols; c += 32) {
-                float v[32];
-                tc::tmem_ld32(t_row + (uint32_t)c, v);
+            EpiCtx cx;
+            cx.stage = epi_stage + (warp - 2) * 32 * TC_STAGE_PITCH;
+            cx.lane = lane;
+            cx.row0 = m0 + q * 32;
+            cx.M = p.M;
+            cx.live = row < p.M;
+            epi.begin(cx, row);
+            // two register buffers: the TMEM load of chunk i+1 is in flight while chunk i is processed
+            float va[32], vb[32];
+            tc::tmem_ld32(t_row, va);
+            for (int c = 0; c < ncols; c += 64) {
                 tc::tmem_ld_wait();
-                if (live) epi.chunk(row, n0 + c, v, (ncols - c < 32) ? ncols - c : 32);
+                const bool has_b = c + 32 < ncols;
+                if (has_b) tc::tmem_ld32(t_row + (uint32_t)(c + 32), vb);
+                epi.chunk(cx, row, n0 + c, va, (ncols - c < 32) ? ncols - c : 32);
+                if (has_b) {
+                    tc::tmem_ld_wait();
+                    if (c + 64 < ncols) tc::tmem_ld32(t_row + (uint32_t)(c + 64), va);
+                    epi.chunk(cx, row, n0 + c + 32, vb, (ncols - c - 32 < 32) ? ncols - c - 32 : 32);
+                }
             }
-            if (live) epi.end(row);
+            epi.end(cx, row);
             tc::tc_fence_before();
             __syncwarp();
             if (lane == 0) tc::mbar_arrive(tempty + grp);
@@ -176,19 +278,35 @@ int gemm_tc(const __nv_bfloat16* A, int64_t a_rows, int Kt_real, int64_t lda, co
     p.BN = ((n16 + nt - 1) / nt + 15) / 16 * 16;
     p.n_tiles = (N + p.BN - 1) / p.BN;
     p.m_tiles = (int)((M + TC_BM - 1) / TC_BM);
-    int stages = (int)((227 * 1024 - 1024 - 256) / tc_stage_bytes(p.BN));
+    const size_t budget = 227 * 1024 - 1024 - 256 - TC_STAGE_BYTES;
+    int stages = (int)(budget / tc_stage_bytes(p.BN));
     if (stages > 8) stages = 8;
-    p.stages = stages;
     NR_REQUIRE(stages >= 2, "%s: tile does not fit shared memory", what);
+    // B-resident mode: the (BN x taps*Kt) slice of B + at least 3 A stages fit, and there are enough CTAs
+    const size_t b_slice = (size_t)taps * (p.Kt / TC_BK) * p.BN * TC_BK * 2;
+    const size_t a_stage = (size_t)TC_BM * TC_BK * 2;
+    p.b_res = 0; p.groups = 0;
+    int grid = sm_count();
+    const int tiles = p.m_tiles * p.n_tiles;
+    if (!tc_disable_bres() && b_slice + 2 * a_stage <= budget && p.n_tiles <= grid && p.m_tiles >= 2 * (grid / p.n_tiles)) {
+        p.b_res = 1;
+        p.groups = grid / p.n_tiles;
+        grid = p.groups * p.n_tiles;
+        stages = (int)((budget - b_slice) / a_stage);
+        if (stages > 8) stages = 8;
+    } else if (grid > tiles) {
+        grid = tiles;
+    }
+    p.stages = stages;
     CUtensorMap tmA, tmB;
     if (int e = make_tmap_bf16_2d(&tmA, A, (uint64_t)a_rows, (uint64_t)Kt_real, (uint64_t)lda, TC_BM, TC_BK)) return e;
     if (int e = make_tmap_bf16_2d(&tmB, B, (uint64_t)N, (uint64_t)taps * p.Kt, (uint64_t)ldb, (uint32_t)p.BN, TC_BK))
         return e;
-    const size_t smem = tc_smem_bytes(p.BN, stages);
+    const size_t smem = p.b_res ? 1024 + b_slice + stages * a_stage + 256 + TC_STAGE_BYTES : tc_smem_bytes(p.BN, stages);
     NR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int grid = sm_count();
-    const int tiles = p.m_tiles * p.n_tiles;
-    if (grid > tiles) grid = tiles;
+    if (tc_debug())
+        fprintf(stderr, "[nr] %s M=%lld N=%d K=%d taps=%d BN=%d tiles=%dx%d b_res=%d groups=%d stages=%d grid=%d smem=%zu\n", what,
+                (long long)M, N, Kt_real, taps, p.BN, p.m_tiles, p.n_tiles, p.b_res, p.groups, stages, grid, smem);
     ProfScope ps(what, st);
     gemm_tc_kernel<Epi><<<grid, TC_THREADS, smem, st>>>(tmA, tmB, p, epi);
     return check_last(what);
@@ -198,6 +316,14 @@ int gemm_tc(const __nv_bfloat16* A, int64_t a_rows, int Kt_real, int64_t lda, co
 // All register-array indexing is compile-time (fully unrolled, predicated tails) so v[] never
 // spills to local memory.  bias pointers must be 16-byte aligned (col0 is a multiple of 16).
 __device__ __forceinline__ void load_bias32(const float* bias, int col0, int nc, float* b) {
+    if (bias && nc == 32) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float4 t = ldg4(bias + col0 + 4 * j);
+            b[4 * j] = t.x; b[4 * j + 1] = t.y; b[4 * j + 2] = t.z; b[4 * j + 3] = t.w;
+        }
+        return;
+    }
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
         float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -229,22 +355,32 @@ __device__ __forceinline__ void store_bf16_32(__nv_bfloat16* out, const float* v
 // C (bf16, leading dimension ldc, ldc % 8 == 0) = acc + bias[col]
 struct TcEpiBiasBf16 {
     __nv_bfloat16* C; int64_t ldc; const float* bias; int N;
-    __device__ __forceinline__ void begin(int64_t) {}
-    __device__ __forceinline__ void end(int64_t) {}
-    __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
+    __device__ __forceinline__ void begin(const EpiCtx&, int64_t) {}
+    __device__ __forceinline__ void end(const EpiCtx&, int64_t) {}
+    __device__ __forceinline__ void chunk(const EpiCtx& cx, int64_t, int col0, const float* v, int nc) {
         float b[32], o[32];
         load_bias32(bias, col0, nc, b);
 #pragma unroll
         for (int j = 0; j < 32; ++j) o[j] = v[j] + b[j];
-        store_bf16_32(C + row * ldc + col0, o, nc);
+        store_rows_bf16(cx, C, ldc, col0, o, nc);
+    }
+};
+// C (bf16) = acc   (bias already inside the product: ones column of A times a bias column of B)
+struct TcEpiStoreBf16 {
+    __nv_bfloat16* C; int64_t ldc;
+    __device__ __forceinline__ void begin(const EpiCtx&, int64_t) {}
+    __device__ __forceinline__ void end(const EpiCtx&, int64_t) {}
+    __device__ __forceinline__ void chunk(const EpiCtx& cx, int64_t, int col0, const float* v, int nc) {
+        store_rows_bf16(cx, C, ldc, col0, v, nc);
     }
 };
 // C (fp32, ldc % 4 == 0) = acc + bias[col]
 struct TcEpiBiasF32 {
     float* C; int64_t ldc; const float* bias; int N;
-    __device__ __forceinline__ void begin(int64_t) {}
-    __device__ __forceinline__ void end(int64_t) {}
-    __device__ __forceinline__ void chunk(int64_t row, int col0, const float* v, int nc) {
+    __device__ __forceinline__ void begin(const EpiCtx&, int64_t) {}
+    __device__ __forceinline__ void end(const EpiCtx&, int64_t) {}
+    __device__ __forceinline__ void chunk(const EpiCtx& cx, int64_t row, int col0, const float* v, int nc) {
+        if (!cx.live) return;
         float b[32];
         load_bias32(bias, col0, nc, b);
         float* out = C + row * ldc + col0;

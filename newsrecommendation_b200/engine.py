@@ -72,6 +72,7 @@ class FlatAdam:
             p.grad = self.flat_g[off:off + n].view(p.shape)
         self.lr, self.betas, self.eps = lr, betas, eps
         self.step_count = 0
+        ops.ACCUMULATE_INTO_GRAD = True      # backward kernels add straight into the flat gradient bucket
 
     def zero_grad(self):
         self.flat_g.zero_()

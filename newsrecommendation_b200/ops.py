@@ -16,6 +16,26 @@ from . import _lib as L
 
 _seed_counter = itertools.count(1)
 
+# Fused weight-gradient accumulation.  When True (engine.FlatAdam turns it on), a backward kernel adds a
+# parameter's gradient straight into its existing `.grad` buffer (a view of the flat gradient bucket) and
+# the autograd Function returns None for it: no per-parameter zero-fill + add launches, and the dense
+# (V,300) embedding gradient is never materialised twice.  With False (default; e.g. the reference's own
+# optim.Adam + DistributedDataParallel loop, whose hooks need the returned gradients) the Functions
+# return ordinary gradient tensors.
+ACCUMULATE_INTO_GRAD = False
+
+
+def _grad_target(param, like):
+    """(buffer to accumulate into, value to return to autograd) for one parameter."""
+    if param is None:
+        return None, None
+    if (ACCUMULATE_INTO_GRAD and isinstance(param, torch.nn.Parameter) and param.grad is not None
+            and param.grad.is_contiguous() and param.grad.dtype == torch.float32
+            and param.grad.shape == param.shape and param.grad.is_cuda):
+        return param.grad, None
+    buf = torch.zeros_like(like)
+    return buf, buf
+
 
 def next_seed():
     """Fresh dropout seed per forward call, derived from torch's seed so that
@@ -231,6 +251,7 @@ class EmbedDenseFn(torch.autograd.Function):
         L.call('nr_embed_dense_fwd', L.ptr(embc), embc.shape[0], idp, F, L.ptr(wc), L.ptr(bc), L.ptr(out), H, n,
                E, H, L.stream())
         ctx.saved = (embc, ids, col, wc)
+        ctx.params = (emb, w, b)
         return out
 
     @staticmethod
@@ -239,12 +260,13 @@ class EmbedDenseFn(torch.autograd.Function):
         dout = L.f32(dout)
         n, F = ids.shape
         E, H = emb.shape[1], w.shape[0]
-        dw = torch.zeros_like(w)
-        db = torch.zeros(H, dtype=torch.float32, device=w.device)
-        demb = torch.zeros_like(emb)
+        pe, pw, pb = ctx.params
+        (bemb, demb), (bw, dw) = _grad_target(pe, emb), _grad_target(pw, w)
+        bb, db = _grad_target(pb, torch.empty(H, dtype=torch.float32, device=w.device))
         ws = L.workspace(0, w.device)
         L.call('nr_embed_dense_bwd', L.ptr(emb), emb.shape[0], ids.data_ptr() + 4 * col, F, L.ptr(w), L.ptr(dout),
-               H, L.ptr(dw), L.ptr(db), L.ptr(demb), n, E, H, L.ptr(ws), ws.numel(), L.stream())
+               H, L.ptr(bw), L.ptr(bb), L.ptr(bemb), n, E, H, L.ptr(ws), ws.numel(), L.stream())
+        ctx.params = None
         return demb, None, None, dw, db
 
 
@@ -263,6 +285,7 @@ class PadBlendFn(torch.autograd.Function):
         L.call('nr_pad_blend_fwd', L.ptr(v), L.ptr(mask), L.ptr(padc), L.ptr(out), n, T, H, L.stream())
         ctx.save_for_backward(mask)
         ctx.pad_shape = pad.shape
+        ctx.pad_param = pad
         return out
 
     @staticmethod
@@ -271,9 +294,10 @@ class PadBlendFn(torch.autograd.Function):
         dout = L.f32(dout)
         n, T, H = dout.shape
         dv = torch.empty_like(dout)
-        dpad = torch.zeros(H, dtype=torch.float32, device=dout.device)
-        L.call('nr_pad_blend_bwd', L.ptr(dout), L.ptr(mask), L.ptr(dv), L.ptr(dpad), n, T, H, L.stream())
-        return dv, None, dpad.view(ctx.pad_shape)
+        buf, dpad = _grad_target(ctx.pad_param, torch.empty(ctx.pad_shape, dtype=torch.float32, device=dout.device))
+        L.call('nr_pad_blend_bwd', L.ptr(dout), L.ptr(mask), L.ptr(dv), L.ptr(buf), n, T, H, L.stream())
+        ctx.pad_param = None
+        return dv, None, dpad
 
 
 def pad_blend(v, mask, pad):
@@ -346,6 +370,7 @@ class TitleEncoderFn(torch.autograd.Function):
         L.call('nr_title_encoder_fwd', C.byref(enc), C.byref(r), n, L.ptr(out), L.ptr(save), save.numel(),
                L.ptr(ws), ws.numel(), L.stream())
         ctx.enc, ctx.rows, ctx.keep = enc, rows, (ws_, pool, mask, save)
+        ctx.params = ((w0, b0, w1, b1, w2, b2), (p_w1, p_b1, p_w2, p_b2), src)
         ctx.src_shape = src.shape
         ctx.n = n
         return out
@@ -357,25 +382,27 @@ class TitleEncoderFn(torch.autograd.Function):
         dev = save.device
         g = L.f32(g)
         gr = L.NrTitleEncoderGrads()
-        dws = [None if t is None else torch.zeros_like(t) for t in ws_]
-        dpool = [torch.zeros_like(t) for t in pool]
+        pw, pp, psrc = ctx.params
+        tw = [_grad_target(p, t) for p, t in zip(pw, ws_)]
+        tp = [_grad_target(p, t) for p, t in zip(pp, pool)]
+        dws, dpool = [r for _, r in tw], [r for _, r in tp]
         for i in range(3):
-            gr.dw[i] = L.ptr(dws[2 * i])
-            gr.db[i] = L.ptr(dws[2 * i + 1])
-        gr.dp_w1, gr.dp_b1, gr.dp_w2, gr.dp_b2 = [L.ptr(t) for t in dpool]
+            gr.dw[i] = L.ptr(tw[2 * i][0])
+            gr.db[i] = L.ptr(tw[2 * i + 1][0])
+        gr.dp_w1, gr.dp_b1, gr.dp_w2, gr.dp_b2 = [L.ptr(b) for b, _ in tp]
         dsrc = None
         if ctx.needs_input_grad[0]:
             if rows.mode == L.ROWS_DENSE:
                 dsrc = torch.empty(ctx.src_shape, dtype=torch.float32, device=dev)
                 gr.dx_dense = L.ptr(dsrc)
             else:
-                dsrc = torch.zeros(ctx.src_shape, dtype=torch.float32, device=dev)
-                gr.dtable = L.ptr(dsrc)
+                buf, dsrc = _grad_target(psrc, rows.table)
+                gr.dtable = L.ptr(buf)
         ws = L.workspace(L.lib.nr_title_encoder_workspace(C.byref(enc), n), dev)
         r = rows.c()
         L.call('nr_title_encoder_bwd', C.byref(enc), C.byref(r), n, L.ptr(g), L.ptr(save), save.numel(), C.byref(gr),
                L.ptr(ws), ws.numel(), L.stream())
-        ctx.keep = None
+        ctx.keep = ctx.params = None
         return (dsrc, None, None, *dws, *dpool, None)
 
 

@@ -22,7 +22,8 @@ def tc_gemm(A, B, bias, M, taps=1, shifts=(0,), c_bf16=False, K=None):
 
 
 @pytest.mark.parametrize('M,N,K', [(1000, 1200, 320), (128, 16, 64), (4096 + 77, 200, 400), (333, 400, 208),
-                                   (20000, 320, 1200)])
+                                   (20000, 320, 1200),
+                                   (40000, 1200, 320), (38000 + 5, 200, 400), (40000, 400, 200)])   # B-resident mode
 def test_tc_gemm_nt(M, N, K):
     g = torch.Generator(device='cpu').manual_seed(M + N + K)
     A = (torch.randn(M, K, generator=g) * 0.5).to(torch.bfloat16).cuda()
