@@ -68,6 +68,12 @@ long long nr_launch_count(void);
 int nr_prof_enable(int on);
 size_t nr_prof_report(char* buf, size_t cap);
 
+/* Device-resident seed salt: salt_dev points to ONE uint64 in device memory (or NULL to clear).  Every
+ * dropout stream is then keyed by seed + *salt_dev, read when the kernel runs.  Lets a train step that
+ * was captured in a CUDA graph (host seeds frozen into the launch arguments) draw fresh masks on every
+ * replay: bump the value from inside the graph.  nr_dropout_keep_mask applies the salt too. */
+int nr_set_seed_salt(const void* salt_dev);
+
 /* keep[i] = 1 if element i of dropout stream (seed, stream_id) is kept at rate p */
 int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed,
                          int32_t stream_id, void* stream);

@@ -96,7 +96,7 @@ __global__ void gather_rows_kernel(const float* __restrict__ table, const int32_
 __global__ void keep_mask_kernel(uint8_t* keep, int64_t count, uint32_t thr, uint64_t seed, uint32_t sid) {
     for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q * 4 < count;
          q += (int64_t)gridDim.x * blockDim.x) {
-        const uint4 r = philox4(seed, sid, (uint64_t)q);
+        const uint4 r = philox4(salted(seed), sid, (uint64_t)q);
         const uint32_t w[4] = {r.x, r.y, r.z, r.w};
         for (int j = 0; j < 4; ++j)
             if (q * 4 + j < count) keep[q * 4 + j] = w[j] >= thr ? 1 : 0;
@@ -302,6 +302,15 @@ int nr_device_info(int32_t* sms, int32_t* major, int32_t* minor) {
     if (sms) *sms = a;
     if (major) *major = b;
     if (minor) *minor = c;
+    return 0;
+}
+
+int nr_set_seed_salt(const void* salt_dev) {
+    if (int e = nr::set_seed_salt_this_tu(salt_dev)) { nr::set_error("nr_set_seed_salt: cudaMemcpyToSymbol failed"); return e; }
+    if (nr::set_seed_salt_ops(salt_dev) || nr::set_seed_salt_ops2(salt_dev) || nr::set_seed_salt_encoder(salt_dev)) {
+        nr::set_error("nr_set_seed_salt: cudaMemcpyToSymbol failed");
+        return 2;
+    }
     return 0;
 }
 

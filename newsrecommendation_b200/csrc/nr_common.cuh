@@ -98,10 +98,23 @@ __host__ __device__ __forceinline__ uint32_t drop_threshold(float p) {
     return (uint32_t)t;
 }
 
+// Device-resident seed salt (nr_set_seed_salt): every dropout stream is keyed by seed + *salt.  A train
+// step captured in a CUDA graph bakes its host seeds into the kernel arguments; bumping the salt from
+// inside the graph gives every replay fresh masks while forward and backward of one replay still agree.
+// One copy of the pointer per translation unit (no relocatable device code); nr_set_seed_salt sets all.
+static __device__ const unsigned long long* g_seed_salt = nullptr;
+inline int set_seed_salt_this_tu(const void* p) {
+    return cudaMemcpyToSymbol(g_seed_salt, &p, sizeof(p)) == cudaSuccess ? 0 : 2;
+}
+__device__ __forceinline__ uint64_t salted(uint64_t seed) {
+    const unsigned long long* p = g_seed_salt;
+    return p ? seed + __ldg(p) : seed;
+}
+
 // Applies inverted dropout to 4 consecutive elements starting at element index e0 (e0 % 4 == 0).
 __device__ __forceinline__ float4 dropout4(float4 v, uint64_t e0, uint64_t seed, uint32_t sid,
                                            uint32_t thr, float scale) {
-    const uint4 r = philox4(seed, sid, e0 >> 2);
+    const uint4 r = philox4(salted(seed), sid, e0 >> 2);
     v.x = (r.x >= thr) ? v.x * scale : 0.f;
     v.y = (r.y >= thr) ? v.y * scale : 0.f;
     v.z = (r.z >= thr) ? v.z * scale : 0.f;
@@ -221,6 +234,10 @@ struct EmbedView {
 };
 
 RowsView make_rows_view(const nr_rows_t* r, int64_t n, int S, int D);
+// per-translation-unit salt setters (defined next to the kernels that draw dropout masks)
+int set_seed_salt_ops(const void* p);
+int set_seed_salt_ops2(const void* p);
+int set_seed_salt_encoder(const void* p);
 int validate_rows(const nr_rows_t* r, const char* who);
 
 }  // namespace nr

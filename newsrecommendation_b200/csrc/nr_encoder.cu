@@ -10,6 +10,10 @@
 
 using namespace nr;
 
+namespace nr {
+int set_seed_salt_encoder(const void* p) { return set_seed_salt_this_tu(p); }
+}  // namespace nr
+
 namespace {
 
 inline int round_up(int v, int m) { return (v + m - 1) / m * m; }

@@ -5,6 +5,10 @@
 
 using namespace nr;
 
+namespace nr {
+int set_seed_salt_ops(const void* p) { return set_seed_salt_this_tu(p); }
+}  // namespace nr
+
 namespace {
 
 template <int DK>

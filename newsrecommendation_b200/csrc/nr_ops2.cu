@@ -5,6 +5,10 @@
 
 using namespace nr;
 
+namespace nr {
+int set_seed_salt_ops2(const void* p) { return set_seed_salt_this_tu(p); }
+}  // namespace nr
+
 extern "C" {
 
 size_t nr_conv1d_k3_workspace(int64_t n, int32_t L, int32_t D, int32_t H, int32_t prec) {

@@ -102,6 +102,61 @@ def train_step(model, opt, history, history_mask, candidate, label):
     return loss.detach(), model.last_hits
 
 
+class GraphedTrainStep:
+    """The forward + backward of one train step (src/main.py:105-109) captured as ONE CUDA graph and
+    replayed per batch; the gradient all-reduce and the fused Adam follow eagerly (two launches whose
+    arguments — NCCL state, Adam's bias-correction step — change per call).
+
+    Why: a step is ~100 kernel launches of 5-500 us; driven from Python the host needs ~1 ms per step,
+    which is fully exposed whenever the caller reads the loss every step (main.py:106 accumulates it,
+    bench.py's e2e arm `.item()`s it).  A replay costs the host ~20 us.
+
+    Dropout: host-side seeds are frozen into the captured launches, so the library's device-resident
+    seed salt (nr_set_seed_salt) is bumped inside the graph — every replay draws fresh masks, and the
+    forward and backward kernels of one replay read the same value.
+
+    The batch shape is fixed at capture; feed a ragged last batch through engine.train_step instead."""
+
+    def __init__(self, model, opt, example_batch, warmup=2):
+        self.model, self.opt = model, opt
+        self.static = [t.clone() for t in example_batch]
+        dev = self.static[0].device
+        self.salt = torch.zeros(1, dtype=torch.int64, device=dev)
+        L.call('nr_set_seed_salt', L.ptr(self.salt))
+        cur = torch.cuda.current_stream()
+        side = torch.cuda.Stream()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):          # warm-up off the capture stream (lazy kernel loading, allocator)
+            for _ in range(warmup):
+                self._fwd_bwd()
+        cur.wait_stream(side)
+        torch.cuda.synchronize()
+        self.graph = torch.cuda.CUDAGraph()
+        n0 = L.lib.nr_launch_count()
+        with torch.cuda.graph(self.graph):
+            self._fwd_bwd()
+        self.launches_per_replay = L.lib.nr_launch_count() - n0
+
+    def _fwd_bwd(self):
+        self.salt.add_(1)
+        self.opt.zero_grad()
+        loss, score = self.model(*self.static)
+        loss.backward()
+        self.loss, self.score, self.hits = loss.detach(), score.detach(), self.model.last_hits
+
+    def __call__(self, history, history_mask, candidate, label):
+        for s, t in zip(self.static, (history, history_mask, candidate, label)):
+            if s.shape != t.shape:
+                raise ValueError(f'GraphedTrainStep captured batch shape {tuple(s.shape)}, got {tuple(t.shape)}')
+            s.copy_(t, non_blocking=True)
+        self.graph.replay()
+        self.opt.step()
+        return self.loss, self.hits
+
+    def close(self):
+        L.call('nr_set_seed_salt', None)
+
+
 # --------------------------------------------------------------------------------------
 # eval path
 # --------------------------------------------------------------------------------------

@@ -183,3 +183,44 @@ def test_score_ce_and_small_ops():
     out.backward(gup.cuda()); ref.backward(gup)
     gclose(ed.grad, eo.grad); gclose(wd.grad, wo.grad); gclose(bd.grad, bo.grad)
     assert (ed.grad[0] == 0).all()
+
+
+def test_graphed_train_step_matches_eager():
+    """engine.GraphedTrainStep (fwd+bwd as one CUDA graph) == engine.train_step, 3 steps, drop_rate 0;
+    with dropout on, consecutive replays draw different masks (device-side seed salt)."""
+    from newsrecommendation_b200 import engine, _lib as L
+    res = {}
+    for mode in ('eager', 'graph'):
+        kind, kw, Pn, bt, model = build_model('nrms_ulm0')
+        model.train()
+        opt = engine.FlatAdam(model, lr=3e-4)
+        batch = [T(a).cuda() for a in bt]
+        losses = []
+        if mode == 'graph':
+            step = engine.GraphedTrainStep(model, opt, batch)
+            for _ in range(3):
+                loss, hits = step(*batch)
+                losses.append(loss.item())
+            step.close()
+        else:
+            for _ in range(3):
+                loss, hits = engine.train_step(model, opt, *batch)
+                losses.append(loss.item())
+        res[mode] = (losses, {k: v.detach().cpu().clone() for k, v in model.state_dict().items()})
+    np.testing.assert_allclose(res['graph'][0], res['eager'][0], rtol=1e-5)
+    assert res['graph'][0][2] < res['graph'][0][0]           # it trains
+    # weights: Adam normalises every update to ~lr, so an entry whose gradient is rounding noise (fp32 atomics
+    # accumulate in a different order run to run) may step the other way; all but a sliver must agree closely
+    for k, v in res['eager'][1].items():
+        d = np.abs(res['graph'][1][k].numpy() - v.numpy())
+        assert d.max() <= 2 * 3 * 3e-4 + 1e-6, k
+        assert (d > 2e-5).mean() < 0.02, (k, float((d > 2e-5).mean()))
+    # dropout: same batch, lr = 0 -> identical weights, so a different loss means a different mask
+    kind, kw, Pn, bt, model = build_model('nrms_ulm0', drop_rate=0.2)
+    model.train()
+    opt = engine.FlatAdam(model, lr=0.0)
+    batch = [T(a).cuda() for a in bt]
+    step = engine.GraphedTrainStep(model, opt, batch)
+    l = [step(*batch)[0].item() for _ in range(3)]
+    step.close()
+    assert len({round(x, 7) for x in l}) == 3, l
