@@ -231,7 +231,8 @@ __host__ __device__ constexpr size_t bwd_smem_per_warp(int DK) {
 template <int DK, bool MASK>
 static __global__ void __launch_bounds__(128)
 attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
-                    int64_t items, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed) {
+                    int64_t items, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed,
+                    uint8_t* __restrict__ keep) {
     constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -315,7 +316,13 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (s < S) {
                 v = *(const float4*)(Os + s * DK + c);
-                if (thr) v = dropout4(v, (uint64_t)((seq * S + s) * H + head * DK + c), seed, NR_STREAM_OUT, thr, dscale);
+                if (thr) {
+                    // the 4 keep bits are saved (one byte per 4 elements, padded-row indexing) so that the
+                    // backward epilogue reads a byte instead of re-running Philox
+                    const uint32_t bits = dropout4_bits((uint64_t)((seq * S + s) * H + head * DK + c), seed, NR_STREAM_OUT, thr);
+                    v = apply_keep4(v, bits, dscale);
+                    if (keep) keep[((seq * 32 + s) * H + head * DK + c) >> 2] = (uint8_t)bits;
+                }
             }
             st_bf4(dst + s * H + c, v);
         }

@@ -122,6 +122,19 @@ __device__ __forceinline__ float4 dropout4(float4 v, uint64_t e0, uint64_t seed,
     return v;
 }
 
+// Same stream as dropout4, returned as 4 keep bits (bit j = element e0 + j kept).
+__device__ __forceinline__ uint32_t dropout4_bits(uint64_t e0, uint64_t seed, uint32_t sid, uint32_t thr) {
+    const uint4 r = philox4(salted(seed), sid, e0 >> 2);
+    return (r.x >= thr ? 1u : 0u) | (r.y >= thr ? 2u : 0u) | (r.z >= thr ? 4u : 0u) | (r.w >= thr ? 8u : 0u);
+}
+__device__ __forceinline__ float4 apply_keep4(float4 v, uint32_t bits, float scale) {
+    v.x = (bits & 1u) ? v.x * scale : 0.f;
+    v.y = (bits & 2u) ? v.y * scale : 0.f;
+    v.z = (bits & 4u) ? v.z * scale : 0.f;
+    v.w = (bits & 8u) ? v.w * scale : 0.f;
+    return v;
+}
+
 // ---- warp / block reductions -------------------------------------------------------
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

@@ -117,7 +117,8 @@ static __global__ void pack_weights_kernel(PackArgs a, bf16* __restrict__ out) {
 template <int DK>
 static __global__ void __launch_bounds__(128)
 attn_fwd_bf16_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
-                     int S, int SP, int heads, float scale, uint32_t thr, float dscale, uint64_t seed) {
+                     int S, int SP, int heads, float scale, uint32_t thr, float dscale, uint64_t seed,
+                     uint8_t* __restrict__ keep) {
     extern __shared__ __align__(16) float smem[];
     const int H = heads * DK;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -166,7 +167,11 @@ attn_fwd_bf16_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key
 #pragma unroll
         for (int d = 0; d < DK; d += 4) {
             float4 t = make_float4(o[d] * inv, o[d + 1] * inv, o[d + 2] * inv, o[d + 3] * inv);
-            if (thr) t = dropout4(t, (uint64_t)((seq * S + i) * H + head * DK + d), seed, NR_STREAM_OUT, thr, dscale);
+            if (thr) {
+                const uint32_t bits = dropout4_bits((uint64_t)((seq * S + i) * H + head * DK + d), seed, NR_STREAM_OUT, thr);
+                t = apply_keep4(t, bits, dscale);
+                if (keep) keep[((seq * SP + i) * H + head * DK + d) >> 2] = (uint8_t)bits;
+            }
             st_bf4(out + d, t);
         }
     }

@@ -49,7 +49,7 @@ struct EpiTanhLogit {
 // dY (bf16) = (dz . W1 + alpha_s g) [* output-dropout mask]; pad rows zero.  nc % 4 == 0 (H % 8 == 0).
 struct EpiPoolDx {
     bf16* dY; float* dx32; int64_t ld; const float* alpha; const float* g; int S, SP, H;
-    uint32_t thr; float dscale; uint64_t seed;
+    const uint8_t* keep; float dscale;      // saved output-dropout keep bits (NULL: no dropout)
     int64_t seq; int s; float a;
     __device__ __forceinline__ void begin(const EpiCtx& cx, int64_t row) {
         seq = row / SP; s = (int)(row - seq * SP);
@@ -59,7 +59,13 @@ struct EpiPoolDx {
     __device__ __forceinline__ void chunk(const EpiCtx& cx, int64_t, int col0, const float* v, int nc) {
         const bool real = cx.live && s < S;
         const float* gr = g + seq * H + col0;
-        const uint64_t e0 = (uint64_t)((seq * S + s) * H + col0);
+        // one byte per 4 elements, indexed by the padded row (written by the attention forward kernel)
+        uint32_t kb0 = 0xFFFFFFFFu, kb1 = 0xFFFFFFFFu;
+        if (keep && real) {
+            const uint32_t* kp = (const uint32_t*)(keep + (((seq * SP + s) * H + col0) >> 2));
+            kb0 = __ldg(kp);
+            if (nc > 16) kb1 = __ldg(kp + 1);
+        }
         float o[32];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -68,7 +74,7 @@ struct EpiPoolDx {
                 const float4 gv = ldg4(gr + 4 * j);
                 t = make_float4(fmaf(a, gv.x, v[4 * j]), fmaf(a, gv.y, v[4 * j + 1]), fmaf(a, gv.z, v[4 * j + 2]),
                                 fmaf(a, gv.w, v[4 * j + 3]));
-                if (thr) t = dropout4(t, e0 + 4 * j, seed, NR_STREAM_OUT, thr, dscale);
+                if (keep) t = apply_keep4(t, ((j < 4 ? kb0 : kb1) >> (8 * (j & 3))) & 0xFu, dscale);
             }
             o[4 * j] = t.x; o[4 * j + 1] = t.y; o[4 * j + 2] = t.z; o[4 * j + 3] = t.w;
         }
@@ -156,7 +162,7 @@ struct Plan {
     int SP, ldx, Kp, HK, QK, K3, Nw;
     int64_t R;
     // save
-    size_t o_wb, o_w1b, o_bias, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
+    size_t o_wb, o_w1b, o_bias, o_keep, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
     // backward workspace
     size_t o_dz, o_dy, o_dqkv, o_w1t, o_wt, ws_bytes;
 };
@@ -178,6 +184,7 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     p.o_wb = take(pool ? 0 : (size_t)p.Nw * taps * p.Kp * 2);
     p.o_w1b = take((size_t)e->Q * p.HK * 2);
     p.o_bias = take((size_t)3 * e->H * 4);
+    p.o_keep = take(e->out_drop_p > 0.f ? (size_t)p.R * e->H / 4 + 64 : 0);     // output-dropout keep bits, 1 byte / 4 elements
     p.o_xb = take(pool ? 0 : (size_t)p.R * p.ldx * 2);
     p.o_qkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
     p.o_y = take((size_t)p.R * e->H * 2);
@@ -227,13 +234,13 @@ int pack(const PackArgs& a, bf16* out, cudaStream_t st) {
 
 template <int DK>
 int launch_attn_fwd(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int SP, int heads, float p,
-                    uint64_t seed, cudaStream_t st) {
+                    uint64_t seed, uint8_t* keep, cudaStream_t st) {
     const size_t smem = attn_bf16_fwd_smem(S, DK);
     NR_CUDA(cudaFuncSetAttribute(attn_fwd_bf16_kernel<DK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ProfScope ps("enc.attn_fwd", st);
     attn_fwd_bf16_kernel<DK><<<(unsigned)(n * ((heads + 3) / 4)), 128, smem, st>>>(
         qkv, mask, ctx, S, SP, heads, 1.0f / sqrtf((float)DK), p > 0.f ? drop_threshold(p) : 0u,
-        p > 0.f ? 1.f / (1.f - p) : 1.f, seed);
+        p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep);
     return check_last("enc.attn_fwd");
 }
 template <int DK>
@@ -249,7 +256,7 @@ int launch_attn_bwd(const bf16* qkv, const float* mask, const bf16* dctx, bf16* 
 // warp-level tensor-core attention (S <= 31 => pitch 32, head dim <= 32)
 template <int DK, bool MASK>
 int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
-                        uint64_t seed, cudaStream_t st) {
+                        uint64_t seed, uint8_t* keep, cudaStream_t st) {
     const size_t smem = 4 * amma::fwd_smem_per_warp(DK);
     auto kern = amma::attn_fwd_mma_kernel<DK, MASK>;
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -262,7 +269,7 @@ int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;    // persistent: one wave
     ProfScope ps("enc.attn_fwd", st);
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads, 1.0f / sqrtf((float)DK),
-                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed);
+                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep);
     return check_last("enc.attn_fwd");
 }
 template <int DK, bool MASK>
@@ -282,8 +289,8 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
     return check_last("enc.attn_bwd");
 }
-#define NR_MMA_FWD(DKV) (mask ? launch_attn_fwd_mma<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, st) \
-                              : launch_attn_fwd_mma<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, st))
+#define NR_MMA_FWD(DKV) (mask ? launch_attn_fwd_mma<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st) \
+                              : launch_attn_fwd_mma<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st))
 #define NR_MMA_BWD(DKV) (mask ? launch_attn_bwd_mma<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st) \
                               : launch_attn_bwd_mma<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))
 
@@ -297,7 +304,7 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
         default: set_error("title encoder: head dim %d not in compiled set {8,16,20,32,40}", dk); return 1; \
     }
 int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int SP, int heads, int dk, float p,
-               uint64_t seed, cudaStream_t st) {
+               uint64_t seed, uint8_t* keep, cudaStream_t st) {
     if (SP == 32) {
         switch (dk) {
             case 8: return NR_MMA_FWD(8);
@@ -307,7 +314,7 @@ int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, 
             default: break;
         }
     }
-    NR_ENC_DISPATCH_DK(dk, launch_attn_fwd<DK>(qkv, mask, ctx, n, S, SP, heads, p, seed, st));
+    NR_ENC_DISPATCH_DK(dk, launch_attn_fwd<DK>(qkv, mask, ctx, n, S, SP, heads, p, seed, keep, st));
 }
 int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int SP, int heads,
                int dk, cudaStream_t st) {
@@ -397,7 +404,8 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         // K = Dm + 1: the ones column of Xb times the bias column of the packed weights
         if (int e = gemm_tc(xb, p.R, Dm + 1, p.ldx, wb, 3 * H, p.Kp, 1, &one, p.R, TcEpiStoreBf16{qkv, 3 * H}, st, "enc.qkv"))
             return e;
-        if (int e = attn_fwd_b(qkv, enc->mask, y, n, S, p.SP, enc->heads, H / enc->heads, enc->out_drop_p, rows->seed, st))
+        if (int e = attn_fwd_b(qkv, enc->mask, y, n, S, p.SP, enc->heads, H / enc->heads, enc->out_drop_p, rows->seed,
+                               enc->out_drop_p > 0.f ? (uint8_t*)(sv + p.o_keep) : nullptr, st))
             return e;
     } else {
         const int sh[3] = {-1, 0, 1};
@@ -468,8 +476,8 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     // 3. dY = dz . W1 + alpha g   (output-dropout mask re-applied for MHSA)
     if (!pool || want_dx) {
         EpiPoolDx ep{dy, pool ? gr->dx_dense : nullptr, H, alpha, g, S, p.SP, H,
-                     enc->out_drop_p > 0.f ? drop_threshold(enc->out_drop_p) : 0u,
-                     enc->out_drop_p > 0.f ? 1.f / (1.f - enc->out_drop_p) : 1.f, rows->seed, 0, 0, 0.f};
+                     enc->out_drop_p > 0.f ? (const uint8_t*)(sv + p.o_keep) : nullptr,
+                     enc->out_drop_p > 0.f ? 1.f / (1.f - enc->out_drop_p) : 1.f, 0, 0, 0.f};
         if (int e = gemm_tc(dz, p.R, Q, Q, w1t, H, p.QK, 1, &one, p.R, ep, st, "enc.pool_dx")) return e;
     }
     if (pool) return 0;

@@ -214,6 +214,10 @@ def test_graphed_train_step_matches_eager():
     for k, v in res['eager'][1].items():
         d = np.abs(res['graph'][1][k].numpy() - v.numpy())
         assert d.max() <= 2 * 3 * 3e-4 + 1e-6, k
+        # att_fc2.bias and W_K.bias have an analytically zero gradient (a constant added to every logit cancels
+        # in the normalisation), so what Adam sees there is pure rounding noise
+        if k.endswith('att_fc2.bias') or k.endswith('W_K.bias'):
+            continue
         assert (d > 2e-5).mean() < 0.02, (k, float((d > 2e-5).mean()))
     # dropout: same batch, lr = 0 -> identical weights, so a different loss means a different mask
     kind, kw, Pn, bt, model = build_model('nrms_ulm0', drop_rate=0.2)
