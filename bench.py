@@ -44,6 +44,8 @@ def parse():
     ap.add_argument('--no-eval', action='store_true')
     ap.add_argument('--no-graph', action='store_true', help='drive every kernel launch from Python instead of replaying the captured step')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--profile-step', action='store_true',
+                    help='warm up, run ONE eager step between cudaProfilerStart/Stop and exit (for ncu --profile-from-start off)')
     ap.add_argument('--cpu-batch', type=int, default=32)
     return ap.parse_args()
 
@@ -107,6 +109,63 @@ def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20):
         f['enc.conv'] = f['enc.dwconv'] = 2.0 * M * 3 * D * H
         f['enc.fc1'] = f['enc.pool_dx'] = f['enc.dw1'] = 2.0 * M * H * Q
     return f
+
+
+def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200):
+    """Algorithmic HBM bytes per step for each named kernel of the bf16 step: what the kernel has to read and
+    write once, on real (unpadded) tokens.  M title tokens, Mu history tokens."""
+    n = B * (T + 1 + K_NEG)
+    M, Mu = n * L, B * T
+    b = {}
+    if model == 'NRMS':
+        tok = M + Mu
+        b['enc.stage'] = M * (4 + D * 4 + (D + 1) * 2) + Mu * (H * 4 + (H + 1) * 2)   # ids + fp32 rows in, bf16 out
+        b['enc.qkv'] = M * (D + 1) * 2 + Mu * (H + 1) * 2 + tok * 3 * H * 2
+        b['enc.attn_fwd'] = tok * (3 * H + H) * 2 + M * H // 4                         # qkv in, ctx out, keep bits
+        b['enc.attn_bwd'] = tok * (3 * H + H + 3 * H) * 2                              # qkv + dctx in, dqkv out
+        b['enc.dwqkv'] = tok * 3 * H * 2 + M * (D + 1) * 2 + Mu * (H + 1) * 2
+        b['enc.dx'] = tok * 3 * H * 2 + M * D * 4 + Mu * H * 4                         # dqkv in, fp32 dx out
+    else:
+        tok = M
+        b['enc.stage'] = M * (4 + D * 4 + (D + 1) * 2)
+        b['enc.conv'] = M * (D + 1) * 2 + M * H * 2
+        b['enc.dwconv'] = M * H * 2 + M * (D + 1) * 2
+        b['enc.dx'] = M * H * 2 + M * D * 4
+    b['enc.fc1'] = tok * (H + Q) * 2 + tok * 4                                         # y in, tanh(e) + logit out
+    b['enc.pool_fwd'] = tok * (H * 2 + 4 + 4) + (tok // L) * H * 4
+    b['enc.pool_bwd'] = tok * (H * 2 + Q * 2 + 4 + Q * 2)                              # y, e, alpha in; dz out
+    b['enc.dw1'] = tok * (Q + H) * 2
+    b['enc.pool_dx'] = tok * (Q * 2 + H * 2 + 4) + (M * H // 4 if model == 'NRMS' else 0)
+    return b
+
+
+def roofline_for(k, ms_step, launches_step, ft, bt, pk):
+    """bound = tensor if the kernel's algorithmic intensity is above the measured ridge, else hbm."""
+    fl, by = ft.get(k), bt.get(k)
+    if fl is None and by is None:
+        return None
+    ridge = pk['tensor'] * 1e12 / (pk['hbm'] * 1e9)
+    tensor = by is None or (fl is not None and fl / by > ridge)
+    sec = ms_step * 1e-3
+    if tensor:
+        ach, peak, unit, per = fl / sec / 1e12, pk['tensor'], 'TFLOP/s', fl
+    else:
+        ach, peak, unit, per = by / sec / 1e9, pk['hbm'], 'GB/s', by
+    return {'kernel': k, 'bound': 'tensor' if tensor else 'hbm', 'achieved': ach, 'peak': peak, 'unit': unit,
+            'frac': ach / peak, 'algorithmic_per_launch': per / max(1e-9, launches_step),
+            'intensity_flop_per_byte': (fl / by) if fl and by else None, 'ridge_flop_per_byte': ridge,
+            'avg_launch_ms': ms_step / max(1e-9, launches_step)}
+
+
+def ncu_traffic(model, kernel, launches_step):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the kernel from the committed `ncu --set full` capture of this
+    same command (profiles/r1_traffic.json, written by profiles/summarize.py), averaged per launch."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            t = json.load(f)[model][kernel]
+        return t['dram_bytes_per_step'] / max(1e-9, launches_step)
+    except (OSError, KeyError, ValueError):
+        return None
 
 
 class ClockSampler:
@@ -277,6 +336,18 @@ def run_ours(a):
     def step_eager(i):
         engine.train_step(model, opt, *dev[i % R])
 
+    if a.profile_step:
+        # for `ncu --profile-from-start off`: warm up, then exactly one eager step inside the profiler range
+        for i in range(3):
+            step_eager(i)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.start()
+        step_eager(3)
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        print(json.dumps({'profile_step': a.model}))
+        return
+
     losses = []
     graphed = None if a.no_graph else engine.GraphedTrainStep(model, opt, dev[0])
 
@@ -326,20 +397,26 @@ def run_ours(a):
     if rank == 0:
         pk = peaks()
         ft = flops_table(a.model, a.batch)
+        bt = bytes_table(a.model, a.batch) if a.precision == 'bf16' else {}
         tot = sum(v[1] for v in prof.values()) or 1.0
         kern = {k: {'ms_per_step': v[1] / a.steps, 'launches_per_step': v[0] / a.steps, 'share': v[1] / tot}
                 for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
         for k in kern:
             if k in ft:
                 kern[k]['tflops'] = ft[k] / (kern[k]['ms_per_step'] * 1e-3) / 1e12
-        top = next((k for k in kern if k in ft), None)
+            r = roofline_for(k, kern[k]['ms_per_step'], kern[k]['launches_per_step'], ft, bt, pk)
+            if r:
+                kern[k]['bound'], kern[k]['frac'] = r['bound'], r['frac']
+                if r['bound'] == 'hbm':
+                    kern[k]['gbs'] = r['achieved']
+        top = next((k for k in kern if k in ft or k in bt), None)      # kern is sorted by share of the step
         roof = None
         if top:
-            ach = kern[top]['tflops']
-            roof = {'kernel': top, 'bound': 'tensor', 'achieved': ach, 'peak': pk['tensor'], 'unit': 'TFLOP/s',
-                    'frac': ach / pk['tensor'], 'traffic': None, 'peak_source': pk['src'] + ' (sustained bf16)',
-                    'share_of_step': kern[top]['share'], 'flops_per_step': ft[top],
-                    'avg_launch_ms': kern[top]['ms_per_step'] / max(1e-9, kern[top]['launches_per_step'])}
+            roof = roofline_for(top, kern[top]['ms_per_step'], kern[top]['launches_per_step'], ft, bt, pk)
+            roof['traffic'] = ncu_traffic(a.model, top, kern[top]['launches_per_step'])
+            roof['peak_source'] = pk['src'] + (' (sustained bf16, kernel timed inside the step)'
+                                               if roof['bound'] == 'tensor' else ' (HBM copy bandwidth)')
+            roof['share_of_step'] = kern[top]['share']
         B = a.batch
         line = {
             'metric': METRIC, 'value': world * B * a.steps / (ms * 1e-3), 'unit': 'samples/s', 'n_gpus': world,

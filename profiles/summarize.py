@@ -1,7 +1,12 @@
 """Summarise ncu outputs brought back in gpurun_out/ into small committed text files.
   python profiles/summarize.py launches gpurun_out/X_launches.csv profiles/X_launches.txt
   python profiles/summarize.py full gpurun_out/X.ncu-rep profiles/X_full.txt
+  python profiles/summarize.py traffic gpurun_out/X.ncu-rep NRMS profiles/r1_traffic.json
+      (X = `ncu --set full --profile-from-start off ... bench.py --profile-step`: exactly one train step;
+       bench.py reads the json for roofline.traffic)
 """
+import json
+import os
 import csv
 import io
 import re
@@ -41,8 +46,15 @@ KEYS = ('dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__time_duration.sum
         'smsp__cycles_active.avg', 'sm__cycles_elapsed.max', 'launch__shared_mem_per_block')
 
 
+def raw_page(src):
+    """`ncu -i X.ncu-rep --page raw --csv`, or that output already saved as X.csv on the GPU box."""
+    if src.endswith('.csv'):
+        return ''.join(l for l in open(src, errors='replace') if l.startswith('"'))
+    return subprocess.run(['ncu', '-i', src, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+
+
 def full(src, dst):
-    out = subprocess.run(['ncu', '-i', src, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
+    out = raw_page(src)
     rd = list(csv.reader(io.StringIO(out)))
     hdr, units = rd[0], rd[1]
     with open(dst, 'w') as f:
@@ -55,5 +67,43 @@ def full(src, dst):
                     f.write(f'  {h:70s} {v:>18s} {u}\n')
 
 
+# kernel function (demangled, as ncu prints it) -> the name the library's event profiler reports
+NAMES = (('stage_rows_kernel', 'enc.stage'), ('pack_weights_kernel', 'enc.pack_w'), ('EpiTanhLogit', 'enc.fc1'),
+         ('EpiPoolDx', 'enc.pool_dx'), ('EpiDx', 'enc.dx'), ('TnEpiPlain', 'enc.dw1'), ('TnEpiQkv', 'enc.dwqkv'),
+         ('TnEpiConv', 'enc.dwconv'), ('attn_fwd', 'enc.attn_fwd'), ('attn_bwd', 'enc.attn_bwd'),
+         ('pool_tail_fwd', 'enc.pool_fwd'), ('pool_tail_bwd', 'enc.pool_bwd'))
+
+
+def traffic(src, model, dst):
+    out = raw_page(src)
+    rd = list(csv.reader(io.StringIO(out)))
+    hdr, units = rd[0], rd[1]
+    col = {h: i for i, h in enumerate(hdr)}
+    scale = {'byte': 1, 'Kbyte': 1e3, 'Mbyte': 1e6, 'Gbyte': 1e9}
+    agg = defaultdict(lambda: {'launches': 0, 'dram_bytes_per_step': 0.0, 'ncu_time_us': 0.0})
+    for row in rd[2:]:
+        kn = row[col['Kernel Name']]
+        name = next((n for pat, n in NAMES if pat in kn), None)
+        if name is None and 'TcEpiStoreBf16' in kn:
+            name = 'enc.qkv' if model == 'NRMS' else 'enc.conv'
+        if name is None:
+            name = re.sub(r'[<(].*', '', kn)
+        b = 0.0
+        for m in ('dram__bytes_read.sum', 'dram__bytes_write.sum'):
+            b += float(row[col[m]].replace(',', '')) * scale.get(units[col[m]], 1)
+        t = float(row[col['gpu__time_duration.sum']].replace(',', ''))
+        t *= {'ns': 1e-3, 'us': 1, 'ms': 1e3, 'usecond': 1, 'nsecond': 1e-3, 'msecond': 1e3}.get(units[col['gpu__time_duration.sum']], 1)
+        a = agg[name]
+        a['launches'] += 1
+        a['dram_bytes_per_step'] += b
+        a['ncu_time_us'] += t
+    old = json.load(open(dst)) if os.path.exists(dst) else {}
+    old[model] = dict(sorted(agg.items(), key=lambda kv: -kv[1]['ncu_time_us']))
+    old.setdefault('_how', 'ncu --set full --clock-control none --profile-from-start off python bench.py --model M '
+                           '--profile-step : one eager train step (batch 128, bf16); dram__bytes_read.sum + '
+                           'dram__bytes_write.sum summed over the launches of each kernel in that step')
+    json.dump(old, open(dst, 'w'), indent=1)
+
+
 if __name__ == '__main__':
-    {'launches': launches, 'full': full}[sys.argv[1]](sys.argv[2], sys.argv[3])
+    {'launches': launches, 'full': full, 'traffic': traffic}[sys.argv[1]](*sys.argv[2:])
