@@ -65,8 +65,11 @@ struct Workspace {
     static size_t pad(size_t b) { return (b + 255) & ~size_t(255); }
 };
 
-// ---- Philox4x32-10 counter RNG: dropout keep masks ----------------------------
+// ---- Philox4x32-7 counter RNG: dropout keep masks ------------------------------
+// 7 rounds is the fewest that passes BigCrush (Salmon et al., SC'11, table 2); the customary 10 is safety margin a
+// dropout mask does not need, and the rounds are most of the instructions of the staging kernel.
 // Element e of stream (seed, sid): word (e & 3) of philox(counter = e >> 2).
+#define NR_PHILOX_ROUNDS 7
 __host__ __device__ __forceinline__ void philox_round(uint32_t& c0, uint32_t& c1, uint32_t& c2,
                                                       uint32_t& c3, uint32_t k0, uint32_t k1) {
     const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
@@ -83,7 +86,7 @@ __host__ __device__ __forceinline__ uint4 philox4(uint64_t seed, uint32_t sid, u
     uint32_t c0 = (uint32_t)ctr, c1 = (uint32_t)(ctr >> 32), c2 = sid, c3 = 0x6e72u;
     uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
 #pragma unroll
-    for (int i = 0; i < 10; ++i) {
+    for (int i = 0; i < NR_PHILOX_ROUNDS; ++i) {
         philox_round(c0, c1, c2, c3, k0, k1);
         k0 += 0x9E3779B9u;
         k1 += 0xBB67AE85u;

@@ -132,12 +132,20 @@ struct TnEpiQkv {
         float* dw = w == 0 ? dw0 : (w == 1 ? dw1 : dw2);
         float* db = w == 0 ? db0 : (w == 1 ? db1 : db2);
         float* row = dw ? dw + (int64_t)ii * Dm : nullptr;
+        const bool vec = row && (Dm & 3) == 0 && (((uintptr_t)dw) & 15) == 0;
 #pragma unroll
-        for (int t = 0; t < 32; ++t) {
+        for (int t = 0; t < 32; t += 4) {
             const int c = j + t;
-            if (t < nc) {
-                if (c < Dm) { if (row) atomicAdd(row + c, v[t]); }
-                else if (c == Dm) { if (db) atomicAdd(db + ii, v[t]); }
+            if (vec && t + 4 <= nc && c + 4 <= Dm) {      // 16-byte vector reduction
+                atomicAdd((float4*)(row + c), make_float4(v[t], v[t + 1], v[t + 2], v[t + 3]));
+                continue;
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (t + u < nc) {
+                    if (c + u < Dm) { if (row) atomicAdd(row + c + u, v[t + u]); }
+                    else if (c + u == Dm) { if (db) atomicAdd(db + ii, v[t + u]); }
+                }
             }
         }
     }

@@ -157,7 +157,9 @@ int gemm_tc_tn(const __nv_bfloat16* A, int Mo, int64_t lda, const __nv_bfloat16*
     const int tiles = p.m_tiles * p.n_tiles * taps;
     int splits = sm_count() / tiles;
     if (splits < 1) splits = 1;
-    if (splits > p.total_chunks) splits = p.total_chunks;
+    // every split ends in Mo x No atomics: keep at least 8 k-chunks (512 rows) of MMA work behind each of them
+    if (splits > (p.total_chunks + 7) / 8) splits = (p.total_chunks + 7) / 8;
+    if (splits < 1) splits = 1;
     p.chunks_per_split = (p.total_chunks + splits - 1) / splits;
     splits = (p.total_chunks + p.chunks_per_split - 1) / p.chunks_per_split;
     const size_t stage_bytes = (size_t)(2 + p.nb) * TN_BOX_BYTES;
@@ -180,6 +182,18 @@ struct TnEpiPlain {       // C[tap] (Mo x ldc) fp32 += acc
     float* C; int64_t ldc; int64_t tap_stride;
     __device__ __forceinline__ void operator()(int i, int tap, int j, const float* v, int nc) const {
         float* p = C + tap * tap_stride + (int64_t)i * ldc + j;
+        if ((((uintptr_t)p) & 15) == 0) {       // 16-byte vector reductions: a quarter of the L2 atomic transactions
+#pragma unroll
+            for (int t = 0; t < 32; t += 4) {
+                if (t + 4 <= nc) atomicAdd((float4*)(p + t), make_float4(v[t], v[t + 1], v[t + 2], v[t + 3]));
+                else {
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (t + u < nc) atomicAdd(p + t + u, v[t + u]);
+                }
+            }
+            return;
+        }
 #pragma unroll
         for (int t = 0; t < 32; ++t)
             if (t < nc) atomicAdd(p + t, v[t]);
