@@ -494,5 +494,309 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Blocked variant for sequences of up to 32*NB positions (the user encoder: 50 clicked titles, pitch 64).
+// One warp still owns one (sequence, head) item, but the score matrix is walked as NB x NB blocks of 32 x 32
+// with the same fragment helpers; tiles are [32*NB rows][PITCH].  The item count here is tiny (batch x heads),
+// so the loads are not double buffered and the normalisers are computed in a first sweep over the key blocks
+// and the products recomputed in a second one (registers stay at the level of the 32 x 32 kernels).
+// ---------------------------------------------------------------------------------------------------------------
+template <int NT>
+__device__ __forceinline__ void mm_32xn_acc(float (&c)[2][NT][4], const uint32_t (&a)[2][2][4], const uint32_t (&b)[NT][2][2]) {
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int ks = 0; ks < 2; ++ks) mma16816(c[mt][nt], a[mt][ks], b[nt][ks]);
+}
+template <int NT>
+__device__ __forceinline__ void zero_o(float (&c)[2][NT][4]) {
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) c[mt][nt][e] = 0.f;
+}
+__host__ __device__ constexpr size_t fwd_blk_smem_per_warp(int DK, int NB) {
+    return (size_t)3 * NB * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 4;
+}
+__host__ __device__ constexpr size_t bwd_blk_smem_per_warp(int DK, int NB) {
+    return (size_t)4 * NB * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 4 + (size_t)2 * 32 * NB * 4;
+}
+
+template <int DK, bool MASK, int NB>
+static __global__ void __launch_bounds__(128)
+attn_fwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
+                    int64_t items, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed,
+                    uint8_t* __restrict__ keep) {
+    constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE, SPB = 32 * NB;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t = lane & 3;
+    const int H = heads * DK;
+    const float sl2 = scale * 1.4426950408889634f;
+    bf16* buf = (bf16*)(smem_raw + warp * fwd_blk_smem_per_warp(DK, NB));      // Q | K | V, NB blocks each
+    float* Os = (float*)(buf + 3 * NB * TILE);
+    for (int i = lane; i < 3 * NB * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncwarp();
+    Slots<DK> sl;
+    sl.init(lane);
+    const int stride = (int)gridDim.x * 4;
+    for (int item = (int)blockIdx.x * 4 + warp; item < items; item += stride) {
+        const int64_t seq = item / heads;
+        const int head = item - (int)seq * heads;
+        const bf16* src = qkv + seq * SPB * 3 * H + head * DK;
+#pragma unroll
+        for (int m = 0; m < 3; ++m)
+#pragma unroll
+            for (int b = 0; b < NB; ++b)
+                prefetch_tile<DK>(buf + (m * NB + b) * TILE, src + m * H + (int64_t)b * 32 * 3 * H, 3 * H, sl);
+        cp_async_commit();
+        cp_async_wait<0>();
+        __syncwarp();
+        const bf16* Qs = buf;
+        const bf16* Ks = buf + NB * TILE;
+        const bf16* Vs = buf + 2 * NB * TILE;
+#pragma unroll 1
+        for (int qb = 0; qb < NB; ++qb) {
+            Frag<DK> fq;
+            load_a<DK>(Qs + qb * TILE, lane, fq);
+            float acc[NB][2][4][4];
+            float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+#pragma unroll
+            for (int kb = 0; kb < NB; ++kb) {
+                Frag<DK> fk;
+                load_b_rows<DK>(Ks + kb * TILE, lane, fk);
+                zero_c(acc[kb]);
+                mm_32x32<DK>(acc[kb], fq, fk);
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const int col = kb * 32 + nt * 8 + 2 * t + e;
+                        const float m = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
+#pragma unroll
+                        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                            for (int h = 0; h < 2; ++h) {
+                                float p = exp2_fast(acc[kb][mt][nt][2 * h + e] * sl2);
+                                if (MASK) p *= m;
+                                p = m != 0.f ? p : 0.f;
+                                acc[kb][mt][nt][2 * h + e] = p;
+                                z[mt][h] += p;
+                            }
+                    }
+            }
+            float inv[2][2];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) inv[mt][h] = 1.f / (quad_sum(z[mt][h]) + kEps);    // model_utils.py:53
+            float o[2][NT][4];
+            zero_o<NT>(o);
+#pragma unroll
+            for (int kb = 0; kb < NB; ++kb) {
+                uint32_t ap[2][2][4], bv[NT][2][2];
+                c_to_a(acc[kb], ap);
+                load_b_cols<DK>(Vs + kb * TILE, lane, bv);
+                mm_32xn_acc<NT>(o, ap, bv);
+            }
+            stage_out<NT, DK>(o, Os, lane, inv[0][0], inv[0][1], inv[1][0], inv[1][1]);
+            __syncwarp();
+            bf16* dst = ctx + (seq * SPB + qb * 32) * H + head * DK;
+#pragma unroll
+            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
+                const int s = sl.s[i], c = sl.c[i], sa = qb * 32 + s;
+                float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (sa < S) {
+                    v = *(const float4*)(Os + s * DK + c);
+                    if (thr) {
+                        const uint32_t bits = dropout4_bits((uint64_t)((seq * S + sa) * H + head * DK + c), seed, NR_STREAM_OUT, thr);
+                        v = apply_keep4(v, bits, dscale);
+                        if (keep) keep[((seq * SPB + sa) * H + head * DK + c) >> 2] = (uint8_t)bits;
+                    }
+                }
+                st_bf4(dst + s * H + c, v);
+            }
+            __syncwarp();
+        }
+    }
+}
+
+template <int DK, bool MASK, int NB>
+static __global__ void __launch_bounds__(128)
+attn_bwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
+                    bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale) {
+    constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE, SPB = 32 * NB;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int H = heads * DK;
+    const float sl2 = scale * 1.4426950408889634f;
+    bf16* buf = (bf16*)(smem_raw + warp * bwd_blk_smem_per_warp(DK, NB));      // Q | K | V | dO, NB blocks each
+    float* Os = (float*)(buf + 4 * NB * TILE);
+    float* zinv = Os + 32 * DK;
+    float* rds = zinv + SPB;
+    for (int i = lane; i < 4 * NB * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncwarp();
+    Slots<DK> sl;
+    sl.init(lane);
+    const int stride = (int)gridDim.x * 4;
+    for (int item = (int)blockIdx.x * 4 + warp; item < items; item += stride) {
+        const int64_t seq = item / heads;
+        const int head = item - (int)seq * heads;
+        const bf16* src = qkv + seq * SPB * 3 * H + head * DK;
+        const bf16* gsrc = dctx + seq * SPB * H + head * DK;
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+#pragma unroll
+            for (int m = 0; m < 3; ++m)
+                prefetch_tile<DK>(buf + (m * NB + b) * TILE, src + m * H + (int64_t)b * 32 * 3 * H, 3 * H, sl);
+            prefetch_tile<DK>(buf + (3 * NB + b) * TILE, gsrc + (int64_t)b * 32 * H, H, sl);
+        }
+        cp_async_commit();
+        cp_async_wait<0>();
+        __syncwarp();
+        const bf16* Qs = buf;
+        const bf16* Ks = buf + NB * TILE;
+        const bf16* Vs = buf + 2 * NB * TILE;
+        const bf16* Gs = buf + 3 * NB * TILE;
+        bf16* dst = dqkv + seq * SPB * 3 * H + head * DK;
+        // ---- query-major: sweep 1 -> Z and rd per query row; sweep 2 -> dS blocks and dQ = sum_kb dS K / sqrt(dk)
+#pragma unroll 1
+        for (int qb = 0; qb < NB; ++qb) {
+            Frag<DK> fq, fg;
+            load_a<DK>(Qs + qb * TILE, lane, fq);
+            load_a<DK>(Gs + qb * TILE, lane, fg);
+            float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, rd[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+            float inv[2][2];
+            float dq[2][NT][4];
+            zero_o<NT>(dq);
+#pragma unroll 1
+            for (int sweep = 0; sweep < 2; ++sweep) {
+#pragma unroll 1
+                for (int kb = 0; kb < NB; ++kb) {
+                    float s[2][4][4], da[2][4][4];
+                    zero_c(s); zero_c(da);
+                    {
+                        Frag<DK> fb;
+                        load_b_rows<DK>(Ks + kb * TILE, lane, fb);
+                        mm_32x32<DK>(s, fq, fb);
+                        load_b_rows<DK>(Vs + kb * TILE, lane, fb);
+                        mm_32x32<DK>(da, fg, fb);
+                    }
+#pragma unroll
+                    for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                            const int col = kb * 32 + nt * 8 + 2 * t + e;
+                            const float m = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
+#pragma unroll
+                            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                                for (int h = 0; h < 2; ++h) {
+                                    float p = exp2_fast(s[mt][nt][2 * h + e] * sl2);
+                                    if (MASK) p *= m;
+                                    p = m != 0.f ? p : 0.f;
+                                    if (sweep == 0) {
+                                        z[mt][h] += p;
+                                        rd[mt][h] = fmaf(p, da[mt][nt][2 * h + e], rd[mt][h]);
+                                    } else {
+                                        s[mt][nt][2 * h + e] = p * inv[mt][h] * (da[mt][nt][2 * h + e] - rd[mt][h]);
+                                    }
+                                }
+                        }
+                    if (sweep == 1) {
+                        uint32_t ads[2][2][4], bk[NT][2][2];
+                        c_to_a(s, ads);
+                        load_b_cols<DK>(Ks + kb * TILE, lane, bk);
+                        mm_32xn_acc<NT>(dq, ads, bk);
+                    }
+                }
+                if (sweep == 0) {
+#pragma unroll
+                    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) {
+                            const int row = qb * 32 + mt * 16 + g + 8 * h;
+                            const float zs = quad_sum(z[mt][h]), rs = quad_sum(rd[mt][h]);   // shuffles: all lanes, no branch
+                            inv[mt][h] = row < S ? 1.f / (zs + kEps) : 0.f;
+                            rd[mt][h] = rs * inv[mt][h];
+                            if (t == 0) { zinv[row] = inv[mt][h]; rds[row] = rd[mt][h]; }
+                        }
+                }
+            }
+            stage_out<NT, DK>(dq, Os, lane, scale, scale, scale, scale);
+            __syncwarp();
+            store_tile<DK>(dst + (int64_t)qb * 32 * 3 * H, 3 * H, Os, S - qb * 32, sl);
+            __syncwarp();
+        }
+        // ---- key-major: dK = sum_qb dS^T Q / sqrt(dk), dV = sum_qb A^T dO
+#pragma unroll 1
+        for (int kb = 0; kb < NB; ++kb) {
+            Frag<DK> fk, fv;
+            load_a<DK>(Ks + kb * TILE, lane, fk);
+            load_a<DK>(Vs + kb * TILE, lane, fv);
+            float mrow[2][2];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int row = kb * 32 + mt * 16 + g + 8 * h;
+                    mrow[mt][h] = row < S ? (MASK ? __ldg(key_mask + seq * S + row) : 1.f) : 0.f;
+                }
+            float ok[2][NT][4], ov[2][NT][4];
+            zero_o<NT>(ok); zero_o<NT>(ov);
+#pragma unroll 1
+            for (int qb = 0; qb < NB; ++qb) {
+                float s[2][4][4], da[2][4][4];
+                zero_c(s); zero_c(da);
+                {
+                    Frag<DK> fb;
+                    load_b_rows<DK>(Qs + qb * TILE, lane, fb);
+                    mm_32x32<DK>(s, fk, fb);
+                    load_b_rows<DK>(Gs + qb * TILE, lane, fb);
+                    mm_32x32<DK>(da, fv, fb);
+                }
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const float zv = zinv[qb * 32 + nt * 8 + 2 * t + e], rv = rds[qb * 32 + nt * 8 + 2 * t + e];
+#pragma unroll
+                        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                            for (int h = 0; h < 2; ++h) {
+                                const float m = mrow[mt][h];
+                                const float mz = MASK ? m * zv : (m != 0.f ? zv : 0.f);
+                                float a = exp2_fast(s[mt][nt][2 * h + e] * sl2) * mz;
+                                a = mz != 0.f ? a : 0.f;
+                                s[mt][nt][2 * h + e] = a;                                     // A^T
+                                da[mt][nt][2 * h + e] = a * (da[mt][nt][2 * h + e] - rv);     // dS^T
+                            }
+                    }
+                uint32_t af[2][2][4], bf[NT][2][2];
+                c_to_a(da, af);
+                load_b_cols<DK>(Qs + qb * TILE, lane, bf);
+                mm_32xn_acc<NT>(ok, af, bf);
+                c_to_a(s, af);
+                load_b_cols<DK>(Gs + qb * TILE, lane, bf);
+                mm_32xn_acc<NT>(ov, af, bf);
+            }
+            stage_out<NT, DK>(ok, Os, lane, scale, scale, scale, scale);
+            __syncwarp();
+            store_tile<DK>(dst + H + (int64_t)kb * 32 * 3 * H, 3 * H, Os, S - kb * 32, sl);
+            __syncwarp();
+            stage_out<NT, DK>(ov, Os, lane, 1.f, 1.f, 1.f, 1.f);
+            __syncwarp();
+            store_tile<DK>(dst + 2 * H + (int64_t)kb * 32 * 3 * H, 3 * H, Os, S - kb * 32, sl);
+            __syncwarp();
+        }
+    }
+}
+
 }  // namespace amma
 }  // namespace nr

@@ -297,6 +297,46 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
     return check_last("enc.attn_bwd");
 }
+// blocked variant: 32 < pitch <= 64 (the user encoder's 50 clicked titles)
+template <int DK, bool MASK>
+int launch_attn_fwd_blk(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
+                        uint64_t seed, uint8_t* keep, cudaStream_t st) {
+    const size_t smem = 4 * amma::fwd_blk_smem_per_warp(DK, 2);
+    auto kern = amma::attn_fwd_blk_kernel<DK, MASK, 2>;
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t items = n * heads;
+    NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
+    int64_t grid = (items + 3) / 4;
+    int per_sm = 1;
+    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
+    ProfScope ps("enc.attn_fwd", st);
+    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads, 1.0f / sqrtf((float)DK),
+                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep);
+    return check_last("enc.attn_fwd");
+}
+template <int DK, bool MASK>
+int launch_attn_bwd_blk(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
+                        cudaStream_t st) {
+    const size_t smem = 4 * amma::bwd_blk_smem_per_warp(DK, 2);
+    auto kern = amma::attn_bwd_blk_kernel<DK, MASK, 2>;
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t items = n * heads;
+    NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
+    int64_t grid = (items + 3) / 4;
+    int per_sm = 1;
+    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
+    ProfScope ps("enc.attn_bwd", st);
+    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
+    return check_last("enc.attn_bwd");
+}
+#define NR_BLK_FWD(DKV) (mask ? launch_attn_fwd_blk<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st) \
+                              : launch_attn_fwd_blk<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st))
+#define NR_BLK_BWD(DKV) (mask ? launch_attn_bwd_blk<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st) \
+                              : launch_attn_bwd_blk<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))
 #define NR_MMA_FWD(DKV) (mask ? launch_attn_fwd_mma<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st) \
                               : launch_attn_fwd_mma<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st))
 #define NR_MMA_BWD(DKV) (mask ? launch_attn_bwd_mma<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st) \
@@ -322,6 +362,15 @@ int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, 
             default: break;
         }
     }
+    if (SP == 64) {
+        switch (dk) {
+            case 8: return NR_BLK_FWD(8);
+            case 16: return NR_BLK_FWD(16);
+            case 20: return NR_BLK_FWD(20);
+            case 32: return NR_BLK_FWD(32);
+            default: break;
+        }
+    }
     NR_ENC_DISPATCH_DK(dk, launch_attn_fwd<DK>(qkv, mask, ctx, n, S, SP, heads, p, seed, keep, st));
 }
 int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int SP, int heads,
@@ -332,6 +381,15 @@ int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv,
             case 16: return NR_MMA_BWD(16);
             case 20: return NR_MMA_BWD(20);
             case 32: return NR_MMA_BWD(32);
+            default: break;
+        }
+    }
+    if (SP == 64) {
+        switch (dk) {
+            case 8: return NR_BLK_BWD(8);
+            case 16: return NR_BLK_BWD(16);
+            case 20: return NR_BLK_BWD(20);
+            case 32: return NR_BLK_BWD(32);
             default: break;
         }
     }

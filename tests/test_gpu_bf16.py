@@ -128,7 +128,7 @@ def test_bf16_model_vs_reference_golden(tag):
         assert (uv[0] == 0).all()              # empty history -> exact zero (B1)
 
 
-@pytest.mark.parametrize('kind', ['nrms', 'naml'])
+@pytest.mark.parametrize('kind', ['nrms', 'nrms_logmask', 'naml'])
 def test_bf16_matches_fp32_path_with_dropout(kind):
     """Both precision modes draw the same counter-based dropout masks, so a train-mode forward/backward
     with drop_rate=0.2 must agree between them to bf16 tolerance (B=16, MIND-small shapes)."""
@@ -138,8 +138,9 @@ def test_bf16_matches_fp32_path_with_dropout(kind):
     for prec in ('fp32', 'bf16'):
         torch.manual_seed(0)
         ops._seed_counter = itertools.count(1)
-        if kind == 'nrms':
-            a = S.default_args(num_words_title=30, drop_rate=0.2, precision=prec)
+        if kind.startswith('nrms'):
+            # history 50 -> pitch 64: the blocked warp-MMA attention; nrms_logmask also feeds it a key mask
+            a = S.default_args(num_words_title=30, drop_rate=0.2, precision=prec, user_log_mask=kind == 'nrms_logmask')
             model = NRMS.Model(a, S.word_table(500))
             news = S.news_titles(300, 30, 500)
         else:
