@@ -50,18 +50,26 @@ struct EpiTanhLogit {
 struct EpiPoolDx {
     bf16* dY; float* dx32; int64_t ld; const float* alpha; const float* g; int S, SP, H;
     const uint8_t* keep; float dscale;      // saved output-dropout keep bits (NULL: no dropout)
-    int64_t seq; int s; float a;
+    int64_t seq; int s; float a; bool real;
+    // The epilogue has 8 warps per SM and nothing to hide a global-load round trip behind, so the lines the NEXT
+    // chunk reads are pulled into L1 (prefetch.global.L1: no destination registers) while this one is processed.
+    __device__ __forceinline__ void warm(int col0, int n1) const {
+        if (!real || col0 >= n1) return;
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(g + seq * H + col0));
+        if (keep) asm volatile("prefetch.global.L1 [%0];" ::"l"(keep + (((seq * SP + s) * H + col0) >> 2)));
+    }
     __device__ __forceinline__ void begin(const EpiCtx& cx, int64_t row) {
         seq = row / SP; s = (int)(row - seq * SP);
-        a = (cx.live && s < S) ? __ldg(alpha + row) : 0.f;
+        real = cx.live && s < S;
+        a = real ? __ldg(alpha + row) : 0.f;
+        warm(cx.n0, cx.n1);
     }
     __device__ __forceinline__ void end(const EpiCtx&, int64_t) {}
     __device__ __forceinline__ void chunk(const EpiCtx& cx, int64_t, int col0, const float* v, int nc) {
-        const bool real = cx.live && s < S;
+        warm(col0 + 32, cx.n1);
         const float* gr = g + seq * H + col0;
-        // one byte per 4 elements, indexed by the padded row (written by the attention forward kernel)
         uint32_t kb0 = 0xFFFFFFFFu, kb1 = 0xFFFFFFFFu;
-        if (keep && real) {
+        if (keep && real) {     // one byte per 4 elements, indexed by the padded row (written by the attention forward)
             const uint32_t* kp = (const uint32_t*)(keep + (((seq * SP + s) * H + col0) >> 2));
             kb0 = __ldg(kp);
             if (nc > 16) kb1 = __ldg(kp + 1);
@@ -543,7 +551,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     if (!pool || want_dx) {
         EpiPoolDx ep{dy, pool ? gr->dx_dense : nullptr, H, alpha, g, S, p.SP, H,
                      enc->out_drop_p > 0.f ? (const uint8_t*)(sv + p.o_keep) : nullptr,
-                     enc->out_drop_p > 0.f ? 1.f / (1.f - enc->out_drop_p) : 1.f, 0, 0, 0.f};
+                     enc->out_drop_p > 0.f ? 1.f / (1.f - enc->out_drop_p) : 1.f, 0, 0, 0.f, false};
         if (int e = gemm_tc(dz, p.R, Q, Q, w1t, H, p.QK, 1, &one, p.R, ep, st, "enc.pool_dx")) return e;
     }
     if (pool) return 0;

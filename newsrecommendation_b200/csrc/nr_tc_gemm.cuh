@@ -63,6 +63,7 @@ struct EpiCtx {
     int64_t row0;           // first row of the warp (lane l owns row0 + l)
     int64_t M;              // rows that exist
     bool live;
+    int n0, n1;             // column range [n0, n1) of the tile being drained (set before begin())
 };
 
 // A thread-per-row epilogue writes 16 bytes per lane into 32 DIFFERENT rows per store instruction (32
@@ -100,7 +101,7 @@ __device__ __forceinline__ void store_rows_bf16(const EpiCtx& cx, __nv_bfloat16*
 }
 
 template <class Epi>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(TC_THREADS, 1)   // 10 warps: 3 on one SM sub-partition -> 168 registers is the hardware ceiling
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const TcGemmParams p, const Epi epi_in) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -217,8 +218,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int64_t m0 = (int64_t)mt * TC_BM;
             const int n0 = nt * p.BN;
             const int64_t row = m0 + q * 32 + lane;
-            tc::mbar_wait(tfull + grp, (uint32_t)(it >> 1) & 1u);
-            tc::tc_fence_after();
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * TC_MAX_BN;
             const int ncols = (p.N - n0 < p.BN) ? p.N - n0 : p.BN;
             EpiCtx cx;
@@ -227,7 +226,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             cx.row0 = m0 + q * 32;
             cx.M = p.M;
             cx.live = row < p.M;
+            cx.n0 = n0; cx.n1 = n0 + ncols;
+            // begin() before the accumulator wait: its global loads (per-row scalars, the first chunk's
+            // operands) are in flight while the MMA warp finishes the tile
             epi.begin(cx, row);
+            tc::mbar_wait(tfull + grp, (uint32_t)(it >> 1) & 1u);
+            tc::tc_fence_after();
             // two register buffers: the TMEM load of chunk i+1 is in flight while chunk i is processed
             float va[32], vb[32];
             tc::tmem_ld32(t_row, va);
