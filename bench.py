@@ -119,12 +119,13 @@ def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200):
     b = {}
     if model == 'NRMS':
         tok = M + Mu
-        b['enc.stage'] = M * (4 + D * 4 + (D + 1) * 2) + Mu * (H * 4 + (H + 1) * 2)   # ids + fp32 rows in, bf16 out
+        tab = min(M, V_SMALL) * D * 4          # the word table is 15 MB: gathered rows are L2 hits after first touch
+        b['enc.stage'] = M * (4 + (D + 1) * 2) + tab + Mu * (H * 4 + (H + 1) * 2)     # ids + table + fp32 rows in, bf16 out
         b['enc.qkv'] = M * (D + 1) * 2 + Mu * (H + 1) * 2 + tok * 3 * H * 2
         b['enc.attn_fwd'] = tok * (3 * H + H) * 2 + M * H // 4                         # qkv in, ctx out, keep bits
         b['enc.attn_bwd'] = tok * (3 * H + H + 3 * H) * 2                              # qkv + dctx in, dqkv out
         b['enc.dwqkv'] = tok * 3 * H * 2 + M * (D + 1) * 2 + Mu * (H + 1) * 2
-        b['enc.dx'] = tok * 3 * H * 2 + M * D * 4 + Mu * H * 4                         # dqkv in, fp32 dx out
+        b['enc.dx'] = tok * 3 * H * 2 + tab + Mu * H * 4                               # dqkv in, table gradient / fp32 dx out
     else:
         tok = M
         b['enc.stage'] = M * (4 + D * 4 + (D + 1) * 2)

@@ -39,7 +39,7 @@ def launches(src, dst):
         f.write(f'{"TOTAL":110s} {sum(v[0] for v in agg.values()):8d} {total / 1e3:12.1f}\n')
 
 
-KEYS = ('dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__time_duration.sum', 'gpu__dram_throughput',
+_OLD_KEYS = ('dram__bytes_read.sum', 'dram__bytes_write.sum', 'gpu__time_duration.sum', 'gpu__dram_throughput',
         'dram__cycles_active', 'sm__pipe_tensor', 'sm__warps_active.avg.pct', 'launch__registers_per_thread',
         'launch__grid_size', 'launch__block_size', 'sm__throughput.avg.pct', 'smsp__inst_executed.sum',
         'launch__occupancy_limit', 'sm__inst_executed_pipe_tensor', 'lts__t_bytes.sum', 'l1tex__t_bytes.sum',
@@ -53,18 +53,37 @@ def raw_page(src):
     return subprocess.run(['ncu', '-i', src, '--page', 'raw', '--csv'], capture_output=True, text=True).stdout
 
 
+COLS = (('time_us', 'gpu__time_duration.sum'), ('dramR_MB', 'dram__bytes_read.sum'), ('dramW_MB', 'dram__bytes_write.sum'),
+        ('dram%', 'gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed'),
+        ('l2%', 'lts__throughput.avg.pct_of_peak_sustained_elapsed'),
+        ('sm%', 'sm__throughput.avg.pct_of_peak_sustained_elapsed'),
+        ('tensor%', 'sm__pipe_tensor_subpipe_hmma_cycles_active.avg.pct_of_peak_sustained_active'),
+        ('issue%', 'smsp__issue_active.avg.pct_of_peak_sustained_active'),
+        ('warps%', 'sm__warps_active.avg.pct_of_peak_sustained_active'),
+        ('regs', 'launch__registers_per_thread'), ('grid', 'launch__grid_size'), ('block', 'launch__block_size'))
+UNIT = {'ns': 1e-3, 'nsecond': 1e-3, 'us': 1, 'usecond': 1, 'ms': 1e3, 'msecond': 1e3,
+        'byte': 1e-6, 'Kbyte': 1e-3, 'Mbyte': 1, 'Gbyte': 1e3}
+
+
 def full(src, dst):
-    out = raw_page(src)
-    rd = list(csv.reader(io.StringIO(out)))
+    """One line per profiled launch: the `ncu --set full` numbers the roofline discussion uses."""
+    rd = list(csv.reader(io.StringIO(raw_page(src))))
     hdr, units = rd[0], rd[1]
+    col = {h: i for i, h in enumerate(hdr)}
     with open(dst, 'w') as f:
         f.write(f'# ncu --set full --clock-control none ; source {src}\n')
+        f.write(f'{"kernel":64s}' + ''.join(f'{n:>10s}' for n, _ in COLS) + '\n')
         for row in rd[2:]:
-            d = dict(zip(hdr, row))
-            f.write(f'\n== {d.get("Kernel Name", "?")[:150]}  grid {d.get("Grid Size")} block {d.get("Block Size")}\n')
-            for h, u, v in zip(hdr, units, row):
-                if any(k in h for k in KEYS):
-                    f.write(f'  {h:70s} {v:>18s} {u}\n')
+            kn = re.sub(r'^void ', '', row[col['Kernel Name']])
+            kn = re.sub(r'\(.*', '', kn).replace('nr::', '').replace('<unnamed>::', '')[:63]
+            out = f'{kn:64s}'
+            for n, m in COLS:
+                if m not in col:
+                    out += f'{"-":>10s}'
+                    continue
+                v = float(row[col[m]].replace(',', '') or 0) * UNIT.get(units[col[m]], 1)
+                out += f'{v:10.1f}' if n not in ('regs', 'grid', 'block') else f'{int(v):10d}'
+            f.write(out + '\n')
 
 
 # kernel function (demangled, as ncu prints it) -> the name the library's event profiler reports
