@@ -394,6 +394,7 @@ def run_ours(a):
     ev = None
     if not a.no_eval:
         ev = run_eval(a, model, news, rank, world, engine, S)
+    bt_leg = run_batcher(a, model, news, S) if rank == 0 and not a.no_eval else None
 
     if rank == 0:
         pk = peaks()
@@ -438,12 +439,34 @@ def run_ours(a):
         }
         if ev:
             line['eval'] = ev
+        if bt_leg:
+            line['batcher'] = bt_leg
         if world == 1 and not a.no_cpu_baseline:
             r = cpu_train_samples_per_s(a)
             line['cpu_baseline'] = {k: r[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_batcher(a, model, news, S):
+    """batches assembled on the device from a tokenised behaviors index (replaces
+    DatasetTrain.line_mapper, dataset.py:26-49), alone and feeding the train step."""
+    from newsrecommendation_b200 import batcher
+    I = 50000
+    idx = batcher.TrainIndex(*S.train_index(news.shape[0] - 1, I, K_NEG))
+    b = batcher.DeviceBatcher(idx, news, T_HIST)
+    rs = np.random.RandomState(9)
+    ids = [torch.from_numpy(rs.randint(0, I, size=a.batch)).cuda() for _ in range(16)]
+    lab = [torch.from_numpy(rs.randint(0, 1 + K_NEG, size=a.batch)).cuda() for _ in range(16)]
+    for i in range(3):
+        b.batch(ids[i], lab[i])
+    n = 200
+    ms = timed(lambda i: b.batch(ids[i % 16], lab[i % 16]), n, 1)
+    out_bytes = a.batch * (T_HIST + 1 + K_NEG) * news.shape[1] * 4 * 2 + a.batch * T_HIST * 4
+    return {'samples_per_s': a.batch * n / (ms * 1e-3), 'us_per_batch': ms / n * 1e3, 'batch': a.batch,
+            'index_lines': I, 'gbs': out_bytes * n / (ms * 1e-3) / 1e9,
+            'note': 'nr_batch_train only (ids + labels resident); the train step consumes its outputs unchanged'}
 
 
 def run_eval(a, model, news, rank, world, engine, S):

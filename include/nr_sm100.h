@@ -234,6 +234,27 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
                          const void* save, size_t save_bytes, const nr_title_encoder_grads_t* grads,
                          void* ws, size_t ws_bytes, void* stream);
 
+/* ---- device-side batch assembly --------------------------------------------------
+ * The behaviors files are tokenised ONCE on the host into a device-resident index:
+ *   hist_off int64 (I+1), hist_idx int32 (sum of history lengths; news indices, unknown id -> 0),
+ *   pos int32 (I), neg int32 (I,K).
+ * nr_batch_train does, for B lines at once, what DatasetTrain.line_mapper does per line
+ * (src/dataset.py:26-49): pad_to_fix_len (:17-24, keep the LAST T clicks, pad the FRONT with 0, mask
+ * 0/1 fp32), candidate order neg[:label] + pos + neg[label:] (:45-46) with the caller's label
+ * (random.randint(0, npratio), :45) and the news_combined[...] feature gathers (:40,:47).
+ *   sample_ids int64 (B): rows of the index; label int64 (B); news_combined int32 (news_rows, F)
+ *   -> history int32 (B,T,F), mask fp32 (B,T), candidate int32 (B,1+K,F).   Bit exact. */
+int nr_batch_train(const int64_t* hist_off, const int32_t* hist_idx, const int32_t* pos, const int32_t* neg,
+                   const int64_t* sample_ids, const int64_t* label, const int32_t* news_combined,
+                   int64_t news_rows, int64_t B, int32_t T, int32_t K, int32_t F, int32_t* history,
+                   float* mask, int32_t* candidate, void* stream);
+/* DatasetTest.line_mapper's history half (src/dataset.py:64-68): padded click indices + mask for B
+ * impressions (imp_ids int64 (B) or NULL = rows 0..B-1) -> out_idx int32 (B,T), out_mask fp32 (B,T);
+ * the candidate half is the CSR gather nr_eval_score already consumes. */
+int nr_batch_eval_history(const int64_t* hist_off, const int32_t* hist_idx, const int64_t* imp_ids,
+                          int64_t news_rows, int64_t B, int32_t T, int32_t* out_idx, float* out_mask,
+                          void* stream);
+
 #ifdef __cplusplus
 }
 #endif

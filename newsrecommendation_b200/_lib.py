@@ -81,6 +81,8 @@ _SIGS = {
     'nr_title_encoder_workspace': (_SZ, [_E, _I64]),
     'nr_title_encoder_fwd': (C.c_int, [_E, _R, _I64, _P, _P, _SZ, _P, _SZ, _P]),
     'nr_title_encoder_bwd': (C.c_int, [_E, _R, _I64, _P, _P, _SZ, _G, _P, _SZ, _P]),
+    'nr_batch_train': (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _I64, _I64, _I32, _I32, _I32, _P, _P, _P, _P]),
+    'nr_batch_eval_history': (C.c_int, [_P, _P, _P, _I64, _I64, _I32, _P, _P, _P]),
     'nr_eval_score': (C.c_int, [_P, _I64, _P, _P, _P, _P, _I64, _I64, _I32, _P]),
     'nr_eval_rank_metrics': (C.c_int, [_P, _P, _P, _P, _P, _I64, _P]),
     'nr_eval_reduce_metrics': (C.c_int, [_P, _P, _P, _I64, _P]),

@@ -94,6 +94,17 @@ def train_batches(news_combined, n_batches, B, T=50, K=4, seed=4):
     return out
 
 
+def train_index(N, I, K=4, seed=6):
+    """Tokenised behaviors_np{K}_{rank}.tsv (batcher.TrainIndex arrays): raw click histories of length
+    ~ lognormal(3.0, 1.0) (un-truncated; 2 % empty), one positive and K negatives per line."""
+    rs = np.random.RandomState(seed)
+    lens = np.minimum(np.rint(rs.lognormal(3.0, 1.0, size=I)), 400).astype(np.int64)
+    lens[rs.random_sample(I) < 0.02] = 0
+    off = np.zeros(I + 1, np.int64)
+    off[1:] = np.cumsum(lens)
+    return (off, _zipf_ids(rs, N + 1, int(off[-1])), _zipf_ids(rs, N + 1, I), _zipf_ids(rs, N + 1, (I, K)))
+
+
 def eval_impressions(N, I, T=50, seed=5):
     """CSR impressions: hist_idx (I,T) int32, hist_mask (I,T) fp32, offsets (I+1) int64,
     cand_idx int32, labels int8.  C ~ clip(lognormal(3.2,.8),2,300); 1-3 positives; a 0.5 %

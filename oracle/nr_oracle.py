@@ -390,3 +390,54 @@ def summarize_metrics(mets: np.ndarray):
     return {'sums': sums, 'scored': int(valid.sum()), 'total': int(mets.shape[0]),
             'mean_scored': sums / max(1, int(valid.sum())),
             'mean_total': sums / max(1, mets.shape[0])}
+
+
+# ----------------------------------------------------------------------------
+# batch assembly  (src/dataset.py:14-49, 64-74) — SURVEY §8f rank 1
+# ----------------------------------------------------------------------------
+def trans_to_nindex(news_index: Dict[str, int], nids: Sequence[str]):
+    """DatasetTrain.trans_to_nindex, src/dataset.py:14-15: unknown ids -> 0."""
+    return [news_index[i] if i in news_index else 0 for i in nids]
+
+
+def train_line_mapper(line: str, news_index: Dict[str, int], news_combined: np.ndarray, T: int, label: int):
+    """DatasetTrain.line_mapper, src/dataset.py:26-49, with the `random.randint(0, npratio)` draw of
+    :45 passed in as `label`.  Returns (history features (T,F), mask (T,), candidate features
+    (1+K,F), label)."""
+    f = line.strip().split('\t')
+    hist, mask = pad_history(trans_to_nindex(news_index, f[3].split()), T)          # :39
+    pos = trans_to_nindex(news_index, f[4].split())                                 # :42
+    neg = trans_to_nindex(news_index, f[5].split())                                 # :43
+    sample = neg[:label] + pos + neg[label:]                                        # :46
+    return news_combined[hist], mask, news_combined[np.asarray(sample, dtype=np.int64)], label
+
+
+def test_line_mapper(line: str, news_index: Dict[str, int], T: int):
+    """DatasetTest.line_mapper, src/dataset.py:64-74, index level: padded click indices (T,), mask (T,),
+    candidate indices (C,), labels (C,)."""
+    f = line.strip().split('\t')
+    hist, mask = pad_history(trans_to_nindex(news_index, f[3].split()), T)          # :66-67
+    imp = f[4].split()
+    cand = trans_to_nindex(news_index, [i.split('-')[0] for i in imp])              # :70
+    labels = np.array([int(i.split('-')[1]) for i in imp])                          # :71
+    return hist, mask, np.asarray(cand, dtype=np.int32), labels
+
+
+def batch_train_np(hist_off, hist_idx, pos, neg, sample_ids, label, news_combined, T):
+    """Vectorised numpy form of train_line_mapper over a tokenised index (for sizes where the per-line
+    Python loop is too slow); same integer results."""
+    sample_ids = np.asarray(sample_ids, dtype=np.int64)
+    label = np.asarray(label, dtype=np.int64)
+    B, K = sample_ids.shape[0], neg.shape[1]
+    o0 = hist_off[sample_ids]
+    ln = hist_off[sample_ids + 1] - o0
+    t = np.arange(T)[None, :]
+    padn = (T - np.minimum(ln, T))[:, None]
+    real = t >= padn
+    src = o0[:, None] + ln[:, None] - (T - t)
+    idx = np.where(real, hist_idx[np.where(real, src, 0)], 0).astype(np.int32)
+    j = np.arange(1 + K)[None, :]
+    lb = label[:, None]
+    negj = np.where(j < lb, j, j - 1).clip(0, K - 1)
+    cand = np.where(j == lb, pos[sample_ids][:, None], neg[sample_ids][np.arange(B)[:, None], negj]).astype(np.int32)
+    return news_combined[idx], real.astype(np.float32), news_combined[cand], label
