@@ -409,4 +409,179 @@ pool_tail_bwd_bf16_kernel(const float* __restrict__ g, const bf16* __restrict__ 
     if (threadIdx.x == 0) atomicAdd(db2, db2_acc);
 }
 
+
+// ---- warp-per-sequence pooling tails (SP <= 64) --------------------------------------------------------------
+// The block-per-sequence kernels above spend their time in __syncthreads (7 per sequence in backward) with
+// half the warps idle; a title is only 30 x 400 bf16 = 24 KB.  Here ONE warp owns a sequence: lane l holds the
+// per-row scalars of rows l and l+32 (logit, alpha, d alpha) in registers, walks the rows with 16-byte loads
+// (chunk c = l + 32k of a row, KH = ceil(H/256) chunks per lane) and broadcasts the row scalar with a shuffle;
+// no shared memory, no block barrier, several rows of loads in flight per lane.
+__device__ __forceinline__ void bf8_to_f(const uint4 w, float* f) {
+    const float2 a = bf2_to_f2(w.x), b = bf2_to_f2(w.y), c = bf2_to_f2(w.z), d = bf2_to_f2(w.w);
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y; f[4] = c.x; f[5] = c.y; f[6] = d.x; f[7] = d.y;
+}
+
+template <int KH>
+static __global__ void __launch_bounds__(256)
+pool_tail_fwd_warp_kernel(const bf16* __restrict__ y, const float* __restrict__ logits, const float* __restrict__ mask,
+                          float* __restrict__ out, float* __restrict__ alpha_save, int64_t n, int S, int SP, int H) {
+    const int lane = threadIdx.x & 31;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int HC = H >> 3;
+    for (int64_t seq = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; seq < n; seq += nw) {
+        float p0 = 0.f, p1 = 0.f;
+        if (lane < S) {
+            p0 = expf(__ldg(logits + seq * SP + lane));
+            if (mask) p0 *= __ldg(mask + seq * S + lane);
+        }
+        if (lane + 32 < S) {
+            p1 = expf(__ldg(logits + seq * SP + lane + 32));
+            if (mask) p1 *= __ldg(mask + seq * S + lane + 32);
+        }
+        const float inv = 1.f / (warp_sum(p0 + p1) + kEps);          // model_utils.py:29
+        const float a0 = p0 * inv, a1 = p1 * inv;
+        if (lane < SP) alpha_save[seq * SP + lane] = a0;
+        if (lane + 32 < SP) alpha_save[seq * SP + lane + 32] = a1;
+        float acc[KH][8];
+#pragma unroll
+        for (int k = 0; k < KH; ++k)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[k][j] = 0.f;
+        const bf16* yt = y + seq * SP * H;
+#pragma unroll 4
+        for (int s = 0; s < S; ++s) {
+            const float a = __shfl_sync(0xffffffffu, s < 32 ? a0 : a1, s & 31);
+#pragma unroll
+            for (int k = 0; k < KH; ++k) {
+                const int c = lane + 32 * k;
+                if (c < HC) {
+                    float f[8];
+                    bf8_to_f(__ldg((const uint4*)(yt + (int64_t)s * H) + c), f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[k][j] = fmaf(a, f[j], acc[k][j]);
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < KH; ++k) {
+            const int c = lane + 32 * k;
+            if (c < HC) {
+                float4* o = (float4*)(out + seq * H + c * 8);
+                o[0] = make_float4(acc[k][0], acc[k][1], acc[k][2], acc[k][3]);
+                o[1] = make_float4(acc[k][4], acc[k][5], acc[k][6], acc[k][7]);
+            }
+        }
+    }
+}
+
+template <int KH, int KQ>
+static __global__ void __launch_bounds__(256)
+pool_tail_bwd_warp_kernel(const float* __restrict__ g, const bf16* __restrict__ y, const bf16* __restrict__ e,
+                          const float* __restrict__ alpha, const float* __restrict__ w2, bf16* __restrict__ dz,
+                          float* __restrict__ dw2, float* __restrict__ db2, float* __restrict__ db1, int64_t n,
+                          int S, int SP, int H, int Q) {
+    extern __shared__ __align__(16) float red[];     // [2Q + 1]: dw2 | db1 | db2 partials of this block
+    const int lane = threadIdx.x & 31;
+    const int64_t nw = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int HC = H >> 3, QC = Q >> 3;
+    for (int q = threadIdx.x; q < 2 * Q + 1; q += blockDim.x) red[q] = 0.f;
+    __syncthreads();
+    float wv[KQ][8], a2[KQ][8], a1[KQ][8];
+#pragma unroll
+    for (int k = 0; k < KQ; ++k) {
+        const int c = lane + 32 * k;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            wv[k][j] = c < QC ? __ldg(w2 + c * 8 + j) : 0.f;
+            a2[k][j] = 0.f; a1[k][j] = 0.f;
+        }
+    }
+    float db2_acc = 0.f;
+    for (int64_t seq = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; seq < n; seq += nw) {
+        float gv[KH][8];
+#pragma unroll
+        for (int k = 0; k < KH; ++k) {
+            const int c = lane + 32 * k;
+            if (c < HC) {
+                const float4 x0 = ldg4(g + seq * H + c * 8), x1 = ldg4(g + seq * H + c * 8 + 4);
+                gv[k][0] = x0.x; gv[k][1] = x0.y; gv[k][2] = x0.z; gv[k][3] = x0.w;
+                gv[k][4] = x1.x; gv[k][5] = x1.y; gv[k][6] = x1.z; gv[k][7] = x1.w;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) gv[k][j] = 0.f;
+            }
+        }
+        // d alpha_s = g . y_s, kept by lane s % 32
+        const bf16* yt = y + seq * SP * H;
+        float d0 = 0.f, d1 = 0.f;
+#pragma unroll 4
+        for (int s = 0; s < S; ++s) {
+            float part = 0.f;
+#pragma unroll
+            for (int k = 0; k < KH; ++k) {
+                const int c = lane + 32 * k;
+                if (c < HC) {
+                    float f[8];
+                    bf8_to_f(__ldg((const uint4*)(yt + (int64_t)s * H) + c), f);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) part = fmaf(gv[k][j], f[j], part);
+                }
+            }
+            part = warp_sum(part);
+            if ((s & 31) == lane) { if (s < 32) d0 = part; else d1 = part; }
+        }
+        const float al0 = lane < S ? __ldg(alpha + seq * SP + lane) : 0.f;
+        const float al1 = lane + 32 < S ? __ldg(alpha + seq * SP + lane + 32) : 0.f;
+        const float c = warp_sum(fmaf(al0, d0, al1 * d1));
+        const float da0 = al0 * (d0 - c), da1 = al1 * (d1 - c);
+        db2_acc += da0 + da1;
+        // dz rows (pad rows written as zero), column sums for dw2 / db1
+        const bf16* et = e + seq * SP * Q;
+        bf16* zt = dz + seq * SP * Q;
+#pragma unroll 4
+        for (int s = 0; s < SP; ++s) {
+            const float d = __shfl_sync(0xffffffffu, s < 32 ? da0 : da1, s & 31);
+#pragma unroll
+            for (int k = 0; k < KQ; ++k) {
+                const int cq = lane + 32 * k;
+                if (cq < QC) {
+                    uint4 o = make_uint4(0u, 0u, 0u, 0u);
+                    if (s < S) {
+                        float f[8], z[8];
+                        bf8_to_f(__ldg((const uint4*)(et + (int64_t)s * Q) + cq), f);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            z[j] = d * wv[k][j] * (1.f - f[j] * f[j]);
+                            a2[k][j] = fmaf(d, f[j], a2[k][j]);
+                            a1[k][j] += z[j];
+                        }
+                        o = make_uint4(tc::pack_bf16(z[0], z[1]), tc::pack_bf16(z[2], z[3]), tc::pack_bf16(z[4], z[5]),
+                                       tc::pack_bf16(z[6], z[7]));
+                    }
+                    *((uint4*)(zt + (int64_t)s * Q) + cq) = o;
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < KQ; ++k) {
+        const int cq = lane + 32 * k;
+        if (cq < QC) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                atomicAdd(red + cq * 8 + j, a2[k][j]);
+                atomicAdd(red + Q + cq * 8 + j, a1[k][j]);
+            }
+        }
+    }
+    db2_acc = warp_sum(db2_acc);
+    if (lane == 0) atomicAdd(red + 2 * Q, db2_acc);
+    __syncthreads();
+    for (int q = threadIdx.x; q < Q; q += blockDim.x) {
+        atomicAdd(dw2 + q, red[q]);
+        atomicAdd(db1 + q, red[Q + q]);
+    }
+    if (threadIdx.x == 0) atomicAdd(db2, red[2 * Q]);
+}
+
 }  // namespace nr

@@ -491,7 +491,15 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
                         EpiTanhLogit{eb, Q, enc->p_b1, enc->p_w2, enc->p_b2, logits, 0.f}, st, "enc.fc1"))
         return e;
     ProfScope ps("enc.pool_fwd", st);
-    pool_tail_fwd_bf16_kernel<<<(unsigned)n, 128, p.SP * sizeof(float), st>>>(y, logits, enc->mask, out, alpha, S, p.SP, H);
+    if (p.SP <= 64 && (H & 7) == 0 && H <= 1024) {         // one warp per sequence
+        int64_t grid = (n + 7) / 8;
+        if (grid > (int64_t)sm_count() * 8) grid = (int64_t)sm_count() * 8;
+        if (H <= 256) pool_tail_fwd_warp_kernel<1><<<(unsigned)grid, 256, 0, st>>>(y, logits, enc->mask, out, alpha, n, S, p.SP, H);
+        else if (H <= 512) pool_tail_fwd_warp_kernel<2><<<(unsigned)grid, 256, 0, st>>>(y, logits, enc->mask, out, alpha, n, S, p.SP, H);
+        else pool_tail_fwd_warp_kernel<4><<<(unsigned)grid, 256, 0, st>>>(y, logits, enc->mask, out, alpha, n, S, p.SP, H);
+    } else {
+        pool_tail_fwd_bf16_kernel<<<(unsigned)n, 128, p.SP * sizeof(float), st>>>(y, logits, enc->mask, out, alpha, S, p.SP, H);
+    }
     return check_last("enc.pool_fwd");
 }
 
@@ -539,10 +547,22 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     }
     // 1. pooling tail backward: dz, dw2, db2, db1
     {
-        int64_t grid = n < 8 * (int64_t)sm_count() ? n : 8 * (int64_t)sm_count();
         ProfScope ps("enc.pool_bwd", st);
-        pool_tail_bwd_bf16_kernel<<<(unsigned)grid, 256, (H + p.SP + 2 * Q) * sizeof(float), st>>>(
-            g, y, eb, alpha, enc->p_w2, dz, gr->dp_w2, gr->dp_b2, gr->dp_b1, n, S, p.SP, H, Q);
+        if (p.SP <= 64 && (H & 7) == 0 && (Q & 7) == 0 && H <= 1024 && Q <= 512) {      // one warp per sequence
+            int64_t grid = (n + 7) / 8;
+            if (grid > (int64_t)sm_count() * 4) grid = (int64_t)sm_count() * 4;
+            const size_t sm = (2 * Q + 1) * sizeof(float);
+#define NR_POOL_BWD(KH, KQ) pool_tail_bwd_warp_kernel<KH, KQ><<<(unsigned)grid, 256, sm, st>>>( \
+                g, y, eb, alpha, enc->p_w2, dz, gr->dp_w2, gr->dp_b2, gr->dp_b1, n, S, p.SP, H, Q)
+            if (H <= 256) { if (Q <= 256) NR_POOL_BWD(1, 1); else NR_POOL_BWD(1, 2); }
+            else if (H <= 512) { if (Q <= 256) NR_POOL_BWD(2, 1); else NR_POOL_BWD(2, 2); }
+            else { if (Q <= 256) NR_POOL_BWD(4, 1); else NR_POOL_BWD(4, 2); }
+#undef NR_POOL_BWD
+        } else {
+            int64_t grid = n < 8 * (int64_t)sm_count() ? n : 8 * (int64_t)sm_count();
+            pool_tail_bwd_bf16_kernel<<<(unsigned)grid, 256, (H + p.SP + 2 * Q) * sizeof(float), st>>>(
+                g, y, eb, alpha, enc->p_w2, dz, gr->dp_w2, gr->dp_b2, gr->dp_b1, n, S, p.SP, H, Q);
+        }
         if (int e = check_last("enc.pool_bwd")) return e;
     }
     // 2. dW1 (Q,H) += dz^T . y
