@@ -68,34 +68,41 @@ struct EpiPoolDx {
     __device__ __forceinline__ void chunk(const EpiCtx& cx, int64_t, int col0, const float* v, int nc) {
         warm(col0 + 32, cx.n1);
         const float* gr = g + seq * H + col0;
+        // Branch-free body (selects and predicated loads only): a 4-bit keep nibble per column quad, forced to 0 for
+        // pad rows / columns beyond the tile so that those come out as exact zeros.
         uint32_t kb0 = 0xFFFFFFFFu, kb1 = 0xFFFFFFFFu;
         if (keep && real) {     // one byte per 4 elements, indexed by the padded row (written by the attention forward)
             const uint32_t* kp = (const uint32_t*)(keep + (((seq * SP + s) * H + col0) >> 2));
             kb0 = __ldg(kp);
             if (nc > 16) kb1 = __ldg(kp + 1);
         }
-        float o[32];
+        if (!real) kb0 = kb1 = 0u;
+        if (nc < 32) {          // nc % 4 == 0: drop the nibbles of quads >= nc / 4
+            const int q = nc >> 2;
+            kb0 = q >= 4 ? kb0 : (kb0 & ((1u << (8 * q)) - 1u));
+            kb1 = q <= 4 ? 0u : (kb1 & ((1u << (8 * (q - 4))) - 1u));
+        }
+        // all eight 16-byte loads of g are issued before the first use (one L1 round trip per chunk, not eight)
+        float4 gc[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) gc[j] = (real && 4 * j < nc) ? ldg4(gr + 4 * j) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float* out32 = dx32 ? dx32 + (seq * S + s) * ld + col0 : nullptr;       // POOL kind: fp32 (n,S,H), no pad rows
+        uint2* srow = (uint2*)(cx.stage + cx.lane * TC_STAGE_PITCH);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (real && 4 * j < nc) {
-                const float4 gv = ldg4(gr + 4 * j);
-                t = make_float4(fmaf(a, gv.x, v[4 * j]), fmaf(a, gv.y, v[4 * j + 1]), fmaf(a, gv.z, v[4 * j + 2]),
-                                fmaf(a, gv.w, v[4 * j + 3]));
-                if (keep) t = apply_keep4(t, ((j < 4 ? kb0 : kb1) >> (8 * (j & 3))) & 0xFu, dscale);
+            const uint32_t nib = (j < 4 ? kb0 : kb1) >> (8 * (j & 3));
+            float4 t;
+            t.x = (nib & 1u) ? fmaf(a, gc[j].x, v[4 * j]) * dscale : 0.f;
+            t.y = (nib & 2u) ? fmaf(a, gc[j].y, v[4 * j + 1]) * dscale : 0.f;
+            t.z = (nib & 4u) ? fmaf(a, gc[j].z, v[4 * j + 2]) * dscale : 0.f;
+            t.w = (nib & 8u) ? fmaf(a, gc[j].w, v[4 * j + 3]) * dscale : 0.f;
+            if (dx32) {
+                if (real && 4 * j < nc) *(float4*)(out32 + 4 * j) = t;
+            } else {
+                srow[j] = make_uint2(tc::pack_bf16(t.x, t.y), tc::pack_bf16(t.z, t.w));
             }
-            o[4 * j] = t.x; o[4 * j + 1] = t.y; o[4 * j + 2] = t.z; o[4 * j + 3] = t.w;
         }
-        if (dx32) {                 // POOL kind: fp32 (n,S,H) gradient, no pad rows
-            if (real) {
-                float* out32 = dx32 + (seq * S + s) * ld + col0;
-#pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    if (4 * j < nc) *(float4*)(out32 + 4 * j) = make_float4(o[4 * j], o[4 * j + 1], o[4 * j + 2], o[4 * j + 3]);
-            }
-        } else {
-            store_rows_bf16(cx, dY, ld, col0, o, nc);     // pad rows are written as zero
-        }
+        if (!dx32) flush_rows_bf16(cx, dY, ld, col0, nc);      // pad rows are written as zero
     }
 };
 

@@ -69,6 +69,9 @@ struct EpiCtx {
 // A thread-per-row epilogue writes 16 bytes per lane into 32 DIFFERENT rows per store instruction (32
 // L1 wavefronts, half-filled sectors).  This helper transposes the warp's 32 x 32 bf16 chunk through
 // shared memory so that every store instruction covers 8 rows x 64 contiguous bytes instead.
+// second half of store_rows_bf16: the lanes have written their rows into cx.stage (row = lane, 32 bf16)
+__device__ __forceinline__ void flush_rows_bf16(const EpiCtx& cx, __nv_bfloat16* C, int64_t ldc, int col0, int nc);
+
 __device__ __forceinline__ void store_rows_bf16(const EpiCtx& cx, __nv_bfloat16* C, int64_t ldc, int col0, const float* o,
                                                 int nc) {
     uint4* srow = (uint4*)(cx.stage + cx.lane * TC_STAGE_PITCH);
@@ -76,6 +79,10 @@ __device__ __forceinline__ void store_rows_bf16(const EpiCtx& cx, __nv_bfloat16*
     for (int j = 0; j < 4; ++j)
         srow[j] = make_uint4(tc::pack_bf16(o[8 * j], o[8 * j + 1]), tc::pack_bf16(o[8 * j + 2], o[8 * j + 3]),
                              tc::pack_bf16(o[8 * j + 4], o[8 * j + 5]), tc::pack_bf16(o[8 * j + 6], o[8 * j + 7]));
+    flush_rows_bf16(cx, C, ldc, col0, nc);
+}
+
+__device__ __forceinline__ void flush_rows_bf16(const EpiCtx& cx, __nv_bfloat16* C, int64_t ldc, int col0, int nc) {
     __syncwarp();
     const int c = (cx.lane & 3) * 8;
     if (nc == 32 && cx.row0 + 32 <= cx.M) {          // full chunk: straight-line code
