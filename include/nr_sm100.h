@@ -131,9 +131,12 @@ int nr_conv1d_k3_bwd(const nr_rows_t* rows, const float* w, const float* dy, flo
 
 /* ---- A8: NAML side view: dense(emb[ids]) (src/model/NAML.py:60-68) ---------------
  * out[i*out_stride : +H] = w (H,E) . emb[ids[i*ids_stride]] + b. */
+size_t nr_embed_dense_workspace(int64_t emb_rows, int32_t H);
+/* ws (>= nr_embed_dense_workspace bytes, or NULL): lets a small vocabulary (emb_rows <= n/2) go through the
+ * transformed table T = emb . w^T + b, the batch then only gathers rows of T */
 int nr_embed_dense_fwd(const float* emb, int64_t emb_rows, const int32_t* ids, int32_t ids_stride,
                        const float* w, const float* b, float* out, int64_t out_stride, int64_t n,
-                       int32_t E, int32_t H, void* stream);
+                       int32_t E, int32_t H, void* ws, size_t ws_bytes, void* stream);
 /* dout (row stride dout_stride) -> dw, db, demb ACCUMULATED (emb row 0 = padding_idx skipped) */
 int nr_embed_dense_bwd(const float* emb, int64_t emb_rows, const int32_t* ids, int32_t ids_stride,
                        const float* w, const float* dout, int64_t dout_stride, float* dw, float* db,

@@ -68,7 +68,8 @@ _SIGS = {
     'nr_conv1d_k3_workspace': (_SZ, [_I64, _I32, _I32, _I32, _I32]),
     'nr_conv1d_k3_fwd': (C.c_int, [_R, _P, _P, _P, _I64, _I32, _I32, _I32, _I32, _P, _SZ, _P]),
     'nr_conv1d_k3_bwd': (C.c_int, [_R, _P, _P, _P, _P, _P, _P, _I64, _I32, _I32, _I32, _I32, _P, _SZ, _P]),
-    'nr_embed_dense_fwd': (C.c_int, [_P, _I64, _P, _I32, _P, _P, _P, _I64, _I64, _I32, _I32, _P]),
+    'nr_embed_dense_workspace': (C.c_size_t, [_I64, _I32]),
+    'nr_embed_dense_fwd': (C.c_int, [_P, _I64, _P, _I32, _P, _P, _P, _I64, _I64, _I32, _I32, _P, C.c_size_t, _P]),
     'nr_embed_dense_bwd': (C.c_int, [_P, _I64, _P, _I32, _P, _P, _I64, _P, _P, _P, _I64, _I32, _I32, _P, _SZ, _P]),
     'nr_pad_blend_fwd': (C.c_int, [_P, _P, _P, _P, _I64, _I32, _I32, _P]),
     'nr_pad_blend_bwd': (C.c_int, [_P, _P, _P, _P, _I64, _I32, _I32, _P]),

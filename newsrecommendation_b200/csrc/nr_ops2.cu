@@ -9,6 +9,29 @@ namespace nr {
 int set_seed_salt_ops2(const void* p) { return set_seed_salt_this_tu(p); }
 }  // namespace nr
 
+namespace nr {
+__global__ void table_gather_kernel(const float* __restrict__ T, int64_t rows, const int32_t* __restrict__ ids,
+                                    int ids_stride, float* __restrict__ out, int64_t out_stride, int64_t n, int h4) {
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n * h4; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / h4;
+        const int q = (int)(t - i * h4);
+        int64_t id = __ldg(ids + i * ids_stride);
+        if (id < 0 || id >= rows) id = 0;
+        *(float4*)(out + i * out_stride + 4 * q) = __ldg((const float4*)(T + id * (int64_t)h4 * 4) + q);
+    }
+}
+__global__ void table_scatter_kernel(const float* __restrict__ dout, int64_t dout_stride, const int32_t* __restrict__ ids,
+                                     int ids_stride, int64_t rows, float* __restrict__ dT, int64_t n, int h4) {
+    for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < n * h4; t += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t i = t / h4;
+        const int q = (int)(t - i * h4);
+        int64_t id = __ldg(ids + i * ids_stride);
+        if (id < 0 || id >= rows) id = 0;
+        atomicAdd((float4*)(dT + id * (int64_t)h4 * 4) + q, ldg4(dout + i * dout_stride + 4 * q));
+    }
+}
+}  // namespace nr
+
 extern "C" {
 
 size_t nr_conv1d_k3_workspace(int64_t n, int32_t L, int32_t D, int32_t H, int32_t prec) {
@@ -61,26 +84,70 @@ int nr_conv1d_k3_bwd(const nr_rows_t* rows, const float* w, const float* dy, flo
     return 0;
 }
 
+// dense(emb[ids]) is linear, so for a small vocabulary (17 categories, 264 sub-categories against 7,040 news per
+// step) the layer is applied to the TABLE once — T = emb . w^T + b, (emb_rows, H) — and the batch only gathers rows
+// of T; backward scatter-adds dout into dT (emb_rows, H) and runs the three gradient products on emb_rows rows
+// instead of n.  Same fp32 arithmetic, different summation order.
+size_t nr_embed_dense_workspace(int64_t emb_rows, int32_t H) {
+    return emb_rows > 0 && H > 0 ? (size_t)emb_rows * H * sizeof(float) + 256 : 256;
+}
+
+static bool use_table(int64_t emb_rows, int64_t n, const void* ws, size_t ws_bytes, int H) {
+    return ws && emb_rows * 2 <= n && ws_bytes >= (size_t)emb_rows * H * sizeof(float) + 256;
+}
+
 int nr_embed_dense_fwd(const float* emb, int64_t emb_rows, const int32_t* ids, int32_t ids_stride,
                        const float* w, const float* b, float* out, int64_t out_stride, int64_t n, int32_t E,
-                       int32_t H, void* stream) {
+                       int32_t H, void* ws, size_t ws_bytes, void* stream) {
     NR_REQUIRE(emb && ids && w && b && out, "nr_embed_dense_fwd: NULL pointer");
     NR_REQUIRE(emb_rows > 0 && ids_stride >= 1 && E > 0 && (E & 3) == 0 && H > 0 && (H & 3) == 0 &&
                    out_stride >= H && (out_stride & 3) == 0,
                "nr_embed_dense_fwd: unsupported shape E=%d H=%d", E, H);
     if (n == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (use_table(emb_rows, n, ws, ws_bytes, H)) {
+        float* T = (float*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+        if (int e = gemm_nt(DenseView{emb, E, emb_rows, E}, DenseView{w, E, H, E}, EpiBias{T, H, b}, emb_rows, H, E, st,
+                            "embed_dense.table"))
+            return e;
+        const int h4 = H >> 2;
+        int64_t blocks = (n * h4 + 255) / 256;
+        if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
+        ProfScope ps("embed_dense.gather", st);
+        table_gather_kernel<<<(unsigned)blocks, 256, 0, st>>>(T, emb_rows, ids, ids_stride, out, out_stride, n, h4);
+        return check_last("embed_dense.gather");
+    }
     return gemm_nt(EmbedView{emb, ids, ids_stride, n, E}, DenseView{w, E, H, E}, EpiBias{out, out_stride, b}, n, H,
-                   E, (cudaStream_t)stream, "embed_dense.fwd");
+                   E, st, "embed_dense.fwd");
 }
 
 int nr_embed_dense_bwd(const float* emb, int64_t emb_rows, const int32_t* ids, int32_t ids_stride,
                        const float* w, const float* dout, int64_t dout_stride, float* dw, float* db, float* demb,
                        int64_t n, int32_t E, int32_t H, void* ws, size_t ws_bytes, void* stream) {
-    (void)ws; (void)ws_bytes; (void)emb_rows;
     NR_REQUIRE(emb && ids && w && dout && dw && db && demb, "nr_embed_dense_bwd: NULL pointer");
     NR_REQUIRE(E > 0 && (E & 3) == 0 && H > 0 && (H & 3) == 0 && (dout_stride & 3) == 0, "nr_embed_dense_bwd: bad shape");
     if (n == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
+    if (use_table(emb_rows, n, ws, ws_bytes, H)) {
+        float* dT = (float*)(((uintptr_t)ws + 255) & ~(uintptr_t)255);
+        NR_CUDA(cudaMemsetAsync(dT, 0, (size_t)emb_rows * H * sizeof(float), st));
+        const int h4 = H >> 2;
+        int64_t blocks = (n * h4 + 255) / 256;
+        if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
+        {
+            ProfScope ps("embed_dense.scatter", st);
+            table_scatter_kernel<<<(unsigned)blocks, 256, 0, st>>>(dout, dout_stride, ids, ids_stride, emb_rows, dT, n, h4);
+            if (int e = check_last("embed_dense.scatter")) return e;
+        }
+        const DenseView dv{dT, H, emb_rows, H};
+        if (int e = gemm_tn(dv, DenseView{emb, E, emb_rows, E}, EpiAtomic{dw, E}, H, E, emb_rows, st, "embed_dense.dw"))
+            return e;
+        if (int e = colsum(dT, emb_rows, H, H, db, db, db, H, st)) return e;
+        if (emb_rows < 2) return 0;
+        // row 0 = padding_idx: no gradient (src/model/NAML.py:19,22)
+        return gemm_nt(DenseView{dT + H, H, emb_rows - 1, H}, TransView{w, H, E}, EpiAtomic{demb + E, E}, emb_rows - 1, E, H,
+                       st, "embed_dense.demb");
+    }
     const DenseView dv{dout, dout_stride, n, H};
     if (int e = gemm_tn(dv, EmbedView{emb, ids, ids_stride, n, E}, EpiAtomic{dw, E}, H, E, n, st, "embed_dense.dw"))
         return e;

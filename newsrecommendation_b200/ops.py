@@ -248,8 +248,9 @@ class EmbedDenseFn(torch.autograd.Function):
         E, H = embc.shape[1], wc.shape[0]
         out = torch.empty(n, H, dtype=torch.float32, device=wc.device)
         idp = ids.data_ptr() + 4 * col
+        ws = L.workspace(L.lib.nr_embed_dense_workspace(embc.shape[0], H), wc.device)
         L.call('nr_embed_dense_fwd', L.ptr(embc), embc.shape[0], idp, F, L.ptr(wc), L.ptr(bc), L.ptr(out), H, n,
-               E, H, L.stream())
+               E, H, L.ptr(ws), ws.numel(), L.stream())
         ctx.saved = (embc, ids, col, wc)
         ctx.params = (emb, w, b)
         return out
@@ -263,7 +264,7 @@ class EmbedDenseFn(torch.autograd.Function):
         pe, pw, pb = ctx.params
         (bemb, demb), (bw, dw) = _grad_target(pe, emb), _grad_target(pw, w)
         bb, db = _grad_target(pb, torch.empty(H, dtype=torch.float32, device=w.device))
-        ws = L.workspace(0, w.device)
+        ws = L.workspace(L.lib.nr_embed_dense_workspace(emb.shape[0], H), w.device)
         L.call('nr_embed_dense_bwd', L.ptr(emb), emb.shape[0], ids.data_ptr() + 4 * col, F, L.ptr(w), L.ptr(dout),
                H, L.ptr(bw), L.ptr(bb), L.ptr(bemb), n, E, H, L.ptr(ws), ws.numel(), L.stream())
         ctx.params = None
