@@ -76,7 +76,13 @@ struct PackArgs {
     int mode, H, Dm, ldt, rows, ldo, nmat;
     const float* b0; const float* b1; const float* b2;     // optional biases (modes 0 and 2)
 };
-static __global__ void pack_weights_kernel(PackArgs a, bf16* __restrict__ out) {
+// up to four packing jobs in ONE launch (blockIdx.y = job): the forward packs its two operands and the two
+// transposed operands the backward GEMMs need, so a step pays one ~5 us launch per encoder instead of four
+struct PackJobs { PackArgs a[4]; bf16* out[4]; };
+static __device__ __forceinline__ void pack_body(const PackArgs& a, bf16* __restrict__ out);
+static __global__ void pack_weights_multi_kernel(const PackJobs j) { pack_body(j.a[blockIdx.y], j.out[blockIdx.y]); }
+static __global__ void pack_weights_kernel(PackArgs a, bf16* __restrict__ out) { pack_body(a, out); }
+static __device__ __forceinline__ void pack_body(const PackArgs& a, bf16* __restrict__ out) {
     const int64_t total = (int64_t)a.rows * a.ldo;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
          t += (int64_t)gridDim.x * blockDim.x) {

@@ -185,9 +185,9 @@ struct Plan {
     int SP, ldx, Kp, HK, QK, K3, Nw;
     int64_t R;
     // save
-    size_t o_wb, o_w1b, o_bias, o_keep, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
+    size_t o_wb, o_w1b, o_w1t, o_wt, o_bias, o_keep, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
     // backward workspace
-    size_t o_dz, o_dy, o_dqkv, o_w1t, o_wt, ws_bytes;
+    size_t o_dz, o_dy, o_dqkv, ws_bytes;
 };
 
 Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
@@ -206,6 +206,9 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     auto take = [&](size_t bytes) { size_t r = o; o += (bytes + 1023) & ~size_t(1023); return r; };
     p.o_wb = take(pool ? 0 : (size_t)p.Nw * taps * p.Kp * 2);
     p.o_w1b = take((size_t)e->Q * p.HK * 2);
+    // transposed operands of the backward dX GEMMs, packed by the forward in the same launch
+    p.o_w1t = take((size_t)e->H * p.QK * 2);
+    p.o_wt = take(pool ? 0 : (e->kind == NR_ENC_MHSA ? (size_t)e->Dm * p.K3 * 2 : (size_t)e->Dm * 3 * p.HK * 2));
     p.o_bias = take((size_t)3 * e->H * 4);
     p.o_keep = take(e->out_drop_p > 0.f ? (size_t)p.R * e->H / 4 + 64 : 0);     // output-dropout keep bits, 1 byte / 4 elements
     p.o_xb = take(pool ? 0 : (size_t)p.R * p.ldx * 2);
@@ -219,8 +222,6 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     p.o_dz = take((size_t)p.R * e->Q * 2);
     p.o_dy = take(pool ? 0 : (size_t)p.R * e->H * 2);
     p.o_dqkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
-    p.o_w1t = take((size_t)e->H * p.QK * 2);
-    p.o_wt = take(pool ? 0 : (e->kind == NR_ENC_MHSA ? (size_t)e->Dm * p.K3 * 2 : (size_t)e->Dm * 3 * p.HK * 2));
     p.ws_bytes = o;
     return p;
 }
@@ -252,6 +253,20 @@ int pack(const PackArgs& a, bf16* out, cudaStream_t st) {
     const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
     ProfScope ps("enc.pack_w", st);
     pack_weights_kernel<<<blocks, 256, 0, st>>>(a, out);
+    return check_last("enc.pack_w");
+}
+
+int pack_multi(const PackArgs* a, bf16* const* out, int n, cudaStream_t st) {
+    PackJobs j;
+    int64_t most = 0;
+    for (int i = 0; i < n; ++i) {
+        j.a[i] = a[i]; j.out[i] = out[i];
+        const int64_t total = (int64_t)a[i].rows * a[i].ldo;
+        if (total > most) most = total;
+    }
+    const int blocks = (int)((most + 255) / 256 < 592 ? (most + 255) / 256 : 592);
+    ProfScope ps("enc.pack_w", st);
+    pack_weights_multi_kernel<<<dim3(blocks, n), 256, 0, st>>>(j);
     return check_last("enc.pack_w");
 }
 
@@ -453,18 +468,24 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         NR_REQUIRE(rows->mode == NR_ROWS_DENSE && rows->drop_p == 0.f, "%s: POOL kind takes dense rows without dropout", who);
         xb = y;                     // the staged input IS the pooling input
     }
-    // 1. weights -> bf16 GEMM operands
-    if (pool) {
-    } else if (enc->kind == NR_ENC_MHSA) {
-        if (int e = pack(PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3, enc->b[0], enc->b[1],
-                                  enc->b[2]}, wb, st))
-            return e;
-    } else {
-        if (int e = pack(PackArgs{enc->w[0], nullptr, nullptr, 2, H, Dm, p.Kp, H, 3 * p.Kp, 1, enc->b[0], nullptr, nullptr},
-                         wb, st))
-            return e;
+    // 1. weights -> bf16 GEMM operands (forward operands + the transposes backward needs), one launch
+    {
+        PackArgs ja[4];
+        bf16* jo[4];
+        int nj = 0;
+        ja[nj] = PackArgs{enc->p_w1, nullptr, nullptr, 0, Q, H, 0, Q, p.HK, 1}; jo[nj++] = w1b;
+        ja[nj] = PackArgs{enc->p_w1, nullptr, nullptr, 1, Q, H, 0, H, p.QK, 1}; jo[nj++] = (bf16*)(sv + p.o_w1t);
+        if (enc->kind == NR_ENC_MHSA) {
+            ja[nj] = PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3, enc->b[0], enc->b[1], enc->b[2]};
+            jo[nj++] = wb;
+            ja[nj] = PackArgs{enc->w[0], enc->w[1], enc->w[2], 1, H, Dm, 0, Dm, p.K3, 3}; jo[nj++] = (bf16*)(sv + p.o_wt);
+        } else if (!pool) {
+            ja[nj] = PackArgs{enc->w[0], nullptr, nullptr, 2, H, Dm, p.Kp, H, 3 * p.Kp, 1, enc->b[0], nullptr, nullptr};
+            jo[nj++] = wb;
+            ja[nj] = PackArgs{enc->w[0], nullptr, nullptr, 3, H, Dm, p.HK, Dm, 3 * p.HK, 1}; jo[nj++] = (bf16*)(sv + p.o_wt);
+        }
+        if (int e = pack_multi(ja, jo, nj, st)) return e;
     }
-    if (int e = pack(PackArgs{enc->p_w1, nullptr, nullptr, 0, Q, H, 0, Q, p.HK, 1}, w1b, st)) return e;
     // 2. stage rows: gather + input dropout + bf16, padded pitch
     {
         const RowsView xv = make_rows_view(rows, n, S, Dm);
@@ -537,21 +558,12 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     bf16* dz = (bf16*)(wsb + p.o_dz);
     bf16* dy = (bf16*)(wsb + p.o_dy);
     bf16* dqkv = (bf16*)(wsb + p.o_dqkv);
-    bf16* w1t = (bf16*)(wsb + p.o_w1t);
-    bf16* wt = (bf16*)(wsb + p.o_wt);
+    const bf16* w1t = (const bf16*)(sv + p.o_w1t);      // packed by the forward
+    const bf16* wt = (const bf16*)(sv + p.o_wt);
     const bool pool = enc->kind == NR_ENC_POOL;
     const bool want_dx = gr->dtable || gr->dx_dense;
     const int one = 0;
 
-    // transposed weights for the dX GEMMs
-    if (int e = pack(PackArgs{enc->p_w1, nullptr, nullptr, 1, Q, H, 0, H, p.QK, 1}, w1t, st)) return e;
-    if (want_dx && !pool) {
-        if (enc->kind == NR_ENC_MHSA) {
-            if (int e = pack(PackArgs{enc->w[0], enc->w[1], enc->w[2], 1, H, Dm, 0, Dm, p.K3, 3}, wt, st)) return e;
-        } else {
-            if (int e = pack(PackArgs{enc->w[0], nullptr, nullptr, 3, H, Dm, p.HK, Dm, 3 * p.HK, 1}, wt, st)) return e;
-        }
-    }
     // 1. pooling tail backward: dz, dw2, db2, db1
     {
         ProfScope ps("enc.pool_bwd", st);
