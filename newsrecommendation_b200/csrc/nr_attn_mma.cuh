@@ -187,36 +187,43 @@ struct Slots {
     int s[Cfg<DK>::SLOTS];          // row
     int so[Cfg<DK>::SLOTS];         // element offset in a shared tile
     int c[Cfg<DK>::SLOTS];          // column (q4*4)
-    __device__ __forceinline__ void init(int lane) {
+    int g1[Cfg<DK>::SLOTS];         // element offset in a global matrix of pitch H   (ctx, dctx)
+    int g3[Cfg<DK>::SLOTS];         // element offset in a global matrix of pitch 3H  (qkv, dqkv)
+    __device__ __forceinline__ void init(int lane, int H) {
 #pragma unroll
         for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
             const int idx = i * 32 + lane;
             s[i] = idx / Cfg<DK>::SLOTS;
             c[i] = (idx - s[i] * Cfg<DK>::SLOTS) * 4;
             so[i] = s[i] * Cfg<DK>::PITCH + c[i];
+            g1[i] = s[i] * H + c[i];
+            g3[i] = s[i] * 3 * H + c[i];
         }
     }
 };
 // asynchronous copy of a head slice into a shared tile (columns >= DK stay zero): the copies of item
 // i+1 are in flight while item i is computed (double buffer)
 template <int DK>
-__device__ __forceinline__ void prefetch_tile(bf16* tile, const bf16* src, int ld, const Slots<DK>& sl) {
+__device__ __forceinline__ void prefetch_tile(bf16* tile, const bf16* src, const int (&off)[Cfg<DK>::SLOTS],
+                                              const Slots<DK>& sl) {
+    const uint32_t t0 = tc::smem_u32(tile);
 #pragma unroll
     for (int i = 0; i < Cfg<DK>::SLOTS; ++i)
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(tc::smem_u32(tile + sl.so[i])),
-                     "l"(src + sl.s[i] * ld + sl.c[i]) : "memory");
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(t0 + 2u * (uint32_t)sl.so[i]), "l"(src + off[i])
+                     : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 // fp32 staging tile -> bf16 rows of dst (rows >= S written as zero)
 template <int DK>
-__device__ __forceinline__ void store_tile(bf16* dst, int ld, const float* os, int S, const Slots<DK>& sl) {
+__device__ __forceinline__ void store_tile(bf16* dst, const int (&off)[Cfg<DK>::SLOTS], const float* os, int S,
+                                           const Slots<DK>& sl) {
 #pragma unroll
     for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (sl.s[i] < S) v = *(const float4*)(os + sl.s[i] * DK + sl.c[i]);
-        st_bf4(dst + sl.s[i] * ld + sl.c[i], v);
+        st_bf4(dst + off[i], v);
     }
 }
 
@@ -239,22 +246,23 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     const int t = lane & 3;
     const int H = heads * DK;
     const float sl2 = scale * 1.4426950408889634f;
+    const uint64_t key = salted(seed);              // dropout key, once per kernel
     uint8_t* base = smem_raw + warp * fwd_smem_per_warp(DK);
     bf16* buf = (bf16*)base;                       // 2 stages x (Q | K | V)
     float* Os = (float*)(buf + 6 * TILE);
     for (int i = lane; i < 6 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
     Slots<DK> sl;
-    sl.init(lane);
+    sl.init(lane, H);
     const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
     int item = (int)blockIdx.x * 4 + warp;
     auto issue = [&](int it, int stage) {
         const int sq = it / heads;
         const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + (it - sq * heads) * DK;
         bf16* b = buf + stage * 3 * TILE;
-        prefetch_tile<DK>(b, src, 3 * H, sl);
-        prefetch_tile<DK>(b + TILE, src + H, 3 * H, sl);
-        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, 3 * H, sl);
+        prefetch_tile<DK>(b, src, sl.g3, sl);
+        prefetch_tile<DK>(b + TILE, src + H, sl.g3, sl);
+        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, sl.g3, sl);
         cp_async_commit();
     };
     if (item < items) issue(item, 0);
@@ -309,22 +317,25 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         mm_32xn<NT>(o, ap, bv);
         stage_out<NT, DK>(o, Os, lane, inv[0][0], inv[0][1], inv[1][0], inv[1][1]);
         __syncwarp();
-        bf16* dst = ctx + seq * 32 * H + head * DK;
+        // per-item bases once; per-slot offsets (s*H + c) come precomputed from sl.g1
+        const int64_t obase = seq * 32 * H + head * DK;              // ctx / keep-bit element index (padded rows)
+        const uint64_t ebase = (uint64_t)(seq * S * H + head * DK);  // dropout element index (real rows)
+        bf16* dst = ctx + obase;
 #pragma unroll
         for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
-            const int s = sl.s[i], c = sl.c[i];
+            const int s = sl.s[i];
             float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
             if (s < S) {
-                v = *(const float4*)(Os + s * DK + c);
+                v = *(const float4*)(Os + s * DK + sl.c[i]);
                 if (thr) {
                     // the 4 keep bits are saved (one byte per 4 elements, padded-row indexing) so that the
                     // backward epilogue reads a byte instead of re-running Philox
-                    const uint32_t bits = dropout4_bits((uint64_t)((seq * S + s) * H + head * DK + c), seed, NR_STREAM_OUT, thr);
+                    const uint32_t bits = dropout4_bits_key(ebase + (uint32_t)sl.g1[i], key, NR_STREAM_OUT, thr);
                     v = apply_keep4(v, bits, dscale);
-                    if (keep) keep[((seq * 32 + s) * H + head * DK + c) >> 2] = (uint8_t)bits;
+                    if (keep) keep[(obase + sl.g1[i]) >> 2] = (uint8_t)bits;
                 }
             }
-            st_bf4(dst + s * H + c, v);
+            st_bf4(dst + sl.g1[i], v);
         }
         __syncwarp();
     }
@@ -348,7 +359,7 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     for (int i = lane; i < 8 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
     Slots<DK> sl;
-    sl.init(lane);
+    sl.init(lane, H);
     const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
     int item = (int)blockIdx.x * 4 + warp;
     auto issue = [&](int it, int stage) {
@@ -356,10 +367,10 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         const int hd = it - sq * heads;
         const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + hd * DK;
         bf16* b = buf + stage * 4 * TILE;
-        prefetch_tile<DK>(b, src, 3 * H, sl);
-        prefetch_tile<DK>(b + TILE, src + H, 3 * H, sl);
-        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, 3 * H, sl);
-        prefetch_tile<DK>(b + 3 * TILE, dctx + (int64_t)sq * 32 * H + hd * DK, H, sl);
+        prefetch_tile<DK>(b, src, sl.g3, sl);
+        prefetch_tile<DK>(b + TILE, src + H, sl.g3, sl);
+        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, sl.g3, sl);
+        prefetch_tile<DK>(b + 3 * TILE, dctx + (int64_t)sq * 32 * H + hd * DK, sl.g1, sl);
         cp_async_commit();
     };
     if (item < items) issue(item, 0);
@@ -441,7 +452,7 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             stage_out<NT, DK>(dq, Os, lane, scale, scale, scale, scale);
         }
         __syncwarp();
-        store_tile<DK>(dst, 3 * H, Os, S, sl);
+        store_tile<DK>(dst, sl.g3, Os, S, sl);
         __syncwarp();
         // ---- key-major pass: S^T = K Q^T, dA^T = V dO^T; dK = dS^T Q / sqrt(dk), dV = A^T dO
         {
@@ -481,7 +492,7 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             mm_32xn<NT>(out, af, bf);
             stage_out<NT, DK>(out, Os, lane, scale, scale, scale, scale);
             __syncwarp();
-            store_tile<DK>(dst + H, 3 * H, Os, S, sl);
+            store_tile<DK>(dst + H, sl.g3, Os, S, sl);
             __syncwarp();
             c_to_a(s, af);
             load_b_cols<DK>(Gs, lane, bf);
@@ -489,7 +500,7 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             stage_out<NT, DK>(out, Os, lane, 1.f, 1.f, 1.f, 1.f);
         }
         __syncwarp();
-        store_tile<DK>(dst + 2 * H, 3 * H, Os, S, sl);
+        store_tile<DK>(dst + 2 * H, sl.g3, Os, S, sl);
         __syncwarp();
     }
 }
@@ -538,12 +549,13 @@ attn_fwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     const int t = lane & 3;
     const int H = heads * DK;
     const float sl2 = scale * 1.4426950408889634f;
+    const uint64_t key = salted(seed);              // dropout key, once per kernel
     bf16* buf = (bf16*)(smem_raw + warp * fwd_blk_smem_per_warp(DK, NB));      // Q | K | V, NB blocks each
     float* Os = (float*)(buf + 3 * NB * TILE);
     for (int i = lane; i < 3 * NB * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
     Slots<DK> sl;
-    sl.init(lane);
+    sl.init(lane, H);
     const int stride = (int)gridDim.x * 4;
     for (int item = (int)blockIdx.x * 4 + warp; item < items; item += stride) {
         const int64_t seq = item / heads;
@@ -553,7 +565,7 @@ attn_fwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         for (int m = 0; m < 3; ++m)
 #pragma unroll
             for (int b = 0; b < NB; ++b)
-                prefetch_tile<DK>(buf + (m * NB + b) * TILE, src + m * H + (int64_t)b * 32 * 3 * H, 3 * H, sl);
+                prefetch_tile<DK>(buf + (m * NB + b) * TILE, src + m * H + (int64_t)b * 32 * 3 * H, sl.g3, sl);
         cp_async_commit();
         cp_async_wait<0>();
         __syncwarp();
@@ -606,20 +618,22 @@ attn_fwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             }
             stage_out<NT, DK>(o, Os, lane, inv[0][0], inv[0][1], inv[1][0], inv[1][1]);
             __syncwarp();
-            bf16* dst = ctx + (seq * SPB + qb * 32) * H + head * DK;
+            const int64_t obase = (seq * SPB + qb * 32) * H + head * DK;
+            const uint64_t ebase = (uint64_t)((seq * S + qb * 32) * H + head * DK);
+            bf16* dst = ctx + obase;
 #pragma unroll
             for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
-                const int s = sl.s[i], c = sl.c[i], sa = qb * 32 + s;
+                const int s = sl.s[i], sa = qb * 32 + s;
                 float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (sa < S) {
-                    v = *(const float4*)(Os + s * DK + c);
+                    v = *(const float4*)(Os + s * DK + sl.c[i]);
                     if (thr) {
-                        const uint32_t bits = dropout4_bits((uint64_t)((seq * S + sa) * H + head * DK + c), seed, NR_STREAM_OUT, thr);
+                        const uint32_t bits = dropout4_bits_key(ebase + (uint32_t)sl.g1[i], key, NR_STREAM_OUT, thr);
                         v = apply_keep4(v, bits, dscale);
-                        if (keep) keep[((seq * SPB + sa) * H + head * DK + c) >> 2] = (uint8_t)bits;
+                        if (keep) keep[(obase + sl.g1[i]) >> 2] = (uint8_t)bits;
                     }
                 }
-                st_bf4(dst + s * H + c, v);
+                st_bf4(dst + sl.g1[i], v);
             }
             __syncwarp();
         }
@@ -643,7 +657,7 @@ attn_bwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     for (int i = lane; i < 4 * NB * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
     Slots<DK> sl;
-    sl.init(lane);
+    sl.init(lane, H);
     const int stride = (int)gridDim.x * 4;
     for (int item = (int)blockIdx.x * 4 + warp; item < items; item += stride) {
         const int64_t seq = item / heads;
@@ -654,8 +668,8 @@ attn_bwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         for (int b = 0; b < NB; ++b) {
 #pragma unroll
             for (int m = 0; m < 3; ++m)
-                prefetch_tile<DK>(buf + (m * NB + b) * TILE, src + m * H + (int64_t)b * 32 * 3 * H, 3 * H, sl);
-            prefetch_tile<DK>(buf + (3 * NB + b) * TILE, gsrc + (int64_t)b * 32 * H, H, sl);
+                prefetch_tile<DK>(buf + (m * NB + b) * TILE, src + m * H + (int64_t)b * 32 * 3 * H, sl.g3, sl);
+            prefetch_tile<DK>(buf + (3 * NB + b) * TILE, gsrc + (int64_t)b * 32 * H, sl.g1, sl);
         }
         cp_async_commit();
         cp_async_wait<0>();
@@ -731,7 +745,7 @@ attn_bwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             }
             stage_out<NT, DK>(dq, Os, lane, scale, scale, scale, scale);
             __syncwarp();
-            store_tile<DK>(dst + (int64_t)qb * 32 * 3 * H, 3 * H, Os, S - qb * 32, sl);
+            store_tile<DK>(dst + (int64_t)qb * 32 * 3 * H, sl.g3, Os, S - qb * 32, sl);
             __syncwarp();
         }
         // ---- key-major: dK = sum_qb dS^T Q / sqrt(dk), dV = sum_qb A^T dO
@@ -788,11 +802,11 @@ attn_bwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             }
             stage_out<NT, DK>(ok, Os, lane, scale, scale, scale, scale);
             __syncwarp();
-            store_tile<DK>(dst + H + (int64_t)kb * 32 * 3 * H, 3 * H, Os, S - kb * 32, sl);
+            store_tile<DK>(dst + H + (int64_t)kb * 32 * 3 * H, sl.g3, Os, S - kb * 32, sl);
             __syncwarp();
             stage_out<NT, DK>(ov, Os, lane, 1.f, 1.f, 1.f, 1.f);
             __syncwarp();
-            store_tile<DK>(dst + 2 * H + (int64_t)kb * 32 * 3 * H, 3 * H, Os, S - kb * 32, sl);
+            store_tile<DK>(dst + 2 * H + (int64_t)kb * 32 * 3 * H, sl.g3, Os, S - kb * 32, sl);
             __syncwarp();
         }
     }

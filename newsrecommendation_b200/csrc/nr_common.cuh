@@ -130,6 +130,12 @@ __device__ __forceinline__ uint32_t dropout4_bits(uint64_t e0, uint64_t seed, ui
     const uint4 r = philox4(salted(seed), sid, e0 >> 2);
     return (r.x >= thr ? 1u : 0u) | (r.y >= thr ? 2u : 0u) | (r.z >= thr ? 4u : 0u) | (r.w >= thr ? 8u : 0u);
 }
+// same bits with the salted key hoisted by the caller (key = salted(seed) once per kernel: inside a loop that also
+// stores to global memory the compiler has to re-load the salt for every call)
+__device__ __forceinline__ uint32_t dropout4_bits_key(uint64_t e0, uint64_t key, uint32_t sid, uint32_t thr) {
+    const uint4 r = philox4(key, sid, e0 >> 2);
+    return (r.x >= thr ? 1u : 0u) | (r.y >= thr ? 2u : 0u) | (r.z >= thr ? 4u : 0u) | (r.w >= thr ? 8u : 0u);
+}
 __device__ __forceinline__ float4 apply_keep4(float4 v, uint32_t bits, float scale) {
     v.x = (bits & 1u) ? v.x * scale : 0.f;
     v.y = (bits & 2u) ? v.y * scale : 0.f;
