@@ -34,8 +34,9 @@ __device__ __forceinline__ void st_bf4(bf16* p, float4 v) {
 // blockDim = (ldx/8, rows per block): threadIdx.x = 8-column chunk, threadIdx.y = row slot, so no
 // per-thread division by the row width and one id lookup (broadcast) per row.
 static __global__ void __launch_bounds__(256)
-stage_rows_kernel(RowsView x, bf16* __restrict__ xb, int R, int SP, int ldx) {
+stage_rows_kernel(RowsView x, bf16* __restrict__ xb, int R, int SP, int ldx, uint8_t* __restrict__ keep_in) {
     const int c = threadIdx.x * 8;
+    const uint64_t key = x.thr ? salted(x.seed) : 0;
     for (int row = blockIdx.x * blockDim.y + threadIdx.y; row < R; row += gridDim.x * blockDim.y) {
         const int seq = row / SP;
         const int s = row - seq * SP;
@@ -50,8 +51,14 @@ stage_rows_kernel(RowsView x, bf16* __restrict__ xb, int R, int SP, int ldx) {
             if (c < x.D) a = ldg4(src + c);
             if (c + 4 < x.D) b = ldg4(src + c + 4);
             if (x.thr) {
-                if (c < x.D) a = dropout4(a, (uint64_t)(r * x.D + c), x.seed, NR_STREAM_IN, x.thr, x.scale);
-                if (c + 4 < x.D) b = dropout4(b, (uint64_t)(r * x.D + c + 4), x.seed, NR_STREAM_IN, x.thr, x.scale);
+                // the 8 keep bits of this thread's columns are saved (1 byte, padded-row indexing) so that the
+                // enc.dx epilogue re-applies the mask from a 4-byte load instead of eight Philox calls per chunk
+                uint32_t bits = 0;
+                if (c < x.D) bits = dropout4_bits_key((uint64_t)(r * x.D + c), key, NR_STREAM_IN, x.thr);
+                if (c + 4 < x.D) bits |= dropout4_bits_key((uint64_t)(r * x.D + c + 4), key, NR_STREAM_IN, x.thr) << 4;
+                a = apply_keep4(a, bits & 0xFu, x.scale);
+                b = apply_keep4(b, bits >> 4, x.scale);
+                if (keep_in) keep_in[(int64_t)row * (ldx >> 3) + threadIdx.x] = (uint8_t)bits;
             }
             if (c <= x.D && x.D < c + 8) {           // the ones column
                 if (x.D < c + 4) a.x = 1.0f; else b.x = 1.0f;    // D % 4 == 0

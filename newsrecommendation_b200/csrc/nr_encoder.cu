@@ -110,6 +110,7 @@ struct EpiPoolDx {
 // scatter-add into the embedding-table gradient (id 0 = padding_idx skipped; NRMS.py:73, B7).
 struct EpiDx {
     float* dx_dense; float* dtable; RowsView x; int SP;
+    const uint8_t* keep_in; int kpitch;     // input-dropout keep bits saved by enc.stage: 1 byte per 8 columns
     int64_t seq; int s; int64_t id;
     __device__ __forceinline__ void begin(const EpiCtx& cx, int64_t row) {
         seq = row / SP; s = (int)(row - seq * SP);
@@ -126,11 +127,20 @@ struct EpiDx {
                    : (x.mode == NR_ROWS_TOKEN ? dtable + id * x.D : dtable + id * ((int64_t)x.S * x.D) + (int64_t)s * x.D))
                      + col0;
         const uint64_t e0 = (uint64_t)(r * x.D + col0);
+        uint32_t kb = 0xFFFFFFFFu;
+        if (x.thr && keep_in) {        // col0 is a multiple of 16 (BN % 16 == 0): 2-byte aligned, not always 4
+            const uint16_t* kp = (const uint16_t*)(keep_in + (seq * SP + s) * kpitch + (col0 >> 3));
+            kb = (uint32_t)__ldg(kp);
+            if (nc > 16) kb |= (uint32_t)__ldg(kp + 1) << 16;
+        }
 #pragma unroll
         for (int j = 0; j < 8; ++j) {      // nc % 4 == 0 (Dm % 4 == 0)
             if (4 * j < nc) {
                 float4 t = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                if (x.thr) t = dropout4(t, e0 + 4 * j, x.seed, NR_STREAM_IN, x.thr, x.scale);
+                if (x.thr) {
+                    if (keep_in) t = apply_keep4(t, (kb >> (4 * j)) & 0xFu, x.scale);
+                    else t = dropout4(t, e0 + 4 * j, x.seed, NR_STREAM_IN, x.thr, x.scale);
+                }
                 if (x.mode == NR_ROWS_DENSE) *(float4*)(dst + 4 * j) = t;
                 else atomicAdd((float4*)(dst + 4 * j), t);
             }
@@ -185,7 +195,7 @@ struct Plan {
     int SP, ldx, Kp, HK, QK, K3, Nw;
     int64_t R;
     // save
-    size_t o_wb, o_w1b, o_w1t, o_wt, o_bias, o_keep, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
+    size_t o_wb, o_w1b, o_w1t, o_wt, o_bias, o_keep, o_keep_in, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
     // backward workspace
     size_t o_dz, o_dy, o_dqkv, ws_bytes;
 };
@@ -211,6 +221,7 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     p.o_wt = take(pool ? 0 : (e->kind == NR_ENC_MHSA ? (size_t)e->Dm * p.K3 * 2 : (size_t)e->Dm * 3 * p.HK * 2));
     p.o_bias = take((size_t)3 * e->H * 4);
     p.o_keep = take(e->out_drop_p > 0.f ? (size_t)p.R * e->H / 4 + 64 : 0);     // output-dropout keep bits, 1 byte / 4 elements
+    p.o_keep_in = take(pool ? 0 : (size_t)p.R * (p.ldx / 8) + 64);              // input-dropout keep bits, 1 byte / 8 columns
     p.o_xb = take(pool ? 0 : (size_t)p.R * p.ldx * 2);
     p.o_qkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
     p.o_y = take((size_t)p.R * e->H * 2);
@@ -496,7 +507,8 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         int64_t blocks = (p.R + ry - 1) / ry;
         if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
         ProfScope ps("enc.stage", st);
-        stage_rows_kernel<<<(unsigned)blocks, dim3(cx, ry), 0, st>>>(xv, xb, (int)p.R, p.SP, p.ldx);
+        stage_rows_kernel<<<(unsigned)blocks, dim3(cx, ry), 0, st>>>(xv, xb, (int)p.R, p.SP, p.ldx,
+                                                                     pool ? nullptr : (uint8_t*)(sv + p.o_keep_in));
         if (int e = check_last("enc.stage")) return e;
     }
     // 3. token mixer
@@ -603,7 +615,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
             return e;
         if (want_dx)
             if (int e = gemm_tc(dqkv, p.R, 3 * H, 3 * H, wt, Dm, p.K3, 1, &one, p.R,
-                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, 0, 0, 0}, st, "enc.dx"))
+                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0}, st, "enc.dx"))
                 return e;
     } else {
         const int sh[3] = {-1, 0, 1};
@@ -613,7 +625,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         if (want_dx) {
             const int shx[3] = {1, 0, -1};
             if (int e = gemm_tc(dy, p.R, H, H, wt, Dm, 3 * p.HK, 3, shx, p.R,
-                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, 0, 0, 0}, st, "enc.dx"))
+                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0}, st, "enc.dx"))
                 return e;
         }
     }

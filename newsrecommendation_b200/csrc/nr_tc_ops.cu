@@ -49,6 +49,9 @@ int nr_tc_gemm_nt(const void* A, int64_t a_rows, int32_t K, int64_t lda, const v
                   const int32_t* shifts_host, void* stream) {
     NR_REQUIRE(A && B && C, "nr_tc_gemm_nt: NULL pointer");
     NR_REQUIRE(M >= 0 && N > 0 && K > 0, "nr_tc_gemm_nt: bad sizes");
+    NR_REQUIRE(ldc >= N && (ldc % (c_bf16 ? 8 : 4)) == 0 && ((uintptr_t)C & 15) == 0,
+               "nr_tc_gemm_nt: C rows must be 16-byte aligned (ldc=%lld: multiple of %d elements)", (long long)ldc,
+               c_bf16 ? 8 : 4);
     int sh[3] = {0, 0, 0};
     for (int t = 0; t < taps && t < 3; ++t) sh[t] = shifts_host ? shifts_host[t] : 0;
     cudaStream_t st = (cudaStream_t)stream;

@@ -74,3 +74,11 @@ def test_tc_conv_taps():
     ref = torch.nn.functional.conv1d(xr.transpose(1, 2), torch.stack([wr[:, t * Dp:t * Dp + D] for t in range(3)], 2),
                                      b.double(), padding=1).transpose(1, 2)
     np.testing.assert_allclose(out.numpy(), ref.numpy(), rtol=1e-5, atol=2e-4)
+
+
+def test_tc_gemm_nt_rejects_misaligned_output():
+    """bf16 C rows must be 16-byte aligned (the epilogue stores 8 bf16 at a time): an error, not a fault."""
+    A = torch.zeros(256, 64, dtype=torch.bfloat16, device='cuda')
+    B = torch.zeros(300, 64, dtype=torch.bfloat16, device='cuda')
+    with pytest.raises(RuntimeError, match='16-byte aligned'):
+        tc_gemm(A, B, None, 256, c_bf16=True)          # out (256, 300): 600-byte rows
