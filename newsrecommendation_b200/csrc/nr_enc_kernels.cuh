@@ -461,7 +461,7 @@ pool_tail_fwd_warp_kernel(const bf16* __restrict__ y, const float* __restrict__ 
 #pragma unroll
             for (int j = 0; j < 8; ++j) acc[k][j] = 0.f;
         const bf16* yt = y + seq * SP * H;
-#pragma unroll 4
+#pragma unroll 8
         for (int s = 0; s < S; ++s) {
             const float a = __shfl_sync(0xffffffffu, s < 32 ? a0 : a1, s & 31);
 #pragma unroll
@@ -527,7 +527,7 @@ pool_tail_bwd_warp_kernel(const float* __restrict__ g, const bf16* __restrict__ 
         // d alpha_s = g . y_s, kept by lane s % 32
         const bf16* yt = y + seq * SP * H;
         float d0 = 0.f, d1 = 0.f;
-#pragma unroll 4
+#pragma unroll 8
         for (int s = 0; s < S; ++s) {
             float part = 0.f;
 #pragma unroll
@@ -551,7 +551,7 @@ pool_tail_bwd_warp_kernel(const float* __restrict__ g, const bf16* __restrict__ 
         // dz rows (pad rows written as zero), column sums for dw2 / db1
         const bf16* et = e + seq * SP * Q;
         bf16* zt = dz + seq * SP * Q;
-#pragma unroll 4
+#pragma unroll 8
         for (int s = 0; s < SP; ++s) {
             const float d = __shfl_sync(0xffffffffu, s < 32 ? da0 : da1, s & 31);
 #pragma unroll

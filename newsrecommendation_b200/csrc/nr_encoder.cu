@@ -531,12 +531,19 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
                         EpiTanhLogit{eb, Q, enc->p_b1, enc->p_w2, enc->p_b2, logits, 0.f}, st, "enc.fc1"))
         return e;
     ProfScope ps("enc.pool_fwd", st);
-    if (p.SP <= 64 && (H & 7) == 0 && H <= 1024) {         // one warp per sequence
-        int64_t grid = (n + 7) / 8;
-        if (grid > (int64_t)sm_count() * 8) grid = (int64_t)sm_count() * 8;
-        if (H <= 256) pool_tail_fwd_warp_kernel<1><<<(unsigned)grid, 256, 0, st>>>(y, logits, enc->mask, out, alpha, n, S, p.SP, H);
-        else if (H <= 512) pool_tail_fwd_warp_kernel<2><<<(unsigned)grid, 256, 0, st>>>(y, logits, enc->mask, out, alpha, n, S, p.SP, H);
-        else pool_tail_fwd_warp_kernel<4><<<(unsigned)grid, 256, 0, st>>>(y, logits, enc->mask, out, alpha, n, S, p.SP, H);
+    // one warp per sequence when there are enough sequences to fill the machine with warps; a few hundred long
+    // sequences (the user encoder: 128 x 50) are latency bound that way and keep the block-per-sequence kernel
+    if (p.SP <= 64 && (H & 7) == 0 && H <= 1024 && n >= 16 * (int64_t)sm_count()) {
+        auto launch = [&](auto kern) {
+            int per_sm = 1;
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, 0);
+            int64_t grid = (n + 7) / 8;                       // persistent warps, exactly one resident wave
+            if (grid > (int64_t)sm_count() * (per_sm > 0 ? per_sm : 1)) grid = (int64_t)sm_count() * (per_sm > 0 ? per_sm : 1);
+            kern<<<(unsigned)grid, 256, 0, st>>>(y, logits, enc->mask, out, alpha, n, S, p.SP, H);
+        };
+        if (H <= 256) launch(pool_tail_fwd_warp_kernel<1>);
+        else if (H <= 512) launch(pool_tail_fwd_warp_kernel<2>);
+        else launch(pool_tail_fwd_warp_kernel<4>);
     } else {
         pool_tail_fwd_bf16_kernel<<<(unsigned)n, 128, p.SP * sizeof(float), st>>>(y, logits, enc->mask, out, alpha, S, p.SP, H);
     }
@@ -579,12 +586,17 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     // 1. pooling tail backward: dz, dw2, db2, db1
     {
         ProfScope ps("enc.pool_bwd", st);
-        if (p.SP <= 64 && (H & 7) == 0 && (Q & 7) == 0 && H <= 1024 && Q <= 512) {      // one warp per sequence
-            int64_t grid = (n + 7) / 8;
-            if (grid > (int64_t)sm_count() * 4) grid = (int64_t)sm_count() * 4;
+        if (p.SP <= 64 && (H & 7) == 0 && (Q & 7) == 0 && H <= 1024 && Q <= 512 && n >= 16 * (int64_t)sm_count()) {
             const size_t sm = (2 * Q + 1) * sizeof(float);
-#define NR_POOL_BWD(KH, KQ) pool_tail_bwd_warp_kernel<KH, KQ><<<(unsigned)grid, 256, sm, st>>>( \
-                g, y, eb, alpha, enc->p_w2, dz, gr->dp_w2, gr->dp_b2, gr->dp_b1, n, S, p.SP, H, Q)
+            auto launch = [&](auto kern) {
+                int per_sm = 1;
+                cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, sm);
+                int64_t grid = (n + 7) / 8;                   // persistent warps, exactly one resident wave
+                if (grid > (int64_t)sm_count() * (per_sm > 0 ? per_sm : 1)) grid = (int64_t)sm_count() * (per_sm > 0 ? per_sm : 1);
+                kern<<<(unsigned)grid, 256, sm, st>>>(g, y, eb, alpha, enc->p_w2, dz, gr->dp_w2, gr->dp_b2, gr->dp_b1, n, S,
+                                                     p.SP, H, Q);
+            };
+#define NR_POOL_BWD(KH, KQ) launch(pool_tail_bwd_warp_kernel<KH, KQ>)
             if (H <= 256) { if (Q <= 256) NR_POOL_BWD(1, 1); else NR_POOL_BWD(1, 2); }
             else if (H <= 512) { if (Q <= 256) NR_POOL_BWD(2, 1); else NR_POOL_BWD(2, 2); }
             else { if (Q <= 256) NR_POOL_BWD(4, 1); else NR_POOL_BWD(4, 2); }

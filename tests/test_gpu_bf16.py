@@ -164,3 +164,36 @@ def test_bf16_matches_fp32_path_with_dropout(kind):
     for k in g32:
         _cmp_grad(k, g16[k], g32[k].numpy(), floor=1e-3 * gmax, errs=errs)
     assert not errs, '\n'.join(errs)
+
+
+@pytest.mark.parametrize('n,S,masked', [(2600, 30, False), (2500, 50, True), (300, 50, True), (2400, 3, False)])
+def test_bf16_pooling_matches_fp32_op(n, S, masked):
+    """AttentionPooling (model_utils.py:7-31) in bf16 tensor-core mode vs the fp32 op, forward and all gradients.
+    n >= 16 x SMs takes the warp-per-sequence tail kernels, smaller n the block-per-sequence ones."""
+    from newsrecommendation_b200.model import model_utils as MU
+    from newsrecommendation_b200 import _lib as L
+    torch.manual_seed(n + S)
+    outs = {}
+    x0 = (torch.randn(n, S, 400) * 0.5).cuda()
+    m = (torch.rand(n, S) > 0.3).float().cuda() if masked else None
+    if masked:
+        m[0] = 0
+    gout = torch.randn(n, 400).cuda()
+    for prec in (L.PREC_FP32, L.PREC_BF16):
+        torch.manual_seed(1)
+        pool = MU.AttentionPooling(400, 200, prec).cuda()
+        x = x0.clone().requires_grad_(True)
+        out = pool(x, m)
+        out.backward(gout)
+        outs[prec] = (out.detach().cpu(), x.grad.cpu(), {k: p.grad.cpu() for k, p in pool.named_parameters()})
+    o32, dx32, g32 = outs[L.PREC_FP32]
+    o16, dx16, g16 = outs[L.PREC_BF16]
+    np.testing.assert_allclose(o16.numpy(), o32.numpy(), rtol=1e-2, atol=1e-2 * o32.abs().max().item())
+    errs = []
+    _cmp_grad('x', dx16, dx32.numpy(), errs=errs)
+    gmax = max(v.abs().max().item() for v in g32.values())
+    for k in g32:
+        _cmp_grad(k, g16[k], g32[k].numpy(), floor=1e-3 * gmax, errs=errs)
+    assert not errs, '\n'.join(errs)
+    if masked:
+        assert (o16[0] == 0).all()          # all-masked sequence -> exact zero (B1)
