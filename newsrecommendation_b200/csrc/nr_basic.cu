@@ -119,9 +119,24 @@ __global__ void pad_blend_fwd_kernel(const float* __restrict__ v, const float* _
     }
 }
 
-// dv = dout*m ; dpad += sum_r dout*(1-m).  grid.x blocks each own a strided set of rows.
+// dv = dout*m ; dpad += sum_r dout*(1-m).  grid.x blocks each own a strided set of rows; a thread owns one
+// 4-column group (H % 4 == 0) so every row is read and written with 16-byte accesses.
 __global__ void pad_blend_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ mask,
                                      float* __restrict__ dv, float* __restrict__ dpad, int64_t rows, int H) {
+    if ((H & 3) == 0) {
+        for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
+            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 8
+            for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
+                const float m = __ldg(mask + r), im = 1.f - m;
+                const float4 g = ldg4(dout + r * H + c);
+                *(float4*)(dv + r * H + c) = make_float4(g.x * m, g.y * m, g.z * m, g.w * m);
+                acc.x = fmaf(g.x, im, acc.x); acc.y = fmaf(g.y, im, acc.y); acc.z = fmaf(g.z, im, acc.z); acc.w = fmaf(g.w, im, acc.w);
+            }
+            atomicAdd(dpad + c, acc.x); atomicAdd(dpad + c + 1, acc.y); atomicAdd(dpad + c + 2, acc.z); atomicAdd(dpad + c + 3, acc.w);
+        }
+        return;
+    }
     for (int c = threadIdx.x; c < H; c += blockDim.x) {
         float acc = 0.f;
         for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
@@ -134,7 +149,21 @@ __global__ void pad_blend_bwd_kernel(const float* __restrict__ dout, const float
     }
 }
 
-// score + CE: one warp per sample.
+// score + CE: one warp per sample.  Each score is computed once (16-byte loads when H % 4 == 0) and kept by lane
+// k % 32, so the log-sum-exp needs no second pass over the vectors; C > 32 walks the candidates in groups of 32
+// with a running maximum.
+__device__ __forceinline__ float dot_row(const float* __restrict__ c, const float* __restrict__ u, int H, int lane) {
+    float s = 0.f;
+    if ((H & 3) == 0) {
+        for (int h = lane * 4; h < H; h += 128) {
+            const float4 a = ldg4(c + h), v = ldg4(u + h);
+            s = fmaf(a.x, v.x, s); s = fmaf(a.y, v.y, s); s = fmaf(a.z, v.z, s); s = fmaf(a.w, v.w, s);
+        }
+    } else {
+        for (int h = lane; h < H; h += 32) s = fmaf(__ldg(c + h), __ldg(u + h), s);
+    }
+    return warp_sum(s);
+}
 __global__ void score_ce_fwd_kernel(const float* __restrict__ cand, const float* __restrict__ user,
                                     const int64_t* __restrict__ label, float* __restrict__ score,
                                     float* __restrict__ per_sample, int64_t B, int C, int H) {
@@ -142,25 +171,21 @@ __global__ void score_ce_fwd_kernel(const float* __restrict__ cand, const float*
     const int64_t b = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (b >= B) return;
     const float* u = user + b * H;
-    float mx = -INFINITY, picked = 0.f;
+    float mx = -INFINITY, picked = 0.f, z = 0.f;
     int arg = 0;
     const int lab = (int)label[b];
-    for (int k = 0; k < C; ++k) {
-        const float* c = cand + (b * C + k) * H;
-        float s = 0.f;
-        for (int h = lane; h < H; h += 32) s = fmaf(__ldg(c + h), __ldg(u + h), s);
-        s = warp_sum(s);
-        if (lane == 0) score[b * C + k] = s;
-        if (s > mx) { mx = s; arg = k; }    // first maximum, as torch.argmax
-        if (k == lab) picked = s;
-    }
-    float z = 0.f;
-    for (int k = 0; k < C; ++k) {
-        const float* c = cand + (b * C + k) * H;
-        float s = 0.f;
-        for (int h = lane; h < H; h += 32) s = fmaf(__ldg(c + h), __ldg(u + h), s);
-        s = warp_sum(s);
-        z += expf(s - mx);
+    for (int k0 = 0; k0 < C; k0 += 32) {
+        float mine = -INFINITY, gmx = mx;
+        const int kn = C - k0 < 32 ? C - k0 : 32;
+        for (int j = 0; j < kn; ++j) {
+            const int k = k0 + j;
+            const float s = dot_row(cand + (b * C + k) * H, u, H, lane);
+            if (lane == j) { mine = s; score[b * C + k] = s; }
+            if (s > gmx) { gmx = s; arg = k; }      // first maximum, as torch.argmax
+            if (k == lab) picked = s;
+        }
+        z = z * expf(mx - gmx) + warp_sum(lane < kn ? expf(mine - gmx) : 0.f);     // exp(-inf) = 0 on the first group
+        mx = gmx;
     }
     if (lane == 0) {
         per_sample[b * 2 + 0] = (mx + logf(z)) - picked;
@@ -352,7 +377,9 @@ int nr_pad_blend_bwd(const float* dout, const float* mask, float* dv, float* dpa
                      int32_t H, void* stream) {
     NR_REQUIRE(dout && mask && dv && dpad, "nr_pad_blend_bwd: NULL pointer");
     if (n * T == 0) return 0;
-    int64_t g = n * T < 2 * sm_count() ? n * T : 2 * sm_count();
+    // every block ends with H atomics onto the same H addresses of dpad: the serial chain per address is the
+    // block count, so one block per SM (not more) and deep unrolling inside
+    int64_t g = n * T < sm_count() ? n * T : sm_count();
     ProfScope ps_pad_blend_bwd("pad_blend_bwd", (cudaStream_t)stream);
     pad_blend_bwd_kernel<<<(unsigned)g, 128, 0, (cudaStream_t)stream>>>(dout, mask, dv, dpad, n * T, H);
     return check_last("nr_pad_blend_bwd");

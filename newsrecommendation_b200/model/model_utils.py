@@ -93,4 +93,24 @@ def encode_both(news_encoder, cand_rows, hist_rows):
     one call over the concatenated rows gives the same vectors with half the launches."""
     nc = cand_rows.shape[0]
     v = news_encoder(torch.cat([cand_rows, hist_rows], dim=0))
-    return v[:nc], v[nc:]
+    return _SplitRows.apply(v, nc)
+
+
+class _SplitRows(torch.autograd.Function):
+    """v -> (v[:k], v[k:]).  Autograd's own slicing backward materialises two zero-filled full-size gradients and
+    adds them (2 fills + 2 copies + 1 add per step); the two incoming gradients are simply the halves of dv."""
+
+    @staticmethod
+    def forward(ctx, v, k):
+        ctx.k, ctx.n, ctx.tail = k, v.shape[0], v.shape[1:]
+        ctx.like = (v.dtype, v.device)
+        return v[:k], v[k:]
+
+    @staticmethod
+    def backward(ctx, ga, gb):
+        dt, dev = ctx.like
+        if ga is None:
+            ga = torch.zeros((ctx.k,) + tuple(ctx.tail), dtype=dt, device=dev)
+        if gb is None:
+            gb = torch.zeros((ctx.n - ctx.k,) + tuple(ctx.tail), dtype=dt, device=dev)
+        return torch.cat([ga, gb], dim=0), None
