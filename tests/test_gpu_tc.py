@@ -82,3 +82,31 @@ def test_tc_gemm_nt_rejects_misaligned_output():
     B = torch.zeros(300, 64, dtype=torch.bfloat16, device='cuda')
     with pytest.raises(RuntimeError, match='16-byte aligned'):
         tc_gemm(A, B, None, 256, c_bf16=True)          # out (256, 300): 600-byte rows
+
+
+@pytest.mark.parametrize('M,N,K,taps', [(76000 + 55, 1200, 320, 1), (20000, 304, 1200, 1), (640 + 5, 200, 400, 1),
+                                        (30000, 400, 320, 3)])
+def test_tc_gemm_nt_multicast_pairs(M, N, K, taps, monkeypatch):
+    """NR_TC_MC=1 (opt-in): clusters of two CTAs on adjacent m tiles, each TMA-multicasting half of the weight box
+    (odd m-tile counts leave the last pair with one dead CTA).  Checked on GPU in fp32 against torch matmul."""
+    monkeypatch.setenv('NR_TC_MC', '1')
+    g = torch.Generator(device='cpu').manual_seed(M + N + K)
+    A = (torch.randn(M, K, generator=g) * 0.5).to(torch.bfloat16).cuda()
+    B = (torch.randn(N, taps * K, generator=g) * 0.1).to(torch.bfloat16).cuda()
+    bias = torch.randn(N, generator=g).cuda()
+    shifts = (-1, 0, 1) if taps == 3 else (0,)
+    out = tc_gemm(A, B, bias, M, taps=taps, shifts=shifts, K=K)
+    Af = A.float()
+    ref = bias.float()[None, :].repeat(M, 1)
+    for t, sh in enumerate(shifts):
+        As = torch.zeros_like(Af)
+        if sh == 0:
+            As = Af
+        elif sh < 0:
+            As[-sh:] = Af[:sh]
+        else:
+            As[:-sh] = Af[sh:]
+        ref += As @ B[:, t * K:(t + 1) * K].float().t()
+    scale = ref.abs().max().item()
+    err = (out - ref).abs().max().item()
+    assert err <= 3e-5 * scale * np.sqrt(K * taps), (err, scale)
