@@ -1,0 +1,218 @@
+"""Host-side MIND file handling on either side of the hot path: what the driver
+(`main.py` here) needs from the reference's `preprocess.py` / `prepare_data.py`, restated so the same data
+directories and the same intermediate files work:
+
+* `read_news`, `get_doc_input`      — `src/preprocess.py:16-74` (news.tsv -> indices, category maps, `news_combined` columns)
+* `read_news_embeddings`            — `src/preprocess.py:227-232` (`title_embeddings.bpemb.npy.gz`), plus a raw
+                                      table file (`*.nrtab`) that is memory-mapped instead of gunzipped: the
+                                      2.3-5.8 GB gzip read is the reference's start-up cost
+* `prepare_training_data`, `prepare_testing_data` — `src/prepare_data.py:14-66`; byte-identical output files for
+                                      the same seed (same sequence of `random` draws), checked against files
+                                      the reference wrote (tests/golden/prepare_*.tsv)
+
+Pure host code: no device work happens here."""
+import gzip
+import os
+import random
+import struct
+
+import numpy as np
+
+TABLE_MAGIC = b'NRTAB1\x00\x00'
+TABLE_HEADER_BYTES = 256            # payload starts 256-byte aligned (rows are copied to HBM with 128-bit loads)
+TITLE_TABLE_GZ = 'title_embeddings.bpemb.npy.gz'
+TITLE_TABLE_RAW = 'title_embeddings.bpemb.nrtab'
+
+
+# ------------------------------------------------------------------------------------------------
+# news.tsv
+# ------------------------------------------------------------------------------------------------
+def _next_index(d, key):
+    """1-based index in order of first appearance (preprocess.py:8-13)."""
+    if key not in d:
+        d[key] = len(d) + 1
+
+
+def read_news(news_path, args, mode='train'):
+    """preprocess.py:16-45.  news: doc_id -> [category, subcategory]; news_index: doc_id -> 1-based row;
+    the category maps are only built in train mode and only for enabled flags."""
+    if mode not in ('train', 'test'):
+        raise ValueError('Wrong mode!')
+    news, news_index, category_dict, subcategory_dict = {}, {}, {}, {}
+    with open(news_path, 'r', encoding='utf-8') as f:
+        for ln, line in enumerate(f):
+            cols = line.strip('\n').split('\t')
+            if len(cols) != 8:
+                raise ValueError(f'{news_path}:{ln + 1}: expected 8 tab-separated columns, got {len(cols)}')
+            doc_id, category, subcategory = cols[0], cols[1], cols[2]
+            _next_index(news_index, doc_id)
+            if doc_id not in news:
+                news[doc_id] = [category, subcategory]
+            if mode == 'train':
+                if args.use_category:
+                    _next_index(category_dict, category)
+                if args.use_subcategory:
+                    _next_index(subcategory_dict, subcategory)
+    if mode == 'train':
+        return news, news_index, category_dict, subcategory_dict
+    return news, news_index
+
+
+def get_doc_input(news, news_index, category_dict, subcategory_dict, args):
+    """preprocess.py:49-74: (N+1, 1) int32 columns; the 'title' column of the fork is the row index itself
+    (F1), unseen categories map to 0, row 0 is the unknown-news row."""
+    n = len(news) + 1
+    rows = np.fromiter((news_index[d] for d in news), dtype=np.int64, count=len(news))
+    title = np.zeros((n, 1), dtype='int32')
+    title[rows, 0] = rows
+    cat = sub = None
+    if args.use_category:
+        cat = np.zeros((n, 1), dtype='int32')
+        cat[rows, 0] = np.fromiter((category_dict.get(news[d][0], 0) for d in news), dtype=np.int64, count=len(news))
+    if args.use_subcategory:
+        sub = np.zeros((n, 1), dtype='int32')
+        sub[rows, 0] = np.fromiter((subcategory_dict.get(news[d][1], 0) for d in news), dtype=np.int64, count=len(news))
+    return title, cat, sub
+
+
+def combine_news_columns(*cols):
+    """main.py:48,183: concatenate the present columns."""
+    return np.ascontiguousarray(np.concatenate([c for c in cols if c is not None], axis=-1))
+
+
+# ------------------------------------------------------------------------------------------------
+# title-embedding table
+# ------------------------------------------------------------------------------------------------
+def write_title_table(path, table):
+    """Raw table file: 256-byte header (magic, rows, cols, dtype code 0 = fp32 little-endian) + row-major
+    payload.  `cols` = L*D of the fork's per-news layout (NAML.py:104-107)."""
+    table = np.ascontiguousarray(table, dtype='<f4')
+    if table.ndim != 2:
+        raise ValueError('title table must be 2-D (N+1, L*D)')
+    head = TABLE_MAGIC + struct.pack('<qqq', table.shape[0], table.shape[1], 0)
+    tmp = str(path) + '.tmp'
+    with open(tmp, 'wb') as f:
+        f.write(head.ljust(TABLE_HEADER_BYTES, b'\x00'))
+        table.tofile(f)
+    os.replace(tmp, path)
+
+
+def read_title_table(path):
+    """Memory-maps a file written by `write_title_table` (read-only; `torch.from_numpy(np.asarray(...))` +
+    `.cuda()` streams it to HBM without a host copy of the decompressed array)."""
+    with open(path, 'rb') as f:
+        head = f.read(TABLE_HEADER_BYTES)
+    if len(head) != TABLE_HEADER_BYTES or head[:8] != TABLE_MAGIC:
+        raise ValueError(f'{path}: not a title table file')
+    rows, cols, code = struct.unpack('<qqq', head[8:32])
+    if code != 0 or rows <= 0 or cols <= 0:
+        raise ValueError(f'{path}: unsupported header (rows={rows}, cols={cols}, dtype code={code})')
+    if os.path.getsize(path) != TABLE_HEADER_BYTES + rows * cols * 4:
+        raise ValueError(f'{path}: size does not match its header (truncated?)')
+    return np.memmap(path, dtype='<f4', mode='r', offset=TABLE_HEADER_BYTES, shape=(rows, cols))
+
+
+def read_news_embeddings(data_dir, cache=False):
+    """preprocess.py:227-232.  Prefers the raw table next to the .npy.gz when it is at least as new;
+    `cache=True` writes it after a gzip read so the next start-up skips the gunzip."""
+    gz = os.path.join(data_dir, TITLE_TABLE_GZ)
+    raw = os.path.join(data_dir, TITLE_TABLE_RAW)
+    if os.path.exists(raw) and (not os.path.exists(gz) or os.path.getmtime(raw) >= os.path.getmtime(gz)):
+        return read_title_table(raw)
+    with gzip.GzipFile(gz, 'r') as f:
+        table = np.load(f)
+    if cache:
+        write_title_table(raw, table)
+    return table
+
+
+# ------------------------------------------------------------------------------------------------
+# behaviors.tsv -> per-rank files
+# ------------------------------------------------------------------------------------------------
+def _draw_negatives(neg, k):
+    """prepare_data.py:7-11: k negatives without replacement, the list repeated when it is too short."""
+    pool = neg if k <= len(neg) else neg * (k // len(neg) + 1)
+    return random.sample(pool, k)
+
+
+def prepare_training_data(train_data_dir, nGPU, npratio, seed):
+    """prepare_data.py:14-50: one line per positive of every impression that has both labels
+    (iid, uid, time, history, pos, 'neg neg ...'), shuffled, dealt round-robin to `behaviors_np{K}_{rank}.tsv`.
+    Uses the global `random` module in the reference's order (seed, one sample per positive, one shuffle)."""
+    random.seed(seed)
+    out = []
+    with open(os.path.join(train_data_dir, 'behaviors.tsv'), 'r', encoding='utf-8') as f:
+        for line in f:
+            iid, uid, time, history, imp = line.strip().split('\t')
+            pos, neg = [], []
+            for item in imp.split(' '):
+                nid, lab = item.split('-')
+                if lab == '1':
+                    pos.append(nid)
+                elif lab == '0':
+                    neg.append(nid)
+            if not pos or not neg:
+                continue
+            for p in pos:
+                out.append('\t'.join((iid, uid, time, history, p, ' '.join(_draw_negatives(neg, npratio)))) + '\n')
+    random.shuffle(out)
+    for r in range(nGPU):
+        with open(os.path.join(train_data_dir, f'behaviors_np{npratio}_{r}.tsv'), 'w') as f:
+            f.writelines(out[r::nGPU])
+    return len(out)
+
+
+def prepare_testing_data(test_data_dir, nGPU):
+    """prepare_data.py:53-66: line i -> `behaviors_{i % nGPU}.tsv`, unchanged."""
+    with open(os.path.join(test_data_dir, 'behaviors.tsv'), 'r', encoding='utf-8') as f:
+        lines = f.readlines()
+    for r in range(nGPU):
+        with open(os.path.join(test_data_dir, f'behaviors_{r}.tsv'), 'w') as f:
+            f.writelines(lines[r::nGPU])
+    return len(lines)
+
+
+def count_lines(path):
+    n = 0
+    with open(path, 'rb') as f:
+        for chunk in iter(lambda: f.read(1 << 20), b''):
+            n += chunk.count(b'\n')
+    return n
+
+
+# ------------------------------------------------------------------------------------------------
+# synthetic MIND-format directory (datasets are unavailable offline; used by tests and the demo)
+# ------------------------------------------------------------------------------------------------
+def write_synthetic_mind_dir(data_dir, n_news=300, n_impressions=400, L=20, D=300, seed=0, n_cat=6, n_sub=15,
+                             unknown_frac=0.03):
+    """news.tsv (8 columns), behaviors.tsv (5 columns, `id-label` impressions) and the gzipped
+    `(N+1, L*D)` title table in the layout `create_news_embeddings` writes (preprocess.py:112-168: row 0
+    zeros, titles zero-padded to L tokens)."""
+    os.makedirs(data_dir, exist_ok=True)
+    rs = np.random.RandomState(seed)
+    with open(os.path.join(data_dir, 'news.tsv'), 'w', encoding='utf-8') as f:
+        for i in range(1, n_news + 1):
+            f.write('\t'.join(['N%d' % i, 'cat%d' % rs.randint(n_cat), 'sub%d' % rs.randint(n_sub), 'title %d' % i,
+                               'abstract %d' % i, 'https://x/%d' % i, '[]', '[]']) + '\n')
+    table = np.zeros((n_news + 1, L, D), dtype=np.float32)
+    for i in range(1, n_news + 1):
+        n_tok = int(np.clip(round(rs.normal(11.5, 4)), 3, L))
+        table[i, :n_tok] = rs.normal(0, 0.4, size=(n_tok, D))
+    with gzip.GzipFile(os.path.join(data_dir, TITLE_TABLE_GZ), 'w', compresslevel=1) as f:
+        np.save(f, table.reshape(n_news + 1, L * D))
+
+    def nid():
+        return 'X%d' % rs.randint(1, 50) if rs.rand() < unknown_frac else 'N%d' % rs.randint(1, n_news + 1)
+
+    with open(os.path.join(data_dir, 'behaviors.tsv'), 'w', encoding='utf-8') as f:
+        for i in range(n_impressions):
+            hl = 0 if rs.rand() < 0.02 else int(min(80, rs.lognormal(3.0, 1.0)))
+            C = int(np.clip(rs.lognormal(3.2, 0.8), 2, 300))
+            labs = np.zeros(C, dtype=int)
+            labs[rs.choice(C, size=min(C - 1, rs.randint(1, 4)), replace=False)] = 1
+            if i % 57 == 56:
+                labs[:] = 0                      # all-negative impression: dropped by prepare, skipped by the metrics
+            f.write('\t'.join([str(i + 1), 'U%d' % rs.randint(1, 1000), '11/11/2019 9:05:58 AM',
+                               ' '.join(nid() for _ in range(hl)),
+                               ' '.join('%s-%d' % (nid(), l) for l in labs)]) + '\n')
+    return table.reshape(n_news + 1, L * D)
