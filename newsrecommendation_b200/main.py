@@ -64,6 +64,13 @@ def _init_rank(rank, args):
     return rank, world, distributed
 
 
+def _finish(distributed):
+    if distributed:
+        torch.cuda.synchronize()
+        dist.barrier(device_ids=[torch.cuda.current_device()])
+        dist.destroy_process_group()
+
+
 def _plugin(args):
     """main.py:63 `importlib.import_module(f'model.{args.model}')` resolved to this package's plugin."""
     if args.model is None:
@@ -97,6 +104,11 @@ def _embedding_table(data_dir, args):
     want = args.num_words_title * args.word_embedding_dim
     if table.shape[1] != want:
         raise ValueError(f'title table has {table.shape[1]} columns, --num_words_title x --word_embedding_dim = {want}')
+    if isinstance(table, np.memmap):          # read-only mapping: it is only ever copied (to HBM), never written
+        import warnings
+        with warnings.catch_warnings():
+            warnings.simplefilter('ignore')
+            table = torch.from_numpy(table)
     return table
 
 
@@ -185,8 +197,7 @@ def train(rank, args):
             logging.info(f'Model saved to {ckpt_path}.')
     if graphed is not None:
         graphed.close()
-    if distributed:
-        dist.barrier()
+    _finish(distributed)
     return model
 
 
@@ -254,8 +265,7 @@ def test(rank, args):
         # main.py:274-277: the distributed branch divides by ALL impressions, the single-process branch by the
         # scored ones; both are reported by reduce_eval_sums, the line printed is the reference's.
         print_metrics('*', red['total'], red['mean_total'] if distributed else red['mean_scored'])
-    if distributed:
-        dist.barrier()
+    _finish(distributed)
     return red, scores, metrics, valid
 
 

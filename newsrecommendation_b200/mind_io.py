@@ -184,7 +184,7 @@ def count_lines(path):
 # synthetic MIND-format directory (datasets are unavailable offline; used by tests and the demo)
 # ------------------------------------------------------------------------------------------------
 def write_synthetic_mind_dir(data_dir, n_news=300, n_impressions=400, L=20, D=300, seed=0, n_cat=6, n_sub=15,
-                             unknown_frac=0.03):
+                             unknown_frac=0.03, table_format='gz'):
     """news.tsv (8 columns), behaviors.tsv (5 columns, `id-label` impressions) and the gzipped
     `(N+1, L*D)` title table in the layout `create_news_embeddings` writes (preprocess.py:112-168: row 0
     zeros, titles zero-padded to L tokens)."""
@@ -195,11 +195,14 @@ def write_synthetic_mind_dir(data_dir, n_news=300, n_impressions=400, L=20, D=30
             f.write('\t'.join(['N%d' % i, 'cat%d' % rs.randint(n_cat), 'sub%d' % rs.randint(n_sub), 'title %d' % i,
                                'abstract %d' % i, 'https://x/%d' % i, '[]', '[]']) + '\n')
     table = np.zeros((n_news + 1, L, D), dtype=np.float32)
+    n_tok = np.clip(np.rint(rs.normal(11.5, 4, size=n_news + 1)), 3, L).astype(int)
     for i in range(1, n_news + 1):
-        n_tok = int(np.clip(round(rs.normal(11.5, 4)), 3, L))
-        table[i, :n_tok] = rs.normal(0, 0.4, size=(n_tok, D))
-    with gzip.GzipFile(os.path.join(data_dir, TITLE_TABLE_GZ), 'w', compresslevel=1) as f:
-        np.save(f, table.reshape(n_news + 1, L * D))
+        table[i, :n_tok[i]] = rs.normal(0, 0.4, size=(n_tok[i], D))
+    if table_format == 'gz':
+        with gzip.GzipFile(os.path.join(data_dir, TITLE_TABLE_GZ), 'w', compresslevel=1) as f:
+            np.save(f, table.reshape(n_news + 1, L * D))
+    else:                                        # large synthetic sets: skip the (slow) gzip, write the raw table
+        write_title_table(os.path.join(data_dir, TITLE_TABLE_RAW), table.reshape(n_news + 1, L * D))
 
     def nid():
         return 'X%d' % rs.randint(1, 50) if rs.rand() < unknown_frac else 'N%d' % rs.randint(1, n_news + 1)
