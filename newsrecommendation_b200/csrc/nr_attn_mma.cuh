@@ -128,6 +128,25 @@ __device__ __forceinline__ void c_to_a(const float (&c)[2][4][4], uint32_t (&a)[
             a[mt][ks][3] = tc::pack_bf16(c[mt][2 * ks + 1][2], c[mt][2 * ks + 1][3]);
         }
 }
+// 8 x 8 bf16 block transpose inside the warp (fragment layout in, fragment layout out)
+__device__ __forceinline__ uint32_t movm_t(uint32_t x) {
+    uint32_t y;
+    asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(y) : "r"(x));
+    return y;
+}
+// A fragments of a (32 x 32) matrix X -> A fragments of X^T.  Register r of a[mt][ks] is the 8 x 8 block
+// (rows mt*16 + 8*(r&1), cols ks*16 + 8*(r>>1)); the transpose swaps the tile indices and the two middle registers.
+__device__ __forceinline__ void transpose_a(const uint32_t (&a)[2][2][4], uint32_t (&t)[2][2][4]) {
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int ks = 0; ks < 2; ++ks) {
+            t[mt][ks][0] = movm_t(a[ks][mt][0]);
+            t[mt][ks][1] = movm_t(a[ks][mt][2]);
+            t[mt][ks][2] = movm_t(a[ks][mt][1]);
+            t[mt][ks][3] = movm_t(a[ks][mt][3]);
+        }
+}
 __device__ __forceinline__ void zero_c(float (&c)[2][4][4]) {
 #pragma unroll
     for (int mt = 0; mt < 2; ++mt)
@@ -227,12 +246,55 @@ __device__ __forceinline__ void store_tile(bf16* dst, const int (&off)[Cfg<DK>::
     }
 }
 
+// bf16 staging variants (backward: nothing but a scale is applied after the MMA, so the tile is rounded once,
+// here, and copied out as 8-byte chunks): half the staging bytes of the fp32 tile -> one more CTA per SM
+template <int NT, int DK>
+__device__ __forceinline__ void stage_out_bf(const float (&c)[2][NT][4], bf16* os, int lane, float mul) {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            const int col = nt * 8 + 2 * t;
+            if (col < DK) {
+                *(uint32_t*)(os + (mt * 16 + g) * DK + col) = tc::pack_bf16(c[mt][nt][0] * mul, c[mt][nt][1] * mul);
+                *(uint32_t*)(os + (mt * 16 + g + 8) * DK + col) = tc::pack_bf16(c[mt][nt][2] * mul, c[mt][nt][3] * mul);
+            }
+        }
+}
+template <int NT, int DK>
+__device__ __forceinline__ void stage_out_bf2(const float (&c)[2][NT][4], bf16* os, int lane, float m00, float m01, float m10,
+                                              float m11) {
+    const int g = lane >> 2, t = lane & 3;
+#pragma unroll
+    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+            const int col = nt * 8 + 2 * t;
+            if (col < DK) {
+                const float lo = mt == 0 ? m00 : m10, hi = mt == 0 ? m01 : m11;
+                *(uint32_t*)(os + (mt * 16 + g) * DK + col) = tc::pack_bf16(c[mt][nt][0] * lo, c[mt][nt][1] * lo);
+                *(uint32_t*)(os + (mt * 16 + g + 8) * DK + col) = tc::pack_bf16(c[mt][nt][2] * hi, c[mt][nt][3] * hi);
+            }
+        }
+}
+template <int DK>
+__device__ __forceinline__ void store_tile_bf(bf16* dst, const int (&off)[Cfg<DK>::SLOTS], const bf16* os, int S,
+                                              const Slots<DK>& sl) {
+#pragma unroll
+    for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
+        uint2 v = make_uint2(0u, 0u);
+        if (sl.s[i] < S) v = *(const uint2*)(os + sl.s[i] * DK + sl.c[i]);
+        *(uint2*)(dst + off[i]) = v;
+    }
+}
+
 __host__ __device__ constexpr int pitch_of(int DK) { return DK == 32 ? 40 : (DK == 8 ? 8 : 24); }
 __host__ __device__ constexpr size_t fwd_smem_per_warp(int DK) {
-    return (size_t)2 * 3 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 4;
+    return (size_t)2 * 3 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 2;
 }
 __host__ __device__ constexpr size_t bwd_smem_per_warp(int DK) {
-    return (size_t)2 * 4 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 4 + 64 * 4;
+    return (size_t)2 * 4 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 2;
 }
 
 template <int DK, bool MASK>
@@ -249,7 +311,7 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     const uint64_t key = salted(seed);              // dropout key, once per kernel
     uint8_t* base = smem_raw + warp * fwd_smem_per_warp(DK);
     bf16* buf = (bf16*)base;                       // 2 stages x (Q | K | V)
-    float* Os = (float*)(buf + 6 * TILE);
+    bf16* Os = buf + 6 * TILE;                   // bf16 staging tile (rounded once, after the final scale)
     for (int i = lane; i < 6 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
     Slots<DK> sl;
@@ -315,7 +377,8 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         load_b_cols<DK>(Vs, lane, bv);
         float o[2][NT][4];
         mm_32xn<NT>(o, ap, bv);
-        stage_out<NT, DK>(o, Os, lane, inv[0][0], inv[0][1], inv[1][0], inv[1][1]);
+        // 1/(1-p) of the output dropout is folded into the row normaliser: the epilogue only zeroes dropped elements
+        stage_out_bf2<NT, DK>(o, Os, lane, inv[0][0] * dscale, inv[0][1] * dscale, inv[1][0] * dscale, inv[1][1] * dscale);
         __syncwarp();
         // per-item bases once; per-slot offsets (s*H + c) come precomputed from sl.g1
         const int64_t obase = seq * 32 * H + head * DK;              // ctx / keep-bit element index (padded rows)
@@ -324,18 +387,19 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 #pragma unroll
         for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
             const int s = sl.s[i];
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            uint2 v = make_uint2(0u, 0u);
             if (s < S) {
-                v = *(const float4*)(Os + s * DK + sl.c[i]);
+                v = *(const uint2*)(Os + s * DK + sl.c[i]);
                 if (thr) {
                     // the 4 keep bits are saved (one byte per 4 elements, padded-row indexing) so that the
                     // backward epilogue reads a byte instead of re-running Philox
                     const uint32_t bits = dropout4_bits_key(ebase + (uint32_t)sl.g1[i], key, NR_STREAM_OUT, thr);
-                    v = apply_keep4(v, bits, dscale);
+                    v.x &= ((bits & 1u) ? 0x0000ffffu : 0u) | ((bits & 2u) ? 0xffff0000u : 0u);
+                    v.y &= ((bits & 4u) ? 0x0000ffffu : 0u) | ((bits & 8u) ? 0xffff0000u : 0u);
                     if (keep) keep[(obase + sl.g1[i]) >> 2] = (uint8_t)bits;
                 }
             }
-            st_bf4(dst + sl.g1[i], v);
+            *(uint2*)(dst + sl.g1[i]) = v;
         }
         __syncwarp();
     }
@@ -353,9 +417,7 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     const float sl2 = scale * 1.4426950408889634f;
     uint8_t* base = smem_raw + warp * bwd_smem_per_warp(DK);
     bf16* buf = (bf16*)base;                       // 2 stages x (Q | K | V | dO)
-    float* Os = (float*)(buf + 8 * TILE);
-    float* zinv = Os + 32 * DK;
-    float* rds = zinv + 32;
+    bf16* Os = buf + 8 * TILE;
     for (int i = lane; i < 8 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
     __syncwarp();
     Slots<DK> sl;
@@ -382,7 +444,7 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         const bf16* Ks = Qs + TILE;
         const bf16* Vs = Ks + TILE;
         const bf16* Gs = Vs + TILE;
-        float mcol[4][2], mrow[2][2];
+        float mcol[4][2];
 #pragma unroll
         for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
@@ -390,17 +452,14 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
                 const int col = nt * 8 + 2 * t + e;
                 mcol[nt][e] = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
             }
-#pragma unroll
-        for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                const int row = mt * 16 + g + 8 * h;
-                mrow[mt][h] = row < S ? (MASK ? __ldg(key_mask + seq * S + row) : 1.f) : 0.f;
-            }
         cp_async_wait<1>();
         __syncwarp();
         bf16* dst = dqkv + seq * 32 * 3 * H + head * DK;
-        // ---- query-major pass: A = P/Z, dA = dO V^T, dS = A (dA - rd), dQ = dS K / sqrt(dk)
+        // ---- A = P/Z, dA = dO V^T, dS = A (dA - rd); dQ = dS K / sqrt(dk).  The key-major operands
+        //      A^T and dS^T of dV = A^T dO and dK = dS^T Q are NOT recomputed (that was a second S^T = K Q^T,
+        //      dA^T = V dO^T and exp pass): every 8 x 8 bf16 block of the packed fragments is transposed in
+        //      registers with movmatrix, which turns the C-layout tile into A fragments of the transpose.
+        uint32_t at[2][2][4], dst_t[2][2][4];
         {
             float s[2][4][4], da[2][4][4];
             zero_c(s); zero_c(da);
@@ -433,74 +492,50 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
                 for (int h = 0; h < 2; ++h) {
                     const int row = mt * 16 + g + 8 * h;
                     const float zs = quad_sum(z[mt][h]), rs = quad_sum(rd[mt][h]);   // shuffles: all lanes, no branch
-                    inv[mt][h] = row < S ? 1.f / (zs + kEps) : 0.f;
+                    inv[mt][h] = row < S ? 1.f / (zs + kEps) : 0.f;                  // pad query rows: A = dS = 0
                     rd[mt][h] = rs * inv[mt][h];
-                    if (t == 0) { zinv[row] = inv[mt][h]; rds[row] = rd[mt][h]; }
                 }
 #pragma unroll
             for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
                 for (int nt = 0; nt < 4; ++nt)
 #pragma unroll
-                    for (int e = 0; e < 4; ++e)
-                        s[mt][nt][e] = s[mt][nt][e] * inv[mt][e >> 1] * (da[mt][nt][e] - rd[mt][e >> 1]);
+                    for (int e = 0; e < 4; ++e) {
+                        const float a = s[mt][nt][e] * inv[mt][e >> 1];
+                        s[mt][nt][e] = a;
+                        da[mt][nt][e] = a * (da[mt][nt][e] - rd[mt][e >> 1]);
+                    }
             uint32_t ads[2][2][4], bk[NT][2][2];
-            c_to_a(s, ads);
+            c_to_a(da, ads);
+            transpose_a(ads, dst_t);
+            {
+                uint32_t aa[2][2][4];
+                c_to_a(s, aa);
+                transpose_a(aa, at);
+            }
             load_b_cols<DK>(Ks, lane, bk);
             float dq[2][NT][4];
             mm_32xn<NT>(dq, ads, bk);
-            stage_out<NT, DK>(dq, Os, lane, scale, scale, scale, scale);
+            stage_out_bf<NT, DK>(dq, Os, lane, scale);
         }
         __syncwarp();
-        store_tile<DK>(dst, sl.g3, Os, S, sl);
+        store_tile_bf<DK>(dst, sl.g3, Os, S, sl);
         __syncwarp();
-        // ---- key-major pass: S^T = K Q^T, dA^T = V dO^T; dK = dS^T Q / sqrt(dk), dV = A^T dO
         {
-            float s[2][4][4], da[2][4][4];
-            zero_c(s); zero_c(da);
-            {
-                Frag<DK> fa, fb;
-                load_a<DK>(Ks, lane, fa); load_b_rows<DK>(Qs, lane, fb);
-                mm_32x32<DK>(s, fa, fb);
-                load_a<DK>(Vs, lane, fa); load_b_rows<DK>(Gs, lane, fb);
-                mm_32x32<DK>(da, fa, fb);
-            }
-            float zi[4][2], ri[4][2];
-#pragma unroll
-            for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-                for (int e = 0; e < 2; ++e) { zi[nt][e] = zinv[nt * 8 + 2 * t + e]; ri[nt][e] = rds[nt * 8 + 2 * t + e]; }
-            // s <- A^T, da <- dS^T
-#pragma unroll
-            for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-                for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float m = mrow[mt][e >> 1];
-                        const float zv = zi[nt][e & 1];
-                        const float mz = MASK ? m * zv : (m != 0.f ? zv : 0.f);
-                        float a = exp2_fast(s[mt][nt][e] * sl2) * mz;
-                        a = mz != 0.f ? a : 0.f;
-                        s[mt][nt][e] = a;
-                        da[mt][nt][e] = a * (da[mt][nt][e] - ri[nt][e & 1]);
-                    }
-            uint32_t af[2][2][4], bf[NT][2][2];
+            uint32_t bf[NT][2][2];
             float out[2][NT][4];
-            c_to_a(da, af);
             load_b_cols<DK>(Qs, lane, bf);
-            mm_32xn<NT>(out, af, bf);
-            stage_out<NT, DK>(out, Os, lane, scale, scale, scale, scale);
+            mm_32xn<NT>(out, dst_t, bf);                          // dK = dS^T Q / sqrt(dk)
+            stage_out_bf<NT, DK>(out, Os, lane, scale);
             __syncwarp();
-            store_tile<DK>(dst + H, sl.g3, Os, S, sl);
+            store_tile_bf<DK>(dst + H, sl.g3, Os, S, sl);
             __syncwarp();
-            c_to_a(s, af);
             load_b_cols<DK>(Gs, lane, bf);
-            mm_32xn<NT>(out, af, bf);
-            stage_out<NT, DK>(out, Os, lane, 1.f, 1.f, 1.f, 1.f);
+            mm_32xn<NT>(out, at, bf);                             // dV = A^T dO
+            stage_out_bf<NT, DK>(out, Os, lane, 1.f);
         }
         __syncwarp();
-        store_tile<DK>(dst + 2 * H, sl.g3, Os, S, sl);
+        store_tile_bf<DK>(dst + 2 * H, sl.g3, Os, S, sl);
         __syncwarp();
     }
 }

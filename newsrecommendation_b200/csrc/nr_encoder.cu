@@ -309,12 +309,17 @@ int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n
     const size_t smem = 4 * amma::fwd_smem_per_warp(DK);
     auto kern = amma::attn_fwd_mma_kernel<DK, MASK>;
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // adjacent heads of a title share 32-byte sectors (40-byte head slices of a 2400-byte row), and the four warps of a
+    // CTA fetch them at slightly different times: the L1 has to keep them, so the carve-out leaves it room (measured:
+    // max-shared carve-out = 1.5x slower)
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 70));
     const int64_t items = n * heads;
     NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
     int64_t grid = (items + 3) / 4;
     int per_sm = 1;
     NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
     if (per_sm < 1) per_sm = 1;
+    if (per_sm > 3) per_sm = 3;
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;    // persistent: one wave
     ProfScope ps("enc.attn_fwd", st);
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads, 1.0f / sqrtf((float)DK),
@@ -327,12 +332,17 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     const size_t smem = 4 * amma::bwd_smem_per_warp(DK);
     auto kern = amma::attn_bwd_mma_kernel<DK, MASK>;
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    // adjacent heads of a title share 32-byte sectors (40-byte head slices of a 2400-byte row), and the four warps of a
+    // CTA fetch them at slightly different times: the L1 has to keep them, so the carve-out leaves it room (measured:
+    // max-shared carve-out = 1.5x slower)
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 50));
     const int64_t items = n * heads;
     NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
     int64_t grid = (items + 3) / 4;
     int per_sm = 1;
     NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
     if (per_sm < 1) per_sm = 1;
+    if (per_sm > 2) per_sm = 2;
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
     ProfScope ps("enc.attn_bwd", st);
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
