@@ -312,14 +312,16 @@ int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n
     // adjacent heads of a title share 32-byte sectors (40-byte head slices of a 2400-byte row), and the four warps of a
     // CTA fetch them at slightly different times: the L1 has to keep them, so the carve-out leaves it room (measured:
     // max-shared carve-out = 1.5x slower)
-    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 70));
+    int cap = 3, carve = 70;
+    if (const char* e = getenv("NR_ATTN_FWD_CFG")) sscanf(e, "%d,%d", &cap, &carve);
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     const int64_t items = n * heads;
     NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
     int64_t grid = (items + 3) / 4;
     int per_sm = 1;
     NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
     if (per_sm < 1) per_sm = 1;
-    if (per_sm > 3) per_sm = 3;
+    if (per_sm > cap) per_sm = cap;
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;    // persistent: one wave
     ProfScope ps("enc.attn_fwd", st);
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads, 1.0f / sqrtf((float)DK),
@@ -335,17 +337,59 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     // adjacent heads of a title share 32-byte sectors (40-byte head slices of a 2400-byte row), and the four warps of a
     // CTA fetch them at slightly different times: the L1 has to keep them, so the carve-out leaves it room (measured:
     // max-shared carve-out = 1.5x slower)
-    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, 50));
+    int cap = 2, carve = 50;
+    if (const char* e = getenv("NR_ATTN_BWD_CFG")) sscanf(e, "%d,%d", &cap, &carve);
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     const int64_t items = n * heads;
     NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
     int64_t grid = (items + 3) / 4;
     int per_sm = 1;
     NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
     if (per_sm < 1) per_sm = 1;
-    if (per_sm > 2) per_sm = 2;
+    if (per_sm > cap) per_sm = cap;
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
     ProfScope ps("enc.attn_bwd", st);
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
+    return check_last("enc.attn_bwd");
+}
+// head-group variants: 4 adjacent heads per CTA, cooperative sector-exact loads and stores (heads % 4 == 0)
+template <int DK, bool MASK>
+int launch_attn_fwd_grp(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
+                        uint64_t seed, uint8_t* keep, cudaStream_t st) {
+    const size_t smem = 4 * amma::fwd_grp_smem_per_warp(DK);
+    auto kern = amma::attn_fwd_grp_kernel<DK, MASK>;
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (const char* e = getenv("NR_ATTN_CARVE")) NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e)));
+    const int64_t groups = n * (heads / 4);
+    NR_REQUIRE(groups < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)groups * 4);
+    int64_t grid = groups;
+    int per_sm = 1;
+    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (const char* e = getenv("NR_ATTN_CTAS")) { int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }
+    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;    // persistent: one wave
+    ProfScope ps("enc.attn_fwd", st);
+    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, groups, S, heads, 1.0f / sqrtf((float)DK),
+                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep);
+    return check_last("enc.attn_fwd");
+}
+template <int DK, bool MASK>
+int launch_attn_bwd_grp(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
+                        cudaStream_t st) {
+    const size_t smem = 4 * amma::bwd_grp_smem_per_warp(DK);
+    auto kern = amma::attn_bwd_grp_kernel<DK, MASK>;
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (const char* e = getenv("NR_ATTN_CARVE")) NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e)));
+    const int64_t groups = n * (heads / 4);
+    NR_REQUIRE(groups < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)groups * 4);
+    int64_t grid = groups;
+    int per_sm = 1;
+    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (const char* e = getenv("NR_ATTN_CTAS")) { int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }
+    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
+    ProfScope ps("enc.attn_bwd", st);
+    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, groups, S, heads, 1.0f / sqrtf((float)DK));
     return check_last("enc.attn_bwd");
 }
 // blocked variant: 32 < pitch <= 64 (the user encoder's 50 clicked titles)
@@ -388,10 +432,18 @@ int launch_attn_bwd_blk(const bf16* qkv, const float* mask, const bf16* dctx, bf
                               : launch_attn_fwd_blk<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st))
 #define NR_BLK_BWD(DKV) (mask ? launch_attn_bwd_blk<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st) \
                               : launch_attn_bwd_blk<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))
-#define NR_MMA_FWD(DKV) (mask ? launch_attn_fwd_mma<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st) \
-                              : launch_attn_fwd_mma<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st))
-#define NR_MMA_BWD(DKV) (mask ? launch_attn_bwd_mma<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st) \
-                              : launch_attn_bwd_mma<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))
+// the head-group kernels are correct and sector-exact but measured slower (two CTA barriers per group): opt-in
+static bool attn_grouped(int heads) { return heads % 4 == 0 && getenv("NR_ATTN_GROUPED"); }
+#define NR_MMA_FWD(DKV) (attn_grouped(heads)                                                                            \
+    ? (mask ? launch_attn_fwd_grp<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st)                              \
+            : launch_attn_fwd_grp<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st))                            \
+    : (mask ? launch_attn_fwd_mma<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st)                              \
+            : launch_attn_fwd_mma<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st)))
+#define NR_MMA_BWD(DKV) (attn_grouped(heads)                                                                            \
+    ? (mask ? launch_attn_bwd_grp<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st)                                      \
+            : launch_attn_bwd_grp<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))                                    \
+    : (mask ? launch_attn_bwd_mma<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st)                                      \
+            : launch_attn_bwd_mma<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st)))
 
 #define NR_ENC_DISPATCH_DK(dk, CALL)                                                   \
     switch (dk) {                                                                      \
