@@ -542,6 +542,290 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 
 
 // ---------------------------------------------------------------------------------------------------------------
+// Register-prefetch variants of the two kernels above.  cp.async.ca parks every in-flight chunk in an L1 line, so
+// the double-buffered kernels need shared memory for two stages AND L1 room for the stage in flight (with the
+// carve-out at maximum they run 1.5x slower); that caps them at 8-12 warps per SM.  Here the next item's chunks
+// are fetched with streaming loads (no L1 allocation) into registers while the current item is computed from a
+// SINGLE shared stage, and written to shared memory afterwards: half the shared memory per warp and no L1
+// dependence, i.e. more warps (and bytes in flight) per SM.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint2 ldg_stream8(const bf16* p) {
+    uint2 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
+}
+__host__ __device__ constexpr size_t fwd_rp_smem_per_warp(int DK) {
+    return (size_t)3 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 2;
+}
+__host__ __device__ constexpr size_t bwd_rp_smem_per_warp(int DK) {
+    return (size_t)4 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 2;
+}
+
+template <int DK, bool MASK>
+static __global__ void __launch_bounds__(128, 4)
+attn_fwd_rp_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
+                    int64_t items, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed,
+                    uint8_t* __restrict__ keep) {
+    constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int t = lane & 3;
+    const int H = heads * DK;
+    const float sl2 = scale * 1.4426950408889634f;
+    const uint64_t key = salted(seed);              // dropout key, once per kernel
+    uint8_t* base = smem_raw + warp * fwd_rp_smem_per_warp(DK);
+    bf16* buf = (bf16*)base;                       // ONE stage (Q | K | V): the next item waits in registers
+    bf16* Os = buf + 3 * TILE;                   // bf16 staging tile (rounded once, after the final scale)
+    for (int i = lane; i < 3 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncwarp();
+    Slots<DK> sl;
+    sl.init(lane, H);
+    const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
+    int item = (int)blockIdx.x * 4 + warp;
+    uint2 pf[3][Cfg<DK>::SLOTS];
+    auto fetch = [&](int it) {
+        const int sq = it / heads;
+        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + (it - sq * heads) * DK;
+#pragma unroll
+        for (int m = 0; m < 3; ++m)
+#pragma unroll
+            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) pf[m][i] = ldg_stream8(src + m * H + sl.g3[i]);
+    };
+    auto deposit = [&]() {
+#pragma unroll
+        for (int m = 0; m < 3; ++m)
+#pragma unroll
+            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) *(uint2*)(buf + m * TILE + sl.so[i]) = pf[m][i];
+    };
+    if (item < items) { fetch(item); deposit(); }
+    __syncwarp();
+    for (; item < items; item += stride) {
+        const int64_t seq = item / heads;
+        const int head = item - (int)seq * heads;
+        const bool more = (int64_t)item + stride < items;
+        if (more) fetch(item + stride);             // in flight during this item's math (registers, no L1 lines)
+        const bf16* Qs = buf;
+        const bf16* Ks = Qs + TILE;
+        const bf16* Vs = Ks + TILE;
+        float mk[4][2];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int col = nt * 8 + 2 * t + e;
+                mk[nt][e] = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
+            }
+        float acc[2][4][4];
+        zero_c(acc);
+        {
+            Frag<DK> fq, fk;
+            load_a<DK>(Qs, lane, fq);
+            load_b_rows<DK>(Ks, lane, fk);
+            mm_32x32<DK>(acc, fq, fk);
+        }
+        float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                    const float m = mk[nt][e & 1];
+                    float p = exp2_fast(acc[mt][nt][e] * sl2);
+                    if (MASK) p *= m;
+                    p = m != 0.f ? p : 0.f;                 // select, not a branch (inf * 0 guard for pad columns)
+                    acc[mt][nt][e] = p;
+                    z[mt][e >> 1] += p;
+                }
+        float inv[2][2];
+#pragma unroll
+        for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) inv[mt][h] = 1.f / (quad_sum(z[mt][h]) + kEps);    // model_utils.py:53
+        uint32_t ap[2][2][4], bv[NT][2][2];
+        c_to_a(acc, ap);
+        load_b_cols<DK>(Vs, lane, bv);
+        float o[2][NT][4];
+        mm_32xn<NT>(o, ap, bv);
+        // 1/(1-p) of the output dropout is folded into the row normaliser: the epilogue only zeroes dropped elements
+        stage_out_bf2<NT, DK>(o, Os, lane, inv[0][0] * dscale, inv[0][1] * dscale, inv[1][0] * dscale, inv[1][1] * dscale);
+        __syncwarp();
+        // per-item bases once; per-slot offsets (s*H + c) come precomputed from sl.g1
+        const int64_t obase = seq * 32 * H + head * DK;              // ctx / keep-bit element index (padded rows)
+        const uint64_t ebase = (uint64_t)(seq * S * H + head * DK);  // dropout element index (real rows)
+        bf16* dst = ctx + obase;
+#pragma unroll
+        for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
+            const int s = sl.s[i];
+            uint2 v = make_uint2(0u, 0u);
+            if (s < S) {
+                v = *(const uint2*)(Os + s * DK + sl.c[i]);
+                if (thr) {
+                    // the 4 keep bits are saved (one byte per 4 elements, padded-row indexing) so that the
+                    // backward epilogue reads a byte instead of re-running Philox
+                    const uint32_t bits = dropout4_bits_key(ebase + (uint32_t)sl.g1[i], key, NR_STREAM_OUT, thr);
+                    v.x &= ((bits & 1u) ? 0x0000ffffu : 0u) | ((bits & 2u) ? 0xffff0000u : 0u);
+                    v.y &= ((bits & 4u) ? 0x0000ffffu : 0u) | ((bits & 8u) ? 0xffff0000u : 0u);
+                    if (keep) keep[(obase + sl.g1[i]) >> 2] = (uint8_t)bits;
+                }
+            }
+            *(uint2*)(dst + sl.g1[i]) = v;
+        }
+        __syncwarp();                               // every lane is done with this item's tiles
+        if (more) deposit();
+        __syncwarp();
+    }
+}
+
+
+template <int DK, bool MASK>
+static __global__ void __launch_bounds__(128)
+attn_bwd_rp_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
+                    bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale) {
+    constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
+    extern __shared__ __align__(16) uint8_t smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int g = lane >> 2, t = lane & 3;
+    const int H = heads * DK;
+    const float sl2 = scale * 1.4426950408889634f;
+    uint8_t* base = smem_raw + warp * bwd_rp_smem_per_warp(DK);
+    bf16* buf = (bf16*)base;                       // ONE stage (Q | K | V | dO): the next item waits in registers
+    bf16* Os = buf + 4 * TILE;
+    for (int i = lane; i < 4 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
+    __syncwarp();
+    Slots<DK> sl;
+    sl.init(lane, H);
+    const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
+    int item = (int)blockIdx.x * 4 + warp;
+    uint2 pf[4][Cfg<DK>::SLOTS];
+    auto fetch = [&](int it) {
+        const int sq = it / heads;
+        const int hd = it - sq * heads;
+        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + hd * DK;
+        const bf16* gsrc = dctx + (int64_t)sq * 32 * H + hd * DK;
+#pragma unroll
+        for (int m = 0; m < 3; ++m)
+#pragma unroll
+            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) pf[m][i] = ldg_stream8(src + m * H + sl.g3[i]);
+#pragma unroll
+        for (int i = 0; i < Cfg<DK>::SLOTS; ++i) pf[3][i] = ldg_stream8(gsrc + sl.g1[i]);
+    };
+    auto deposit = [&]() {
+#pragma unroll
+        for (int m = 0; m < 4; ++m)
+#pragma unroll
+            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) *(uint2*)(buf + m * TILE + sl.so[i]) = pf[m][i];
+    };
+    if (item < items) { fetch(item); deposit(); }
+    __syncwarp();
+    for (; item < items; item += stride) {
+        const int64_t seq = item / heads;
+        const int head = item - (int)seq * heads;
+        const bool more = (int64_t)item + stride < items;
+        if (more) fetch(item + stride);
+        const bf16* Qs = buf;
+        const bf16* Ks = Qs + TILE;
+        const bf16* Vs = Ks + TILE;
+        const bf16* Gs = Vs + TILE;
+        float mcol[4][2];
+#pragma unroll
+        for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int col = nt * 8 + 2 * t + e;
+                mcol[nt][e] = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
+            }
+        bf16* dst = dqkv + seq * 32 * 3 * H + head * DK;
+        // ---- A = P/Z, dA = dO V^T, dS = A (dA - rd); dQ = dS K / sqrt(dk).  The key-major operands
+        //      A^T and dS^T of dV = A^T dO and dK = dS^T Q are NOT recomputed (that was a second S^T = K Q^T,
+        //      dA^T = V dO^T and exp pass): every 8 x 8 bf16 block of the packed fragments is transposed in
+        //      registers with movmatrix, which turns the C-layout tile into A fragments of the transpose.
+        uint32_t at[2][2][4], dst_t[2][2][4];
+        {
+            float s[2][4][4], da[2][4][4];
+            zero_c(s); zero_c(da);
+            {
+                Frag<DK> fa, fb;
+                load_a<DK>(Qs, lane, fa); load_b_rows<DK>(Ks, lane, fb);
+                mm_32x32<DK>(s, fa, fb);
+                load_a<DK>(Gs, lane, fa); load_b_rows<DK>(Vs, lane, fb);
+                mm_32x32<DK>(da, fa, fb);
+            }
+            float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, rd[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float m = mcol[nt][e & 1];
+                        float p = exp2_fast(s[mt][nt][e] * sl2);
+                        if (MASK) p *= m;
+                        p = m != 0.f ? p : 0.f;
+                        s[mt][nt][e] = p;
+                        z[mt][e >> 1] += p;
+                        rd[mt][e >> 1] = fmaf(p, da[mt][nt][e], rd[mt][e >> 1]);
+                    }
+            float inv[2][2];
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int row = mt * 16 + g + 8 * h;
+                    const float zs = quad_sum(z[mt][h]), rs = quad_sum(rd[mt][h]);   // shuffles: all lanes, no branch
+                    inv[mt][h] = row < S ? 1.f / (zs + kEps) : 0.f;                  // pad query rows: A = dS = 0
+                    rd[mt][h] = rs * inv[mt][h];
+                }
+#pragma unroll
+            for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) {
+                        const float a = s[mt][nt][e] * inv[mt][e >> 1];
+                        s[mt][nt][e] = a;
+                        da[mt][nt][e] = a * (da[mt][nt][e] - rd[mt][e >> 1]);
+                    }
+            uint32_t ads[2][2][4], bk[NT][2][2];
+            c_to_a(da, ads);
+            transpose_a(ads, dst_t);
+            {
+                uint32_t aa[2][2][4];
+                c_to_a(s, aa);
+                transpose_a(aa, at);
+            }
+            load_b_cols<DK>(Ks, lane, bk);
+            float dq[2][NT][4];
+            mm_32xn<NT>(dq, ads, bk);
+            stage_out_bf<NT, DK>(dq, Os, lane, scale);
+        }
+        __syncwarp();
+        store_tile_bf<DK>(dst, sl.g3, Os, S, sl);
+        __syncwarp();
+        {
+            uint32_t bf[NT][2][2];
+            float out[2][NT][4];
+            load_b_cols<DK>(Qs, lane, bf);
+            mm_32xn<NT>(out, dst_t, bf);                          // dK = dS^T Q / sqrt(dk)
+            stage_out_bf<NT, DK>(out, Os, lane, scale);
+            __syncwarp();
+            store_tile_bf<DK>(dst + H, sl.g3, Os, S, sl);
+            __syncwarp();
+            load_b_cols<DK>(Gs, lane, bf);
+            mm_32xn<NT>(out, at, bf);                             // dV = A^T dO
+            stage_out_bf<NT, DK>(out, Os, lane, 1.f);
+        }
+        __syncwarp();
+        store_tile_bf<DK>(dst + 2 * H, sl.g3, Os, S, sl);
+        __syncwarp();
+        if (more) deposit();
+        __syncwarp();
+    }
+}
+
+
+
+// ---------------------------------------------------------------------------------------------------------------
 // Head-group variants (heads % 4 == 0): the 4 warps of a CTA own 4 ADJACENT heads of one title, and the CTA moves
 // their data together.  A head slice is only DK*2 = 40 bytes of a 3H*2 = 2400-byte row, so a warp that copies its
 // own head touches 2-3 32-byte sectors per row and uses 40 of their 64-96 bytes; the neighbouring head (another

@@ -3,6 +3,7 @@
 // NAML (gather -> dropout -> Conv1d(k=3) -> additive pooling, src/model/NAML.py:47-56) and the NRMS
 // UserEncoder (NRMS.py:55-62) as one pipeline of tcgen05 GEMMs (nr_tc_gemm.cuh, nr_tc_gemm_tn.cuh)
 // with fused epilogues and fp32 SIMT tails (nr_enc_kernels.cuh).  Gradient math: SURVEY Appendix C.
+#include <string.h>
 #include "nr_enc_kernels.cuh"
 #include "nr_attn_mma.cuh"
 #include "nr_tc_gemm.cuh"
@@ -24,6 +25,26 @@ __device__ __forceinline__ float tanh_fast(float x) {      // MUFU.TANH, rel. er
     float y;
     asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
+}
+
+// 16 epilogue warps for the named GEMM?  NR_TC_EW16 = comma-separated kernel names (or "all"/"none"); default below.
+#ifndef NR_TC_EW16_DEFAULT
+#define NR_TC_EW16_DEFAULT "enc.pool_dx"   // measured: pool_dx 0.163 -> 0.139 ms; dx (L2 reductions) and qkv (operand delivery) do not gain
+#endif
+static bool tc_ew16(const char* what) {
+    const char* e = getenv("NR_TC_EW16");
+    if (!e) e = NR_TC_EW16_DEFAULT;
+    if (!strcmp(e, "all")) return true;
+    const char* hit = strstr(e, what);
+    if (!hit) return false;
+    const char c = hit[strlen(what)];
+    return c == 0 || c == ',';
+}
+template <class Epi>
+int gemm_tc_pick(const bf16* A, int64_t a_rows, int Kt_real, int64_t lda, const bf16* B, int N, int64_t ldb, int taps,
+                 const int* shifts, int64_t M, const Epi& epi, cudaStream_t st, const char* what) {
+    if (tc_ew16(what)) return gemm_tc<Epi, 16>(A, a_rows, Kt_real, lda, B, N, ldb, taps, shifts, M, epi, st, what);
+    return gemm_tc<Epi, 8>(A, a_rows, Kt_real, lda, B, N, ldb, taps, shifts, M, epi, st, what);
 }
 
 // AttentionPooling fc1 + tanh + fc2 (model_utils.py:21-23): e (bf16) = tanh(acc + b1);
@@ -352,6 +373,44 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
     return check_last("enc.attn_bwd");
 }
+// register-prefetch variants (single shared stage, streaming loads): the default for pitch-32 sequences
+template <int DK, bool MASK>
+int launch_attn_fwd_rp(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
+                       uint64_t seed, uint8_t* keep, cudaStream_t st) {
+    const size_t smem = 4 * amma::fwd_rp_smem_per_warp(DK);
+    auto kern = amma::attn_fwd_rp_kernel<DK, MASK>;
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t items = n * heads;
+    NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
+    int64_t grid = (items + 3) / 4;
+    int per_sm = 1;
+    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (const char* e = getenv("NR_ATTN_CTAS")) { int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }
+    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;    // persistent: one wave
+    ProfScope ps("enc.attn_fwd", st);
+    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads, 1.0f / sqrtf((float)DK),
+                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep);
+    return check_last("enc.attn_fwd");
+}
+template <int DK, bool MASK>
+int launch_attn_bwd_rp(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
+                       cudaStream_t st) {
+    const size_t smem = 4 * amma::bwd_rp_smem_per_warp(DK);
+    auto kern = amma::attn_bwd_rp_kernel<DK, MASK>;
+    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t items = n * heads;
+    NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
+    int64_t grid = (items + 3) / 4;
+    int per_sm = 1;
+    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (const char* e = getenv("NR_ATTN_CTAS")) { int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }
+    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
+    ProfScope ps("enc.attn_bwd", st);
+    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
+    return check_last("enc.attn_bwd");
+}
 // head-group variants: 4 adjacent heads per CTA, cooperative sector-exact loads and stores (heads % 4 == 0)
 template <int DK, bool MASK>
 int launch_attn_fwd_grp(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
@@ -434,16 +493,26 @@ int launch_attn_bwd_blk(const bf16* qkv, const float* mask, const bf16* dctx, bf
                               : launch_attn_bwd_blk<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))
 // the head-group kernels are correct and sector-exact but measured slower (two CTA barriers per group): opt-in
 static bool attn_grouped(int heads) { return heads % 4 == 0 && getenv("NR_ATTN_GROUPED"); }
-#define NR_MMA_FWD(DKV) (attn_grouped(heads)                                                                            \
-    ? (mask ? launch_attn_fwd_grp<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st)                              \
-            : launch_attn_fwd_grp<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st))                            \
-    : (mask ? launch_attn_fwd_mma<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st)                              \
-            : launch_attn_fwd_mma<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st)))
-#define NR_MMA_BWD(DKV) (attn_grouped(heads)                                                                            \
-    ? (mask ? launch_attn_bwd_grp<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st)                                      \
-            : launch_attn_bwd_grp<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))                                    \
-    : (mask ? launch_attn_bwd_mma<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st)                                      \
-            : launch_attn_bwd_mma<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st)))
+static bool attn_rp_fwd() { const char* e = getenv("NR_ATTN_RP"); return e && (atoi(e) & 1); }
+static bool attn_rp_bwd() { const char* e = getenv("NR_ATTN_RP"); return e && (atoi(e) & 2); }
+template <int DKV, bool MASK>
+int pick_attn_fwd(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p, uint64_t seed,
+                  uint8_t* keep, cudaStream_t st) {
+    if (attn_grouped(heads)) return launch_attn_fwd_grp<DKV, MASK>(qkv, mask, ctx, n, S, heads, p, seed, keep, st);
+    if (attn_rp_fwd()) return launch_attn_fwd_rp<DKV, MASK>(qkv, mask, ctx, n, S, heads, p, seed, keep, st);
+    return launch_attn_fwd_mma<DKV, MASK>(qkv, mask, ctx, n, S, heads, p, seed, keep, st);
+}
+template <int DKV, bool MASK>
+int pick_attn_bwd(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
+                  cudaStream_t st) {
+    if (attn_grouped(heads)) return launch_attn_bwd_grp<DKV, MASK>(qkv, mask, dctx, dqkv, n, S, heads, st);
+    if (attn_rp_bwd()) return launch_attn_bwd_rp<DKV, MASK>(qkv, mask, dctx, dqkv, n, S, heads, st);
+    return launch_attn_bwd_mma<DKV, MASK>(qkv, mask, dctx, dqkv, n, S, heads, st);
+}
+#define NR_MMA_FWD(DKV) (mask ? pick_attn_fwd<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st) \
+                              : pick_attn_fwd<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st))
+#define NR_MMA_BWD(DKV) (mask ? pick_attn_bwd<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st) \
+                              : pick_attn_bwd<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))
 
 #define NR_ENC_DISPATCH_DK(dk, CALL)                                                   \
     switch (dk) {                                                                      \
@@ -578,14 +647,14 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     if (pool) {
     } else if (enc->kind == NR_ENC_MHSA) {
         // K = Dm + 1: the ones column of Xb times the bias column of the packed weights
-        if (int e = gemm_tc(xb, p.R, Dm + 1, p.ldx, wb, 3 * H, p.Kp, 1, &one, p.R, TcEpiStoreBf16{qkv, 3 * H}, st, "enc.qkv"))
+        if (int e = gemm_tc_pick(xb, p.R, Dm + 1, p.ldx, wb, 3 * H, p.Kp, 1, &one, p.R, TcEpiStoreBf16{qkv, 3 * H}, st, "enc.qkv"))
             return e;
         if (int e = attn_fwd_b(qkv, enc->mask, y, n, S, p.SP, enc->heads, H / enc->heads, enc->out_drop_p, rows->seed,
                                enc->out_drop_p > 0.f ? (uint8_t*)(sv + p.o_keep) : nullptr, st))
             return e;
     } else {
         const int sh[3] = {-1, 0, 1};
-        if (int e = gemm_tc(xb, p.R, Dm + 1, p.ldx, wb, H, 3 * p.Kp, 3, sh, p.R, TcEpiStoreBf16{y, H}, st, "enc.conv"))
+        if (int e = gemm_tc_pick(xb, p.R, Dm + 1, p.ldx, wb, H, 3 * p.Kp, 3, sh, p.R, TcEpiStoreBf16{y, H}, st, "enc.conv"))
             return e;
     }
     // 4. additive attention: fc1 + tanh + fc2 in the GEMM epilogue, then the softmax-like tail
@@ -677,7 +746,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         EpiPoolDx ep{dy, pool ? gr->dx_dense : nullptr, H, alpha, g, S, p.SP, H,
                      enc->out_drop_p > 0.f ? (const uint8_t*)(sv + p.o_keep) : nullptr,
                      enc->out_drop_p > 0.f ? 1.f / (1.f - enc->out_drop_p) : 1.f, 0, 0, 0.f, false};
-        if (int e = gemm_tc(dz, p.R, Q, Q, w1t, H, p.QK, 1, &one, p.R, ep, st, "enc.pool_dx")) return e;
+        if (int e = gemm_tc_pick(dz, p.R, Q, Q, w1t, H, p.QK, 1, &one, p.R, ep, st, "enc.pool_dx")) return e;
     }
     if (pool) return 0;
     const RowsView xv = make_rows_view(rows, n, S, Dm);
@@ -688,7 +757,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
                                "enc.dwqkv"))
             return e;
         if (want_dx)
-            if (int e = gemm_tc(dqkv, p.R, 3 * H, 3 * H, wt, Dm, p.K3, 1, &one, p.R,
+            if (int e = gemm_tc_pick(dqkv, p.R, 3 * H, 3 * H, wt, Dm, p.K3, 1, &one, p.R,
                                 EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0}, st, "enc.dx"))
                 return e;
     } else {
@@ -698,7 +767,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
             return e;
         if (want_dx) {
             const int shx[3] = {1, 0, -1};
-            if (int e = gemm_tc(dy, p.R, H, H, wt, Dm, 3 * p.HK, 3, shx, p.R,
+            if (int e = gemm_tc_pick(dy, p.R, H, H, wt, Dm, 3 * p.HK, 3, shx, p.R,
                                 EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0}, st, "enc.dx"))
                 return e;
         }

@@ -25,7 +25,7 @@ namespace nr {
 
 constexpr int TC_BM = 128, TC_BK = 64, TC_THREADS = 320, TC_MAX_BN = 256;
 constexpr int TC_STAGE_PITCH = 40;                                  // epilogue staging: 80-byte rows (conflict-free 16-byte accesses)
-constexpr int TC_STAGE_BYTES = 8 * 32 * TC_STAGE_PITCH * 2;         // 8 epilogue warps
+constexpr int TC_STAGE_BYTES = 8 * 32 * TC_STAGE_PITCH * 2;         // 8 epilogue warps (x2 for 16)
 
 struct TcGemmParams {
     int64_t M;        // output rows
@@ -43,7 +43,7 @@ struct TcGemmParams {
 };
 
 inline size_t tc_stage_bytes(int BN) { return (size_t)TC_BM * TC_BK * 2 + (size_t)BN * TC_BK * 2; }
-inline size_t tc_smem_bytes(int BN, int stages) { return 1024 + stages * tc_stage_bytes(BN) + 256 + TC_STAGE_BYTES; }
+inline size_t tc_smem_bytes(int BN, int stages, int ew = 8) { return 1024 + stages * tc_stage_bytes(BN) + 256 + TC_STAGE_BYTES * (ew / 8); }
 inline bool tc_debug() {
     static const bool on = [] { const char* e = getenv("NR_TC_DEBUG"); return e && e[0] == '1'; }();
     return on;
@@ -119,8 +119,11 @@ __device__ __forceinline__ void flush_rows_bf16(const EpiCtx& cx, __nv_bfloat16*
     __syncwarp();
 }
 
-template <class Epi>
-__global__ void __launch_bounds__(TC_THREADS, 1)   // 10 warps: 3 on one SM sub-partition -> 168 registers is the hardware ceiling
+// EW = epilogue warps: 8 (two groups of 4, one per accumulator) or 16 (two groups per accumulator, each draining
+// half of the tile's 32-column chunks; 18 warps -> at most 112 registers per thread).  Functors that carry per-row
+// state across chunks (Epi::kRowState) need the whole row in one thread and stay at EW = 8.
+template <class Epi, int EW>
+__global__ void __launch_bounds__(64 + 32 * EW, 1)   // EW = 8: 10 warps, 3 on one SM sub-partition -> 168 registers is the ceiling
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmBh, const TcGemmParams p, const Epi epi_in) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -174,7 +177,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tc::prefetch_tmap(&tmB);
         // multicast mode: a stage is free only when BOTH CTAs' MMAs have retired it (the peer writes half of it)
         for (int s = 0; s < stages; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, mc ? 2 : 1); }
-        for (int a = 0; a < 2; ++a) { tc::mbar_init(tfull + a, 1); tc::mbar_init(tempty + a, 4); }
+        for (int a = 0; a < 2; ++a) { tc::mbar_init(tfull + a, 1); tc::mbar_init(tempty + a, EW / 2); }
         tc::mbar_init(bfull, 1);
         tc::fence_barrier_init();
     }
@@ -249,7 +252,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         // lanes [32*(w%4), +32) =====
         Epi epi = epi_in;
         const int q = warp & 3;
-        const int grp = (warp - 2) >> 2;
+        const int grp4 = (warp - 2) >> 2;            // EW = 8: 0..1; EW = 16: 0..3
+        const int grp = grp4 & 1;                    // accumulator
+        const int half = grp4 >> 1;                  // which half of the chunks (EW = 16)
         int mt, nt;
         for (int it = grp; tile_of(it, mt, nt); it += 2) {
             const int64_t m0 = (int64_t)mt * TC_BM;
@@ -257,30 +262,46 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const int64_t row = m0 + q * 32 + lane;
             const uint32_t t_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)grp * TC_MAX_BN;
             const int ncols = (p.N - n0 < p.BN) ? p.N - n0 : p.BN;
+            int c_lo = 0, c_hi = ncols;
+            if (EW == 16) {
+                const int split = ((ncols + 31) / 32 + 1) / 2 * 32;      // first half takes the extra chunk
+                if (half) c_lo = split < ncols ? split : ncols; else c_hi = split < ncols ? split : ncols;
+            }
             EpiCtx cx;
             cx.stage = epi_stage + (warp - 2) * 32 * TC_STAGE_PITCH;
             cx.lane = lane;
             cx.row0 = m0 + q * 32;
             cx.M = p.M;
             cx.live = row < p.M;
-            cx.n0 = n0; cx.n1 = n0 + ncols;
+            cx.n0 = n0 + c_lo; cx.n1 = n0 + c_hi;
             // begin() before the accumulator wait: its global loads (per-row scalars, the first chunk's
             // operands) are in flight while the MMA warp finishes the tile
             epi.begin(cx, row);
             tc::mbar_wait(tfull + grp, (uint32_t)(it >> 1) & 1u);
             tc::tc_fence_after();
             // two register buffers: the TMEM load of chunk i+1 is in flight while chunk i is processed
-            float va[32], vb[32];
-            tc::tmem_ld32(t_row, va);
-            for (int c = 0; c < ncols; c += 64) {
-                tc::tmem_ld_wait();
-                const bool has_b = c + 32 < ncols;
-                if (has_b) tc::tmem_ld32(t_row + (uint32_t)(c + 32), vb);
-                epi.chunk(cx, row, n0 + c, va, (ncols - c < 32) ? ncols - c : 32);
-                if (has_b) {
+            if (EW == 16) {
+                // 18 warps leave 96 registers per thread: one TMEM buffer; the other three epilogue groups of the SM
+                // sub-partition cover the TMEM round trip instead of a second register buffer
+                float va[32];
+                for (int c = c_lo; c < c_hi; c += 32) {
+                    tc::tmem_ld32(t_row + (uint32_t)c, va);
                     tc::tmem_ld_wait();
-                    if (c + 64 < ncols) tc::tmem_ld32(t_row + (uint32_t)(c + 64), va);
-                    epi.chunk(cx, row, n0 + c + 32, vb, (ncols - c - 32 < 32) ? ncols - c - 32 : 32);
+                    epi.chunk(cx, row, n0 + c, va, (c_hi - c < 32) ? c_hi - c : 32);
+                }
+            } else {
+                float va[32], vb[32];
+                if (c_lo < c_hi) tc::tmem_ld32(t_row + (uint32_t)c_lo, va);
+                for (int c = c_lo; c < c_hi; c += 64) {
+                    tc::tmem_ld_wait();
+                    const bool has_b = c + 32 < c_hi;
+                    if (has_b) tc::tmem_ld32(t_row + (uint32_t)(c + 32), vb);
+                    epi.chunk(cx, row, n0 + c, va, (c_hi - c < 32) ? c_hi - c : 32);
+                    if (has_b) {
+                        tc::tmem_ld_wait();
+                        if (c + 64 < c_hi) tc::tmem_ld32(t_row + (uint32_t)(c + 64), va);
+                        epi.chunk(cx, row, n0 + c + 32, vb, (c_hi - c - 32 < 32) ? c_hi - c - 32 : 32);
+                    }
                 }
             }
             epi.end(cx, row);
@@ -302,7 +323,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // A: (a_rows x Kt_real) bf16 with leading dimension lda; B: (N x b_cols) bf16 with leading dimension ldb
 // (b_cols = taps * Kt_pad).  Kt_pad = Kt_real rounded up to 64: A columns past Kt_real are zero filled
 // by TMA, so B's padding columns may hold anything finite (they multiply zeros).
-template <class Epi>
+template <class Epi, int EW = 8>
 int gemm_tc(const __nv_bfloat16* A, int64_t a_rows, int Kt_real, int64_t lda, const __nv_bfloat16* B, int N,
             int64_t ldb, int taps, const int* shifts, int64_t M, const Epi& epi, cudaStream_t st,
             const char* what) {
@@ -320,7 +341,7 @@ int gemm_tc(const __nv_bfloat16* A, int64_t a_rows, int Kt_real, int64_t lda, co
     p.BN = ((n16 + nt - 1) / nt + 15) / 16 * 16;
     p.n_tiles = (N + p.BN - 1) / p.BN;
     p.m_tiles = (int)((M + TC_BM - 1) / TC_BM);
-    const size_t budget = 227 * 1024 - 1024 - 256 - TC_STAGE_BYTES;
+    const size_t budget = 227 * 1024 - 1024 - 256 - TC_STAGE_BYTES * (EW / 8);
     int stages = (int)(budget / tc_stage_bytes(p.BN));
     if (stages > 8) stages = 8;
     NR_REQUIRE(stages >= 2, "%s: tile does not fit shared memory", what);
@@ -349,8 +370,8 @@ int gemm_tc(const __nv_bfloat16* A, int64_t a_rows, int Kt_real, int64_t lda, co
         return e;
     if (int e = make_tmap_bf16_2d(&tmBh, B, (uint64_t)N, (uint64_t)taps * p.Kt, (uint64_t)ldb, (uint32_t)(p.BN / 2), TC_BK))
         return e;
-    const size_t smem = p.b_res ? 1024 + b_slice + stages * a_stage + 256 + TC_STAGE_BYTES : tc_smem_bytes(p.BN, stages);
-    NR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const size_t smem = p.b_res ? 1024 + b_slice + stages * a_stage + 256 + TC_STAGE_BYTES * (EW / 8) : tc_smem_bytes(p.BN, stages, EW);
+    NR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<Epi, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (tc_debug())
         fprintf(stderr, "[nr] %s M=%lld N=%d K=%d taps=%d BN=%d tiles=%dx%d b_res=%d groups=%d stages=%d grid=%d smem=%zu\n", what,
                 (long long)M, N, Kt_real, taps, p.BN, p.m_tiles, p.n_tiles, p.b_res, p.groups, stages, grid, smem);
@@ -360,19 +381,19 @@ int gemm_tc(const __nv_bfloat16* A, int64_t a_rows, int Kt_real, int64_t lda, co
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeClusterDimension;
         at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-        cfg.blockDim = dim3(TC_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
+        cfg.blockDim = dim3(64 + 32 * EW); cfg.dynamicSmemBytes = smem; cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
         cfg.gridDim = dim3(2);
         int clusters = 0;
-        NR_CUDA(cudaOccupancyMaxActiveClusters(&clusters, gemm_tc_kernel<Epi>, &cfg));
+        NR_CUDA(cudaOccupancyMaxActiveClusters(&clusters, gemm_tc_kernel<Epi, EW>, &cfg));
         const int64_t pairs = (int64_t)((p.m_tiles + 1) / 2) * p.n_tiles;
         if (clusters < 1) clusters = 1;
         if (clusters > pairs) clusters = (int)pairs;
         cfg.gridDim = dim3(2 * clusters);
         if (tc_debug()) fprintf(stderr, "[nr] %s multicast pairs: %d clusters\n", what, clusters);
-        NR_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<Epi>, tmA, tmB, tmBh, p, epi));
+        NR_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<Epi, EW>, tmA, tmB, tmBh, p, epi));
         return check_last(what);
     }
-    gemm_tc_kernel<Epi><<<grid, TC_THREADS, smem, st>>>(tmA, tmB, tmBh, p, epi);
+    gemm_tc_kernel<Epi, EW><<<grid, 64 + 32 * EW, smem, st>>>(tmA, tmB, tmBh, p, epi);
     return check_last(what);
 }
 
