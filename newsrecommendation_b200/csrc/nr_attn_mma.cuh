@@ -12,7 +12,10 @@
 //   backward: both orientations are computed (S and S^T, dA and dA^T) so that every operand of the
 //             five gradient products is already in MMA fragment layout: dQ = dS K, dK = dS^T Q, dV = A^T dO.
 //
-// Layout: qkv (n*32, 3H) bf16 with q | k | v column blocks, head h at columns h*DK; pitch SP = 32.
+// Layout: qkv (n*32, 3H) bf16, pitch SP = 32.  Two column orders, chosen by the caller through (hs, ms) = element
+// strides between heads and between the q/k/v slices of a head: canonical q | k | v blocks (hs = DK, ms = H) or
+// HEAD-MAJOR [head][q|k|v] (hs = 3DK, ms = DK), where the three slices a warp needs are 6*DK contiguous bytes per row
+// instead of three 2*DK-byte pieces 2H bytes apart (fewer partially used 32-byte sectors).
 // Shared tiles are [32 rows][PITCH] bf16 with PITCH chosen per head width so that ldmatrix is bank
 // conflict free (48-byte rows for DK = 16/20, 80-byte rows for DK = 32, 16-byte rows for DK = 8) and the
 // k extent is covered by DK/16 full k-steps plus one 8-wide half step (m16n8k8) when DK % 16 != 0.
@@ -301,7 +304,7 @@ template <int DK, bool MASK>
 static __global__ void __launch_bounds__(128)
 attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
                     int64_t items, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed,
-                    uint8_t* __restrict__ keep) {
+                    uint8_t* __restrict__ keep, int hs, int ms) {
     constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -320,11 +323,11 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     int item = (int)blockIdx.x * 4 + warp;
     auto issue = [&](int it, int stage) {
         const int sq = it / heads;
-        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + (it - sq * heads) * DK;
+        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + (it - sq * heads) * hs;
         bf16* b = buf + stage * 3 * TILE;
         prefetch_tile<DK>(b, src, sl.g3, sl);
-        prefetch_tile<DK>(b + TILE, src + H, sl.g3, sl);
-        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, sl.g3, sl);
+        prefetch_tile<DK>(b + TILE, src + ms, sl.g3, sl);
+        prefetch_tile<DK>(b + 2 * TILE, src + 2 * ms, sl.g3, sl);
         cp_async_commit();
     };
     if (item < items) issue(item, 0);
@@ -408,7 +411,7 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 template <int DK, bool MASK>
 static __global__ void __launch_bounds__(128)
 attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
-                    bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale) {
+                    bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale, int hs, int ms) {
     constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -427,11 +430,11 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     auto issue = [&](int it, int stage) {
         const int sq = it / heads;
         const int hd = it - sq * heads;
-        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + hd * DK;
+        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + hd * hs;
         bf16* b = buf + stage * 4 * TILE;
         prefetch_tile<DK>(b, src, sl.g3, sl);
-        prefetch_tile<DK>(b + TILE, src + H, sl.g3, sl);
-        prefetch_tile<DK>(b + 2 * TILE, src + 2 * H, sl.g3, sl);
+        prefetch_tile<DK>(b + TILE, src + ms, sl.g3, sl);
+        prefetch_tile<DK>(b + 2 * TILE, src + 2 * ms, sl.g3, sl);
         prefetch_tile<DK>(b + 3 * TILE, dctx + (int64_t)sq * 32 * H + hd * DK, sl.g1, sl);
         cp_async_commit();
     };
@@ -454,7 +457,7 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             }
         cp_async_wait<1>();
         __syncwarp();
-        bf16* dst = dqkv + seq * 32 * 3 * H + head * DK;
+        bf16* dst = dqkv + seq * 32 * 3 * H + head * hs;
         // ---- A = P/Z, dA = dO V^T, dS = A (dA - rd); dQ = dS K / sqrt(dk).  The key-major operands
         //      A^T and dS^T of dV = A^T dO and dK = dS^T Q are NOT recomputed (that was a second S^T = K Q^T,
         //      dA^T = V dO^T and exp pass): every 8 x 8 bf16 block of the packed fragments is transposed in
@@ -528,583 +531,15 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             mm_32xn<NT>(out, dst_t, bf);                          // dK = dS^T Q / sqrt(dk)
             stage_out_bf<NT, DK>(out, Os, lane, scale);
             __syncwarp();
-            store_tile_bf<DK>(dst + H, sl.g3, Os, S, sl);
+            store_tile_bf<DK>(dst + ms, sl.g3, Os, S, sl);
             __syncwarp();
             load_b_cols<DK>(Gs, lane, bf);
             mm_32xn<NT>(out, at, bf);                             // dV = A^T dO
             stage_out_bf<NT, DK>(out, Os, lane, 1.f);
         }
         __syncwarp();
-        store_tile_bf<DK>(dst + 2 * H, sl.g3, Os, S, sl);
+        store_tile_bf<DK>(dst + 2 * ms, sl.g3, Os, S, sl);
         __syncwarp();
-    }
-}
-
-
-// ---------------------------------------------------------------------------------------------------------------
-// Register-prefetch variants of the two kernels above.  cp.async.ca parks every in-flight chunk in an L1 line, so
-// the double-buffered kernels need shared memory for two stages AND L1 room for the stage in flight (with the
-// carve-out at maximum they run 1.5x slower); that caps them at 8-12 warps per SM.  Here the next item's chunks
-// are fetched with streaming loads (no L1 allocation) into registers while the current item is computed from a
-// SINGLE shared stage, and written to shared memory afterwards: half the shared memory per warp and no L1
-// dependence, i.e. more warps (and bytes in flight) per SM.
-// ---------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ uint2 ldg_stream8(const bf16* p) {
-    uint2 v;
-    asm volatile("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
-    return v;
-}
-__host__ __device__ constexpr size_t fwd_rp_smem_per_warp(int DK) {
-    return (size_t)3 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 2;
-}
-__host__ __device__ constexpr size_t bwd_rp_smem_per_warp(int DK) {
-    return (size_t)4 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 2;
-}
-
-template <int DK, bool MASK>
-static __global__ void __launch_bounds__(128, 4)
-attn_fwd_rp_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
-                    int64_t items, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed,
-                    uint8_t* __restrict__ keep) {
-    constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int t = lane & 3;
-    const int H = heads * DK;
-    const float sl2 = scale * 1.4426950408889634f;
-    const uint64_t key = salted(seed);              // dropout key, once per kernel
-    uint8_t* base = smem_raw + warp * fwd_rp_smem_per_warp(DK);
-    bf16* buf = (bf16*)base;                       // ONE stage (Q | K | V): the next item waits in registers
-    bf16* Os = buf + 3 * TILE;                   // bf16 staging tile (rounded once, after the final scale)
-    for (int i = lane; i < 3 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
-    __syncwarp();
-    Slots<DK> sl;
-    sl.init(lane, H);
-    const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
-    int item = (int)blockIdx.x * 4 + warp;
-    uint2 pf[3][Cfg<DK>::SLOTS];
-    auto fetch = [&](int it) {
-        const int sq = it / heads;
-        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + (it - sq * heads) * DK;
-#pragma unroll
-        for (int m = 0; m < 3; ++m)
-#pragma unroll
-            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) pf[m][i] = ldg_stream8(src + m * H + sl.g3[i]);
-    };
-    auto deposit = [&]() {
-#pragma unroll
-        for (int m = 0; m < 3; ++m)
-#pragma unroll
-            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) *(uint2*)(buf + m * TILE + sl.so[i]) = pf[m][i];
-    };
-    if (item < items) { fetch(item); deposit(); }
-    __syncwarp();
-    for (; item < items; item += stride) {
-        const int64_t seq = item / heads;
-        const int head = item - (int)seq * heads;
-        const bool more = (int64_t)item + stride < items;
-        if (more) fetch(item + stride);             // in flight during this item's math (registers, no L1 lines)
-        const bf16* Qs = buf;
-        const bf16* Ks = Qs + TILE;
-        const bf16* Vs = Ks + TILE;
-        float mk[4][2];
-#pragma unroll
-        for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int col = nt * 8 + 2 * t + e;
-                mk[nt][e] = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
-            }
-        float acc[2][4][4];
-        zero_c(acc);
-        {
-            Frag<DK> fq, fk;
-            load_a<DK>(Qs, lane, fq);
-            load_b_rows<DK>(Ks, lane, fk);
-            mm_32x32<DK>(acc, fq, fk);
-        }
-        float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
-#pragma unroll
-        for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-            for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const float m = mk[nt][e & 1];
-                    float p = exp2_fast(acc[mt][nt][e] * sl2);
-                    if (MASK) p *= m;
-                    p = m != 0.f ? p : 0.f;                 // select, not a branch (inf * 0 guard for pad columns)
-                    acc[mt][nt][e] = p;
-                    z[mt][e >> 1] += p;
-                }
-        float inv[2][2];
-#pragma unroll
-        for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-            for (int h = 0; h < 2; ++h) inv[mt][h] = 1.f / (quad_sum(z[mt][h]) + kEps);    // model_utils.py:53
-        uint32_t ap[2][2][4], bv[NT][2][2];
-        c_to_a(acc, ap);
-        load_b_cols<DK>(Vs, lane, bv);
-        float o[2][NT][4];
-        mm_32xn<NT>(o, ap, bv);
-        // 1/(1-p) of the output dropout is folded into the row normaliser: the epilogue only zeroes dropped elements
-        stage_out_bf2<NT, DK>(o, Os, lane, inv[0][0] * dscale, inv[0][1] * dscale, inv[1][0] * dscale, inv[1][1] * dscale);
-        __syncwarp();
-        // per-item bases once; per-slot offsets (s*H + c) come precomputed from sl.g1
-        const int64_t obase = seq * 32 * H + head * DK;              // ctx / keep-bit element index (padded rows)
-        const uint64_t ebase = (uint64_t)(seq * S * H + head * DK);  // dropout element index (real rows)
-        bf16* dst = ctx + obase;
-#pragma unroll
-        for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
-            const int s = sl.s[i];
-            uint2 v = make_uint2(0u, 0u);
-            if (s < S) {
-                v = *(const uint2*)(Os + s * DK + sl.c[i]);
-                if (thr) {
-                    // the 4 keep bits are saved (one byte per 4 elements, padded-row indexing) so that the
-                    // backward epilogue reads a byte instead of re-running Philox
-                    const uint32_t bits = dropout4_bits_key(ebase + (uint32_t)sl.g1[i], key, NR_STREAM_OUT, thr);
-                    v.x &= ((bits & 1u) ? 0x0000ffffu : 0u) | ((bits & 2u) ? 0xffff0000u : 0u);
-                    v.y &= ((bits & 4u) ? 0x0000ffffu : 0u) | ((bits & 8u) ? 0xffff0000u : 0u);
-                    if (keep) keep[(obase + sl.g1[i]) >> 2] = (uint8_t)bits;
-                }
-            }
-            *(uint2*)(dst + sl.g1[i]) = v;
-        }
-        __syncwarp();                               // every lane is done with this item's tiles
-        if (more) deposit();
-        __syncwarp();
-    }
-}
-
-
-template <int DK, bool MASK>
-static __global__ void __launch_bounds__(128)
-attn_bwd_rp_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
-                    bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale) {
-    constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int g = lane >> 2, t = lane & 3;
-    const int H = heads * DK;
-    const float sl2 = scale * 1.4426950408889634f;
-    uint8_t* base = smem_raw + warp * bwd_rp_smem_per_warp(DK);
-    bf16* buf = (bf16*)base;                       // ONE stage (Q | K | V | dO): the next item waits in registers
-    bf16* Os = buf + 4 * TILE;
-    for (int i = lane; i < 4 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
-    __syncwarp();
-    Slots<DK> sl;
-    sl.init(lane, H);
-    const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
-    int item = (int)blockIdx.x * 4 + warp;
-    uint2 pf[4][Cfg<DK>::SLOTS];
-    auto fetch = [&](int it) {
-        const int sq = it / heads;
-        const int hd = it - sq * heads;
-        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + hd * DK;
-        const bf16* gsrc = dctx + (int64_t)sq * 32 * H + hd * DK;
-#pragma unroll
-        for (int m = 0; m < 3; ++m)
-#pragma unroll
-            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) pf[m][i] = ldg_stream8(src + m * H + sl.g3[i]);
-#pragma unroll
-        for (int i = 0; i < Cfg<DK>::SLOTS; ++i) pf[3][i] = ldg_stream8(gsrc + sl.g1[i]);
-    };
-    auto deposit = [&]() {
-#pragma unroll
-        for (int m = 0; m < 4; ++m)
-#pragma unroll
-            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) *(uint2*)(buf + m * TILE + sl.so[i]) = pf[m][i];
-    };
-    if (item < items) { fetch(item); deposit(); }
-    __syncwarp();
-    for (; item < items; item += stride) {
-        const int64_t seq = item / heads;
-        const int head = item - (int)seq * heads;
-        const bool more = (int64_t)item + stride < items;
-        if (more) fetch(item + stride);
-        const bf16* Qs = buf;
-        const bf16* Ks = Qs + TILE;
-        const bf16* Vs = Ks + TILE;
-        const bf16* Gs = Vs + TILE;
-        float mcol[4][2];
-#pragma unroll
-        for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int col = nt * 8 + 2 * t + e;
-                mcol[nt][e] = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
-            }
-        bf16* dst = dqkv + seq * 32 * 3 * H + head * DK;
-        // ---- A = P/Z, dA = dO V^T, dS = A (dA - rd); dQ = dS K / sqrt(dk).  The key-major operands
-        //      A^T and dS^T of dV = A^T dO and dK = dS^T Q are NOT recomputed (that was a second S^T = K Q^T,
-        //      dA^T = V dO^T and exp pass): every 8 x 8 bf16 block of the packed fragments is transposed in
-        //      registers with movmatrix, which turns the C-layout tile into A fragments of the transpose.
-        uint32_t at[2][2][4], dst_t[2][2][4];
-        {
-            float s[2][4][4], da[2][4][4];
-            zero_c(s); zero_c(da);
-            {
-                Frag<DK> fa, fb;
-                load_a<DK>(Qs, lane, fa); load_b_rows<DK>(Ks, lane, fb);
-                mm_32x32<DK>(s, fa, fb);
-                load_a<DK>(Gs, lane, fa); load_b_rows<DK>(Vs, lane, fb);
-                mm_32x32<DK>(da, fa, fb);
-            }
-            float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, rd[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
-#pragma unroll
-            for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-                for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float m = mcol[nt][e & 1];
-                        float p = exp2_fast(s[mt][nt][e] * sl2);
-                        if (MASK) p *= m;
-                        p = m != 0.f ? p : 0.f;
-                        s[mt][nt][e] = p;
-                        z[mt][e >> 1] += p;
-                        rd[mt][e >> 1] = fmaf(p, da[mt][nt][e], rd[mt][e >> 1]);
-                    }
-            float inv[2][2];
-#pragma unroll
-            for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int row = mt * 16 + g + 8 * h;
-                    const float zs = quad_sum(z[mt][h]), rs = quad_sum(rd[mt][h]);   // shuffles: all lanes, no branch
-                    inv[mt][h] = row < S ? 1.f / (zs + kEps) : 0.f;                  // pad query rows: A = dS = 0
-                    rd[mt][h] = rs * inv[mt][h];
-                }
-#pragma unroll
-            for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-                for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float a = s[mt][nt][e] * inv[mt][e >> 1];
-                        s[mt][nt][e] = a;
-                        da[mt][nt][e] = a * (da[mt][nt][e] - rd[mt][e >> 1]);
-                    }
-            uint32_t ads[2][2][4], bk[NT][2][2];
-            c_to_a(da, ads);
-            transpose_a(ads, dst_t);
-            {
-                uint32_t aa[2][2][4];
-                c_to_a(s, aa);
-                transpose_a(aa, at);
-            }
-            load_b_cols<DK>(Ks, lane, bk);
-            float dq[2][NT][4];
-            mm_32xn<NT>(dq, ads, bk);
-            stage_out_bf<NT, DK>(dq, Os, lane, scale);
-        }
-        __syncwarp();
-        store_tile_bf<DK>(dst, sl.g3, Os, S, sl);
-        __syncwarp();
-        {
-            uint32_t bf[NT][2][2];
-            float out[2][NT][4];
-            load_b_cols<DK>(Qs, lane, bf);
-            mm_32xn<NT>(out, dst_t, bf);                          // dK = dS^T Q / sqrt(dk)
-            stage_out_bf<NT, DK>(out, Os, lane, scale);
-            __syncwarp();
-            store_tile_bf<DK>(dst + H, sl.g3, Os, S, sl);
-            __syncwarp();
-            load_b_cols<DK>(Gs, lane, bf);
-            mm_32xn<NT>(out, at, bf);                             // dV = A^T dO
-            stage_out_bf<NT, DK>(out, Os, lane, 1.f);
-        }
-        __syncwarp();
-        store_tile_bf<DK>(dst + 2 * H, sl.g3, Os, S, sl);
-        __syncwarp();
-        if (more) deposit();
-        __syncwarp();
-    }
-}
-
-
-
-// ---------------------------------------------------------------------------------------------------------------
-// Head-group variants (heads % 4 == 0): the 4 warps of a CTA own 4 ADJACENT heads of one title, and the CTA moves
-// their data together.  A head slice is only DK*2 = 40 bytes of a 3H*2 = 2400-byte row, so a warp that copies its
-// own head touches 2-3 32-byte sectors per row and uses 40 of their 64-96 bytes; the neighbouring head (another
-// warp, a little earlier or later) needs the same sectors again, which only the L1 can absorb (measured: with the
-// shared-memory carve-out at maximum, i.e. a ~30 KB L1, the per-warp kernels run 1.5x slower).  Here every
-// cp.async instruction of a warp covers 256 contiguous bytes of the 4-head span (8*DK = 160 bytes per row, sector
-// aligned), each sector is requested exactly once, and results leave the same way: the warps stage bf16 tiles and
-// the CTA writes whole 160-byte row segments.  Cost: two __syncthreads per group instead of none.
-// ---------------------------------------------------------------------------------------------------------------
-template <int DK>
-struct GSlots {
-    static constexpr int N = Cfg<DK>::SLOTS;      // 32 rows * DK chunks of 8 bytes / 128 threads
-    int row[N];                                   // title row of the chunk
-    int so[N];                                    // element offset of the chunk inside the CTA's tile area (stage 0, matrix 0)
-    int oo[N];                                    // element offset inside the CTA's staging area (output 0)
-    int g1[N];                                    // element offset in a global matrix of pitch H
-    int g3[N];                                    // ... of pitch 3H
-    __device__ __forceinline__ void init(int tid, int H, int warp_elems, int os_base) {
-#pragma unroll
-        for (int i = 0; i < N; ++i) {
-            const int idx = i * 128 + tid;
-            const int r = idx / DK, j = idx - r * DK;            // j: 8-byte chunk inside the 4-head row segment
-            const int hl = j / N, cj = (j - hl * N) * 4;         // owning warp, first column inside its head
-            row[i] = r;
-            so[i] = hl * warp_elems + r * Cfg<DK>::PITCH + cj;
-            oo[i] = hl * warp_elems + os_base + r * DK + cj;
-            g1[i] = r * H + j * 4;
-            g3[i] = r * 3 * H + j * 4;
-        }
-    }
-};
-template <int DK>
-__device__ __forceinline__ void prefetch_group(bf16* tiles, const bf16* src, const int (&off)[Cfg<DK>::SLOTS],
-                                               const GSlots<DK>& sl) {
-    const uint32_t t0 = tc::smem_u32(tiles);
-#pragma unroll
-    for (int i = 0; i < Cfg<DK>::SLOTS; ++i)
-        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(t0 + 2u * (uint32_t)sl.so[i]), "l"(src + off[i])
-                     : "memory");
-}
-__host__ __device__ constexpr size_t fwd_grp_smem_per_warp(int DK) {
-    return (size_t)2 * 3 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 2;
-}
-__host__ __device__ constexpr size_t bwd_grp_smem_per_warp(int DK) {
-    return (size_t)2 * 4 * 32 * pitch_of(DK) * 2 + (size_t)3 * 32 * DK * 2;
-}
-
-template <int DK, bool MASK>
-static __global__ void __launch_bounds__(128)
-attn_fwd_grp_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
-                    int64_t groups, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed,
-                    uint8_t* __restrict__ keep) {
-    constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
-    constexpr int WE = (int)(fwd_grp_smem_per_warp(DK) / 2);      // elements per warp region
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int t = lane & 3;
-    const int H = heads * DK, hg = heads >> 2;
-    const float sl2 = scale * 1.4426950408889634f;
-    const uint64_t key = salted(seed);
-    bf16* all = (bf16*)smem_raw;
-    bf16* buf = all + warp * WE;                   // this warp's 2 stages x (Q | K | V), then its staging tile
-    bf16* Os = buf + 6 * TILE;
-    for (int i = lane; i < 6 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
-    GSlots<DK> sl;
-    sl.init(tid, H, WE, 6 * TILE);
-    __syncthreads();
-    const int stride = (int)gridDim.x;
-    int grp = (int)blockIdx.x;
-    auto issue = [&](int gidx, int stage) {
-        const int sq = gidx / hg;
-        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + (gidx - sq * hg) * 4 * DK;
-        bf16* b = all + stage * 3 * TILE;
-        prefetch_group<DK>(b, src, sl.g3, sl);
-        prefetch_group<DK>(b + TILE, src + H, sl.g3, sl);
-        prefetch_group<DK>(b + 2 * TILE, src + 2 * H, sl.g3, sl);
-        cp_async_commit();
-    };
-    if (grp < groups) issue(grp, 0);
-    for (int stage = 0; grp < groups; grp += stride, stage ^= 1) {
-        const int64_t seq = grp / hg;
-        const int gcol = (grp - (int)seq * hg) * 4 * DK;           // first column of the 4-head span
-        if ((int64_t)grp + stride < groups) issue(grp + stride, stage ^ 1); else cp_async_commit();
-        const bf16* Qs = buf + stage * 3 * TILE;
-        const bf16* Ks = Qs + TILE;
-        const bf16* Vs = Ks + TILE;
-        float mk[4][2];
-#pragma unroll
-        for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int col = nt * 8 + 2 * t + e;
-                mk[nt][e] = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
-            }
-        cp_async_wait<1>();
-        __syncthreads();                            // every thread's chunks of this stage have landed
-        float acc[2][4][4];
-        zero_c(acc);
-        {
-            Frag<DK> fq, fk;
-            load_a<DK>(Qs, lane, fq);
-            load_b_rows<DK>(Ks, lane, fk);
-            mm_32x32<DK>(acc, fq, fk);
-        }
-        float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
-#pragma unroll
-        for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-            for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                    const float m = mk[nt][e & 1];
-                    float p = exp2_fast(acc[mt][nt][e] * sl2);
-                    if (MASK) p *= m;
-                    p = m != 0.f ? p : 0.f;
-                    acc[mt][nt][e] = p;
-                    z[mt][e >> 1] += p;
-                }
-        float inv[2][2];
-#pragma unroll
-        for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-            for (int h = 0; h < 2; ++h) inv[mt][h] = dscale / (quad_sum(z[mt][h]) + kEps);    // model_utils.py:53 (+ 1/(1-p))
-        uint32_t ap[2][2][4], bv[NT][2][2];
-        c_to_a(acc, ap);
-        load_b_cols<DK>(Vs, lane, bv);
-        float o[2][NT][4];
-        mm_32xn<NT>(o, ap, bv);
-        stage_out_bf2<NT, DK>(o, Os, lane, inv[0][0], inv[0][1], inv[1][0], inv[1][1]);
-        __syncthreads();                            // all four heads staged
-        const int64_t obase = seq * 32 * H + gcol;                  // ctx / keep-bit element index (padded rows)
-        const uint64_t ebase = (uint64_t)(seq * S * H + gcol);      // dropout element index (real rows)
-        bf16* dst = ctx + obase;
-#pragma unroll
-        for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
-            uint2 v = make_uint2(0u, 0u);
-            if (sl.row[i] < S) {
-                v = *(const uint2*)(all + sl.oo[i]);
-                if (thr) {
-                    const uint32_t bits = dropout4_bits_key(ebase + (uint32_t)sl.g1[i], key, NR_STREAM_OUT, thr);
-                    v.x &= ((bits & 1u) ? 0x0000ffffu : 0u) | ((bits & 2u) ? 0xffff0000u : 0u);
-                    v.y &= ((bits & 4u) ? 0x0000ffffu : 0u) | ((bits & 8u) ? 0xffff0000u : 0u);
-                    if (keep) keep[(obase + sl.g1[i]) >> 2] = (uint8_t)bits;
-                }
-            }
-            *(uint2*)(dst + sl.g1[i]) = v;
-        }
-    }
-}
-
-template <int DK, bool MASK>
-static __global__ void __launch_bounds__(128)
-attn_bwd_grp_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
-                    bf16* __restrict__ dqkv, int64_t groups, int S, int heads, float scale) {
-    constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
-    constexpr int WE = (int)(bwd_grp_smem_per_warp(DK) / 2);
-    extern __shared__ __align__(16) uint8_t smem_raw[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int g = lane >> 2, t = lane & 3;
-    const int H = heads * DK, hg = heads >> 2;
-    const float sl2 = scale * 1.4426950408889634f;
-    bf16* all = (bf16*)smem_raw;
-    bf16* buf = all + warp * WE;                   // 2 stages x (Q | K | V | dO), then staging tiles dQ | dK | dV
-    bf16* Os = buf + 8 * TILE;
-    for (int i = lane; i < 8 * TILE / 8; i += 32) ((uint4*)buf)[i] = make_uint4(0u, 0u, 0u, 0u);
-    GSlots<DK> sl;
-    sl.init(tid, H, WE, 8 * TILE);
-    __syncthreads();
-    const int stride = (int)gridDim.x;
-    int grp = (int)blockIdx.x;
-    auto issue = [&](int gidx, int stage) {
-        const int sq = gidx / hg;
-        const int gc = (gidx - sq * hg) * 4 * DK;
-        const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + gc;
-        bf16* b = all + stage * 4 * TILE;
-        prefetch_group<DK>(b, src, sl.g3, sl);
-        prefetch_group<DK>(b + TILE, src + H, sl.g3, sl);
-        prefetch_group<DK>(b + 2 * TILE, src + 2 * H, sl.g3, sl);
-        prefetch_group<DK>(b + 3 * TILE, dctx + (int64_t)sq * 32 * H + gc, sl.g1, sl);
-        cp_async_commit();
-    };
-    if (grp < groups) issue(grp, 0);
-    for (int stage = 0; grp < groups; grp += stride, stage ^= 1) {
-        const int64_t seq = grp / hg;
-        const int gcol = (grp - (int)seq * hg) * 4 * DK;
-        if ((int64_t)grp + stride < groups) issue(grp + stride, stage ^ 1); else cp_async_commit();
-        const bf16* Qs = buf + stage * 4 * TILE;
-        const bf16* Ks = Qs + TILE;
-        const bf16* Vs = Ks + TILE;
-        const bf16* Gs = Vs + TILE;
-        float mcol[4][2];
-#pragma unroll
-        for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int col = nt * 8 + 2 * t + e;
-                mcol[nt][e] = col < S ? (MASK ? __ldg(key_mask + seq * S + col) : 1.f) : 0.f;
-            }
-        cp_async_wait<1>();
-        __syncthreads();
-        uint32_t at[2][2][4], dst_t[2][2][4];       // A^T and dS^T as A fragments (movmatrix, see attn_bwd_mma_kernel)
-        {
-            float s[2][4][4], da[2][4][4];
-            zero_c(s); zero_c(da);
-            {
-                Frag<DK> fa, fb;
-                load_a<DK>(Qs, lane, fa); load_b_rows<DK>(Ks, lane, fb);
-                mm_32x32<DK>(s, fa, fb);
-                load_a<DK>(Gs, lane, fa); load_b_rows<DK>(Vs, lane, fb);
-                mm_32x32<DK>(da, fa, fb);
-            }
-            float z[2][2] = {{0.f, 0.f}, {0.f, 0.f}}, rd[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
-#pragma unroll
-            for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-                for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float m = mcol[nt][e & 1];
-                        float p = exp2_fast(s[mt][nt][e] * sl2);
-                        if (MASK) p *= m;
-                        p = m != 0.f ? p : 0.f;
-                        s[mt][nt][e] = p;
-                        z[mt][e >> 1] += p;
-                        rd[mt][e >> 1] = fmaf(p, da[mt][nt][e], rd[mt][e >> 1]);
-                    }
-            float inv[2][2];
-#pragma unroll
-            for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int row = mt * 16 + g + 8 * h;
-                    const float zs = quad_sum(z[mt][h]), rs = quad_sum(rd[mt][h]);
-                    inv[mt][h] = row < S ? 1.f / (zs + kEps) : 0.f;
-                    rd[mt][h] = rs * inv[mt][h];
-                }
-#pragma unroll
-            for (int mt = 0; mt < 2; ++mt)
-#pragma unroll
-                for (int nt = 0; nt < 4; ++nt)
-#pragma unroll
-                    for (int e = 0; e < 4; ++e) {
-                        const float a = s[mt][nt][e] * inv[mt][e >> 1];
-                        s[mt][nt][e] = a;
-                        da[mt][nt][e] = a * (da[mt][nt][e] - rd[mt][e >> 1]);
-                    }
-            uint32_t ads[2][2][4], bk[NT][2][2];
-            c_to_a(da, ads);
-            transpose_a(ads, dst_t);
-            {
-                uint32_t aa[2][2][4];
-                c_to_a(s, aa);
-                transpose_a(aa, at);
-            }
-            load_b_cols<DK>(Ks, lane, bk);
-            float dq[2][NT][4];
-            mm_32xn<NT>(dq, ads, bk);
-            stage_out_bf<NT, DK>(dq, Os, lane, scale);
-        }
-        {
-            uint32_t bf[NT][2][2];
-            float out[2][NT][4];
-            load_b_cols<DK>(Qs, lane, bf);
-            mm_32xn<NT>(out, dst_t, bf);                          // dK = dS^T Q / sqrt(dk)
-            stage_out_bf<NT, DK>(out, Os + 32 * DK, lane, scale);
-            load_b_cols<DK>(Gs, lane, bf);
-            mm_32xn<NT>(out, at, bf);                             // dV = A^T dO
-            stage_out_bf<NT, DK>(out, Os + 2 * 32 * DK, lane, 1.f);
-        }
-        __syncthreads();                            // dQ | dK | dV of all four heads staged
-        bf16* dst = dqkv + seq * 32 * 3 * H + gcol;
-#pragma unroll
-        for (int m = 0; m < 3; ++m)
-#pragma unroll
-            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
-                uint2 v = make_uint2(0u, 0u);
-                if (sl.row[i] < S) v = *(const uint2*)(all + sl.oo[i] + m * 32 * DK);
-                *(uint2*)(dst + m * H + sl.g3[i]) = v;
-            }
     }
 }
 
@@ -1145,7 +580,7 @@ template <int DK, bool MASK, int NB>
 static __global__ void __launch_bounds__(128)
 attn_fwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, bf16* __restrict__ ctx,
                     int64_t items, int S, int heads, float scale, uint32_t thr, float dscale, uint64_t seed,
-                    uint8_t* __restrict__ keep) {
+                    uint8_t* __restrict__ keep, int hs, int ms) {
     constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE, SPB = 32 * NB;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1163,12 +598,12 @@ attn_fwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     for (int item = (int)blockIdx.x * 4 + warp; item < items; item += stride) {
         const int64_t seq = item / heads;
         const int head = item - (int)seq * heads;
-        const bf16* src = qkv + seq * SPB * 3 * H + head * DK;
+        const bf16* src = qkv + seq * SPB * 3 * H + head * hs;
 #pragma unroll
         for (int m = 0; m < 3; ++m)
 #pragma unroll
             for (int b = 0; b < NB; ++b)
-                prefetch_tile<DK>(buf + (m * NB + b) * TILE, src + m * H + (int64_t)b * 32 * 3 * H, sl.g3, sl);
+                prefetch_tile<DK>(buf + (m * NB + b) * TILE, src + m * ms + (int64_t)b * 32 * 3 * H, sl.g3, sl);
         cp_async_commit();
         cp_async_wait<0>();
         __syncwarp();
@@ -1246,7 +681,7 @@ attn_fwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 template <int DK, bool MASK, int NB>
 static __global__ void __launch_bounds__(128)
 attn_bwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
-                    bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale) {
+                    bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale, int hs, int ms) {
     constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE, SPB = 32 * NB;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -1265,13 +700,13 @@ attn_bwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     for (int item = (int)blockIdx.x * 4 + warp; item < items; item += stride) {
         const int64_t seq = item / heads;
         const int head = item - (int)seq * heads;
-        const bf16* src = qkv + seq * SPB * 3 * H + head * DK;
+        const bf16* src = qkv + seq * SPB * 3 * H + head * hs;
         const bf16* gsrc = dctx + seq * SPB * H + head * DK;
 #pragma unroll
         for (int b = 0; b < NB; ++b) {
 #pragma unroll
             for (int m = 0; m < 3; ++m)
-                prefetch_tile<DK>(buf + (m * NB + b) * TILE, src + m * H + (int64_t)b * 32 * 3 * H, sl.g3, sl);
+                prefetch_tile<DK>(buf + (m * NB + b) * TILE, src + m * ms + (int64_t)b * 32 * 3 * H, sl.g3, sl);
             prefetch_tile<DK>(buf + (3 * NB + b) * TILE, gsrc + (int64_t)b * 32 * H, sl.g1, sl);
         }
         cp_async_commit();
@@ -1281,7 +716,7 @@ attn_bwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         const bf16* Ks = buf + NB * TILE;
         const bf16* Vs = buf + 2 * NB * TILE;
         const bf16* Gs = buf + 3 * NB * TILE;
-        bf16* dst = dqkv + seq * SPB * 3 * H + head * DK;
+        bf16* dst = dqkv + seq * SPB * 3 * H + head * hs;
         // ---- query-major: sweep 1 -> Z and rd per query row; sweep 2 -> dS blocks and dQ = sum_kb dS K / sqrt(dk)
 #pragma unroll 1
         for (int qb = 0; qb < NB; ++qb) {
@@ -1405,11 +840,11 @@ attn_bwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             }
             stage_out<NT, DK>(ok, Os, lane, scale, scale, scale, scale);
             __syncwarp();
-            store_tile<DK>(dst + H + (int64_t)kb * 32 * 3 * H, sl.g3, Os, S - kb * 32, sl);
+            store_tile<DK>(dst + ms + (int64_t)kb * 32 * 3 * H, sl.g3, Os, S - kb * 32, sl);
             __syncwarp();
             stage_out<NT, DK>(ov, Os, lane, 1.f, 1.f, 1.f, 1.f);
             __syncwarp();
-            store_tile<DK>(dst + 2 * H + (int64_t)kb * 32 * 3 * H, sl.g3, Os, S - kb * 32, sl);
+            store_tile<DK>(dst + 2 * ms + (int64_t)kb * 32 * 3 * H, sl.g3, Os, S - kb * 32, sl);
             __syncwarp();
         }
     }

@@ -82,7 +82,14 @@ struct PackArgs {
     const float* w0; const float* w1; const float* w2;
     int mode, H, Dm, ldt, rows, ldo, nmat;
     const float* b0; const float* b1; const float* b2;     // optional biases (modes 0 and 2)
+    int hm_dk;                                             // modes 0/1 with nmat = 3: head width when the 3H axis is HEAD-MAJOR
 };
+// index on a head-major 3H axis ([head][q|k|v][d]) -> canonical index ([q|k|v][head][d]) = row of [W_Q; W_K; W_V]
+__host__ __device__ __forceinline__ int qkv_canonical(int r, int dk, int H) {
+    const int hd = r / (3 * dk), rem = r - hd * 3 * dk;
+    const int m = rem / dk, d = rem - m * dk;
+    return m * H + hd * dk + d;
+}
 // up to four packing jobs in ONE launch (blockIdx.y = job): the forward packs its two operands and the two
 // transposed operands the backward GEMMs need, so a step pays one ~5 us launch per encoder instead of four
 struct PackJobs { PackArgs a[4]; bf16* out[4]; };
@@ -93,8 +100,12 @@ static __device__ __forceinline__ void pack_body(const PackArgs& a, bf16* __rest
     const int64_t total = (int64_t)a.rows * a.ldo;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;
          t += (int64_t)gridDim.x * blockDim.x) {
-        const int r = (int)(t / a.ldo), c = (int)(t - (int64_t)r * a.ldo);
+        int r = (int)(t / a.ldo), c = (int)(t - (int64_t)r * a.ldo);
         float v = 0.f;
+        if (a.hm_dk) {       // the packed 3H axis is head-major: read the canonical source row / column
+            if (a.mode == 0) r = qkv_canonical(r, a.hm_dk, a.H);
+            else if (a.mode == 1 && c < a.nmat * a.H) c = qkv_canonical(c, a.hm_dk, a.H);
+        }
         if (a.mode == 0) {
             const int w = r / a.H;
             if (c < a.Dm) {

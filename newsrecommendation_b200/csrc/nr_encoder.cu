@@ -47,6 +47,14 @@ int gemm_tc_pick(const bf16* A, int64_t a_rows, int Kt_real, int64_t lda, const 
     return gemm_tc<Epi, 8>(A, a_rows, Kt_real, lda, B, N, ldb, taps, shifts, M, epi, st, what);
 }
 
+// Head-major qkv columns ([head][q|k|v], see nr_attn_mma.cuh) whenever one of the warp-MMA kernels runs the
+// attention; the SIMT fall-back kernels keep the canonical q | k | v blocks.  The weight packers, the dW epilogue
+// and the attention launchers all ask this one predicate.  NR_QKV_CANONICAL=1 forces the old order (A/B runs).
+static bool qkv_head_major(int SP, int dk) {
+    static const bool off = [] { const char* e = getenv("NR_QKV_CANONICAL"); return e && e[0] == '1'; }();
+    return !off && (SP == 32 || SP == 64) && (dk == 8 || dk == 16 || dk == 20 || dk == 32);
+}
+
 // AttentionPooling fc1 + tanh + fc2 (model_utils.py:21-23): e (bf16) = tanh(acc + b1);
 // logits[row] = e . w2 + b2 (fp32, from the unrounded tanh).  Needs the whole row in one n tile.
 struct EpiTanhLogit {
@@ -173,7 +181,9 @@ struct EpiDx {
 // rows i of [dW_Q; dW_K; dW_V] (3H x Dm); column Dm of the product (ones column of Xb) = bias gradient
 struct TnEpiQkv {
     float* dw0; float* dw1; float* dw2; float* db0; float* db1; float* db2; int H, Dm;
+    int hm_dk;      // head width when the rows of dqkv^T . Xb arrive head-major (see qkv_head_major), else 0
     __device__ __forceinline__ void operator()(int i, int, int j, const float* v, int nc) const {
+        if (hm_dk) i = qkv_canonical(i, hm_dk, H);
         const int w = i / H, ii = i - w * H;
         float* dw = w == 0 ? dw0 : (w == 1 ? dw1 : dw2);
         float* db = w == 0 ? db0 : (w == 1 ? db1 : db2);
@@ -326,7 +336,7 @@ int launch_attn_bwd(const bf16* qkv, const float* mask, const bf16* dctx, bf16* 
 // warp-level tensor-core attention (S <= 31 => pitch 32, head dim <= 32)
 template <int DK, bool MASK>
 int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
-                        uint64_t seed, uint8_t* keep, cudaStream_t st) {
+                        uint64_t seed, uint8_t* keep, bool hm, cudaStream_t st) {
     const size_t smem = 4 * amma::fwd_smem_per_warp(DK);
     auto kern = amma::attn_fwd_mma_kernel<DK, MASK>;
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -346,12 +356,13 @@ int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;    // persistent: one wave
     ProfScope ps("enc.attn_fwd", st);
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads, 1.0f / sqrtf((float)DK),
-                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep);
+                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep,
+                                            hm ? 3 * DK : DK, hm ? DK : heads * DK);
     return check_last("enc.attn_fwd");
 }
 template <int DK, bool MASK>
 int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
-                        cudaStream_t st) {
+                        bool hm, cudaStream_t st) {
     const size_t smem = 4 * amma::bwd_smem_per_warp(DK);
     auto kern = amma::attn_bwd_mma_kernel<DK, MASK>;
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -370,91 +381,14 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     if (per_sm > cap) per_sm = cap;
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
     ProfScope ps("enc.attn_bwd", st);
-    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
-    return check_last("enc.attn_bwd");
-}
-// register-prefetch variants (single shared stage, streaming loads): the default for pitch-32 sequences
-template <int DK, bool MASK>
-int launch_attn_fwd_rp(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
-                       uint64_t seed, uint8_t* keep, cudaStream_t st) {
-    const size_t smem = 4 * amma::fwd_rp_smem_per_warp(DK);
-    auto kern = amma::attn_fwd_rp_kernel<DK, MASK>;
-    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t items = n * heads;
-    NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
-    int64_t grid = (items + 3) / 4;
-    int per_sm = 1;
-    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
-    if (per_sm < 1) per_sm = 1;
-    if (const char* e = getenv("NR_ATTN_CTAS")) { int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }
-    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;    // persistent: one wave
-    ProfScope ps("enc.attn_fwd", st);
-    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads, 1.0f / sqrtf((float)DK),
-                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep);
-    return check_last("enc.attn_fwd");
-}
-template <int DK, bool MASK>
-int launch_attn_bwd_rp(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
-                       cudaStream_t st) {
-    const size_t smem = 4 * amma::bwd_rp_smem_per_warp(DK);
-    auto kern = amma::attn_bwd_rp_kernel<DK, MASK>;
-    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t items = n * heads;
-    NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
-    int64_t grid = (items + 3) / 4;
-    int per_sm = 1;
-    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
-    if (per_sm < 1) per_sm = 1;
-    if (const char* e = getenv("NR_ATTN_CTAS")) { int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }
-    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
-    ProfScope ps("enc.attn_bwd", st);
-    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
-    return check_last("enc.attn_bwd");
-}
-// head-group variants: 4 adjacent heads per CTA, cooperative sector-exact loads and stores (heads % 4 == 0)
-template <int DK, bool MASK>
-int launch_attn_fwd_grp(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
-                        uint64_t seed, uint8_t* keep, cudaStream_t st) {
-    const size_t smem = 4 * amma::fwd_grp_smem_per_warp(DK);
-    auto kern = amma::attn_fwd_grp_kernel<DK, MASK>;
-    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    if (const char* e = getenv("NR_ATTN_CARVE")) NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e)));
-    const int64_t groups = n * (heads / 4);
-    NR_REQUIRE(groups < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)groups * 4);
-    int64_t grid = groups;
-    int per_sm = 1;
-    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
-    if (per_sm < 1) per_sm = 1;
-    if (const char* e = getenv("NR_ATTN_CTAS")) { int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }
-    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;    // persistent: one wave
-    ProfScope ps("enc.attn_fwd", st);
-    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, groups, S, heads, 1.0f / sqrtf((float)DK),
-                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep);
-    return check_last("enc.attn_fwd");
-}
-template <int DK, bool MASK>
-int launch_attn_bwd_grp(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
-                        cudaStream_t st) {
-    const size_t smem = 4 * amma::bwd_grp_smem_per_warp(DK);
-    auto kern = amma::attn_bwd_grp_kernel<DK, MASK>;
-    NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    if (const char* e = getenv("NR_ATTN_CARVE")) NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, atoi(e)));
-    const int64_t groups = n * (heads / 4);
-    NR_REQUIRE(groups < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)groups * 4);
-    int64_t grid = groups;
-    int per_sm = 1;
-    NR_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 128, smem));
-    if (per_sm < 1) per_sm = 1;
-    if (const char* e = getenv("NR_ATTN_CTAS")) { int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }
-    if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
-    ProfScope ps("enc.attn_bwd", st);
-    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, groups, S, heads, 1.0f / sqrtf((float)DK));
+    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK),
+                                            hm ? 3 * DK : DK, hm ? DK : heads * DK);
     return check_last("enc.attn_bwd");
 }
 // blocked variant: 32 < pitch <= 64 (the user encoder's 50 clicked titles)
 template <int DK, bool MASK>
 int launch_attn_fwd_blk(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p,
-                        uint64_t seed, uint8_t* keep, cudaStream_t st) {
+                        uint64_t seed, uint8_t* keep, bool hm, cudaStream_t st) {
     const size_t smem = 4 * amma::fwd_blk_smem_per_warp(DK, 2);
     auto kern = amma::attn_fwd_blk_kernel<DK, MASK, 2>;
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -467,12 +401,13 @@ int launch_attn_fwd_blk(const bf16* qkv, const float* mask, bf16* ctx, int64_t n
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
     ProfScope ps("enc.attn_fwd", st);
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, ctx, items, S, heads, 1.0f / sqrtf((float)DK),
-                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep);
+                                            p > 0.f ? drop_threshold(p) : 0u, p > 0.f ? 1.f / (1.f - p) : 1.f, seed, keep,
+                                            hm ? 3 * DK : DK, hm ? DK : heads * DK);
     return check_last("enc.attn_fwd");
 }
 template <int DK, bool MASK>
 int launch_attn_bwd_blk(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
-                        cudaStream_t st) {
+                        bool hm, cudaStream_t st) {
     const size_t smem = 4 * amma::bwd_blk_smem_per_warp(DK, 2);
     auto kern = amma::attn_bwd_blk_kernel<DK, MASK, 2>;
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -484,35 +419,18 @@ int launch_attn_bwd_blk(const bf16* qkv, const float* mask, const bf16* dctx, bf
     if (per_sm < 1) per_sm = 1;
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
     ProfScope ps("enc.attn_bwd", st);
-    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK));
+    kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK),
+                                            hm ? 3 * DK : DK, hm ? DK : heads * DK);
     return check_last("enc.attn_bwd");
 }
-#define NR_BLK_FWD(DKV) (mask ? launch_attn_fwd_blk<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st) \
-                              : launch_attn_fwd_blk<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st))
-#define NR_BLK_BWD(DKV) (mask ? launch_attn_bwd_blk<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st) \
-                              : launch_attn_bwd_blk<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))
-// the head-group kernels are correct and sector-exact but measured slower (two CTA barriers per group): opt-in
-static bool attn_grouped(int heads) { return heads % 4 == 0 && getenv("NR_ATTN_GROUPED"); }
-static bool attn_rp_fwd() { const char* e = getenv("NR_ATTN_RP"); return e && (atoi(e) & 1); }
-static bool attn_rp_bwd() { const char* e = getenv("NR_ATTN_RP"); return e && (atoi(e) & 2); }
-template <int DKV, bool MASK>
-int pick_attn_fwd(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int heads, float p, uint64_t seed,
-                  uint8_t* keep, cudaStream_t st) {
-    if (attn_grouped(heads)) return launch_attn_fwd_grp<DKV, MASK>(qkv, mask, ctx, n, S, heads, p, seed, keep, st);
-    if (attn_rp_fwd()) return launch_attn_fwd_rp<DKV, MASK>(qkv, mask, ctx, n, S, heads, p, seed, keep, st);
-    return launch_attn_fwd_mma<DKV, MASK>(qkv, mask, ctx, n, S, heads, p, seed, keep, st);
-}
-template <int DKV, bool MASK>
-int pick_attn_bwd(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
-                  cudaStream_t st) {
-    if (attn_grouped(heads)) return launch_attn_bwd_grp<DKV, MASK>(qkv, mask, dctx, dqkv, n, S, heads, st);
-    if (attn_rp_bwd()) return launch_attn_bwd_rp<DKV, MASK>(qkv, mask, dctx, dqkv, n, S, heads, st);
-    return launch_attn_bwd_mma<DKV, MASK>(qkv, mask, dctx, dqkv, n, S, heads, st);
-}
-#define NR_MMA_FWD(DKV) (mask ? pick_attn_fwd<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, st) \
-                              : pick_attn_fwd<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, st))
-#define NR_MMA_BWD(DKV) (mask ? pick_attn_bwd<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, st) \
-                              : pick_attn_bwd<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, st))
+#define NR_BLK_FWD(DKV) (mask ? launch_attn_fwd_blk<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, hm, st) \
+                              : launch_attn_fwd_blk<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, hm, st))
+#define NR_BLK_BWD(DKV) (mask ? launch_attn_bwd_blk<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st) \
+                              : launch_attn_bwd_blk<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, hm, st))
+#define NR_MMA_FWD(DKV) (mask ? launch_attn_fwd_mma<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, hm, st) \
+                              : launch_attn_fwd_mma<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, hm, st))
+#define NR_MMA_BWD(DKV) (mask ? launch_attn_bwd_mma<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st) \
+                              : launch_attn_bwd_mma<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, hm, st))
 
 #define NR_ENC_DISPATCH_DK(dk, CALL)                                                   \
     switch (dk) {                                                                      \
@@ -525,6 +443,7 @@ int pick_attn_bwd(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dq
     }
 int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, int SP, int heads, int dk, float p,
                uint64_t seed, uint8_t* keep, cudaStream_t st) {
+    const bool hm = qkv_head_major(SP, dk);
     if (SP == 32) {
         switch (dk) {
             case 8: return NR_MMA_FWD(8);
@@ -547,6 +466,7 @@ int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, 
 }
 int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int SP, int heads,
                int dk, cudaStream_t st) {
+    const bool hm = qkv_head_major(SP, dk);
     if (SP == 32) {
         switch (dk) {
             case 8: return NR_MMA_BWD(8);
@@ -618,9 +538,11 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         ja[nj] = PackArgs{enc->p_w1, nullptr, nullptr, 0, Q, H, 0, Q, p.HK, 1}; jo[nj++] = w1b;
         ja[nj] = PackArgs{enc->p_w1, nullptr, nullptr, 1, Q, H, 0, H, p.QK, 1}; jo[nj++] = (bf16*)(sv + p.o_w1t);
         if (enc->kind == NR_ENC_MHSA) {
-            ja[nj] = PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3, enc->b[0], enc->b[1], enc->b[2]};
+            const int hm_dk = qkv_head_major(p.SP, H / enc->heads) ? H / enc->heads : 0;
+            ja[nj] = PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3, enc->b[0], enc->b[1], enc->b[2], hm_dk};
             jo[nj++] = wb;
-            ja[nj] = PackArgs{enc->w[0], enc->w[1], enc->w[2], 1, H, Dm, 0, Dm, p.K3, 3}; jo[nj++] = (bf16*)(sv + p.o_wt);
+            ja[nj] = PackArgs{enc->w[0], enc->w[1], enc->w[2], 1, H, Dm, 0, Dm, p.K3, 3, nullptr, nullptr, nullptr, hm_dk};
+            jo[nj++] = (bf16*)(sv + p.o_wt);
         } else if (!pool) {
             ja[nj] = PackArgs{enc->w[0], nullptr, nullptr, 2, H, Dm, p.Kp, H, 3 * p.Kp, 1, enc->b[0], nullptr, nullptr};
             jo[nj++] = wb;
@@ -753,7 +675,8 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     if (enc->kind == NR_ENC_MHSA) {
         if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st)) return e;
         if (int e = gemm_tc_tn(dqkv, 3 * H, 3 * H, xb, Dm + 1, p.ldx, p.R, 1, &one,
-                               TnEpiQkv{gr->dw[0], gr->dw[1], gr->dw[2], gr->db[0], gr->db[1], gr->db[2], H, Dm}, st,
+                               TnEpiQkv{gr->dw[0], gr->dw[1], gr->dw[2], gr->db[0], gr->db[1], gr->db[2], H, Dm,
+                                        qkv_head_major(p.SP, H / enc->heads) ? H / enc->heads : 0}, st,
                                "enc.dwqkv"))
             return e;
         if (want_dx)
