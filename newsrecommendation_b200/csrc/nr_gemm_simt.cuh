@@ -264,13 +264,22 @@ gemm_simt_kernel(const AV a, const BV b, const Epi epi, const int64_t M, const i
 
 // NT: C(M x N) = A(M x K) . B(N x K)^T, both operands K-contiguous views.
 template <class AV, class BV, class Epi>
+// splits > 1 (ACCUMULATING epilogues only, e.g. EpiAtomic): the contraction is cut into `splits` k-chunks on
+// blockIdx.z — for the few-tile GEMMs over the category tables, whose latency is one CTA walking all of K.
 int gemm_nt(const AV& a, const BV& b, const Epi& e, int64_t M, int N, int K, cudaStream_t st,
-            const char* what) {
+            const char* what, int splits = 1) {
     if (M == 0 || N == 0) return 0;
     if ((N & 3) || (K & 3)) { set_error("%s: N=%d K=%d must be multiples of 4", what, N, K); return 1; }
-    dim3 grid((unsigned)((M + GBM - 1) / GBM), (unsigned)((N + GBN - 1) / GBN), 1);
+    int k_chunk = K;
+    if (splits > 1) {
+        k_chunk = ((K + splits - 1) / splits + GBK - 1) / GBK * GBK;
+        splits = (K + k_chunk - 1) / k_chunk;
+    } else {
+        splits = 1;
+    }
+    dim3 grid((unsigned)((M + GBM - 1) / GBM), (unsigned)((N + GBN - 1) / GBN), (unsigned)splits);
     ProfScope ps(what, st);
-    gemm_simt_kernel<true, true, AV, BV, Epi><<<grid, GTHREADS, 0, st>>>(a, b, e, M, N, K, K);
+    gemm_simt_kernel<true, true, AV, BV, Epi><<<grid, GTHREADS, 0, st>>>(a, b, e, M, N, K, k_chunk);
     return check_last(what);
 }
 

@@ -30,6 +30,39 @@ __global__ void table_scatter_kernel(const float* __restrict__ dout, int64_t dou
         atomicAdd((float4*)(dT + id * (int64_t)h4 * 4) + q, ldg4(dout + i * dout_stride + 4 * q));
     }
 }
+// Small tables (17 categories): every one of the n rows lands on one of a handful of table rows, i.e. ~n / rows
+// same-address reductions per element in L2.  Each CTA first reduces its slice of the rows into a private copy of
+// a column tile of dT in shared memory (shared-memory atomics), then adds that copy to dT once.
+// grid = (column tiles, row slices); block = cw4 float4 columns x (256 / cw4) row lanes.
+__global__ void __launch_bounds__(256)
+table_scatter_small_kernel(const float* __restrict__ dout, int64_t dout_stride, const int32_t* __restrict__ ids,
+                           int ids_stride, int rows, float* __restrict__ dT, int64_t n, int h4, int cw4, int slice) {
+    extern __shared__ __align__(16) float acc[];          // [rows][cw4 * 4]
+    const int lanes = 256 / cw4;
+    const int cq = threadIdx.x % cw4, rl = threadIdx.x / cw4;
+    const int q = blockIdx.x * cw4 + cq;                   // float4 column
+    for (int i = threadIdx.x; i < rows * cw4 * 4; i += 256) acc[i] = 0.f;
+    __syncthreads();
+    const int64_t i0 = (int64_t)blockIdx.y * slice;
+    const int64_t i1 = i0 + slice < n ? i0 + slice : n;
+    if (rl < lanes && q < h4) {
+        for (int64_t i = i0 + rl; i < i1; i += lanes) {
+            int id = __ldg(ids + i * ids_stride);
+            if (id < 0 || id >= rows) id = 0;
+            const float4 v = ldg4(dout + i * dout_stride + 4 * q);
+            float* a = acc + (id * cw4 + cq) * 4;
+            atomicAdd(a, v.x); atomicAdd(a + 1, v.y); atomicAdd(a + 2, v.z); atomicAdd(a + 3, v.w);
+        }
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < rows * cw4; t += 256) {
+        const int r = t / cw4, c = t - r * cw4;
+        const int qq = blockIdx.x * cw4 + c;
+        if (qq >= h4) continue;
+        const float4 v = *(const float4*)(acc + t * 4);
+        if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) atomicAdd((float4*)(dT + (int64_t)r * h4 * 4) + qq, v);
+    }
+}
 }  // namespace nr
 
 extern "C" {
@@ -136,7 +169,18 @@ int nr_embed_dense_bwd(const float* emb, int64_t emb_rows, const int32_t* ids, i
         if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
         {
             ProfScope ps("embed_dense.scatter", st);
-            table_scatter_kernel<<<(unsigned)blocks, 256, 0, st>>>(dout, dout_stride, ids, ids_stride, emb_rows, dT, n, h4);
+            const int cw4 = (h4 % 20 == 0) ? 20 : 16;
+            if (emb_rows <= 64 && n >= 64 * emb_rows) {
+                const int tiles = (h4 + cw4 - 1) / cw4;
+                int slices = 2 * sm_count() / tiles;
+                if (slices < 1) slices = 1;
+                const int slice = (int)((n + slices - 1) / slices);
+                slices = (int)((n + slice - 1) / slice);
+                table_scatter_small_kernel<<<dim3(tiles, slices), 256, (size_t)emb_rows * cw4 * 16, st>>>(
+                    dout, dout_stride, ids, ids_stride, (int)emb_rows, dT, n, h4, cw4, slice);
+            } else {
+                table_scatter_kernel<<<(unsigned)blocks, 256, 0, st>>>(dout, dout_stride, ids, ids_stride, emb_rows, dT, n, h4);
+            }
             if (int e = check_last("embed_dense.scatter")) return e;
         }
         const DenseView dv{dT, H, emb_rows, H};
@@ -146,7 +190,7 @@ int nr_embed_dense_bwd(const float* emb, int64_t emb_rows, const int32_t* ids, i
         if (emb_rows < 2) return 0;
         // row 0 = padding_idx: no gradient (src/model/NAML.py:19,22)
         return gemm_nt(DenseView{dT + H, H, emb_rows - 1, H}, TransView{w, H, E}, EpiAtomic{demb + E, E}, emb_rows - 1, E, H,
-                       st, "embed_dense.demb");
+                       st, "embed_dense.demb", 8);
     }
     const DenseView dv{dout, dout_stride, n, H};
     if (int e = gemm_tn(dv, EmbedView{emb, ids, ids_stride, n, E}, EpiAtomic{dw, E}, H, E, n, st, "embed_dense.dw"))
