@@ -153,3 +153,50 @@ def test_demo_flow_bf16_graph_and_raw_table(tmp_path):
     red2, *_ = drv.main(base + ['--mode', 'test', '--load_ckpt_name', 'foreign.pt', '--prepare', 'False', '--user_log_mask', 'False'])
     torch.set_grad_enabled(True)
     np.testing.assert_allclose(red2['mean_scored'], red['mean_scored'], atol=1e-12)
+
+
+@pytest.mark.parametrize('model', ['NRMS', 'NAML'])
+def test_driver_word_id_layouts(tmp_path, model):
+    """`--model NRMS` behind the driver (F2/F3: token ids + word table read from title_token_ids.npy /
+    word_embeddings.npy) and NAML over word ids (`--naml_word_ids True`, the layout commented out at NAML.py:40-45):
+    train one epoch, test, and check the printed metrics against the oracle on the saved checkpoint."""
+    from newsrecommendation_b200 import main as drv, mind_io, synthetic as S
+    tr, te = _dirs(tmp_path)
+    V = 3000
+    for d, seed in ((tr, 11), (te, 12)):
+        n_news = mind_io.count_lines(os.path.join(d, 'news.tsv'))
+        np.save(os.path.join(d, 'title_token_ids.npy'), S.news_titles(n_news, L_TITLE, V, seed=seed))
+        np.save(os.path.join(d, 'word_embeddings.npy'), S.word_table(V, D, seed=7))
+    mdir = str(tmp_path / 'model')
+    base = ['--model', model, '--model_dir', mdir, '--train_data_dir', tr, '--test_data_dir', te, '--num_words_title', str(L_TITLE),
+            '--precision', 'fp32', '--nGPU', '1', '--doc_sim_pairs', '1000', '--log_steps', '100', '--prepare', 'True',
+            '--use_category', 'True', '--use_subcategory', 'True', '--naml_word_ids', 'True', '--drop_rate', '0.2']
+    red, scores, metrics, valid = drv.main(base + ['--mode', 'train_test', '--epochs', '1', '--batch_size', '32', '--lr', '0.0003',
+                                                   '--user_log_mask', 'True'])
+    torch.set_grad_enabled(True)
+    ck = torch.load(os.path.join(mdir, 'epoch-1.pt'), map_location='cpu', weights_only=False)
+    P = dict(ck['model_state_dict'])
+    a = argparse.Namespace(use_category=model == 'NAML', use_subcategory=model == 'NAML')
+    news_t, idx_t = mind_io.read_news(os.path.join(te, 'news.tsv'), a, 'test')
+    _, cat, sub = mind_io.get_doc_input(news_t, idx_t, ck['category_dict'], ck['subcategory_dict'], a)
+    tok = np.load(os.path.join(te, 'title_token_ids.npy'))
+    if model == 'NRMS':
+        assert 'news_encoder.embedding_matrix.weight' in P and P['news_encoder.embedding_matrix.weight'].shape == (V, D)
+        comb = tok
+        enc = lambda x: O.nrms_news_encoder(x, P, 20)
+        uenc = lambda v, m: O.nrms_user_encoder(v, m, P, 20, True)
+    else:
+        comb = mind_io.combine_news_columns(tok, cat, sub)
+        enc = lambda x: O.naml_news_encoder(x, P, L_TITLE, D, True, True, word_ids=True)
+        uenc = lambda v, m: O.naml_user_encoder(v, m, P, True)
+    table_o = O.build_news_cache(enc, comb)
+    H, M, off, cand, lab = [], [], [0], [], []
+    for line in open(os.path.join(te, 'behaviors_0.tsv')):
+        h, m, c, l = O.test_line_mapper(line, idx_t, 50)
+        H.append(h); M.append(m); cand.extend(c); lab.extend(l); off.append(len(cand))
+    mets_o, scores_o = O.eval_impressions(uenc, table_o, np.stack(H), np.stack(M), np.asarray(off), np.asarray(cand, np.int32),
+                                          np.asarray(lab, np.int8))
+    summ = O.summarize_metrics(mets_o)
+    assert red['scored'] == summ['scored']
+    np.testing.assert_allclose(scores.cpu().numpy(), scores_o, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(red['mean_scored'], summ['mean_scored'], atol=1e-3)
