@@ -331,6 +331,48 @@ pool_tail_fwd_bf16_kernel(const bf16* __restrict__ y, const float* __restrict__ 
         alpha_save[seq * SP + s] = a;
     }
     __syncthreads();
+    // Few, long sequences (the user encoder: 128 x 50 rows): the block is alone on its SM, so what matters is how
+    // many loads are in flight.  Warp w takes rows w, w+4, ... (each lane 16-byte chunks c = lane, lane+32, ...),
+    // all of a warp's row loads are independent, and the four partial sums are combined through shared memory.
+    if ((H & 7) == 0 && H <= 512 && blockDim.x == 128) {
+        float* part = sp + SP;                      // [4][H] partial sums (dynamic smem sized by the launcher)
+        const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+        const int HC = H >> 3;
+        float acc[2][8];
+#pragma unroll
+        for (int k = 0; k < 2; ++k)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[k][j] = 0.f;
+        const bf16* yt = y + seq * SP * H;
+#pragma unroll 4
+        for (int s = w; s < S; s += 4) {
+            const float a = sp[s];
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                const int c = lane + 32 * k;
+                if (c < HC) {
+                    float f[8];
+                    const uint4 v = __ldg((const uint4*)(yt + (int64_t)s * H) + c);
+                    const float2 x0 = bf2_to_f2(v.x), x1 = bf2_to_f2(v.y), x2 = bf2_to_f2(v.z), x3 = bf2_to_f2(v.w);
+                    f[0] = x0.x; f[1] = x0.y; f[2] = x1.x; f[3] = x1.y; f[4] = x2.x; f[5] = x2.y; f[6] = x3.x; f[7] = x3.y;
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) acc[k][j] = fmaf(a, f[j], acc[k][j]);
+                }
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int c = lane + 32 * k;
+            if (c < HC) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) part[w * H + c * 8 + j] = acc[k][j];
+            }
+        }
+        __syncthreads();
+        for (int h = threadIdx.x; h < H; h += blockDim.x)
+            out[seq * H + h] = (part[h] + part[H + h]) + (part[2 * H + h] + part[3 * H + h]);
+        return;
+    }
     for (int h = threadIdx.x * 4; h < H; h += blockDim.x * 4) {
         float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
         const bf16* yr = y + seq * SP * H + h;
@@ -375,9 +417,11 @@ pool_tail_bwd_bf16_kernel(const float* __restrict__ g, const bf16* __restrict__ 
         __syncthreads();
         for (int h = threadIdx.x * 4; h < H; h += blockDim.x * 4) *(float4*)(gs + h) = ldg4(g + seq * H + h);
         __syncthreads();
+#pragma unroll 4      // the rows of a warp are independent: keep several rows of loads in flight (few, long sequences)
         for (int s = warp; s < S; s += nw) {
             const bf16* yr = y + (seq * SP + s) * H;
             float d = 0.f;
+#pragma unroll 2
             for (int h = lane * 8; h < H; h += 256) {
                 const uint4 w = __ldg((const uint4*)(yr + h));
                 const float2 y0 = bf2_to_f2(w.x), y1 = bf2_to_f2(w.y), y2 = bf2_to_f2(w.z), y3 = bf2_to_f2(w.w);
@@ -406,6 +450,7 @@ pool_tail_bwd_bf16_kernel(const float* __restrict__ g, const bf16* __restrict__ 
             db2_acc += t;
         }
         if (worker) {
+#pragma unroll 4
             for (int s = rg; s < SP; s += RG) {
                 bf16* zr = dz + (seq * SP + s) * Q + q4;
                 if (s >= S) { *(uint2*)zr = make_uint2(0u, 0u); continue; }

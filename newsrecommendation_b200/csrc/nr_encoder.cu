@@ -598,7 +598,7 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         else if (H <= 512) launch(pool_tail_fwd_warp_kernel<2>);
         else launch(pool_tail_fwd_warp_kernel<4>);
     } else {
-        pool_tail_fwd_bf16_kernel<<<(unsigned)n, 128, p.SP * sizeof(float), st>>>(y, logits, enc->mask, out, alpha, S, p.SP, H);
+        pool_tail_fwd_bf16_kernel<<<(unsigned)n, 128, (p.SP + 4 * (size_t)H) * sizeof(float), st>>>(y, logits, enc->mask, out, alpha, S, p.SP, H);
     }
     return check_last("enc.pool_fwd");
 }
