@@ -69,7 +69,9 @@ struct Workspace {
 // 7 rounds is the fewest that passes BigCrush (Salmon et al., SC'11, table 2); the customary 10 is safety margin a
 // dropout mask does not need, and the rounds are most of the instructions of the staging kernel.
 // Element e of stream (seed, sid): word (e & 3) of philox(counter = e >> 2).
+#ifndef NR_PHILOX_ROUNDS
 #define NR_PHILOX_ROUNDS 7
+#endif
 __host__ __device__ __forceinline__ void philox_round(uint32_t& c0, uint32_t& c1, uint32_t& c2,
                                                       uint32_t& c3, uint32_t k0, uint32_t k1) {
     const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
