@@ -425,7 +425,9 @@ def run_ours(a):
         roof = None
         if top:
             roof = roofline_for(top, kern[top]['ms_per_step'], kern[top]['launches_per_step'], ft, bt, pk)
-            roof['traffic'] = ncu_traffic(a.model, top, kern[top]['launches_per_step'])
+            # the committed ncu capture is of the default workload (batch 128/GPU, bf16); other sizes have no capture
+            roof['traffic'] = (ncu_traffic(a.model, top, kern[top]['launches_per_step'])
+                               if a.batch == 128 and a.precision == 'bf16' else None)
             roof['peak_source'] = pk['src'] + (' (sustained bf16, kernel timed inside the step)'
                                                if roof['bound'] == 'tensor' else ' (HBM copy bandwidth)')
             roof['share_of_step'] = kern[top]['share']
