@@ -95,7 +95,6 @@ __host__ __device__ __forceinline__ int qkv_canonical(int r, int dk, int H) {
 struct PackJobs { PackArgs a[4]; bf16* out[4]; };
 static __device__ __forceinline__ void pack_body(const PackArgs& a, bf16* __restrict__ out);
 static __global__ void pack_weights_multi_kernel(const PackJobs j) { pack_body(j.a[blockIdx.y], j.out[blockIdx.y]); }
-static __global__ void pack_weights_kernel(PackArgs a, bf16* __restrict__ out) { pack_body(a, out); }
 static __device__ __forceinline__ void pack_body(const PackArgs& a, bf16* __restrict__ out) {
     const int64_t total = (int64_t)a.rows * a.ldo;
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total;

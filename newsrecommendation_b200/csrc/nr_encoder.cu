@@ -290,14 +290,6 @@ int validate(const nr_title_encoder_t* e, const char* who) {
     return 0;
 }
 
-int pack(const PackArgs& a, bf16* out, cudaStream_t st) {
-    const int64_t total = (int64_t)a.rows * a.ldo;
-    const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
-    ProfScope ps("enc.pack_w", st);
-    pack_weights_kernel<<<blocks, 256, 0, st>>>(a, out);
-    return check_last("enc.pack_w");
-}
-
 int pack_multi(const PackArgs* a, bf16* const* out, int n, cudaStream_t st) {
     PackJobs j;
     int64_t most = 0;
