@@ -28,6 +28,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 V_SMALL, N_SMALL, L_TITLE, T_HIST, K_NEG = 12508, 65238, 30, 50, 4
+L_ABSTRACT = 50
 METRIC = 'NRMS/NAML train samples/s & eval impressions/s at 1/2/4/8 B200 vs CPU ref'
 
 
@@ -47,6 +48,9 @@ def parse():
     ap.add_argument('--profile-step', action='store_true',
                     help='warm up, run ONE eager step between cudaProfilerStart/Stop and exit (for ncu --profile-from-start off)')
     ap.add_argument('--cpu-batch', type=int, default=32)
+    ap.add_argument('--abstract', action='store_true',
+                    help='NAML with the abstract view of BASELINE config 3 "(+abstract)": a second per-news table of '
+                         '50 tokens x 300 (3.9 GB at 65k news); no reference code exists for this view (SURVEY F9)')
     return ap.parse_args()
 
 
@@ -75,6 +79,11 @@ def make_workload(a, rank):
         table = S.title_table(N_SMALL, L_TITLE)
         news = S.naml_features(N_SMALL)
         ctor = (table, 17, 264)
+        if a.abstract:
+            import numpy as np
+            args.use_abstract, args.num_words_abstract = True, L_ABSTRACT
+            ctor = ctor + (S.title_table(N_SMALL, L_ABSTRACT, seed=7),)
+            news = np.ascontiguousarray(np.concatenate([news[:, :1], news[:, :1], news[:, 1:]], axis=1))   # [title, abstract, cat, sub]
     return args, ctor, news
 
 
@@ -408,8 +417,10 @@ def run_ours(a):
 
     if rank == 0:
         pk = peaks()
-        ft = flops_table(a.model, a.batch)
-        bt = bytes_table(a.model, a.batch) if a.precision == 'bf16' else {}
+        # with the abstract view every news contributes L_TITLE + L_ABSTRACT token rows to the conv / pooling kernels
+        Ltok = L_TITLE + (L_ABSTRACT if (a.model == 'NAML' and a.abstract) else 0)
+        ft = flops_table(a.model, a.batch, L=Ltok)
+        bt = bytes_table(a.model, a.batch, L=Ltok) if a.precision == 'bf16' else {}
         tot = sum(v[1] for v in prof.values()) or 1.0
         kern = {k: {'ms_per_step': v[1] / a.steps, 'launches_per_step': v[0] / a.steps, 'share': v[1] / tot}
                 for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
@@ -427,7 +438,7 @@ def run_ours(a):
             roof = roofline_for(top, kern[top]['ms_per_step'], kern[top]['launches_per_step'], ft, bt, pk)
             # the committed ncu capture is of the default workload (batch 128/GPU, bf16); other sizes have no capture
             roof['traffic'] = (ncu_traffic(a.model, top, kern[top]['launches_per_step'])
-                               if a.batch == 128 and a.precision == 'bf16' else None)
+                               if a.batch == 128 and a.precision == 'bf16' and not a.abstract else None)
             roof['peak_source'] = pk['src'] + (' (sustained bf16, kernel timed inside the step)'
                                                if roof['bound'] == 'tensor' else ' (HBM copy bandwidth)')
             roof['share_of_step'] = kern[top]['share']
@@ -439,7 +450,8 @@ def run_ours(a):
             'data': 'synthetic',
             'config': {'workload': f'{a.model} train step (fwd+bwd+allreduce+Adam), MIND-small shape: batch {B}/GPU, '
                                    f'title len {L_TITLE}, history {T_HIST}, npratio {K_NEG}, 300-d emb, 20x20 heads, '
-                                   f'drop 0.2, V={V_SMALL}', 'model_family': a.model, 'per_gpu_batch': B,
+                                   f'drop 0.2, V={V_SMALL}' + (f', + abstract view ({L_ABSTRACT} tokens)' if (a.model == 'NAML' and a.abstract) else ''),
+                       'model_family': a.model, 'per_gpu_batch': B,
                        'global_batch': B * world, 'precision': a.precision, 'parallelism': f'dp{world}',
                        'launch': 'eager' if a.no_graph else 'fwd+bwd replayed from one CUDA graph, all-reduce + Adam eager',
                        'l2_policy': f'{R} distinct resident batches rotated; per-step activations '

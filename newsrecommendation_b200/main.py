@@ -36,6 +36,7 @@ from . import batcher, engine, mind_io
 from .parameters import parse_args
 
 TITLE_KEY = 'news_encoder.title_embeddings.weight'
+ABSTRACT_KEY = 'news_encoder.abstract_embeddings.weight'
 
 
 def setuplogger():
@@ -71,6 +72,14 @@ def _finish(distributed):
         dist.destroy_process_group()
 
 
+def _build_model(data_dir, args, n_cat, n_sub):
+    """main.py:63-64 / :169-170 (+ the abstract table when --use_abstract)."""
+    kw = {}
+    if args.model == 'NAML' and args.use_abstract:
+        kw['abstract_embeddings_weight'] = _embedding_table(data_dir, args, 'abstract')
+    return _plugin(args).Model(args, _embedding_table(data_dir, args), n_cat, n_sub, **kw)
+
+
 def _plugin(args):
     """main.py:63 `importlib.import_module(f'model.{args.model}')` resolved to this package's plugin."""
     if args.model is None:
@@ -94,16 +103,22 @@ def _news_inputs(data_dir, args, mode, category_dict=None, subcategory_dict=None
         title = tok
     if args.model == 'NRMS':
         cat = sub = None                      # NRMS is title-only (NRMS.py:79-95)
-    return news_index, category_dict, subcategory_dict, mind_io.combine_news_columns(title, cat, sub)
+    abstract = None
+    if args.model == 'NAML' and args.use_abstract:
+        if args.naml_word_ids:
+            abstract = np.load(os.path.join(data_dir, 'abstract_token_ids.npy')).astype(np.int32)
+        else:
+            abstract = title[:, :1].copy()    # fork layout: the row index again, into the abstract table
+    return news_index, category_dict, subcategory_dict, mind_io.combine_news_columns(title, abstract, cat, sub)
 
 
-def _embedding_table(data_dir, args):
+def _embedding_table(data_dir, args, field='title'):
     if args.model == 'NRMS' or args.naml_word_ids:
         return np.load(os.path.join(data_dir, 'word_embeddings.npy'))
-    table = mind_io.read_news_embeddings(data_dir)
-    want = args.num_words_title * args.word_embedding_dim
+    table = mind_io.read_news_embeddings(data_dir, field=field)
+    want = (args.num_words_title if field == 'title' else args.num_words_abstract) * args.word_embedding_dim
     if table.shape[1] != want:
-        raise ValueError(f'title table has {table.shape[1]} columns, --num_words_title x --word_embedding_dim = {want}')
+        raise ValueError(f'{field} table has {table.shape[1]} columns, --num_words_{field} x --word_embedding_dim = {want}')
     if isinstance(table, np.memmap):          # read-only mapping: it is only ever copied (to HBM), never written
         import warnings
         with warnings.catch_warnings():
@@ -115,18 +130,24 @@ def _embedding_table(data_dir, args):
 def _checkpoint_dict(model, args, category_dict, subcategory_dict):
     """main.py:120-127 with the filter that was meant (F5): the frozen title table stays out."""
     sd = {k: v.detach().cpu() for k, v in model.state_dict().items()
-          if not (k == TITLE_KEY and args.freeze_embedding)}
+          if not (k in (TITLE_KEY, ABSTRACT_KEY) and args.freeze_embedding)}
     return {'model_state_dict': sd, 'category_dict': category_dict, 'subcategory_dict': subcategory_dict}
 
 
-def _load_weights(model, state, table_key=TITLE_KEY):
+def _load_weights(model, state):
+    for key in (TITLE_KEY, ABSTRACT_KEY):
+        state = _keep_own_table(model, state, key)
+    model.load_state_dict(state, strict=True)
+
+
+def _keep_own_table(model, state, table_key):
     """Strict load of everything except a title table that is absent from the checkpoint or belongs to
     another news set (F5): the model keeps the table of the directory it was built from."""
     own = model.state_dict()
     state = dict(state)
     if table_key in own and (table_key not in state or state[table_key].shape != own[table_key].shape):
         state[table_key] = own[table_key]
-    model.load_state_dict(state, strict=True)
+    return state
 
 
 def train(rank, args):
@@ -135,7 +156,7 @@ def train(rank, args):
     news_index, category_dict, subcategory_dict, news_combined = _news_inputs(args.train_data_dir, args, 'train')
     if rank == 0:
         logging.info('Initializing word embedding matrix...')
-    model = _plugin(args).Model(args, _embedding_table(args.train_data_dir, args), len(category_dict), len(subcategory_dict))
+    model = _build_model(args.train_data_dir, args, len(category_dict), len(subcategory_dict))
     if rank == 0:
         print("Model's state_dict:")
         for k, v in model.state_dict().items():
@@ -230,7 +251,7 @@ def test(rank, args):
     checkpoint = torch.load(ckpt_path, map_location='cpu', weights_only=False)
     category_dict, subcategory_dict = checkpoint['category_dict'], checkpoint['subcategory_dict']
 
-    model = _plugin(args).Model(args, _embedding_table(args.test_data_dir, args), len(category_dict), len(subcategory_dict))
+    model = _build_model(args.test_data_dir, args, len(category_dict), len(subcategory_dict))
     _load_weights(model, checkpoint['model_state_dict'])
     logging.info(f'Model loaded from {ckpt_path}')
     model.cuda(dev).eval()

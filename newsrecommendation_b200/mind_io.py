@@ -112,11 +112,12 @@ def read_title_table(path):
     return np.memmap(path, dtype='<f4', mode='r', offset=TABLE_HEADER_BYTES, shape=(rows, cols))
 
 
-def read_news_embeddings(data_dir, cache=False):
+def read_news_embeddings(data_dir, cache=False, field='title'):
     """preprocess.py:227-232.  Prefers the raw table next to the .npy.gz when it is at least as new;
-    `cache=True` writes it after a gzip read so the next start-up skips the gunzip."""
-    gz = os.path.join(data_dir, TITLE_TABLE_GZ)
-    raw = os.path.join(data_dir, TITLE_TABLE_RAW)
+    `cache=True` writes it after a gzip read so the next start-up skips the gunzip.  `field='abstract'` reads the
+    second table of the abstract view (same format, `abstract_embeddings.bpemb.*`)."""
+    gz = os.path.join(data_dir, TITLE_TABLE_GZ.replace('title_', field + '_'))
+    raw = os.path.join(data_dir, TITLE_TABLE_RAW.replace('title_', field + '_'))
     if os.path.exists(raw) and (not os.path.exists(gz) or os.path.getmtime(raw) >= os.path.getmtime(gz)):
         return read_title_table(raw)
     with gzip.GzipFile(gz, 'r') as f:

@@ -49,6 +49,9 @@ def build_parser():
                     help='bf16 = tensor-core kernels (rel 1e-2), fp32 = parity kernels (rel 1e-5)')
     ap.add_argument('--naml_word_ids', type=str2bool, default=False,
                     help='NAML over token ids + word table (the layout commented out at NAML.py:40-45)')
+    ap.add_argument('--use_abstract', type=str2bool, default=False,
+                    help='NAML abstract view (BASELINE config 3 "+abstract"; uses --num_words_abstract and a second '
+                         'per-news table abstract_embeddings.bpemb.npy.gz / .nrtab in the data directory)')
     ap.add_argument('--graph', type=str2bool, default=True,
                     help='replay forward+backward of full batches from one CUDA graph')
     ap.add_argument('--doc_sim_pairs', type=int, default=1000000, help='random pairs of the doc-sim diagnostic (main.py:201-208)')

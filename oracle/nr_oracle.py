@@ -199,11 +199,15 @@ def nrms_forward(history: Tensor, history_mask: Tensor, candidate: Tensor, label
 # ----------------------------------------------------------------------------
 def naml_news_encoder(x: Tensor, P: Dict[str, Tensor], L: int, D: int, use_category: bool,
                       use_subcategory: bool, p: float = 0.0,
-                      keep1: Optional[Tensor] = None, word_ids: bool = False) -> Tensor:
+                      keep1: Optional[Tensor] = None, word_ids: bool = False, La: int = 0) -> Tensor:
     """NAML NewsEncoder.forward, src/model/NAML.py:35-75 (fork layout: column 0
     of x is the NEWS index into the per-news title table (N+1, L*D), NAML.py:47-50).
     word_ids=True is the upstream/commented layout NAML.py:40-45:
-    columns [0,L) are token ids into a (V,D) word table, side columns follow."""
+    columns [0,L) are token ids into a (V,D) word table, side columns follow.
+    La > 0 adds the ABSTRACT view (BASELINE config 3 "+abstract").  The reference has NO code for it
+    (parameters.py:43 is an unused flag): this is the title view's chain (NAML.py:47-55) applied to a
+    second text field with its own weights `news_encoder.abstract_*`, stacked second — parity UNPINNED by the
+    reference for this view."""
     if word_ids:
         tok = x[:, :L].long()                                                # :40
         emb = embedding_lookup(P['news_encoder.title_embeddings.weight'], tok)             # :41
@@ -216,6 +220,15 @@ def naml_news_encoder(x: Tensor, P: Dict[str, Tensor], L: int, D: int, use_categ
     c = conv1d_k3(w, P['news_encoder.cnn.weight'], P['news_encoder.cnn.bias'])   # :54
     title = attention_pooling(c, *_pool_w(P, 'news_encoder.attn'))           # :55
     views = [title]
+    if La > 0:                                                               # by analogy with :47-55 (no reference code)
+        if word_ids:
+            aemb = embedding_lookup(P['news_encoder.abstract_embeddings.weight'], x[:, start:start + La].long())
+            start += La
+        else:
+            aemb = embedding_lookup(P['news_encoder.abstract_embeddings.weight'], x[:, start].long()).reshape(-1, La, D)
+            start += 1
+        ca = conv1d_k3(aemb, P['news_encoder.abstract_cnn.weight'], P['news_encoder.abstract_cnn.bias'])
+        views.append(attention_pooling(ca, *_pool_w(P, 'news_encoder.abstract_attn')))
     if use_category:                                                         # :60-64
         cat = x[:, start].long()
         views.append(embedding_lookup(P['news_encoder.category_emb.weight'], cat)
@@ -246,15 +259,15 @@ def naml_user_encoder(news_vecs: Tensor, log_mask: Tensor, P: Dict[str, Tensor],
 def naml_forward(history: Tensor, history_mask: Tensor, candidate: Tensor, label: Tensor,
                  P: Dict[str, Tensor], L: int, D: int, use_category: bool, use_subcategory: bool,
                  user_log_mask: bool, p: float = 0.0, keep: Optional[Dict[str, Tensor]] = None,
-                 word_ids: bool = False):
+                 word_ids: bool = False, La: int = 0):
     """NAML Model.forward, src/model/NAML.py:113-130.  Returns (loss, score)."""
     B, T, F = history.shape
     C = candidate.shape[1]
     k = keep or {}
     cv = naml_news_encoder(candidate.reshape(-1, F), P, L, D, use_category, use_subcategory,
-                           p, k.get('cand1'), word_ids).reshape(B, C, -1)     # :121-122
+                           p, k.get('cand1'), word_ids, La).reshape(B, C, -1)     # :121-122
     hv = naml_news_encoder(history.reshape(-1, F), P, L, D, use_category, use_subcategory,
-                           p, k.get('hist1'), word_ids).reshape(B, T, -1)     # :124-125
+                           p, k.get('hist1'), word_ids, La).reshape(B, T, -1)     # :124-125
     u = naml_user_encoder(hv, history_mask, P, user_log_mask)                 # :127
     return score_and_loss(cv, u, label)                                       # :128-129
 

@@ -200,3 +200,40 @@ def test_driver_word_id_layouts(tmp_path, model):
     assert red['scored'] == summ['scored']
     np.testing.assert_allclose(scores.cpu().numpy(), scores_o, rtol=1e-4, atol=1e-5)
     np.testing.assert_allclose(red['mean_scored'], summ['mean_scored'], atol=1e-3)
+
+
+def test_demo_flow_with_abstract_view(tmp_path):
+    """`--use_abstract True` through the driver: second per-news table read from the raw table file, extra feature
+    column, checkpoint without either frozen table, test-time metrics vs the oracle composition."""
+    from newsrecommendation_b200 import main as drv, mind_io
+    tr, te = _dirs(tmp_path)
+    La = 50
+    for d, seed in ((tr, 21), (te, 22)):
+        n_rows = mind_io.count_lines(os.path.join(d, 'news.tsv')) + 1
+        t = (np.random.RandomState(seed).standard_normal((n_rows, La * D)) * 0.4).astype(np.float32)
+        t[0] = 0
+        mind_io.write_title_table(os.path.join(d, mind_io.TITLE_TABLE_RAW.replace('title_', 'abstract_')), t)
+    mdir = str(tmp_path / 'model')
+    base = _common(tr, te, mdir, 'fp32') + ['--use_abstract', 'True', '--num_words_abstract', str(La), '--prepare', 'True']
+    red, scores, metrics, valid = drv.main(base + ['--mode', 'train_test', '--epochs', '1', '--batch_size', '32', '--lr', '0.0003',
+                                                   '--user_log_mask', 'True', '--drop_rate', '0.2'])
+    torch.set_grad_enabled(True)
+    ck = torch.load(os.path.join(mdir, 'epoch-1.pt'), map_location='cpu', weights_only=False)
+    sd = ck['model_state_dict']
+    assert drv.TITLE_KEY not in sd and drv.ABSTRACT_KEY not in sd and 'news_encoder.abstract_cnn.weight' in sd
+    a = argparse.Namespace(use_category=True, use_subcategory=True)
+    news_t, idx_t = mind_io.read_news(os.path.join(te, 'news.tsv'), a, 'test')
+    title, cat, sub = mind_io.get_doc_input(news_t, idx_t, ck['category_dict'], ck['subcategory_dict'], a)
+    comb = mind_io.combine_news_columns(title, title, cat, sub)
+    P = dict(sd)
+    P[drv.TITLE_KEY] = torch.from_numpy(np.asarray(mind_io.read_news_embeddings(te)))
+    P[drv.ABSTRACT_KEY] = torch.from_numpy(np.asarray(mind_io.read_news_embeddings(te, field='abstract')))
+    table_o = O.build_news_cache(lambda x: O.naml_news_encoder(x, P, L_TITLE, D, True, True, La=La), comb)
+    H, M, off, cand, lab = [], [], [0], [], []
+    for line in open(os.path.join(te, 'behaviors_0.tsv')):
+        h, m, c, l = O.test_line_mapper(line, idx_t, 50)
+        H.append(h); M.append(m); cand.extend(c); lab.extend(l); off.append(len(cand))
+    mets_o, scores_o = O.eval_impressions(lambda v, m: O.naml_user_encoder(v, m, P, True), table_o, np.stack(H), np.stack(M),
+                                          np.asarray(off), np.asarray(cand, np.int32), np.asarray(lab, np.int8))
+    np.testing.assert_allclose(scores.cpu().numpy(), scores_o, rtol=1e-4, atol=1e-5)
+    np.testing.assert_allclose(red['mean_scored'], O.summarize_metrics(mets_o)['mean_scored'], atol=1e-3)
