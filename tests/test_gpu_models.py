@@ -294,3 +294,29 @@ def test_naml_abstract_view_vs_oracle_composition(prec, word_ids):
         nv = model.news_encoder(T(feats).cuda())
         no = O.naml_news_encoder(T(feats), P, Lt, D, True, True, word_ids=word_ids, La=La)
     np.testing.assert_allclose(nv.cpu().numpy(), no.numpy(), rtol=tol, atol=tol * float(no.abs().max()))
+
+
+@pytest.mark.parametrize('prec', ['fp32', 'bf16'])
+def test_masked_slots_and_batch_composition_do_not_matter(prec):
+    """(B2) with user_log_mask=True the CONTENT of masked history slots has no influence on the
+    user vector (max diff 0.0 in the reference; bit-identical here); (B3) with user_log_mask=False masked slots are
+    replaced by pad_doc, so their content is irrelevant too; (B6) one encoder call over candidates + history equals
+    the two separate calls of NRMS.py:87,90 (eval mode)."""
+    for tag in ('nrms_ulm1', 'nrms_ulm0'):
+        kind, kw, P, bt, model = build_model(tag, precision=prec)
+        model.eval()
+        hist, mask, cand, label = [T(a).cuda() for a in bt]
+        F = hist.shape[-1]
+        with torch.no_grad():
+            nv = model.news_encoder(hist.reshape(-1, F)).reshape(hist.shape[0], hist.shape[1], -1)
+            u0 = model.user_encoder(nv, mask)
+            junk = nv.clone()
+            junk[mask == 0] = torch.randn_like(junk[mask == 0]) * 3.0
+            u1 = model.user_encoder(junk, mask)
+            assert torch.equal(u0, u1), tag
+            both = model.news_encoder(torch.cat([cand.reshape(-1, F), hist.reshape(-1, F)], 0))
+            cv = model.news_encoder(cand.reshape(-1, F))
+            n_c = cv.shape[0]
+            tol = 2e-6 if prec == 'fp32' else 1e-2
+            torch.testing.assert_close(both[:n_c], cv, rtol=tol, atol=tol * float(cv.abs().max()))
+            torch.testing.assert_close(both[n_c:], nv.reshape(-1, nv.shape[-1]), rtol=tol, atol=tol * float(nv.abs().max()))
