@@ -33,6 +33,7 @@ METRIC = 'NRMS/NAML train samples/s & eval impressions/s at 1/2/4/8 B200 vs CPU 
 
 
 def parse():
+    global V_SMALL, N_SMALL
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=20)
@@ -51,7 +52,11 @@ def parse():
     ap.add_argument('--abstract', action='store_true',
                     help='NAML with the abstract view of BASELINE config 3 "(+abstract)": a second per-news table of '
                          '50 tokens x 300 (3.9 GB at 65k news); no reference code exists for this view (SURVEY F9)')
-    return ap.parse_args()
+    ap.add_argument('--vocab', type=int, default=V_SMALL, help='NRMS word-table rows (config 5: 70000)')
+    ap.add_argument('--news', type=int, default=N_SMALL, help='news in the synthetic corpus (config 5: 160000)')
+    a = ap.parse_args()
+    V_SMALL, N_SMALL = a.vocab, a.news          # the MIND-small sizes unless a larger corpus is asked for
+    return a
 
 
 def peaks():
@@ -438,7 +443,7 @@ def run_ours(a):
             roof = roofline_for(top, kern[top]['ms_per_step'], kern[top]['launches_per_step'], ft, bt, pk)
             # the committed ncu capture is of the default workload (batch 128/GPU, bf16); other sizes have no capture
             roof['traffic'] = (ncu_traffic(a.model, top, kern[top]['launches_per_step'])
-                               if a.batch == 128 and a.precision == 'bf16' and not a.abstract else None)
+                               if a.batch == 128 and a.precision == 'bf16' and not a.abstract and a.vocab == 12508 else None)
             roof['peak_source'] = pk['src'] + (' (sustained bf16, kernel timed inside the step)'
                                                if roof['bound'] == 'tensor' else ' (HBM copy bandwidth)')
             roof['share_of_step'] = kern[top]['share']
@@ -450,7 +455,7 @@ def run_ours(a):
             'data': 'synthetic',
             'config': {'workload': f'{a.model} train step (fwd+bwd+allreduce+Adam), MIND-small shape: batch {B}/GPU, '
                                    f'title len {L_TITLE}, history {T_HIST}, npratio {K_NEG}, 300-d emb, 20x20 heads, '
-                                   f'drop 0.2, V={V_SMALL}' + (f', + abstract view ({L_ABSTRACT} tokens)' if (a.model == 'NAML' and a.abstract) else ''),
+                                   f'drop 0.2, V={V_SMALL}, N={N_SMALL}' + (f', + abstract view ({L_ABSTRACT} tokens)' if (a.model == 'NAML' and a.abstract) else ''),
                        'model_family': a.model, 'per_gpu_batch': B,
                        'global_batch': B * world, 'precision': a.precision, 'parallelism': f'dp{world}',
                        'launch': 'eager' if a.no_graph else 'fwd+bwd replayed from one CUDA graph, all-reduce + Adam eager',
