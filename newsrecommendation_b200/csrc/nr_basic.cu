@@ -119,24 +119,44 @@ __global__ void pad_blend_fwd_kernel(const float* __restrict__ v, const float* _
     }
 }
 
-// dv = dout*m ; dpad += sum_r dout*(1-m).  grid.x blocks each own a strided set of rows; a thread owns one
-// 4-column group (H % 4 == 0) so every row is read and written with 16-byte accesses.
+// dv = dout*m ; dpad += sum_r dout*(1-m).
+// Fast path (H % 4 == 0, H/4 <= 256): a block is RS row slots x H/4 column threads; every thread streams its
+// 4-column group of rows slot, slot + RS*grid, ... with 16-byte accesses (RS*H/4 threads in flight per block instead
+// of H/4: the kernel is latency-bound, 10 MB in and out), the slots' partial column sums meet in shared memory and
+// slot 0 issues the block's H atomics (the serial chain per dpad address is the block count, so one block per SM).
+constexpr int PADB_THREADS = 512;
+__global__ void __launch_bounds__(PADB_THREADS) pad_blend_bwd_slots_kernel(
+        const float* __restrict__ dout, const float* __restrict__ mask, float* __restrict__ dv,
+        float* __restrict__ dpad, int64_t rows, int H) {
+    __shared__ float4 part[PADB_THREADS];
+    const int tpr = H >> 2, RS = PADB_THREADS / tpr;
+    const int slot = threadIdx.x / tpr, cg = threadIdx.x - slot * tpr;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (slot < RS) {
+        const int c = cg * 4;
+#pragma unroll 4
+        for (int64_t r = (int64_t)blockIdx.x * RS + slot; r < rows; r += (int64_t)gridDim.x * RS) {
+            const float m = __ldg(mask + r), im = 1.f - m;
+            const float4 g = ldg4(dout + r * H + c);
+            *(float4*)(dv + r * H + c) = make_float4(g.x * m, g.y * m, g.z * m, g.w * m);
+            acc.x = fmaf(g.x, im, acc.x); acc.y = fmaf(g.y, im, acc.y); acc.z = fmaf(g.z, im, acc.z); acc.w = fmaf(g.w, im, acc.w);
+        }
+    }
+    part[threadIdx.x] = acc;
+    __syncthreads();
+    if (slot == 0) {
+        for (int s2 = 1; s2 < RS; ++s2) {           // fixed slot order
+            const float4 o = part[s2 * tpr + cg];
+            acc.x += o.x; acc.y += o.y; acc.z += o.z; acc.w += o.w;
+        }
+        const int c = cg * 4;
+        atomicAdd(dpad + c, acc.x); atomicAdd(dpad + c + 1, acc.y); atomicAdd(dpad + c + 2, acc.z); atomicAdd(dpad + c + 3, acc.w);
+    }
+}
+
+// general shapes: grid.x blocks each own a strided set of rows, a thread owns one column
 __global__ void pad_blend_bwd_kernel(const float* __restrict__ dout, const float* __restrict__ mask,
                                      float* __restrict__ dv, float* __restrict__ dpad, int64_t rows, int H) {
-    if ((H & 3) == 0) {
-        for (int c = threadIdx.x * 4; c < H; c += blockDim.x * 4) {
-            float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 8
-            for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
-                const float m = __ldg(mask + r), im = 1.f - m;
-                const float4 g = ldg4(dout + r * H + c);
-                *(float4*)(dv + r * H + c) = make_float4(g.x * m, g.y * m, g.z * m, g.w * m);
-                acc.x = fmaf(g.x, im, acc.x); acc.y = fmaf(g.y, im, acc.y); acc.z = fmaf(g.z, im, acc.z); acc.w = fmaf(g.w, im, acc.w);
-            }
-            atomicAdd(dpad + c, acc.x); atomicAdd(dpad + c + 1, acc.y); atomicAdd(dpad + c + 2, acc.z); atomicAdd(dpad + c + 3, acc.w);
-        }
-        return;
-    }
     for (int c = threadIdx.x; c < H; c += blockDim.x) {
         float acc = 0.f;
         for (int64_t r = blockIdx.x; r < rows; r += gridDim.x) {
@@ -151,18 +171,34 @@ __global__ void pad_blend_bwd_kernel(const float* __restrict__ dout, const float
 
 // score + CE: one warp per sample.  Each score is computed once (16-byte loads when H % 4 == 0) and kept by lane
 // k % 32, so the log-sum-exp needs no second pass over the vectors; C > 32 walks the candidates in groups of 32
-// with a running maximum.
-__device__ __forceinline__ float dot_row(const float* __restrict__ c, const float* __restrict__ u, int H, int lane) {
-    float s = 0.f;
+// with a running maximum.  The dot products are taken 8 candidates at a time so that a lane has 8 independent
+// loads in flight per step of h (the kernel is pure latency at B = 128: 1 MB of vectors, one warp per sample).
+__device__ __forceinline__ void dot_rows8(const float* __restrict__ c, const float* __restrict__ u, int H, int cnt,
+                                          int lane, float (&out)[8]) {
+    float s[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s[j] = 0.f;
     if ((H & 3) == 0) {
         for (int h = lane * 4; h < H; h += 128) {
-            const float4 a = ldg4(c + h), v = ldg4(u + h);
-            s = fmaf(a.x, v.x, s); s = fmaf(a.y, v.y, s); s = fmaf(a.z, v.z, s); s = fmaf(a.w, v.w, s);
+            const float4 v = ldg4(u + h);
+            float4 a[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a[j] = j < cnt ? ldg4(c + (int64_t)j * H + h) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                s[j] = fmaf(a[j].x, v.x, s[j]); s[j] = fmaf(a[j].y, v.y, s[j]);
+                s[j] = fmaf(a[j].z, v.z, s[j]); s[j] = fmaf(a[j].w, v.w, s[j]);
+            }
         }
     } else {
-        for (int h = lane; h < H; h += 32) s = fmaf(__ldg(c + h), __ldg(u + h), s);
+        for (int h = lane; h < H; h += 32) {
+            const float v = __ldg(u + h);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) s[j] = fmaf(j < cnt ? __ldg(c + (int64_t)j * H + h) : 0.f, v, s[j]);
+        }
     }
-    return warp_sum(s);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) out[j] = warp_sum(s[j]);
 }
 __global__ void score_ce_fwd_kernel(const float* __restrict__ cand, const float* __restrict__ user,
                                     const int64_t* __restrict__ label, float* __restrict__ score,
@@ -177,12 +213,20 @@ __global__ void score_ce_fwd_kernel(const float* __restrict__ cand, const float*
     for (int k0 = 0; k0 < C; k0 += 32) {
         float mine = -INFINITY, gmx = mx;
         const int kn = C - k0 < 32 ? C - k0 : 32;
-        for (int j = 0; j < kn; ++j) {
-            const int k = k0 + j;
-            const float s = dot_row(cand + (b * C + k) * H, u, H, lane);
-            if (lane == j) { mine = s; score[b * C + k] = s; }
-            if (s > gmx) { gmx = s; arg = k; }      // first maximum, as torch.argmax
-            if (k == lab) picked = s;
+        for (int j0 = 0; j0 < kn; j0 += 8) {
+            float s8[8];
+            const int cnt = kn - j0 < 8 ? kn - j0 : 8;
+            dot_rows8(cand + (b * C + k0 + j0) * H, u, H, cnt, lane, s8);
+#pragma unroll
+            for (int jj = 0; jj < 8; ++jj) {
+                if (jj < cnt) {
+                    const int j = j0 + jj, k = k0 + j;
+                    const float s = s8[jj];
+                    if (lane == j) { mine = s; score[b * C + k] = s; }
+                    if (s > gmx) { gmx = s; arg = k; }      // first maximum, as torch.argmax
+                    if (k == lab) picked = s;
+                }
+            }
         }
         z = z * expf(mx - gmx) + warp_sum(lane < kn ? expf(mine - gmx) : 0.f);     // exp(-inf) = 0 on the first group
         mx = gmx;
@@ -381,7 +425,10 @@ int nr_pad_blend_bwd(const float* dout, const float* mask, float* dv, float* dpa
     // block count, so one block per SM (not more) and deep unrolling inside
     int64_t g = n * T < sm_count() ? n * T : sm_count();
     ProfScope ps_pad_blend_bwd("pad_blend_bwd", (cudaStream_t)stream);
-    pad_blend_bwd_kernel<<<(unsigned)g, 128, 0, (cudaStream_t)stream>>>(dout, mask, dv, dpad, n * T, H);
+    if ((H & 3) == 0 && H / 4 <= PADB_THREADS / 2)
+        pad_blend_bwd_slots_kernel<<<(unsigned)g, PADB_THREADS, 0, (cudaStream_t)stream>>>(dout, mask, dv, dpad, n * T, H);
+    else
+        pad_blend_bwd_kernel<<<(unsigned)g, 128, 0, (cudaStream_t)stream>>>(dout, mask, dv, dpad, n * T, H);
     return check_last("nr_pad_blend_bwd");
 }
 
@@ -389,7 +436,7 @@ int nr_score_ce_fwd(const float* cand, const float* user, const int64_t* label, 
                     float* hits, float* per_sample_ws, int64_t B, int32_t C, int32_t H, void* stream) {
     NR_REQUIRE(cand && user && label && score && loss && hits && per_sample_ws, "nr_score_ce_fwd: NULL pointer");
     NR_REQUIRE(B > 0 && C > 0 && H > 0, "nr_score_ce_fwd: bad sizes");
-    const int threads = 128;
+    const int threads = B <= 2 * (int64_t)sm_count() ? 32 : 128;      // small batches: one warp per block, spread over the SMs
     ProfScope ps_score_ce_fwd("score_ce_fwd", (cudaStream_t)stream);
     score_ce_fwd_kernel<<<(unsigned)((B * 32 + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
         cand, user, label, score, per_sample_ws, B, C, H);
