@@ -258,15 +258,20 @@ class EmbedDenseFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dout):
         emb, ids, col, w = ctx.saved
-        dout = L.f32(dout)
         n, F = ids.shape
         E, H = emb.shape[1], w.shape[0]
+        # the gradient of torch.stack(views, 1) arrives as a row-strided slice: the kernels take the row stride, so
+        # no contiguous copy (11 MB per view at B = 128)
+        if not (dout.is_cuda and dout.dtype == torch.float32 and dout.dim() == 2 and dout.stride(1) == 1 and dout.stride(0) >= H
+                and dout.stride(0) % 4 == 0 and dout.data_ptr() % 16 == 0):
+            dout = L.f32(dout)
+        ld = dout.stride(0)
         pe, pw, pb = ctx.params
         (bemb, demb), (bw, dw) = _grad_target(pe, emb), _grad_target(pw, w)
         bb, db = _grad_target(pb, torch.empty(H, dtype=torch.float32, device=w.device))
         ws = L.workspace(L.lib.nr_embed_dense_workspace(emb.shape[0], H), w.device)
-        L.call('nr_embed_dense_bwd', L.ptr(emb), emb.shape[0], ids.data_ptr() + 4 * col, F, L.ptr(w), L.ptr(dout),
-               H, L.ptr(bw), L.ptr(bb), L.ptr(bemb), n, E, H, L.ptr(ws), ws.numel(), L.stream())
+        L.call('nr_embed_dense_bwd', L.ptr(emb), emb.shape[0], ids.data_ptr() + 4 * col, F, L.ptr(w), dout.data_ptr(),
+               ld, L.ptr(bw), L.ptr(bb), L.ptr(bemb), n, E, H, L.ptr(ws), ws.numel(), L.stream())
         ctx.params = None
         return demb, None, None, dw, db
 
