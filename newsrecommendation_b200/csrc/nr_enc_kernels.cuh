@@ -304,8 +304,8 @@ inline size_t attn_bf16_bwd_smem(int S, int DK) {
 
 // ---- AttentionPooling tails over bf16 (model_utils.py:23-30) -----------------------------------------
 // logits (n*SP) fp32 come from the fc1 GEMM epilogue (tanh, dot w2, + b2).  p = exp(a)*m;
-// alpha = p/(sum p + eps); out = sum_s alpha_s y_s.  One block (128 threads) per sequence.
-static __global__ void __launch_bounds__(128)
+// alpha = p/(sum p + eps); out = sum_s alpha_s y_s.  One block (128 or 256 threads) per sequence.
+static __global__ void __launch_bounds__(256)
 pool_tail_fwd_bf16_kernel(const bf16* __restrict__ y, const float* __restrict__ logits,
                           const float* __restrict__ mask, float* __restrict__ out,
                           float* __restrict__ alpha_save, int S, int SP, int H) {
@@ -331,11 +331,11 @@ pool_tail_fwd_bf16_kernel(const bf16* __restrict__ y, const float* __restrict__ 
     }
     __syncthreads();
     // Few, long sequences (the user encoder: 128 x 50 rows): the block is alone on its SM, so what matters is how
-    // many loads are in flight.  Warp w takes rows w, w+4, ... (each lane 16-byte chunks c = lane, lane+32, ...),
-    // all of a warp's row loads are independent, and the four partial sums are combined through shared memory.
-    if ((H & 7) == 0 && H <= 512 && blockDim.x == 128) {
-        float* part = sp + SP;                      // [4][H] partial sums (dynamic smem sized by the launcher)
-        const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    // many loads are in flight.  Warp w takes rows w, w+NW, ... (each lane 16-byte chunks c = lane, lane+32, ...),
+    // all of a warp's row loads are independent, and the NW partial sums are combined through shared memory.
+    if ((H & 7) == 0 && H <= 512) {
+        float* part = sp + SP;                      // [NW][H] partial sums (dynamic smem sized by the launcher)
+        const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, NW = blockDim.x >> 5;
         const int HC = H >> 3;
         float acc[2][8];
 #pragma unroll
@@ -344,7 +344,7 @@ pool_tail_fwd_bf16_kernel(const bf16* __restrict__ y, const float* __restrict__ 
             for (int j = 0; j < 8; ++j) acc[k][j] = 0.f;
         const bf16* yt = y + seq * SP * H;
 #pragma unroll 4
-        for (int s = w; s < S; s += 4) {
+        for (int s = w; s < S; s += NW) {
             const float a = sp[s];
 #pragma unroll
             for (int k = 0; k < 2; ++k) {
@@ -368,8 +368,11 @@ pool_tail_fwd_bf16_kernel(const bf16* __restrict__ y, const float* __restrict__ 
             }
         }
         __syncthreads();
-        for (int h = threadIdx.x; h < H; h += blockDim.x)
-            out[seq * H + h] = (part[h] + part[H + h]) + (part[2 * H + h] + part[3 * H + h]);
+        for (int h = threadIdx.x; h < H; h += blockDim.x) {
+            float o = 0.f;
+            for (int k = 0; k < NW; k += 2) o += part[k * H + h] + part[(k + 1) * H + h];     // NW is even; fixed order
+            out[seq * H + h] = o;
+        }
         return;
     }
     for (int h = threadIdx.x * 4; h < H; h += blockDim.x * 4) {

@@ -590,7 +590,9 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         else if (H <= 512) launch(pool_tail_fwd_warp_kernel<2>);
         else launch(pool_tail_fwd_warp_kernel<4>);
     } else {
-        pool_tail_fwd_bf16_kernel<<<(unsigned)n, 128, (p.SP + 4 * (size_t)H) * sizeof(float), st>>>(y, logits, enc->mask, out, alpha, S, p.SP, H);
+        // few sequences (fewer than two per SM): 8 warps per block so that all of a sequence's rows are in flight at once
+        const int threads = (S > 16 && n <= 2 * (int64_t)sm_count()) ? 256 : 128;
+        pool_tail_fwd_bf16_kernel<<<(unsigned)n, threads, (p.SP + (threads / 32) * (size_t)H) * sizeof(float), st>>>(y, logits, enc->mask, out, alpha, S, p.SP, H);
     }
     return check_last("enc.pool_fwd");
 }
