@@ -292,7 +292,7 @@ def cpu_train_samples_per_s(a, budget_s=25.0, max_steps=6):
             for k in train:
                 g = P[k].grad if P[k].grad is not None else torch.zeros_like(P[k])
                 O.adam_step(P[k], g, st[k][0], st[k][1], s, 3e-4)
-        return float(loss)
+        return float(loss.detach())
 
     step(0, 1)                                   # warm-up
     t0 = time.perf_counter()
