@@ -11,7 +11,6 @@ Eval: news-vector cache encoded in row shards + all-gather (reference: every ran
 everything, main.py:190-196); impressions as CSR, scored by gather+dot from the device
 table; AUC/MRR/nDCG@5/10 per impression on device; 5-scalar all-reduce.
 """
-import ctypes as C
 
 import torch
 import torch.distributed as dist

@@ -1,6 +1,5 @@
 """GPU parity, op level: libnr_sm100.so (through the C ABI / ops shims) vs the CPU oracle
 and the reference-generated golden fixtures.  fp32 mode: rel 1e-5 (BASELINE north_star)."""
-import argparse
 import os
 
 import numpy as np
