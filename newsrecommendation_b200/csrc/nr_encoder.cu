@@ -4,6 +4,7 @@
 // UserEncoder (NRMS.py:55-62) as one pipeline of tcgen05 GEMMs (nr_tc_gemm.cuh, nr_tc_gemm_tn.cuh)
 // with fused epilogues and fp32 SIMT tails (nr_enc_kernels.cuh).  Gradient math: SURVEY Appendix C.
 #include <string.h>
+#include <mutex>
 #include "nr_enc_kernels.cuh"
 #include "nr_attn_mma.cuh"
 #include "nr_tc_gemm.cuh"
@@ -482,6 +483,55 @@ int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv,
 
 }  // namespace
 
+// ---- optional fork of the weight-gradient GEMMs (NR_BWD_FORK=1; OFF by default: prepared, not yet measured) ------
+// The small launches of a backward (the user encoder: 128 x 50 rows) are latency-bound and serial, yet dW1 and
+// dW_QKV / dW_conv feed nothing downstream.  With the fork they run on a side stream, ordered by events after the
+// kernel that produces their input and joined before the call returns (workspace reuse stays safe, and the pattern
+// is capturable: the side stream joins the capture through the event wait and is joined back before the end).
+namespace {
+struct BwdFork {
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
+};
+BwdFork* bwd_fork_for_device() {
+    static const bool on = [] { const char* e = getenv("NR_BWD_FORK"); return e && e[0] == '1'; }();
+    if (!on) return nullptr;
+    static std::mutex mu;
+    static BwdFork forks[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+    std::lock_guard<std::mutex> lk(mu);
+    BwdFork& f = forks[dev];
+    if (!f.side) {
+        cudaStream_t s = nullptr;
+        if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
+        for (auto& e : f.ev)
+            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
+        f.side = s;
+    }
+    return &f;
+}
+struct ForkScope {
+    BwdFork* f;
+    cudaStream_t main;
+    bool used = false;
+    // the side stream may start after everything enqueued on `main` so far
+    cudaStream_t after_main(int slot) {
+        if (!f) return main;
+        cudaEventRecord(f->ev[slot], main);
+        cudaStreamWaitEvent(f->side, f->ev[slot], 0);
+        used = true;
+        return f->side;
+    }
+    ~ForkScope() {
+        if (f && used) {
+            cudaEventRecord(f->ev[2], f->side);
+            cudaStreamWaitEvent(main, f->ev[2], 0);
+        }
+    }
+};
+}  // namespace
+
 extern "C" {
 
 size_t nr_title_encoder_save_bytes(const nr_title_encoder_t* enc, int64_t n) {
@@ -629,6 +679,8 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     const bool pool = enc->kind == NR_ENC_POOL;
     const bool want_dx = gr->dtable || gr->dx_dense;
     const int one = 0;
+    // small launches only: a backward that fills the GPU gains nothing from a second stream
+    ForkScope fork{p.R <= 16384 ? bwd_fork_for_device() : nullptr, st};
 
     // 1. pooling tail backward: dz, dw2, db2, db1
     {
@@ -656,7 +708,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         if (int e = check_last("enc.pool_bwd")) return e;
     }
     // 2. dW1 (Q,H) += dz^T . y
-    if (int e = gemm_tc_tn(dz, Q, Q, y, H, H, p.R, 1, &one, TnEpiPlain{gr->dp_w1, H, 0}, st, "enc.dw1")) return e;
+    if (int e = gemm_tc_tn(dz, Q, Q, y, H, H, p.R, 1, &one, TnEpiPlain{gr->dp_w1, H, 0}, fork.after_main(0), "enc.dw1")) return e;
     // 3. dY = dz . W1 + alpha g   (output-dropout mask re-applied for MHSA)
     if (!pool || want_dx) {
         EpiPoolDx ep{dy, pool ? gr->dx_dense : nullptr, H, alpha, g, S, p.SP, H,
@@ -670,7 +722,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st)) return e;
         if (int e = gemm_tc_tn(dqkv, 3 * H, 3 * H, xb, Dm + 1, p.ldx, p.R, 1, &one,
                                TnEpiQkv{gr->dw[0], gr->dw[1], gr->dw[2], gr->db[0], gr->db[1], gr->db[2], H, Dm,
-                                        qkv_head_major(p.SP, H / enc->heads) ? H / enc->heads : 0}, st,
+                                        qkv_head_major(p.SP, H / enc->heads) ? H / enc->heads : 0}, fork.after_main(1),
                                "enc.dwqkv"))
             return e;
         if (want_dx)
@@ -679,7 +731,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
                 return e;
     } else {
         const int sh[3] = {-1, 0, 1};
-        if (int e = gemm_tc_tn(dy, H, H, xb, Dm + 1, p.ldx, p.R, 3, sh, TnEpiConv{gr->dw[0], gr->db[0], Dm}, st,
+        if (int e = gemm_tc_tn(dy, H, H, xb, Dm + 1, p.ldx, p.R, 3, sh, TnEpiConv{gr->dw[0], gr->db[0], Dm}, fork.after_main(1),
                                "enc.dwconv"))
             return e;
         if (want_dx) {
