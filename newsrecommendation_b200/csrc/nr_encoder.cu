@@ -483,7 +483,7 @@ int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv,
 
 }  // namespace
 
-// ---- optional fork of the weight-gradient GEMMs (NR_BWD_FORK=1; OFF by default: prepared, not yet measured) ------
+// ---- optional fork of the weight-gradient GEMMs (NR_BWD_FORK=1; OFF by default: one run, no gain beyond noise) ------
 // The small launches of a backward (the user encoder: 128 x 50 rows) are latency-bound and serial, yet dW1 and
 // dW_QKV / dW_conv feed nothing downstream.  With the fork they run on a side stream, ordered by events after the
 // kernel that produces their input and joined before the call returns (workspace reuse stays safe, and the pattern
