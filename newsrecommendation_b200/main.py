@@ -116,6 +116,9 @@ def _embedding_table(data_dir, args, field='title'):
     if args.model == 'NRMS' or args.naml_word_ids:
         return np.load(os.path.join(data_dir, 'word_embeddings.npy'))
     table = mind_io.read_news_embeddings(data_dir, field=field)
+    raw = os.path.join(data_dir, mind_io.TITLE_TABLE_RAW.replace('title_', field + '_'))
+    if args.precision == 'fp32' and mind_io.raw_table_dtype(raw) == 'bf16' and not isinstance(table, np.memmap):
+        logging.warning(f'{raw} holds a bf16 payload: --precision fp32 will not match a run on the fp32 table')
     want = (args.num_words_title if field == 'title' else args.num_words_abstract) * args.word_embedding_dim
     if table.shape[1] != want:
         raise ValueError(f'{field} table has {table.shape[1]} columns, --num_words_{field} x --word_embedding_dim = {want}')
@@ -360,7 +363,7 @@ def main(argv=None):
     if args.mode == 'read_embeddings':
         for d in (args.train_data_dir, args.test_data_dir):
             if os.path.exists(os.path.join(d, mind_io.TITLE_TABLE_GZ)):
-                t = mind_io.read_news_embeddings(d, cache=True)
+                t = mind_io.read_news_embeddings(d, cache=True, cache_dtype=args.table_dtype)
                 logging.info(f'{d}: title table {t.shape}')
     return out
 

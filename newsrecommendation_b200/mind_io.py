@@ -83,38 +83,78 @@ def combine_news_columns(*cols):
 # ------------------------------------------------------------------------------------------------
 # title-embedding table
 # ------------------------------------------------------------------------------------------------
-def write_title_table(path, table):
-    """Raw table file: 256-byte header (magic, rows, cols, dtype code 0 = fp32 little-endian) + row-major
-    payload.  `cols` = L*D of the fork's per-news layout (NAML.py:104-107)."""
-    table = np.ascontiguousarray(table, dtype='<f4')
-    if table.ndim != 2:
+TABLE_DTYPES = {'fp32': 0, 'bf16': 1}     # header dtype codes
+_ROW_BLOCK = 4096                         # rows converted per step (keeps the temporaries of a 5.8 GB table small)
+
+
+def _bf16_bits(a):
+    """fp32 -> bf16 bit patterns, round to nearest even (what the staging kernel's conversion does)."""
+    u = np.ascontiguousarray(a, dtype='<f4').view(np.uint32)
+    return ((u + (((u >> 16) & 1) + np.uint32(0x7FFF))) >> 16).astype('<u2')
+
+
+def write_title_table(path, table, dtype='fp32'):
+    """Raw table file: 256-byte header (magic, rows, cols, dtype code) + row-major little-endian payload.
+    `cols` = L*D of the fork's per-news layout (NAML.py:104-107).  dtype 'fp32' is lossless; 'bf16' halves the
+    file (1.2 GB instead of 2.35 GB for MIND-small) for the bf16 mode, whose staging kernel rounds every table
+    row to bf16 anyway — it is NOT for the fp32 parity mode."""
+    if dtype not in TABLE_DTYPES:
+        raise ValueError(f'title table dtype must be one of {sorted(TABLE_DTYPES)}')
+    if getattr(table, 'ndim', 0) != 2:
         raise ValueError('title table must be 2-D (N+1, L*D)')
-    head = TABLE_MAGIC + struct.pack('<qqq', table.shape[0], table.shape[1], 0)
+    head = TABLE_MAGIC + struct.pack('<qqq', table.shape[0], table.shape[1], TABLE_DTYPES[dtype])
     tmp = str(path) + '.tmp'
     with open(tmp, 'wb') as f:
         f.write(head.ljust(TABLE_HEADER_BYTES, b'\x00'))
-        table.tofile(f)
+        for r0 in range(0, table.shape[0], _ROW_BLOCK):
+            blk = np.ascontiguousarray(table[r0:r0 + _ROW_BLOCK], dtype='<f4')
+            if dtype == 'bf16':
+                if not np.isfinite(blk).all():
+                    raise ValueError('title table holds non-finite values')
+                blk = _bf16_bits(blk)
+            blk.tofile(f)
     os.replace(tmp, path)
 
 
 def read_title_table(path):
-    """Memory-maps a file written by `write_title_table` (read-only; `torch.from_numpy(np.asarray(...))` +
-    `.cuda()` streams it to HBM without a host copy of the decompressed array)."""
+    """Reads a file written by `write_title_table`.  fp32 payloads are memory-mapped (read-only;
+    `torch.from_numpy(np.asarray(...))` + `.cuda()` streams them to HBM without a host copy of a decompressed
+    array); bf16 payloads are widened to an fp32 array block by block (exact: bf16 is the top half of fp32)."""
     with open(path, 'rb') as f:
         head = f.read(TABLE_HEADER_BYTES)
     if len(head) != TABLE_HEADER_BYTES or head[:8] != TABLE_MAGIC:
         raise ValueError(f'{path}: not a title table file')
     rows, cols, code = struct.unpack('<qqq', head[8:32])
-    if code != 0 or rows <= 0 or cols <= 0:
+    if code not in TABLE_DTYPES.values() or rows <= 0 or cols <= 0:
         raise ValueError(f'{path}: unsupported header (rows={rows}, cols={cols}, dtype code={code})')
-    if os.path.getsize(path) != TABLE_HEADER_BYTES + rows * cols * 4:
+    width = 4 if code == 0 else 2
+    if os.path.getsize(path) != TABLE_HEADER_BYTES + rows * cols * width:
         raise ValueError(f'{path}: size does not match its header (truncated?)')
-    return np.memmap(path, dtype='<f4', mode='r', offset=TABLE_HEADER_BYTES, shape=(rows, cols))
+    if code == 0:
+        return np.memmap(path, dtype='<f4', mode='r', offset=TABLE_HEADER_BYTES, shape=(rows, cols))
+    bits = np.memmap(path, dtype='<u2', mode='r', offset=TABLE_HEADER_BYTES, shape=(rows, cols))
+    out = np.empty((rows, cols), dtype=np.float32)
+    for r0 in range(0, rows, _ROW_BLOCK):
+        out[r0:r0 + _ROW_BLOCK] = (bits[r0:r0 + _ROW_BLOCK].astype(np.uint32) << 16).view(np.float32)
+    return out
 
 
-def read_news_embeddings(data_dir, cache=False, field='title'):
+def raw_table_dtype(path):
+    """'fp32' / 'bf16' payload of a raw table file, None when `path` is not one."""
+    try:
+        with open(path, 'rb') as f:
+            head = f.read(32)
+    except OSError:
+        return None
+    if len(head) < 32 or head[:8] != TABLE_MAGIC:
+        return None
+    code = struct.unpack('<q', head[24:32])[0]
+    return {v: k for k, v in TABLE_DTYPES.items()}.get(code)
+
+
+def read_news_embeddings(data_dir, cache=False, field='title', cache_dtype='fp32'):
     """preprocess.py:227-232.  Prefers the raw table next to the .npy.gz when it is at least as new;
-    `cache=True` writes it after a gzip read so the next start-up skips the gunzip.  `field='abstract'` reads the
+    `cache=True` writes it (as `cache_dtype`) after a gzip read so the next start-up skips the gunzip.  `field='abstract'` reads the
     second table of the abstract view (same format, `abstract_embeddings.bpemb.*`)."""
     gz = os.path.join(data_dir, TITLE_TABLE_GZ.replace('title_', field + '_'))
     raw = os.path.join(data_dir, TITLE_TABLE_RAW.replace('title_', field + '_'))
@@ -123,7 +163,7 @@ def read_news_embeddings(data_dir, cache=False, field='title'):
     with gzip.GzipFile(gz, 'r') as f:
         table = np.load(f)
     if cache:
-        write_title_table(raw, table)
+        write_title_table(raw, table, dtype=cache_dtype)
     return table
 
 

@@ -52,6 +52,9 @@ def build_parser():
     ap.add_argument('--use_abstract', type=str2bool, default=False,
                     help='NAML abstract view (BASELINE config 3 "+abstract"; uses --num_words_abstract and a second '
                          'per-news table abstract_embeddings.bpemb.npy.gz / .nrtab in the data directory)')
+    ap.add_argument('--table_dtype', type=str, default='fp32', choices=['fp32', 'bf16'],
+                    help='payload of the raw title table that --mode read_embeddings writes next to the .npy.gz '
+                         '(bf16: half the file, for --precision bf16 only)')
     ap.add_argument('--graph', type=str2bool, default=True,
                     help='replay forward+backward of full batches from one CUDA graph')
     ap.add_argument('--doc_sim_pairs', type=int, default=1000000, help='random pairs of the doc-sim diagnostic (main.py:201-208)')

@@ -91,3 +91,47 @@ def test_title_table_file_roundtrip(tmp_path):
     (tmp_path / 'junk.nrtab').write_bytes(b'\x00' * 300)
     with pytest.raises(ValueError):
         mind_io.read_title_table(tmp_path / 'junk.nrtab')
+
+
+def test_title_table_file_bf16_payload(tmp_path):
+    """dtype code 1: bf16 payload, round-to-nearest-even on write (checked against torch's conversion, ties and
+    signed values included), exact widening on read, half the file."""
+    import torch
+    from newsrecommendation_b200 import mind_io
+    rs = np.random.RandomState(3)
+    rows = mind_io._ROW_BLOCK + 37                               # more than one conversion block
+    full = (rs.standard_normal((rows, 24)) * 0.4).astype(np.float32)
+    full[0] = 0
+    # exact ties between two bf16 neighbours (low half = 0x8000) with even and odd upper halves, both signs
+    ties = np.array([0x3F808000, 0x3F818000, 0xBF808000, 0xBF818000, 0x3F80FFFF, 0x00000001, 0x7F7F7FFF],
+                    dtype=np.uint32).view(np.float32)
+    full[1, :ties.size] = ties
+    path = tmp_path / 'title_embeddings.bpemb.nrtab'
+    mind_io.write_title_table(path, full, dtype='bf16')
+    assert os.path.getsize(path) == mind_io.TABLE_HEADER_BYTES + full.size * 2
+    back = mind_io.read_title_table(path)
+    want = torch.from_numpy(full).to(torch.bfloat16).float().numpy()
+    assert back.dtype == np.float32 and back.shape == full.shape
+    assert np.array_equal(back.view(np.uint32), want.view(np.uint32))
+    assert np.array_equal(mind_io.read_news_embeddings(str(tmp_path)), back)       # picked up like the fp32 file
+    with pytest.raises(ValueError):
+        mind_io.write_title_table(tmp_path / 'x.nrtab', full, dtype='fp16')
+    bad = full.copy(); bad[2, 2] = np.inf
+    with pytest.raises(ValueError):
+        mind_io.write_title_table(tmp_path / 'y.nrtab', bad, dtype='bf16')
+    # the driver's conversion mode writes what --table_dtype asks for
+    from newsrecommendation_b200 import parameters
+    assert parameters.parse_args([]).table_dtype == 'fp32'
+    assert parameters.parse_args(['--table_dtype', 'bf16']).table_dtype == 'bf16'
+
+
+def test_raw_table_dtype(tmp_path):
+    from newsrecommendation_b200 import mind_io
+    t = np.ones((3, 8), dtype=np.float32)
+    mind_io.write_title_table(tmp_path / 'a.nrtab', t)
+    mind_io.write_title_table(tmp_path / 'b.nrtab', t, dtype='bf16')
+    (tmp_path / 'c.nrtab').write_bytes(b'not a table')
+    assert mind_io.raw_table_dtype(tmp_path / 'a.nrtab') == 'fp32'
+    assert mind_io.raw_table_dtype(tmp_path / 'b.nrtab') == 'bf16'
+    assert mind_io.raw_table_dtype(tmp_path / 'c.nrtab') is None
+    assert mind_io.raw_table_dtype(tmp_path / 'missing.nrtab') is None
