@@ -124,3 +124,73 @@ def test_eval_pipeline_vs_oracle(tag):
     sel = valid_o & untied
     assert sel.sum() > I // 3
     np.testing.assert_allclose(md[sel], mets_o[sel], rtol=0, atol=1e-12)
+
+
+def _eval_case(kind, kw, rs, I, Tn=50):
+    """Synthetic eval corpus + impressions for the end-to-end checks (news rows, padded histories, CSR candidates)."""
+    Lw = kw['L']
+    if kind == 'nrms':
+        N = 300
+        news = rs.randint(1, kw['V'], size=(N + 1, Lw)).astype(np.int32)
+        tl = rs.randint(3, Lw + 1, size=N + 1)
+        news[np.arange(Lw)[None, :] >= tl[:, None]] = 0
+        news[0] = 0
+    else:
+        N = kw['N']
+        news = np.zeros((N + 1, 3), np.int32)
+        news[:, 0] = np.arange(N + 1)
+        news[1:, 1] = rs.randint(1, synth.NCAT + 1, size=N)
+        news[1:, 2] = rs.randint(1, synth.NSUB + 1, size=N)
+    hist = np.zeros((I, Tn), np.int32); hmask = np.zeros((I, Tn), np.float32)
+    for i in range(I):
+        k = 0 if i == 0 else int(rs.randint(1, 70))
+        hist[i], hmask[i] = O.pad_history(rs.randint(1, N + 1, size=k).tolist(), Tn)     # dataset.py:17-24
+    cs = rs.randint(2, min(40, N), size=I)
+    off = np.zeros(I + 1, np.int64); off[1:] = np.cumsum(cs)
+    cand = np.concatenate([rs.permutation(N + 1)[:c] for c in cs]).astype(np.int32)
+    labels = (rs.rand(off[-1]) < 0.15).astype(np.int8)
+    for i in range(I):
+        labels[off[i]] = 1; labels[off[i] + 1] = 0
+    return news, hist, hmask, off, cand, labels
+
+
+@pytest.mark.parametrize('tag', ['nrms_ulm0', 'nrms_ulm1', 'naml_ulm1_c11'])
+def test_eval_pipeline_bf16_vs_oracle(tag):
+    """The mode bench.py's eval leg runs: bf16 tensor-core encoders -> device cache -> scoring -> mean
+    AUC/MRR/nDCG@5/10, against the fp32 oracle restatement of src/main.py:190-263 on 4,000 impressions.
+    Tolerances (BASELINE north_star): metric means 1e-3; per-impression rankings exact wherever the oracle's
+    scores are separated by more than twice the observed bf16 score error."""
+    from newsrecommendation_b200 import engine
+    kind, kw, Pn, bt, model = build_model(tag, precision='bf16')
+    model.eval()
+    rs = np.random.RandomState(91)
+    I = 4000
+    news, hist, hmask, off, cand, labels = _eval_case(kind, kw, rs, I)
+    P = {k: T(v) for k, v in Pn.items()}
+    if kind == 'nrms':
+        enc = lambda x: O.nrms_news_encoder(x, P, 20)
+        uenc = lambda v, m: O.nrms_user_encoder(v, m, P, 20, kw['user_log_mask'])
+    else:
+        enc = lambda x: O.naml_news_encoder(x, P, kw['L'], synth.D, True, True)
+        uenc = lambda v, m: O.naml_user_encoder(v, m, P, kw['user_log_mask'])
+    table_o = O.build_news_cache(enc, news)
+    mets_o, scores_o = O.eval_impressions(uenc, table_o, hist, hmask, off, cand, labels)
+    summ_o = O.summarize_metrics(mets_o)
+    table_d = engine.build_news_cache(model, T(news).cuda(), batch=64)
+    close(table_d, table_o, rtol=1e-2, atol=1e-2 * float(np.abs(table_o).max()))          # bf16 mode: rel 1e-2
+    scores_d, mets_d, valid_d, sums_d = engine.score_impressions(
+        model, table_d, T(hist).cuda(), T(hmask).cuda(), T(off).cuda(), T(cand).cuda(), T(labels).cuda(), batch=512)
+    sd = scores_d.cpu().numpy()
+    err = float(np.abs(sd - scores_o).max())
+    assert err <= 2e-2 * float(np.abs(scores_o).max()) + 1e-4, (err, float(np.abs(scores_o).max()))
+    valid_o = ~np.isnan(mets_o[:, 0])
+    assert (valid_d.cpu().numpy().astype(bool) == valid_o).all()
+    res = engine.reduce_eval_sums(sums_d, I)
+    assert res['scored'] == summ_o['scored'] and res['total'] == I
+    np.testing.assert_allclose(res['mean_scored'], summ_o['mean_scored'], rtol=0, atol=1e-3)
+    # exact rankings where the oracle's scores are separated by more than the bf16 error can bridge
+    md = mets_d.cpu().numpy()
+    gap = np.array([np.min(np.diff(np.sort(scores_o[off[i]:off[i + 1]]))) for i in range(I)])
+    sel = valid_o & (gap > 2.0 * err + 1e-7)
+    assert sel.sum() >= 20, int(sel.sum())
+    np.testing.assert_allclose(md[sel], mets_o[sel], rtol=0, atol=1e-12)
