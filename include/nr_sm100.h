@@ -157,6 +157,18 @@ int nr_pad_blend_bwd(const float* dout, const float* mask, float* dv, float* dpa
 int nr_score_ce_fwd(const float* cand, const float* user, const int64_t* label, float* score,
                     float* loss, float* hits, float* per_sample_ws, int64_t B, int32_t C,
                     int32_t H, void* stream);
+/* Allocation-free variant of nr_score_ce_fwd.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  Same inputs, outputs and arithmetic as nr_score_ce_fwd, but the (B,2) fp32
+ * per-sample scratch lives in a file-scope `static __device__` array inside the library instead of a caller buffer:
+ * NR_SCORE_CE_NOALLOC_MAX_B * 2 floats = 128 KB on every GPU that loads the library, held until the process exits.
+ * B > NR_SCORE_CE_NOALLOC_MAX_B is an error (use nr_score_ce_fwd).  The call performs no cudaMalloc / cudaFree and
+ * calls no allocating library routine.  All calls on a device SHARE the one array: calls that can overlap on the GPU
+ * (different streams, no ordering between them) race on it; calls on one stream, or otherwise ordered, are safe.
+ * The array keeps the previous call's contents; every element the call reads is written by the call first. */
+#define NR_SCORE_CE_NOALLOC_MAX_B 16384
+int nr_score_ce_fwd_noalloc(const float* cand, const float* user, const int64_t* label, float* score,
+                            float* loss, float* hits, int64_t B, int32_t C, int32_t H, void* stream);
 /* gloss (1) upstream grad of loss -> dcand (B,C,H), duser (B,H) written */
 int nr_score_ce_bwd(const float* cand, const float* user, const int64_t* label, const float* score,
                     const float* gloss, float* dcand, float* duser, int64_t B, int32_t C, int32_t H,

@@ -22,6 +22,7 @@ lib = C.CDLL(LIB_PATH)
 ROWS_DENSE, ROWS_TOKEN, ROWS_NEWS = 0, 1, 2
 PREC_FP32, PREC_BF16 = 0, 1
 STREAM_IN, STREAM_OUT = 1, 2
+SCORE_CE_NOALLOC_MAX_B = 16384      # include/nr_sm100.h: NR_SCORE_CE_NOALLOC_MAX_B
 
 
 class NrRows(C.Structure):
@@ -74,6 +75,7 @@ _SIGS = {
     'nr_pad_blend_fwd': (C.c_int, [_P, _P, _P, _P, _I64, _I32, _I32, _P]),
     'nr_pad_blend_bwd': (C.c_int, [_P, _P, _P, _P, _I64, _I32, _I32, _P]),
     'nr_score_ce_fwd': (C.c_int, [_P] * 7 + [_I64, _I32, _I32, _P]),
+    'nr_score_ce_fwd_noalloc': (C.c_int, [_P] * 6 + [_I64, _I32, _I32, _P]),
     'nr_score_ce_bwd': (C.c_int, [_P] * 7 + [_I64, _I32, _I32, _P]),
     'nr_adam_step': (C.c_int, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _I32, _F, _P]),
     'nr_tc_gemm_nt': (C.c_int, [_P, _I64, _I32, _I64, _P, _I32, _I64, _P, _P, _I64, _I32, _I64, _I32, _P, _P]),

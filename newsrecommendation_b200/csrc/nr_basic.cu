@@ -471,3 +471,49 @@ int nr_adam_step(float* p, const float* g, float* m, float* v, int64_t count, fl
 }
 
 }  // extern "C"
+
+// ---- allocation-free variant of nr_score_ce_fwd (no counterpart in the reference; added
+// for callers that cannot allocate: CUDA-graph capture, tight serving loops) -----------------------
+// nr_score_ce_fwd needs a caller-provided (B,2) fp32 scratch (per-sample loss / hit).  Here that scratch is a
+// file-scope device array of NR_SCORE_CE_NOALLOC_MAX_B * 2 floats = 128 KB, held by every GPU that loads the library
+// until the process exits.  In HOST code the array's name is only a stand-in, not a device address: the address is
+// taken once per device with cudaGetSymbolAddress (that device current) and passed to the kernels as a pointer.
+namespace nr {
+static __device__ __align__(256) float g_score_ce_scratch[2 * NR_SCORE_CE_NOALLOC_MAX_B];
+static std::mutex g_scratch_mu;
+static float* g_scratch_ptr[64] = {nullptr};      // per device ordinal
+static int score_ce_scratch(float** out) {
+    int dev = -1;
+    NR_CUDA(cudaGetDevice(&dev));
+    NR_REQUIRE(dev >= 0 && dev < 64, "nr_score_ce_fwd_noalloc: device ordinal %d outside [0,64)", dev);
+    std::lock_guard<std::mutex> lk(g_scratch_mu);
+    if (!g_scratch_ptr[dev]) {
+        float* p = nullptr;
+        NR_CUDA(cudaGetSymbolAddress((void**)&p, g_score_ce_scratch));      // address on the CURRENT device
+        NR_REQUIRE(p != nullptr, "nr_score_ce_fwd_noalloc: cudaGetSymbolAddress returned NULL");
+        g_scratch_ptr[dev] = p;
+    }
+    *out = g_scratch_ptr[dev];
+    return 0;
+}
+}  // namespace nr
+
+extern "C" int nr_score_ce_fwd_noalloc(const float* cand, const float* user, const int64_t* label, float* score,
+                                       float* loss, float* hits, int64_t B, int32_t C, int32_t H, void* stream) {
+    NR_REQUIRE(cand && user && label && score && loss && hits, "nr_score_ce_fwd_noalloc: NULL pointer");
+    NR_REQUIRE(B > 0 && C > 0 && H > 0, "nr_score_ce_fwd_noalloc: bad sizes");
+    NR_REQUIRE(B <= (int64_t)NR_SCORE_CE_NOALLOC_MAX_B,
+               "nr_score_ce_fwd_noalloc: B=%lld exceeds the built-in scratch (NR_SCORE_CE_NOALLOC_MAX_B = %d samples); "
+               "use nr_score_ce_fwd with a caller-owned workspace", (long long)B, (int)NR_SCORE_CE_NOALLOC_MAX_B);
+    float* per_sample = nullptr;
+    if (int e = nr::score_ce_scratch(&per_sample)) return e;
+    // every element [0, 2B) of the scratch is overwritten by the first kernel before the second reads it: nothing has
+    // to start at zero, the previous call's contents are irrelevant.  No ProfScope here (it may create events).
+    nr::g_launches.fetch_add(2, std::memory_order_relaxed);
+    const int threads = B <= 2 * (int64_t)nr::sm_count() ? 32 : 128;     // same launch shape as nr_score_ce_fwd
+    nr::score_ce_fwd_kernel<<<(unsigned)((B * 32 + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
+        cand, user, label, score, per_sample, B, C, H);
+    if (int e = nr::check_last("nr_score_ce_fwd_noalloc")) return e;
+    nr::score_ce_reduce_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(per_sample, loss, hits, B);
+    return nr::check_last("nr_score_ce_fwd_noalloc(reduce)");
+}
