@@ -44,6 +44,7 @@ def parse():
     ap.add_argument('--batch', type=int, default=128, help='samples per GPU per step (weak scaling)')
     ap.add_argument('--eval-impressions', type=int, default=73152)
     ap.add_argument('--no-eval', action='store_true')
+    ap.add_argument('--single', action='store_true', help='measure only --model (default: the other model family follows as a second leg)')
     ap.add_argument('--no-graph', action='store_true', help='drive every kernel launch from Python instead of replaying the captured step')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--profile-step', action='store_true',
@@ -174,9 +175,9 @@ def roofline_for(k, ms_step, launches_step, ft, bt, pk):
 
 def ncu_traffic(model, kernel, launches_step):
     """dram__bytes_read.sum + dram__bytes_write.sum of the kernel from the committed `ncu --set full` capture of this
-    same command (profiles/r1_traffic.json, written by profiles/summarize.py), averaged per launch."""
+    same command (profiles/r2_traffic.json, written by profiles/summarize.py), averaged per launch."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
             t = json.load(f)[model][kernel]
         return t['dram_bytes_per_step'] / max(1e-9, launches_step)
     except (OSError, KeyError, ValueError):
@@ -244,98 +245,43 @@ def timed(fn, steps, world):
 
 
 # ----------------------------------------------------------------------------------------
-# CPU arm: the oracle port of the reference's train step (src/main.py:105-110), all host threads
+# CPU arm: the reference's own modules (oracle/_ref) driven as src/main.py drives them; see bench_cpu.py.
+# This arm imports neither the package's compute modules nor the CUDA library.
 # ----------------------------------------------------------------------------------------
-def cpu_train_samples_per_s(a, budget_s=25.0, max_steps=6):
-    from oracle import nr_oracle as O
-    from newsrecommendation_b200 import synthetic as S
-    cores = os.cpu_count() or 1
-    torch.set_num_threads(cores)
-    B, p = a.cpu_batch, 0.2
-    if a.model == 'NRMS':
-        table = S.word_table(V_SMALL)
-        news = S.news_titles(2000, L_TITLE, V_SMALL)
-        sys.path.insert(0, os.path.join(ROOT, 'tests', 'golden'))
-        import synth
-        P = synth.nrms_weights(0, 8)
-        P['news_encoder.embedding_matrix.weight'] = table
-    else:
-        sys.path.insert(0, os.path.join(ROOT, 'tests', 'golden'))
-        import synth
-        P = synth.naml_weights(0, 2000, L_TITLE, True, True)
-        news = S.naml_features(2000)
-    P = {k: torch.from_numpy(v).clone() for k, v in P.items()}
-    train = [k for k in P if not (a.model == 'NAML' and k.endswith('title_embeddings.weight'))]
-    for k in train:
-        P[k].requires_grad_(True)
-    st = {k: (torch.zeros_like(P[k]), torch.zeros_like(P[k])) for k in train}
-    batches = S.train_batches(news, 2, B)
-    n = B * (T_HIST + 1 + K_NEG)
-
-    def step(i, s):
-        h, m, c, y = [torch.from_numpy(x) for x in batches[i % 2]]
-        # F.dropout's Bernoulli draws are part of the reference step (39.6 % of its CPU time)
-        keep = {}
-        nc, nh = B * (1 + K_NEG), B * T_HIST
-        for tag, cnt in (('cand', nc), ('hist', nh)):
-            keep[tag + '1'] = torch.empty(cnt, L_TITLE, 300).bernoulli_(1 - p)
-            if a.model == 'NRMS':
-                keep[tag + '2'] = torch.empty(cnt, L_TITLE, 400).bernoulli_(1 - p)
-        if a.model == 'NRMS':
-            loss, _ = O.nrms_forward(h, m, c, y, P, 20, False, p, keep)
-        else:
-            loss, _ = O.naml_forward(h, m, c, y, P, L_TITLE, 300, True, True, False, p, keep)
-        for k in train:
-            P[k].grad = None
-        loss.backward()
-        with torch.no_grad():
-            for k in train:
-                g = P[k].grad if P[k].grad is not None else torch.zeros_like(P[k])
-                O.adam_step(P[k], g, st[k][0], st[k][1], s, 3e-4)
-        return float(loss.detach())
-
-    step(0, 1)                                   # warm-up
-    t0 = time.perf_counter()
-    done = 0
-    while done < max_steps and (time.perf_counter() - t0 < budget_s or done < 2):
-        step(done + 1, done + 2)
-        done += 1
-    dt = time.perf_counter() - t0
-    return {'value': done * B / dt, 'unit': 'samples/s', 'cores': cores, 'kind': 'port',
-            'sample': f'{done} train steps of batch {B} ({a.model}, L={L_TITLE}, T={T_HIST}, drop 0.2, '
-                      f'Adam) through oracle/nr_oracle.py on torch-CPU, {cores} threads',
-            'ms_per_step': dt / done * 1e3, 'batch': B}
-
-
 def run_reference(a):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    r = cpu_train_samples_per_s(a, budget_s=20.0 * max(1, a.steps) / 4, max_steps=max(2, a.steps))
+    import bench_cpu
+    r = bench_cpu.ref_train(a.model, V_SMALL, a.cpu_batch, budget_s=20.0 * max(1, a.steps) / 4, max_steps=max(2, a.steps))
     line = {'metric': METRIC, 'impl': 'reference', 'value': r['value'], 'unit': 'samples/s', 'n_gpus': a.gpus,
             'steps': a.steps, 'warmup': a.warmup, 'ms_per_step': r['ms_per_step'], 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
             'config': {'workload': f'{a.model} train step, MIND-small shape (L=30, T=50, npratio=4, D=300, '
-                                   f'20x20 heads), CPU batch {r["batch"]}', 'model_family': a.model},
+                                   f'20x20 heads), CPU batch {r["batch"]} (samples/s normalises the batch)',
+                       'model_family': a.model},
             'cpu_baseline': {k: r[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')},
-            'e2e': {'value': r['value'], 'unit': 'samples/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0}}
+            'e2e': {'value': r['value'], 'unit': 'samples/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'native_so_mapped': [l.split()[-1] for l in open('/proc/self/maps') if 'libnr_sm100' in l][:1]}
+    if not a.no_eval:
+        ev = bench_cpu.ref_eval(a.model, V_SMALL, impressions=1000)
+        if ev:
+            line['eval'] = ev
     print(json.dumps(line))
 
 
 # ----------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------
-def run_ours(a):
-    rank = int(os.environ.get('RANK', '0'))
-    local = int(os.environ.get('LOCAL_RANK', '0'))
-    world = int(os.environ.get('WORLD_SIZE', '1'))
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
-    from newsrecommendation_b200 import _lib as L, engine, synthetic as S
-    from newsrecommendation_b200 import model as model_pkg  # noqa: F401
+def train_leg(a, model_name, rank, world, sampler_idx=None, keep_load=False):
+    """One model's train measurement: device-timed value, e2e, per-kernel profile, roofline.  Returns (leg, model, news)
+    with the model left in train mode for the eval leg."""
+    import copy
     import importlib
-    mod = importlib.import_module(f'newsrecommendation_b200.model.{a.model}')   # main.py:63
+    from newsrecommendation_b200 import _lib as L, engine, synthetic as S
+    a = copy.copy(a)
+    a.model = model_name
+    mod = importlib.import_module(f'newsrecommendation_b200.model.{model_name}')   # main.py:63
     torch.manual_seed(0)
     args, ctor, news = make_workload(a, rank)
     model = mod.Model(args, *ctor).cuda()
@@ -360,12 +306,10 @@ def run_ours(a):
         step_eager(3)
         torch.cuda.synchronize()
         torch.cuda.profiler.stop()
-        print(json.dumps({'profile_step': a.model}))
-        return
+        return {'profile_step': model_name}, model, news
 
     losses = []
     graphed = None if a.no_graph else engine.GraphedTrainStep(model, opt, dev[0])
-
     if graphed is None:
         step_dev = step_eager
 
@@ -384,9 +328,9 @@ def run_ours(a):
             loss, _ = graphed(*pinned[i % R])     # pinned host -> captured input buffers (H2D), replay, Adam
             losses.append(loss.item())            # D2H of the step's result
 
-    # the clock sampler spans warm-up, the timed region and the e2e region: 20 steps are ~45 ms, less than one
+    # the clock sampler spans warm-up, the timed region and the e2e region: 20 steps are ~40 ms, less than one
     # nvidia-smi sampling period, so a sampler bracketing only the timed loop often comes back empty
-    sampler = ClockSampler(local) if rank == 0 else None
+    sampler = ClockSampler(sampler_idx) if sampler_idx is not None else None
     for i in range(max(3, a.warmup)):
         step_dev(i)
     n0 = L.lib.nr_launch_count()
@@ -397,15 +341,24 @@ def run_ours(a):
     for i in range(2):
         step_e2e(i)
     ms_e2e = timed(step_e2e, a.steps, world)
-    if (ms + ms_e2e) < 600.0:
-        # short run: keep the same step going (untimed) until the sampler has seen ~0.6 s of this load; the count
-        # comes from the all-reduced time, so every rank runs the same number of steps (and all-reduces)
-        for k in range(int(600.0 / max(ms / a.steps, 1e-3)) + 1):
-            step_dev(k)
-            if k % 16 == 15:
-                torch.cuda.synchronize()
-        torch.cuda.synchronize()
+    if keep_load:
+        if (ms + ms_e2e) < 600.0:
+            # short run: keep the same step going (untimed) until the sampler has seen ~0.6 s of this load; the count
+            # comes from the all-reduced time, so every rank runs the same number of steps (and all-reduces)
+            for k in range(int(600.0 / max(ms / a.steps, 1e-3)) + 1):
+                step_dev(k)
+                if k % 16 == 15:
+                    torch.cuda.synchronize()
+            torch.cuda.synchronize()
     clocks = sampler.stop() if sampler else None
+    # multi-rank numeric check: after identical broadcast + all-reduced steps every rank must hold
+    # bit-identical parameters
+    params_identical = None
+    if world > 1:
+        h = opt.flat_p.view(torch.int32).to(torch.int64).sum().reshape(1)
+        hs = [torch.zeros_like(h) for _ in range(world)]
+        dist.all_gather(hs, h)
+        params_identical = bool(all(int(x.item()) == int(hs[0].item()) for x in hs))
     # profiled pass: library-side CUDA-event pairs around every kernel, on the launch stream
     if graphed is not None:
         graphed.close()
@@ -415,70 +368,49 @@ def run_ours(a):
     prof = L.prof_report()
     L.lib.nr_prof_enable(0)
 
-    ev = None
-    if not a.no_eval:
-        ev = run_eval(a, model, news, rank, world, engine, S)
-    bt_leg = run_batcher(a, model, news, S) if rank == 0 and not a.no_eval else None
-
-    if rank == 0:
-        pk = peaks()
-        # with the abstract view every news contributes L_TITLE + L_ABSTRACT token rows to the conv / pooling kernels
-        Ltok = L_TITLE + (L_ABSTRACT if (a.model == 'NAML' and a.abstract) else 0)
-        ft = flops_table(a.model, a.batch, L=Ltok)
-        bt = bytes_table(a.model, a.batch, L=Ltok) if a.precision == 'bf16' else {}
-        tot = sum(v[1] for v in prof.values()) or 1.0
-        kern = {k: {'ms_per_step': v[1] / a.steps, 'launches_per_step': v[0] / a.steps, 'share': v[1] / tot}
-                for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
-        for k in kern:
-            if k in ft:
-                kern[k]['tflops'] = ft[k] / (kern[k]['ms_per_step'] * 1e-3) / 1e12
-            r = roofline_for(k, kern[k]['ms_per_step'], kern[k]['launches_per_step'], ft, bt, pk)
-            if r:
-                kern[k]['bound'], kern[k]['frac'] = r['bound'], r['frac']
-                if r['bound'] == 'hbm':
-                    kern[k]['gbs'] = r['achieved']
-        top = next((k for k in kern if k in ft or k in bt), None)      # kern is sorted by share of the step
-        roof = None
-        if top:
-            roof = roofline_for(top, kern[top]['ms_per_step'], kern[top]['launches_per_step'], ft, bt, pk)
-            # the committed ncu capture is of the default workload (batch 128/GPU, bf16); other sizes have no capture
-            roof['traffic'] = (ncu_traffic(a.model, top, kern[top]['launches_per_step'])
-                               if a.batch == 128 and a.precision == 'bf16' and not a.abstract and a.vocab == 12508 else None)
-            roof['peak_source'] = pk['src'] + (' (sustained bf16, kernel timed inside the step)'
-                                               if roof['bound'] == 'tensor' else ' (HBM copy bandwidth)')
-            roof['share_of_step'] = kern[top]['share']
-        B = a.batch
-        line = {
-            'metric': METRIC, 'value': world * B * a.steps / (ms * 1e-3), 'unit': 'samples/s', 'n_gpus': world,
-            'steps': a.steps, 'warmup': max(3, a.warmup), 'ms_per_step': ms / a.steps, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16' if a.precision == 'bf16' else 'f32',
-            'data': 'synthetic',
-            'config': {'workload': f'{a.model} train step (fwd+bwd+allreduce+Adam), MIND-small shape: batch {B}/GPU, '
-                                   f'title len {L_TITLE}, history {T_HIST}, npratio {K_NEG}, 300-d emb, 20x20 heads, '
-                                   f'drop 0.2, V={V_SMALL}, N={N_SMALL}' + (f', + abstract view ({L_ABSTRACT} tokens)' if (a.model == 'NAML' and a.abstract) else ''),
-                       'model_family': a.model, 'per_gpu_batch': B,
-                       'global_batch': B * world, 'precision': a.precision, 'parallelism': f'dp{world}',
-                       'launch': 'eager' if a.no_graph else 'fwd+bwd replayed from one CUDA graph, all-reduce + Adam eager',
-                       'l2_policy': f'{R} distinct resident batches rotated; per-step activations '
-                                    f'(>1 GB fp32) exceed the 126 MB L2'},
-            'e2e': {'value': world * B * a.steps / (ms_e2e * 1e-3), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d,
-                    'd2h_bytes_per_step': 4, 'ms_per_step': ms_e2e / a.steps},
-            'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roof, 'kernels': kern,
-            'final_loss': losses[-1] if losses else None,
-        }
-        if ev:
-            line['eval'] = ev
-        if bt_leg:
-            line['batcher'] = bt_leg
-        if world == 1 and not a.no_cpu_baseline:
-            r = cpu_train_samples_per_s(a)
-            line['cpu_baseline'] = {k: r[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
-        print(json.dumps(line))
-    if world > 1:
-        dist.destroy_process_group()
+    pk = peaks()
+    # with the abstract view every news contributes L_TITLE + L_ABSTRACT token rows to the conv / pooling kernels
+    Ltok = L_TITLE + (L_ABSTRACT if (model_name == 'NAML' and a.abstract) else 0)
+    ft = flops_table(model_name, a.batch, L=Ltok)
+    bt = bytes_table(model_name, a.batch, L=Ltok) if a.precision == 'bf16' else {}
+    tot = sum(v[1] for v in prof.values()) or 1.0
+    kern = {k: {'ms_per_step': v[1] / a.steps, 'launches_per_step': v[0] / a.steps, 'share': v[1] / tot}
+            for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
+    for k in kern:
+        if k in ft:
+            kern[k]['tflops'] = ft[k] / (kern[k]['ms_per_step'] * 1e-3) / 1e12
+        r = roofline_for(k, kern[k]['ms_per_step'], kern[k]['launches_per_step'], ft, bt, pk)
+        if r:
+            kern[k]['bound'], kern[k]['frac'] = r['bound'], r['frac']
+            if r['bound'] == 'hbm':
+                kern[k]['gbs'] = r['achieved']
+    top = next((k for k in kern if k in ft or k in bt), None)      # kern is sorted by share of the step
+    roof = None
+    if top:
+        roof = roofline_for(top, kern[top]['ms_per_step'], kern[top]['launches_per_step'], ft, bt, pk)
+        # the committed ncu capture is of the default workload (batch 128/GPU, bf16); other sizes have no capture
+        roof['traffic'] = (ncu_traffic(model_name, top, kern[top]['launches_per_step'])
+                           if a.batch == 128 and a.precision == 'bf16' and not a.abstract and a.vocab == 12508 else None)
+        roof['peak_source'] = pk['src'] + (' (sustained bf16, kernel timed inside the step)'
+                                           if roof['bound'] == 'tensor' else ' (HBM copy bandwidth)')
+        roof['share_of_step'] = kern[top]['share']
+    B = a.batch
+    # whole-step view against SURVEY 8d's ceilings: algorithmic FLOPs per sample vs sustained bf16
+    gf_sample = 4.78 if model_name == 'NRMS' else 4.49
+    leg = {'value': world * B * a.steps / (ms * 1e-3), 'unit': 'samples/s', 'ms_per_step': ms / a.steps,
+           'e2e': {'value': world * B * a.steps / (ms_e2e * 1e-3), 'unit': 'samples/s', 'h2d_bytes_per_step': h2d,
+                   'd2h_bytes_per_step': 4, 'ms_per_step': ms_e2e / a.steps},
+           'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roof, 'kernels': kern,
+           'step_tensor_frac': (gf_sample * 1e9 * B * a.steps / (ms * 1e-3) / 1e12) / pk['tensor'],
+           'final_loss': losses[-1] if losses else None, 'params_identical_across_ranks': params_identical,
+           'workload': f'{model_name} train step (fwd+bwd+allreduce+Adam), MIND-small shape: batch {B}/GPU, '
+                       f'title len {L_TITLE}, history {T_HIST}, npratio {K_NEG}, 300-d emb, 20x20 heads, '
+                       f'drop 0.2, V={V_SMALL}, N={N_SMALL}' + (f', + abstract view ({L_ABSTRACT} tokens)' if (model_name == 'NAML' and a.abstract) else '')}
+    del graphed, opt, dev, pinned
+    return leg, model, news
 
 
-def run_batcher(a, model, news, S):
+def run_batcher(a, news, S):
     """batches assembled on the device from a tokenised behaviors index (replaces
     DatasetTrain.line_mapper, dataset.py:26-49), alone and feeding the train step."""
     from newsrecommendation_b200 import batcher
@@ -498,8 +430,11 @@ def run_batcher(a, model, news, S):
             'note': 'nr_batch_train only (ids + labels resident); the train step consumes its outputs unchanged'}
 
 
-def run_eval(a, model, news, rank, world, engine, S):
-    """Config 4: news-vector cache (sharded encode + all-gather), impressions sharded i % world."""
+def run_eval(a, model, news, rank, world, reps=10):
+    """Config 4: news-vector cache (sharded encode + all-gather), impressions sharded i % world; each leg timed over
+    `reps` repetitions with CUDA events (max over ranks).  Roofline: (50 + C_mean) * H * 4 bytes per
+    impression against the measured HBM copy bandwidth."""
+    from newsrecommendation_b200 import _lib as L, engine, synthetic as S
     I = a.eval_impressions // world
     hidx, hmask, off, cand, labels = [torch.from_numpy(x).cuda() for x in
                                       S.eval_impressions(news.shape[0] - 1, I, seed=500 + rank)]
@@ -507,21 +442,111 @@ def run_eval(a, model, news, rank, world, engine, S):
     out = {}
 
     def cache(_):
-        out['table'] = engine.build_news_cache(model, news_d, batch=4096)
+        out['table'] = engine.build_news_cache(model, news_d)
 
     def score(_):
-        out['res'] = engine.score_impressions(model, out['table'], hidx, hmask, off, cand, labels, batch=4096)
+        out['res'] = engine.score_impressions(model, out['table'], hidx, hmask, off, cand, labels)
 
-    cache(0)
-    ms_cache = timed(cache, 1, world)
-    score(0)
-    ms_score = timed(score, 2, world) / 2
+    for i in range(2):
+        cache(i)
+    ms_cache = timed(cache, reps, world) / reps
+    for i in range(2):
+        score(i)
+    n0 = L.lib.nr_launch_count()
+    ms_score = timed(score, reps, world) / reps
+    launches = (L.lib.nr_launch_count() - n0) / reps
+    L.lib.nr_prof_enable(1)
+    cache(0); score(0)
+    prof = L.prof_report()
+    L.lib.nr_prof_enable(0)
     res = engine.reduce_eval_sums(out['res'][3], I)
     model.train()
-    return {'news': int(news.shape[0]), 'news_per_s': news.shape[0] / (ms_cache * 1e-3),
-            'impressions': I * world, 'impressions_per_s': I * world / (ms_score * 1e-3),
+    pk = peaks()
+    H = out['table'].shape[1]
+    c_mean = float(cand.numel()) / I
+    by = (T_HIST + c_mean) * H * 4
+    ips = I * world / (ms_score * 1e-3)
+    ach = ips / world * by / 1e9
+    return {'news': int(news.shape[0]), 'news_per_s': news.shape[0] / (ms_cache * 1e-3), 'ms_cache': ms_cache,
+            'impressions': I * world, 'impressions_per_s': ips, 'ms_score': ms_score, 'reps': reps,
             'impressions_per_s_incl_cache': I * world / ((ms_score + ms_cache) * 1e-3),
-            'metrics_mean_scored': [float(x) for x in res['mean_scored']], 'scored': res['scored']}
+            'gpu_launches_per_rep': launches,
+            'metrics_mean_scored': [float(x) for x in res['mean_scored']], 'scored': res['scored'],
+            'roofline': {'bound': 'hbm', 'achieved': ach, 'peak': pk['hbm'], 'unit': 'GB/s', 'frac': ach / pk['hbm'],
+                         'traffic': None, 'bytes_per_impression': by, 'candidates_mean': c_mean,
+                         'note': 'per GPU; algorithmic bytes = (50 history + C candidates) x H x 4 B per impression '
+                                 '(SURVEY 8d); the 104 MB fp32 news table is L2-resident on B200'},
+            'kernels': {k: {'ms': v[1], 'launches': v[0]} for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}}
+
+
+def run_ours(a):
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=torch.device('cuda', local))
+    from newsrecommendation_b200 import synthetic as S
+    legs = [a.model] if (a.single or a.profile_step or a.abstract) else [a.model, 'NAML' if a.model == 'NRMS' else 'NRMS']
+    results = {}
+    for li, name in enumerate(legs):
+        leg, model, news = train_leg(a, name, rank, world, sampler_idx=local if (rank == 0 and li == 0) else None,
+                                     keep_load=(li == 0))
+        if a.profile_step:
+            print(json.dumps(leg))
+            return
+        if not a.no_eval:
+            leg['eval'] = run_eval(a, model, news, rank, world)
+            if rank == 0 and li == 0:
+                leg['batcher'] = run_batcher(a, news, S)
+        results[name] = leg
+        del model
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+    if world > 1:
+        dist.barrier()
+    if rank == 0:
+        import bench_cpu
+        main = results[legs[0]]
+        B = a.batch
+        line = {
+            'metric': METRIC, 'value': main['value'], 'unit': 'samples/s', 'n_gpus': world,
+            'steps': a.steps, 'warmup': max(3, a.warmup), 'ms_per_step': main['ms_per_step'], 'higher_is_better': True,
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'bf16' if a.precision == 'bf16' else 'f32',
+            'data': 'synthetic',
+            'config': {'workload': main['workload'], 'model_family': legs[0], 'per_gpu_batch': B,
+                       'global_batch': B * world, 'precision': a.precision, 'parallelism': f'dp{world}',
+                       'launch': 'eager' if a.no_graph else 'fwd+bwd replayed from one CUDA graph, all-reduce + Adam eager',
+                       'l2_policy': '8 distinct resident batches rotated; per-step activations '
+                                    '(>1 GB) exceed the 126 MB L2',
+                       'legs': legs},
+            'e2e': main['e2e'], 'gpu_launches': main['gpu_launches'], 'clocks': main['clocks'],
+            'roofline': main['roofline'], 'kernels': main['kernels'], 'step_tensor_frac': main['step_tensor_frac'],
+            'final_loss': main['final_loss'],
+        }
+        if world > 1:
+            line['params_identical_across_ranks'] = main['params_identical_across_ranks']
+        for k in ('eval', 'batcher'):
+            if k in main:
+                line[k] = main[k]
+        for name in legs[1:]:
+            line[name.lower()] = {k: v for k, v in results[name].items() if k != 'clocks'}
+        if world == 1 and not a.no_cpu_baseline:
+            for li, name in enumerate(legs):
+                tgt = line if li == 0 else line[name.lower()]
+                r = bench_cpu.ref_train(name, V_SMALL, a.cpu_batch, budget_s=20.0 if li == 0 else 10.0)
+                tgt['cpu_baseline'] = {k: r[k] for k in ('value', 'unit', 'cores', 'kind', 'sample')}
+                if 'eval' in tgt:
+                    ev = bench_cpu.ref_eval(name, V_SMALL, impressions=1000)
+                    if ev:
+                        tgt['eval']['cpu_baseline'] = ev
+                ge = bench_cpu.gpu_eager(name, V_SMALL, N_SMALL if name == 'NRMS' else 20000, a.batch)
+                if ge:
+                    tgt['gpu_eager'] = ge
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 if __name__ == '__main__':
