@@ -440,6 +440,9 @@ def run_eval(a, model, news, rank, world, reps=10):
                                       S.eval_impressions(news.shape[0] - 1, I, seed=500 + rank)]
     news_d = torch.from_numpy(news).cuda()
     out = {}
+    # demo.sh tests with --user_log_mask True (src/demo.sh:26) although it trains with False (:19)
+    ulm_train = model.args.user_log_mask
+    model.args.user_log_mask = True
 
     def cache(_):
         out['table'] = engine.build_news_cache(model, news_d)
@@ -460,6 +463,7 @@ def run_eval(a, model, news, rank, world, reps=10):
     prof = L.prof_report()
     L.lib.nr_prof_enable(0)
     res = engine.reduce_eval_sums(out['res'][3], I)
+    model.args.user_log_mask = ulm_train
     model.train()
     pk = peaks()
     H = out['table'].shape[1]

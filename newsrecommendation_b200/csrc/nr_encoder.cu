@@ -569,7 +569,7 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
 
     const bool pool = enc->kind == NR_ENC_POOL;
     if (pool) {
-        NR_REQUIRE(rows->mode == NR_ROWS_DENSE && rows->drop_p == 0.f, "%s: POOL kind takes dense rows without dropout", who);
+        NR_REQUIRE(rows->mode != NR_ROWS_NEWS && rows->drop_p == 0.f, "%s: POOL kind takes dense or token-gathered rows without dropout", who);
         xb = y;                     // the staged input IS the pooling input
     }
     // 1. weights -> bf16 GEMM operands (forward operands + the transposes backward needs), one launch

@@ -31,6 +31,52 @@ eval_score_kernel(const float* __restrict__ table, const float* __restrict__ use
     }
 }
 
+// One WARP per impression: the user vector stays in registers (KV float4 per lane, H <= 128 KV), the impression's
+// candidates are walked linearly from the CSR offsets (no per-candidate search), four candidate rows in flight per
+// lane; the four dot products are reduced together and lanes 0..3 store one score each.
+template <int KV>
+__global__ void __launch_bounds__(256)
+eval_score_warp_kernel(const float* __restrict__ table, const float* __restrict__ user,
+                       const int64_t* __restrict__ offsets, const int32_t* __restrict__ cand,
+                       float* __restrict__ scores, int64_t I, int H) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int HV = H >> 2;
+    for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < I; i += warps) {
+        float4 u[KV];
+        const float4* up = (const float4*)(user + i * H);
+#pragma unroll
+        for (int k = 0; k < KV; ++k) u[k] = lane + 32 * k < HV ? __ldg(up + lane + 32 * k) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const int64_t lo = __ldg(offsets + i), hi = __ldg(offsets + i + 1);
+        for (int64_t j0 = lo; j0 < hi; j0 += 4) {
+            float s[4];
+            int32_t id[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) id[c] = j0 + c < hi ? __ldg(cand + j0 + c) : 0;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const float4* cp = (const float4*)(table + (int64_t)id[c] * H);
+                float a = 0.f;
+#pragma unroll
+                for (int k = 0; k < KV; ++k) {
+                    if (lane + 32 * k < HV) {
+                        const float4 v = __ldg(cp + lane + 32 * k);
+                        a = fmaf(v.x, u[k].x, a); a = fmaf(v.y, u[k].y, a); a = fmaf(v.z, u[k].z, a); a = fmaf(v.w, u[k].w, a);
+                    }
+                }
+                s[c] = a;
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) s[c] += __shfl_xor_sync(0xffffffffu, s[c], o);
+            }
+            const float mine = lane == 0 ? s[0] : (lane == 1 ? s[1] : (lane == 2 ? s[2] : s[3]));
+            if (lane < 4 && j0 + lane < hi) scores[j0 + lane] = mine;
+        }
+    }
+}
+
 // One block per impression.  rank_i = 1 + #{j : s_j > s_i or (s_j == s_i and j > i)}
 // (descending order, ties higher-index-first = stable argsort reversed).
 // AUC = sum over positives of (#neg with smaller score + 0.5 #neg with equal score) / (n+ n-).
@@ -135,10 +181,21 @@ int nr_eval_score(const float* table, int64_t table_rows, const float* user_vecs
     NR_REQUIRE(table && user_vecs && offsets && cand_idx && scores, "nr_eval_score: NULL pointer");
     NR_REQUIRE(table_rows > 0 && I >= 0 && total_cands >= 0 && H > 0 && (H & 3) == 0, "nr_eval_score: bad sizes");
     if (I == 0 || total_cands == 0) return 0;
+    ProfScope ps("eval_score", (cudaStream_t)stream);
+    if (H <= 512) {
+        int64_t wb = (I + 7) / 8;
+        if (wb > (int64_t)sm_count() * 8) wb = (int64_t)sm_count() * 8;
+        const int kv = (H / 4 + 31) / 32;
+        cudaStream_t st = (cudaStream_t)stream;
+        if (kv <= 1) eval_score_warp_kernel<1><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H);
+        else if (kv == 2) eval_score_warp_kernel<2><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H);
+        else if (kv == 3) eval_score_warp_kernel<3><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H);
+        else eval_score_warp_kernel<4><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H);
+        return check_last("nr_eval_score");
+    }
     int64_t blocks = (total_cands * 32 + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 16;
     if (blocks > cap) blocks = cap;
-    ProfScope ps("eval_score", (cudaStream_t)stream);
     eval_score_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(table, user_vecs, offsets, cand_idx,
                                                                          scores, I, total_cands, H);
     return check_last("nr_eval_score");

@@ -160,7 +160,7 @@ class GraphedTrainStep:
 # eval path
 # --------------------------------------------------------------------------------------
 @torch.no_grad()
-def build_news_cache(model, news_combined, batch=1024, shard=True):
+def build_news_cache(model, news_combined, batch=16384, shard=True):
     """src/main.py:185-198: news_encoder over EVERY row of news_combined (row 0 = the pad
     news included) -> device table (N+1, news_dim) fp32.  With a process group, rank r
     encodes the contiguous row range [r*per, (r+1)*per) and the shards are all-gathered
@@ -180,14 +180,15 @@ def build_news_cache(model, news_combined, batch=1024, shard=True):
     if hi < (r + 1) * per:
         table[hi:(r + 1) * per].zero_()
     if W > 1:
-        dist.all_gather_into_tensor(table, table[r * per:(r + 1) * per].clone())
+        # in place: rank r's slab already sits at its final offset of the output (NCCL in-place all-gather layout)
+        dist.all_gather_into_tensor(table, table[r * per:(r + 1) * per])
     if was_training:
         model.train()
     return table[:rows]
 
 
 @torch.no_grad()
-def score_impressions(model, table, hist_idx, hist_mask, offsets, cand_idx, labels, batch=1024):
+def score_impressions(model, table, hist_idx, hist_mask, offsets, cand_idx, labels, batch=8192):
     """src/main.py:240-263 + src/dataset.py:64-74 on device.
     Impressions as CSR (offsets int64 (I+1), cand_idx int32, labels int8) with front-padded
     history indices hist_idx int32 (I,T) and hist_mask fp32 (I,T).
@@ -201,10 +202,14 @@ def score_impressions(model, table, hist_idx, hist_mask, offsets, cand_idx, labe
     total = cand_idx.numel()
     table = L.f32(table)
     user = torch.empty(I, H, dtype=torch.float32, device=dev)
+    gathered = getattr(model.user_encoder, 'forward_gathered', None)
     for b0 in range(0, I, batch):
         b1 = min(I, b0 + batch)
-        log_vecs = ops.gather_rows(table, hist_idx[b0:b1])                 # dataset.py:67-68
-        user[b0:b1] = model.user_encoder(log_vecs, hist_mask[b0:b1])       # main.py:247
+        u = gathered(table, hist_idx[b0:b1], hist_mask[b0:b1]) if gathered else None
+        if u is None:
+            log_vecs = ops.gather_rows(table, hist_idx[b0:b1])             # dataset.py:67-68
+            u = model.user_encoder(log_vecs, hist_mask[b0:b1])             # main.py:247
+        user[b0:b1] = u
     scores = torch.empty(total, dtype=torch.float32, device=dev)
     metrics = torch.empty(I, 4, dtype=torch.float64, device=dev)
     valid = torch.empty(I, dtype=torch.uint8, device=dev)

@@ -106,6 +106,13 @@ class UserEncoder(nn.Module):
             return self.attn(news_vecs, log_mask)
         return self.attn(ops.pad_blend(news_vecs, log_mask, self.pad_doc))
 
+    def forward_gathered(self, table, idx, log_mask):
+        """Eval: masked pooling straight over rows of the cached news-vector table (see NRMS.UserEncoder)."""
+        if self.attn.prec != L.PREC_BF16 or not self.args.user_log_mask:
+            return None
+        return ops.title_encoder(L.ENC_POOL, table, idx, log_mask, (), self.attn._p(), mode=L.ROWS_TOKEN,
+                                 S=idx.shape[1], Dm=table.shape[1])
+
 
 class Model(nn.Module):
     def __init__(self, args, news_embeddings_weight, num_category, num_subcategory, abstract_embeddings_weight=None,

@@ -75,6 +75,18 @@ class UserEncoder(nn.Module):
         return self.attn(self.multi_head_self_attn(v))
 
 
+    def forward_gathered(self, table, idx, log_mask):
+        """Eval (src/dataset.py:67-68 + main.py:247): user vectors straight from the cached news-vector table and the
+        padded click indices — the (b,50,400) fp32 gather of the reference is never materialised, the staging kernel
+        of the encoder reads the table rows itself.  Returns None when this mode needs the materialised rows
+        (pad_doc blend, fp32 parity mode): the caller then gathers and calls forward()."""
+        if self.prec != L.PREC_BF16 or not self.args.user_log_mask:
+            return None
+        m = self.multi_head_self_attn
+        return ops.title_encoder(L.ENC_MHSA, table, idx, log_mask, m._w(), self.attn._p(), mode=L.ROWS_TOKEN,
+                                 S=idx.shape[1], Dm=m.d_model, heads=m.n_heads)
+
+
 class Model(nn.Module):
     def __init__(self, args, embedding_matrix, num_category=None, num_subcategory=None, **kwargs):
         # two extra positionals tolerated: main.py:64 passes them to every model (SURVEY F3)
