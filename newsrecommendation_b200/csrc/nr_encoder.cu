@@ -9,6 +9,7 @@
 #include "nr_attn_mma.cuh"
 #include "nr_tc_gemm.cuh"
 #include "nr_tc_gemm_tn.cuh"
+#include "nr_fused_enc.cuh"
 
 using namespace nr;
 
@@ -46,6 +47,13 @@ int gemm_tc_pick(const bf16* A, int64_t a_rows, int Kt_real, int64_t lda, const 
                  const int* shifts, int64_t M, const Epi& epi, cudaStream_t st, const char* what) {
     if (tc_ew16(what)) return gemm_tc<Epi, 16>(A, a_rows, Kt_real, lda, B, N, ldb, taps, shifts, M, epi, st, what);
     return gemm_tc<Epi, 8>(A, a_rows, Kt_real, lda, B, N, ldb, taps, shifts, M, epi, st, what);
+}
+
+// NR_ENC_FUSED=0 routes titles through the separate qkv / attention / fc1 / pooling launches again (A/B measurements;
+// the parity tests run both paths).
+static bool fused_enabled() {
+    const char* e = getenv("NR_ENC_FUSED");
+    return !(e && e[0] == '0');
 }
 
 // Head-major qkv columns ([head][q|k|v], see nr_attn_mma.cuh) whenever one of the warp-MMA kernels runs the
@@ -608,6 +616,21 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     }
     // 3. token mixer
     const int one = 0;
+    if (enc->kind == NR_ENC_MHSA && fused_enabled() && fe::fused_supported(p.SP, H / enc->heads, enc->heads, H, Q, p.Kp)) {
+        // titles (pitch 32): QKV projection, attention, fc1 and pooling in ONE persistent kernel (nr_fused_enc.cuh)
+        fe::FusedArgs fa{xb, p.R, p.ldx, Dm + 1, wb, p.Kp, w1b, p.HK, y};
+        fe::FusedParams fp{};
+        fp.R = p.R; fp.n = n; fp.S = S; fp.H = H; fp.Q = Q; fp.heads = enc->heads;
+        fp.out = out; fp.mask = enc->mask; fp.b1 = enc->p_b1; fp.w2 = enc->p_w2; fp.b2 = enc->p_b2;
+        fp.scale = 1.0f / sqrtf((float)(H / enc->heads));
+        fp.qkv = qkv; fp.E = eb; fp.alpha = alpha;
+        fp.keep = enc->out_drop_p > 0.f ? (uint8_t*)(sv + p.o_keep) : nullptr;
+        fp.thr = enc->out_drop_p > 0.f ? drop_threshold(enc->out_drop_p) : 0u;
+        fp.dscale = enc->out_drop_p > 0.f ? 1.f / (1.f - enc->out_drop_p) : 1.f;
+        fp.seed = rows->seed;
+        if (H / enc->heads == 20) return fe::launch_fused<20, true>(fa, fp, st);
+        return fe::launch_fused<16, true>(fa, fp, st);
+    }
     if (pool) {
     } else if (enc->kind == NR_ENC_MHSA) {
         // K = Dm + 1: the ones column of Xb times the bias column of the packed weights
