@@ -241,6 +241,11 @@ typedef struct nr_title_encoder_grads {   /* all ACCUMULATED (+=); any pointer m
 } nr_title_encoder_grads_t;
 size_t nr_title_encoder_save_bytes(const nr_title_encoder_t* enc, int64_t n);
 size_t nr_title_encoder_workspace(const nr_title_encoder_t* enc, int64_t n);
+/* Inference (eval mode, the news-vector cache of src/main.py:190-196): nr_title_encoder_fwd with save == NULL keeps
+ * nothing for a backward and runs the whole MHSA title encoder after the row staging as ONE fused tcgen05 kernel
+ * (QKV projection -> per-head attention straight from TMEM -> fc1 -> pooling; csrc/nr_fused_enc.cuh).  `ws` must then
+ * hold nr_title_encoder_infer_bytes(enc, n) bytes; 0 = this encoder is outside the fused envelope (pass a save buffer). */
+size_t nr_title_encoder_infer_bytes(const nr_title_encoder_t* enc, int64_t n);
 /* out (n,H) fp32 */
 int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, float* out,
                          void* save, size_t save_bytes, void* ws, size_t ws_bytes, void* stream);

@@ -82,6 +82,7 @@ _SIGS = {
     'nr_tc_gemm_tn': (C.c_int, [_P, _I32, _I64, _P, _I32, _I64, _I64, _I32, _P, _P, _I64, _I64, _P]),
     'nr_title_encoder_save_bytes': (_SZ, [_E, _I64]),
     'nr_title_encoder_workspace': (_SZ, [_E, _I64]),
+    'nr_title_encoder_infer_bytes': (_SZ, [_E, _I64]),
     'nr_title_encoder_fwd': (C.c_int, [_E, _R, _I64, _P, _P, _SZ, _P, _SZ, _P]),
     'nr_title_encoder_bwd': (C.c_int, [_E, _R, _I64, _P, _P, _SZ, _G, _P, _SZ, _P]),
     'nr_batch_train': (C.c_int, [_P, _P, _P, _P, _P, _P, _P, _I64, _I64, _I32, _I32, _I32, _P, _P, _P, _P]),

@@ -49,11 +49,13 @@ int gemm_tc_pick(const bf16* A, int64_t a_rows, int Kt_real, int64_t lda, const 
     return gemm_tc<Epi, 8>(A, a_rows, Kt_real, lda, B, N, ldb, taps, shifts, M, epi, st, what);
 }
 
-// NR_ENC_FUSED=0 routes titles through the separate qkv / attention / fc1 / pooling launches again (A/B measurements;
-// the parity tests run both paths).
+// The fused title-encoder kernel (nr_fused_enc.cuh) is THE inference path (save == NULL: news-vector cache).  In
+// training it also has to write qkv / E / keep bits for the backward and is compute-warp bound by those stores and the
+// Philox draws (0.60 ms vs 0.55 ms for the separate launches), so training uses it only with
+// NR_ENC_FUSED=1 (read per call; tests/test_gpu_fused.py runs the parity matrix over both paths).
 static bool fused_enabled() {
     const char* e = getenv("NR_ENC_FUSED");
-    return !(e && e[0] == '0');
+    return e && e[0] == '1';
 }
 
 // Head-major qkv columns ([head][q|k|v], see nr_attn_mma.cuh) whenever one of the warp-MMA kernels runs the
@@ -551,15 +553,83 @@ size_t nr_title_encoder_workspace(const nr_title_encoder_t* enc, int64_t n) {
     return make_plan(enc, n).ws_bytes + 1024;
 }
 
+static bool infer_supported(const nr_title_encoder_t* e) {
+    if (e->kind != NR_ENC_MHSA || e->heads < 1 || e->H % e->heads) return false;
+    const int SP = round_up(e->S + 1, 32), Kp = round_up(e->Dm + 1, 64);
+    return e->S <= 31 && e->out_drop_p == 0.f && fe::fused_supported(SP, e->H / e->heads, e->heads, e->H, e->Q, Kp);
+}
+struct InferPlan { int SP, ldx, Kp, HK; int64_t R; size_t o_wb, o_w1b, o_xb, bytes; };
+static InferPlan make_infer_plan(const nr_title_encoder_t* e, int64_t n) {
+    InferPlan p;
+    p.SP = round_up(e->S + 1, 32); p.ldx = round_up(e->Dm + 1, 64); p.Kp = p.ldx; p.HK = round_up(e->H, 64);
+    p.R = n * p.SP;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { size_t r = o; o += (bytes + 1023) & ~size_t(1023); return r; };
+    p.o_wb = take((size_t)3 * e->H * p.Kp * 2);
+    p.o_w1b = take((size_t)e->Q * p.HK * 2);
+    p.o_xb = take((size_t)p.R * p.ldx * 2);
+    p.bytes = o;
+    return p;
+}
+size_t nr_title_encoder_infer_bytes(const nr_title_encoder_t* enc, int64_t n) {
+    if (!enc || n <= 0 || !infer_supported(enc)) return 0;
+    return make_infer_plan(enc, n).bytes + 1024;
+}
+
+// save == NULL: inference.  Nothing is kept for a backward; the whole encoder after the row staging is ONE kernel.
+static int title_encoder_infer(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, float* out, void* ws,
+                               size_t ws_bytes, cudaStream_t st) {
+    const char* who = "nr_title_encoder_fwd(inference)";
+    NR_REQUIRE(infer_supported(enc), "%s: save == NULL needs an MHSA title encoder inside the fused envelope (S <= 31, "
+               "head width 16 or 20, heads %% 4 == 0, no output dropout); pass a save buffer otherwise", who);
+    NR_REQUIRE(rows->drop_p == 0.f, "%s: input dropout in inference mode", who);
+    NR_REQUIRE(ws, "%s: workspace is NULL", who);
+    const InferPlan p = make_infer_plan(enc, n);
+    char* w = (char*)(((uintptr_t)ws + 1023) & ~(uintptr_t)1023);
+    NR_REQUIRE((size_t)(w - (char*)ws) + p.bytes <= ws_bytes, "%s: workspace too small (%zu < %zu)", who, ws_bytes, p.bytes + 1024);
+    const int S = enc->S, Dm = enc->Dm, H = enc->H, Q = enc->Q, dk = H / enc->heads;
+    bf16* wb = (bf16*)(w + p.o_wb);
+    bf16* w1b = (bf16*)(w + p.o_w1b);
+    bf16* xb = (bf16*)(w + p.o_xb);
+    {
+        PackArgs ja[2];
+        bf16* jo[2];
+        ja[0] = PackArgs{enc->p_w1, nullptr, nullptr, 0, Q, H, 0, Q, p.HK, 1}; jo[0] = w1b;
+        ja[1] = PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3, enc->b[0], enc->b[1], enc->b[2], dk};
+        jo[1] = wb;
+        if (int e = pack_multi(ja, jo, 2, st)) return e;
+    }
+    {
+        const RowsView xv = make_rows_view(rows, n, S, Dm);
+        NR_REQUIRE(p.R < ((int64_t)1 << 31) && p.ldx <= 2048, "%s: n*pitch = %lld rows / ldx %d outside the staging envelope",
+                   who, (long long)p.R, p.ldx);
+        const int cx = p.ldx >> 3;
+        const int ry = 256 / cx > 0 ? 256 / cx : 1;
+        int64_t blocks = (p.R + ry - 1) / ry;
+        if (blocks > (int64_t)sm_count() * 16) blocks = (int64_t)sm_count() * 16;
+        ProfScope ps("enc.stage", st);
+        stage_rows_kernel<<<(unsigned)blocks, dim3(cx, ry), 0, st>>>(xv, xb, (int)p.R, p.SP, p.ldx, nullptr);
+        if (int e = check_last("enc.stage")) return e;
+    }
+    fe::FusedArgs fa{xb, p.R, p.ldx, Dm + 1, wb, p.Kp, w1b, p.HK, nullptr};
+    fe::FusedParams fp{};
+    fp.R = p.R; fp.n = n; fp.S = S; fp.H = H; fp.Q = Q; fp.heads = enc->heads;
+    fp.out = out; fp.mask = enc->mask; fp.b1 = enc->p_b1; fp.w2 = enc->p_w2; fp.b2 = enc->p_b2;
+    fp.scale = 1.0f / sqrtf((float)dk);
+    fp.dscale = 1.f;
+    if (dk == 20) return fe::launch_fused<20, false>(fa, fp, st);
+    return fe::launch_fused<16, false>(fa, fp, st);
+}
+
 int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, float* out, void* save,
                          size_t save_bytes, void* ws, size_t ws_bytes, void* stream) {
-    (void)ws; (void)ws_bytes;
     const char* who = "nr_title_encoder_fwd";
     if (int e = validate(enc, who)) return e;
     if (int e = validate_rows(rows, who)) return e;
-    NR_REQUIRE(out && save, "%s: NULL pointer", who);
+    NR_REQUIRE(out, "%s: NULL pointer", who);
     NR_REQUIRE(n >= 0, "%s: n < 0", who);
     if (n == 0) return 0;
+    if (!save) return title_encoder_infer(enc, rows, n, out, ws, ws_bytes, (cudaStream_t)stream);
     const Plan p = make_plan(enc, n);
     char* sv = (char*)(((uintptr_t)save + 1023) & ~(uintptr_t)1023);
     NR_REQUIRE((size_t)(sv - (char*)save) + p.save_bytes <= save_bytes, "%s: save buffer too small (%zu < %zu)", who,
@@ -628,6 +698,7 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         fp.thr = enc->out_drop_p > 0.f ? drop_threshold(enc->out_drop_p) : 0u;
         fp.dscale = enc->out_drop_p > 0.f ? 1.f / (1.f - enc->out_drop_p) : 1.f;
         fp.seed = rows->seed;
+        if (const char* e = getenv("NR_FE_DBG")) fp.dbg = atoi(e);
         if (H / enc->heads == 20) return fe::launch_fused<20, true>(fa, fp, st);
         return fe::launch_fused<16, true>(fa, fp, st);
     }

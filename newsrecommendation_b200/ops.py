@@ -353,7 +353,7 @@ class TitleEncoderFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, src, ids, mask, w0, b0, w1, b1, w2, b2, p_w1, p_b1, p_w2, p_b2, cfg):
-        kind, mode, S, Dm, heads, in_drop, out_drop, seed = cfg
+        kind, mode, S, Dm, heads, in_drop, out_drop, seed, infer = cfg
         rows = _make_rows(src, ids, mode, S, Dm, in_drop, seed)
         n = rows.n
         ws_ = [None if t is None else L.f32(t) for t in (w0, b0, w1, b1, w2, b2)]
@@ -369,10 +369,18 @@ class TitleEncoderFn(torch.autograd.Function):
         enc.p_w1, enc.p_b1, enc.p_w2, enc.p_b2 = [L.ptr(t) for t in pool]
         enc.mask = L.ptr(mask)
         enc.out_drop_p = float(out_drop)
-        save = torch.empty(L.lib.nr_title_encoder_save_bytes(C.byref(enc), n), dtype=torch.uint8, device=dev)
         out = torch.empty(n, H, dtype=torch.float32, device=dev)
-        ws = L.workspace(0, dev)
         r = rows.c()
+        if infer and in_drop == 0.0 and out_drop == 0.0:
+            # inference (model.eval() under no_grad: the news-vector cache): nothing is saved, one fused kernel
+            nb = L.lib.nr_title_encoder_infer_bytes(C.byref(enc), n)
+            if nb:
+                ws = L.workspace(nb, dev)
+                L.call('nr_title_encoder_fwd', C.byref(enc), C.byref(r), n, L.ptr(out), None, 0, L.ptr(ws), ws.numel(),
+                       L.stream())
+                return out
+        save = torch.empty(L.lib.nr_title_encoder_save_bytes(C.byref(enc), n), dtype=torch.uint8, device=dev)
+        ws = L.workspace(0, dev)
         L.call('nr_title_encoder_fwd', C.byref(enc), C.byref(r), n, L.ptr(out), L.ptr(save), save.numel(),
                L.ptr(ws), ws.numel(), L.stream())
         ctx.enc, ctx.rows, ctx.keep = enc, rows, (ws_, pool, mask, save)
@@ -416,4 +424,6 @@ def title_encoder(kind, src, ids, mask, weights, pool, *, mode, S, Dm, heads=1, 
     """weights: MHSA (W_Q, b_Q, W_K, b_K, W_V, b_V); CONV (conv.weight, conv.bias).
     pool: (att_fc1.weight, att_fc1.bias, att_fc2.weight, att_fc2.bias)."""
     w = list(weights) + [None] * (6 - len(weights))
-    return TitleEncoderFn.apply(src, ids, mask, *w, *pool, (kind, mode, S, Dm, heads, in_drop, out_drop, seed))
+    # grad mode is read HERE: inside autograd.Function.forward it is always off
+    infer = not torch.is_grad_enabled()
+    return TitleEncoderFn.apply(src, ids, mask, *w, *pool, (kind, mode, S, Dm, heads, in_drop, out_drop, seed, infer))

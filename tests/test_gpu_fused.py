@@ -1,0 +1,104 @@
+"""The fused NRMS title-encoder kernel (csrc/nr_fused_enc.cuh: QKV projection -> attention from TMEM -> fc1 ->
+pooling in one persistent tcgen05 kernel) against the separate-launch bf16 pipeline and the CPU oracle
+(src/model/NRMS.py:28-35, model_utils.py:13-31,39-55,78-95).
+
+  * inference variant (save == NULL; what the news-vector cache runs, main.py:190-196): vs oracle at the bf16
+    tolerance (rel 1e-2 of the output scale) and vs the separate launches (same rounding points: 2e-3)
+  * training variant (NR_ENC_FUSED=1): loss / score / every gradient vs the separate launches, with and without
+    dropout (both paths draw the same Philox stream), and vs the oracle at drop_rate 0."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import synth
+from oracle import nr_oracle as O
+from test_gpu_ops import T
+from test_gpu_models import build_model
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture
+def fused_training():
+    old = os.environ.get('NR_ENC_FUSED')
+    os.environ['NR_ENC_FUSED'] = '1'
+    yield
+    if old is None:
+        del os.environ['NR_ENC_FUSED']
+    else:
+        os.environ['NR_ENC_FUSED'] = old
+
+
+def _titles(rs, n, L, V):
+    ids = rs.randint(1, V, size=(n, L)).astype(np.int32)
+    tl = rs.randint(1, L + 1, size=n)
+    ids[np.arange(L)[None, :] >= tl[:, None]] = 0
+    ids[0] = 0                                   # the all-pad news (B4)
+    return ids
+
+
+@pytest.mark.parametrize('n', [1, 3, 4, 5, 131, 1000])
+def test_fused_inference_vs_oracle_and_separate_launches(n):
+    kind, kw, Pn, bt, model = build_model('nrms_ulm0', precision='bf16')
+    model.eval()
+    rs = np.random.RandomState(n)
+    ids = _titles(rs, n, kw['L'], kw['V'])
+    x = T(ids).cuda()
+    with torch.no_grad():
+        v_fused = model.news_encoder(x)                       # no grad -> save == NULL -> fused kernel
+    from newsrecommendation_b200 import _lib as L
+    n0 = L.lib.nr_launch_count()
+    with torch.no_grad():
+        model.news_encoder(x)
+    assert L.lib.nr_launch_count() - n0 == 3                  # pack + stage + ONE encoder kernel
+    v_sep = model.news_encoder(x).detach()                    # grad mode -> saving path, separate launches
+    P = {k: T(v) for k, v in Pn.items()}
+    v_or = O.nrms_news_encoder(T(ids), P, 20).numpy()
+    scale = float(np.abs(v_or).max())
+    np.testing.assert_allclose(v_fused.cpu().numpy(), v_or, rtol=1e-2, atol=1e-2 * scale)
+    np.testing.assert_allclose(v_fused.cpu().numpy(), v_sep.cpu().numpy(), rtol=2e-3, atol=2e-3 * scale)
+    assert torch.isfinite(v_fused).all()
+
+
+def _run(model, bt, seed=None):
+    hist, mask, cand, label = [T(a).cuda() for a in bt]
+    if seed is not None:
+        torch.manual_seed(seed)
+        from newsrecommendation_b200 import ops
+        import itertools
+        ops._seed_counter = itertools.count(1)               # same dropout seeds for both runs
+    model.zero_grad(set_to_none=True)
+    loss, score = model(hist, mask, cand, label)
+    loss.backward()
+    return loss.item(), score.detach().cpu().numpy(), {k: p.grad.detach().cpu().numpy().copy()
+                                                       for k, p in model.named_parameters() if p.grad is not None}
+
+
+@pytest.mark.parametrize('tag,drop', [('nrms_ulm0', 0.0), ('nrms_ulm1', 0.0), ('nrms_ulm0', 0.2)])
+def test_fused_training_vs_separate_launches(tag, drop, fused_training):
+    kind, kw, Pn, bt, model = build_model(tag, precision='bf16', drop_rate=drop)
+    model.train()
+    l_f, s_f, g_f = _run(model, bt, seed=5)
+    os.environ['NR_ENC_FUSED'] = '0'
+    l_s, s_s, g_s = _run(model, bt, seed=5)
+    os.environ['NR_ENC_FUSED'] = '1'
+    assert abs(l_f - l_s) <= 2e-3 * abs(l_s)
+    np.testing.assert_allclose(s_f, s_s, rtol=0, atol=3e-3 * float(np.abs(s_s).max()))
+    assert g_f.keys() == g_s.keys()
+    gmax = max(float(np.abs(g).max()) for g in g_s.values())
+    for k in g_s:
+        m = float(np.abs(g_s[k]).max())
+        # tensors whose gradient is analytically zero (W_K.bias: the normaliser cancels a key shift) hold rounding
+        # noise only: they are held to the noise floor of the step, not to their own scale
+        np.testing.assert_allclose(g_f[k], g_s[k], rtol=0, atol=2e-2 * m + 1e-5 * gmax, err_msg=k)
+        if m > 1e-3 * gmax:
+            a, b = g_f[k].ravel().astype(np.float64), g_s[k].ravel().astype(np.float64)
+            assert a @ b / (np.linalg.norm(a) * np.linalg.norm(b) + 1e-30) > 0.999, k
+    if drop == 0.0:
+        P = {k: T(v) for k, v in Pn.items()}
+        hist, mask, cand, label = [T(a) for a in bt]
+        lo, so = O.nrms_forward(hist, mask, cand, label, P, 20, kw['user_log_mask'])
+        assert abs(l_f - lo.item()) <= 1e-2 * abs(lo.item())
+        np.testing.assert_allclose(s_f, so.numpy(), rtol=1e-2, atol=1e-2 * float(so.abs().max()))
