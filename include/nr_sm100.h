@@ -50,7 +50,9 @@ typedef struct nr_rows {
     const float* dense;    /* NR_ROWS_DENSE */
     const float* table;    /* NR_ROWS_TOKEN / NR_ROWS_NEWS */
     const int32_t* ids;
-    int64_t table_rows;    /* bound check: ids must lie in [0, table_rows) */
+    int64_t table_rows;    /* row count of `table` (>= 1).  Enforced on the device: an id outside [0, table_rows)
+                            * reads row 0, the padding row, and gets no gradient (the reference's nn.Embedding
+                            * raises IndexError; the host drivers validate their id files up front) */
     float drop_p;          /* 0 => no dropout */
     uint64_t seed;
 } nr_rows_t;

@@ -61,6 +61,7 @@ RowsView make_rows_view(const nr_rows_t* r, int64_t n, int S, int D) {
     v.S = S;
     v.D = D;
     v.rows = n * S;
+    v.table_rows = r->table_rows;
     v.thr = r->drop_p > 0.f ? drop_threshold(r->drop_p) : 0u;
     v.scale = r->drop_p > 0.f ? 1.0f / (1.0f - r->drop_p) : 1.0f;
     v.seed = r->seed;
@@ -75,6 +76,8 @@ int validate_rows(const nr_rows_t* r, const char* who) {
     } else {
         NR_REQUIRE(r->table != nullptr && r->ids != nullptr, "%s: rows.table/ids is NULL", who);
         NR_REQUIRE(r->ids_stride >= 1, "%s: rows.ids_stride must be >= 1", who);
+        NR_REQUIRE(r->table_rows >= 1, "%s: rows.table_rows must be the row count of rows.table (got %lld)", who,
+                   (long long)r->table_rows);
     }
     NR_REQUIRE(r->drop_p >= 0.f && r->drop_p < 1.f, "%s: drop_p %f outside [0,1)", who, r->drop_p);
     return 0;
@@ -83,12 +86,13 @@ int validate_rows(const nr_rows_t* r, const char* who) {
 // ---- kernels -----------------------------------------------------------------------------
 // A1/A2 gather: one float4 per thread; consecutive threads walk one row -> 128-bit coalesced.
 __global__ void gather_rows_kernel(const float* __restrict__ table, const int32_t* __restrict__ ids,
-                                   float* __restrict__ out, int64_t total4, int w4) {
+                                   float* __restrict__ out, int64_t total4, int w4, int64_t table_rows) {
     for (int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; t < total4;
          t += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = t / w4;
         const int q = (int)(t - i * w4);
-        const int64_t id = __ldg(ids + i);
+        int64_t id = __ldg(ids + i);
+        if ((uint64_t)id >= (uint64_t)table_rows) id = 0;        // out-of-range ids read the padding row
         ((float4*)out)[t] = __ldg((const float4*)table + id * w4 + q);
     }
 }
@@ -402,7 +406,7 @@ int nr_gather_rows(const float* table, int64_t table_rows, const int32_t* ids, i
     const int64_t total4 = count * (width / 4);
     ProfScope ps_gather_rows("gather_rows", (cudaStream_t)stream);
     gather_rows_kernel<<<grid_for(total4, 256, 16), 256, 0, (cudaStream_t)stream>>>(table, ids, out, total4,
-                                                                                    width / 4);
+                                                                                    width / 4, table_rows);
     return check_last("nr_gather_rows");
 }
 

@@ -202,12 +202,14 @@ struct RowsView {
     int ids_stride;
     int S, D;
     int64_t rows;   // n*S
+    int64_t table_rows;   // ids outside [0, table_rows) read (and skip the gradient of) row 0, the padding row
     uint32_t thr;   // 0 => no dropout
     float scale;
     uint64_t seed;
     __device__ __forceinline__ int64_t id_of(int64_t seq, int s) const {
-        return mode == NR_ROWS_TOKEN ? (int64_t)__ldg(ids + seq * ids_stride + s)
-                                     : (int64_t)__ldg(ids + seq * ids_stride);
+        const int64_t id = mode == NR_ROWS_TOKEN ? (int64_t)__ldg(ids + seq * ids_stride + s)
+                                                 : (int64_t)__ldg(ids + seq * ids_stride);
+        return (uint64_t)id < (uint64_t)table_rows ? id : 0;
     }
     // element (row r = seq*S+s, col c)
     __device__ __forceinline__ float4 load4(int64_t r, int c) const {
@@ -250,9 +252,11 @@ struct EmbedView {
     int ids_stride;
     int64_t rows;
     int cols;
+    int64_t emb_rows;     // ids outside [0, emb_rows) read row 0
     __device__ __forceinline__ float4 load4(int64_t r, int c) const {
         if (r >= rows || c >= cols) return make_float4(0.f, 0.f, 0.f, 0.f);
-        const int64_t id = __ldg(ids + r * ids_stride);
+        int64_t id = __ldg(ids + r * ids_stride);
+        if ((uint64_t)id >= (uint64_t)emb_rows) id = 0;
         return ldg4(emb + id * cols + c);
     }
 };

@@ -45,8 +45,8 @@ stage_rows_kernel(RowsView x, bf16* __restrict__ xb, int R, int SP, int ldx, uin
             const int64_t r = (int64_t)seq * x.S + s;
             const float* src;
             if (x.mode == NR_ROWS_DENSE) src = x.dense + r * x.D;
-            else if (x.mode == NR_ROWS_TOKEN) src = x.table + (int64_t)__ldg(x.ids + (int64_t)seq * x.ids_stride + s) * x.D;
-            else src = x.table + (int64_t)__ldg(x.ids + (int64_t)seq * x.ids_stride) * ((int64_t)x.S * x.D) + (int64_t)s * x.D;
+            else if (x.mode == NR_ROWS_TOKEN) src = x.table + x.id_of(seq, s) * x.D;
+            else src = x.table + x.id_of(seq, s) * ((int64_t)x.S * x.D) + (int64_t)s * x.D;
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
             if (c < x.D) a = ldg4(src + c);
             if (c + 4 < x.D) b = ldg4(src + c + 4);

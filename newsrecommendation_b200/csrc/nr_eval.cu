@@ -9,7 +9,7 @@ namespace nr {
 __global__ void __launch_bounds__(256)
 eval_score_kernel(const float* __restrict__ table, const float* __restrict__ user,
                   const int64_t* __restrict__ offsets, const int32_t* __restrict__ cand,
-                  float* __restrict__ scores, int64_t I, int64_t total, int H) {
+                  float* __restrict__ scores, int64_t I, int64_t total, int H, int64_t table_rows) {
     const int lane = threadIdx.x & 31;
     const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t j = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; j < total; j += warps) {
@@ -19,7 +19,9 @@ eval_score_kernel(const float* __restrict__ table, const float* __restrict__ use
             const int64_t mid = (lo + hi) >> 1;
             if (__ldg(offsets + mid) <= j) lo = mid; else hi = mid;
         }
-        const float4* c = (const float4*)(table + (int64_t)__ldg(cand + j) * H);
+        int64_t cid = __ldg(cand + j);
+        if ((uint64_t)cid >= (uint64_t)table_rows) cid = 0;          // unknown ids score the padding news (dataset.py:14-15)
+        const float4* c = (const float4*)(table + cid * H);
         const float4* u = (const float4*)(user + lo * H);
         float s = 0.f;
         for (int q = lane; q < H / 4; q += 32) {
@@ -38,7 +40,7 @@ template <int KV>
 __global__ void __launch_bounds__(256)
 eval_score_warp_kernel(const float* __restrict__ table, const float* __restrict__ user,
                        const int64_t* __restrict__ offsets, const int32_t* __restrict__ cand,
-                       float* __restrict__ scores, int64_t I, int H) {
+                       float* __restrict__ scores, int64_t I, int H, int64_t table_rows) {
     const int lane = threadIdx.x & 31;
     const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     const int HV = H >> 2;
@@ -52,7 +54,10 @@ eval_score_warp_kernel(const float* __restrict__ table, const float* __restrict_
             float s[4];
             int32_t id[4];
 #pragma unroll
-            for (int c = 0; c < 4; ++c) id[c] = j0 + c < hi ? __ldg(cand + j0 + c) : 0;
+            for (int c = 0; c < 4; ++c) {
+                id[c] = j0 + c < hi ? __ldg(cand + j0 + c) : 0;
+                if ((uint64_t)(int64_t)id[c] >= (uint64_t)table_rows) id[c] = 0;   // unknown ids score the padding news (dataset.py:14-15)
+            }
 #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 const float4* cp = (const float4*)(table + (int64_t)id[c] * H);
@@ -187,17 +192,17 @@ int nr_eval_score(const float* table, int64_t table_rows, const float* user_vecs
         if (wb > (int64_t)sm_count() * 8) wb = (int64_t)sm_count() * 8;
         const int kv = (H / 4 + 31) / 32;
         cudaStream_t st = (cudaStream_t)stream;
-        if (kv <= 1) eval_score_warp_kernel<1><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H);
-        else if (kv == 2) eval_score_warp_kernel<2><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H);
-        else if (kv == 3) eval_score_warp_kernel<3><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H);
-        else eval_score_warp_kernel<4><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H);
+        if (kv <= 1) eval_score_warp_kernel<1><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H, table_rows);
+        else if (kv == 2) eval_score_warp_kernel<2><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H, table_rows);
+        else if (kv == 3) eval_score_warp_kernel<3><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H, table_rows);
+        else eval_score_warp_kernel<4><<<(unsigned)wb, 256, 0, st>>>(table, user_vecs, offsets, cand_idx, scores, I, H, table_rows);
         return check_last("nr_eval_score");
     }
     int64_t blocks = (total_cands * 32 + 255) / 256;
     const int64_t cap = (int64_t)sm_count() * 16;
     if (blocks > cap) blocks = cap;
     eval_score_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(table, user_vecs, offsets, cand_idx,
-                                                                         scores, I, total_cands, H);
+                                                                         scores, I, total_cands, H, table_rows);
     return check_last("nr_eval_score");
 }
 

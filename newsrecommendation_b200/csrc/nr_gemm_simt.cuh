@@ -90,10 +90,10 @@ struct EpiScatterTok {
 };
 // dE of a small embedding table looked up by one id column (category / subcategory views)
 struct EpiScatterEmb {
-    float* demb; const int32_t* ids; int ids_stride; int E;
+    float* demb; const int32_t* ids; int ids_stride; int E; int64_t emb_rows;
     __device__ __forceinline__ void operator()(int64_t r, int c, float4 a) const {
         const int64_t id = __ldg(ids + r * ids_stride);
-        if (id == 0) return;     // padding_idx=0, src/model/NAML.py:19,22
+        if (id == 0 || (uint64_t)id >= (uint64_t)emb_rows) return;     // padding_idx=0, src/model/NAML.py:19,22; out of range = padding
         float* p = demb + id * E + c;
         atomicAdd(p, a.x); atomicAdd(p + 1, a.y); atomicAdd(p + 2, a.z); atomicAdd(p + 3, a.w);
     }

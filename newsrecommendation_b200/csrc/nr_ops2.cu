@@ -150,7 +150,7 @@ int nr_embed_dense_fwd(const float* emb, int64_t emb_rows, const int32_t* ids, i
         table_gather_kernel<<<(unsigned)blocks, 256, 0, st>>>(T, emb_rows, ids, ids_stride, out, out_stride, n, h4);
         return check_last("embed_dense.gather");
     }
-    return gemm_nt(EmbedView{emb, ids, ids_stride, n, E}, DenseView{w, E, H, E}, EpiBias{out, out_stride, b}, n, H,
+    return gemm_nt(EmbedView{emb, ids, ids_stride, n, E, emb_rows}, DenseView{w, E, H, E}, EpiBias{out, out_stride, b}, n, H,
                    E, st, "embed_dense.fwd");
 }
 
@@ -193,10 +193,10 @@ int nr_embed_dense_bwd(const float* emb, int64_t emb_rows, const int32_t* ids, i
                        st, "embed_dense.demb", 8);
     }
     const DenseView dv{dout, dout_stride, n, H};
-    if (int e = gemm_tn(dv, EmbedView{emb, ids, ids_stride, n, E}, EpiAtomic{dw, E}, H, E, n, st, "embed_dense.dw"))
+    if (int e = gemm_tn(dv, EmbedView{emb, ids, ids_stride, n, E, emb_rows}, EpiAtomic{dw, E}, H, E, n, st, "embed_dense.dw"))
         return e;
     if (int e = colsum(dout, n, dout_stride, H, db, db, db, H, st)) return e;
-    return gemm_nt(dv, TransView{w, H, E}, EpiScatterEmb{demb, ids, ids_stride, E}, n, E, H, st, "embed_dense.demb");
+    return gemm_nt(dv, TransView{w, H, E}, EpiScatterEmb{demb, ids, ids_stride, E, emb_rows}, n, E, H, st, "embed_dense.demb");
 }
 
 }  // extern "C"

@@ -153,6 +153,33 @@ def _keep_own_table(model, state, table_key):
     return state
 
 
+def _check_ids(model, news_combined, args):
+    """nn.Embedding raises IndexError for an id outside its table (what the reference does with a mismatched
+    news.tsv / table pair).  The kernels read the padding row instead (include/nr_sm100.h: nr_rows_t.table_rows), so
+    the driver rejects such inputs here, once per table, before anything runs."""
+    enc = model.news_encoder
+    nc = np.asarray(news_combined)
+
+    def chk(cols, rows, what):
+        if cols.size and (int(cols.min()) < 0 or int(cols.max()) >= rows):
+            raise IndexError(f'{what}: ids span [{int(cols.min())}, {int(cols.max())}] but the table has {rows} rows')
+
+    if args.model == 'NRMS':
+        chk(nc[:, :args.num_words_title], enc.embedding_matrix.weight.shape[0], 'title token ids vs word_embeddings.npy')
+        return
+    col = args.num_words_title if enc.word_ids else 1
+    chk(nc[:, :col], enc.title_embeddings.weight.shape[0], 'title ids vs the title table')
+    if enc.use_abstract:
+        w = enc.num_words_abstract if enc.word_ids else 1
+        chk(nc[:, col:col + w], enc.abstract_embeddings.weight.shape[0], 'abstract ids vs the abstract table')
+        col += w
+    if enc.use_category:
+        chk(nc[:, col], enc.category_emb.weight.shape[0], 'category ids vs category_emb')
+        col += 1
+    if enc.use_subcategory:
+        chk(nc[:, col], enc.subcategory_emb.weight.shape[0], 'subcategory ids vs subcategory_emb')
+
+
 def train(rank, args):
     rank, world, distributed = _init_rank(rank, args)
     dev = torch.device('cuda', torch.cuda.current_device())
@@ -160,6 +187,7 @@ def train(rank, args):
     if rank == 0:
         logging.info('Initializing word embedding matrix...')
     model = _build_model(args.train_data_dir, args, len(category_dict), len(subcategory_dict))
+    _check_ids(model, news_combined, args)
     if rank == 0:
         print("Model's state_dict:")
         for k, v in model.state_dict().items():
@@ -261,6 +289,7 @@ def test(rank, args):
     torch.set_grad_enabled(False)
 
     news_index, _, _, news_combined = _news_inputs(args.test_data_dir, args, 'test', category_dict, subcategory_dict)
+    _check_ids(model, news_combined, args)
     t0 = time.time()
     table = engine.build_news_cache(model, torch.from_numpy(news_combined).to(dev), batch=max(args.batch_size, 1024))
     torch.cuda.synchronize()

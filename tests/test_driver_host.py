@@ -135,3 +135,22 @@ def test_raw_table_dtype(tmp_path):
     assert mind_io.raw_table_dtype(tmp_path / 'b.nrtab') == 'bf16'
     assert mind_io.raw_table_dtype(tmp_path / 'c.nrtab') is None
     assert mind_io.raw_table_dtype(tmp_path / 'missing.nrtab') is None
+
+
+def test_driver_rejects_ids_outside_their_table():
+    """a title_token_ids / word_embeddings pair that does not match is an IndexError up front, as
+    nn.Embedding would raise in the reference (src/model/NRMS.py:28), not an out-of-bounds device read."""
+    import argparse
+    import types
+    import pytest
+    import torch
+    from newsrecommendation_b200 import main as drv
+    enc = types.SimpleNamespace(embedding_matrix=types.SimpleNamespace(weight=torch.zeros(10, 4)))
+    model = types.SimpleNamespace(news_encoder=enc)
+    args = argparse.Namespace(model='NRMS', num_words_title=3)
+    ok = np.array([[0, 1, 9], [2, 3, 4]], np.int32)
+    drv._check_ids(model, ok, args)
+    with pytest.raises(IndexError, match='title token ids'):
+        drv._check_ids(model, np.array([[0, 1, 10]], np.int32), args)
+    with pytest.raises(IndexError):
+        drv._check_ids(model, np.array([[0, -1, 2]], np.int32), args)

@@ -188,3 +188,40 @@ def test_conv_news_rows_dropout_and_table_grad(ops):
     y.backward(gup.cuda()); ref.backward(gup)
     gclose(td.grad, to.grad, 'dtable'); gclose(wd.grad, wo.grad, 'dw'); gclose(bd.grad, bo.grad, 'db')
     assert (td.grad[0] == 0).all()
+
+
+def test_out_of_range_ids_read_the_padding_row():
+    """nr_rows_t.table_rows is enforced on the device.  An id outside [0, table_rows) behaves like id 0 (the
+    padding row: zeros in, no gradient out) in the gather, the encoders (forward and table gradient) and the eval
+    scoring — no out-of-bounds read or atomic."""
+    from newsrecommendation_b200 import _lib as L, ops
+    rs = np.random.RandomState(5)
+    V, D, n, S = 50, 300, 6, 30
+    table = rs.standard_normal((V, D)).astype(np.float32); table[0] = 0
+    ids = rs.randint(1, V, size=(n, S)).astype(np.int32)
+    bad = ids.copy(); bad[1, 3] = V + 7; bad[2, 0] = -3; bad[4, 29] = 2 ** 30
+    ref = ids.copy(); ref[1, 3] = 0; ref[2, 0] = 0; ref[4, 29] = 0
+    tb = T(table).cuda()
+    assert torch.equal(ops.gather_rows(tb, T(bad).cuda()), ops.gather_rows(tb, T(ref).cuda()))
+    w = [T((rs.standard_normal(s) * 0.05).astype(np.float32)).cuda() for s in ((400, D), (400,), (400, D), (400,), (400, D), (400,))]
+    pool = [T((rs.standard_normal(s) * 0.05).astype(np.float32)).cuda() for s in ((200, 400), (200,), (1, 200), (1,))]
+    outs = []
+    for x in (bad, ref):
+        t = tb.clone().requires_grad_(True)
+        y = ops.title_encoder(L.ENC_MHSA, t, T(x).cuda(), None, w, pool, mode=L.ROWS_TOKEN, S=S, Dm=D, heads=20)
+        y.square().sum().backward()
+        outs.append((y.detach(), t.grad.detach()))
+    assert torch.equal(outs[0][0], outs[1][0])
+    close(outs[0][1], outs[1][1].cpu().numpy(), rtol=1e-4, atol=1e-5 * float(outs[1][1].abs().max()))   # atomics: order differs
+    assert (outs[0][1][0] == 0).all()
+    # eval scoring
+    cache = T(rs.standard_normal((V, 400)).astype(np.float32)).cuda()
+    user = T(rs.standard_normal((2, 400)).astype(np.float32)).cuda()
+    off = T(np.array([0, 3, 7], np.int64)).cuda()
+    sc = []
+    for c in ([1, V + 1, 4, 5, -1, 6, 7], [1, 0, 4, 5, 0, 6, 7]):
+        cand = T(np.array(c, np.int32)).cuda()
+        s = torch.empty(7, dtype=torch.float32, device='cuda')
+        L.call('nr_eval_score', L.ptr(cache), V, L.ptr(user), L.ptr(off), L.ptr(cand), L.ptr(s), 2, 7, 400, L.stream())
+        sc.append(s)
+    assert torch.equal(sc[0], sc[1])
