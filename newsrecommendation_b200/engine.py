@@ -69,9 +69,14 @@ class FlatAdam:
             self.flat_p[off:off + n].copy_(p.data.reshape(-1))
             p.data = self.flat_p[off:off + n].view(p.shape)          # Parameter object unchanged
             p.grad = self.flat_g[off:off + n].view(p.shape)
+            p._nr_fused_grad = True          # backward kernels add straight into the flat gradient bucket (ops._grad_target)
         self.lr, self.betas, self.eps = lr, betas, eps
         self.step_count = 0
-        ops.ACCUMULATE_INTO_GRAD = True      # backward kernels add straight into the flat gradient bucket
+
+    def release(self):
+        """Hand the Parameters back to ordinary autograd (another optimizer may take the model over)."""
+        for p in self.params:
+            p._nr_fused_grad = False
 
     def zero_grad(self):
         self.flat_g.zero_()

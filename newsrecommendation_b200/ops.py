@@ -16,20 +16,17 @@ from . import _lib as L
 
 _seed_counter = itertools.count(1)
 
-# Fused weight-gradient accumulation.  When True (engine.FlatAdam turns it on), a backward kernel adds a
-# parameter's gradient straight into its existing `.grad` buffer (a view of the flat gradient bucket) and
-# the autograd Function returns None for it: no per-parameter zero-fill + add launches, and the dense
-# (V,300) embedding gradient is never materialised twice.  With False (default; e.g. the reference's own
-# optim.Adam + DistributedDataParallel loop, whose hooks need the returned gradients) the Functions
-# return ordinary gradient tensors.
-ACCUMULATE_INTO_GRAD = False
-
-
+# Fused weight-gradient accumulation.  engine.FlatAdam tags the Parameters it owns (`p._nr_fused_grad = True`): for
+# those, a backward kernel adds the gradient straight into the existing `.grad` buffer (a view of the optimizer's flat
+# gradient bucket) and the autograd Function returns None for it — no per-parameter zero-fill + add launches, and the
+# dense (V,300) embedding gradient is never materialised twice.  Every other Parameter (e.g. a model driven by the
+# reference's own optim.Adam + DistributedDataParallel loop, whose hooks need the returned gradients) gets an ordinary
+# gradient tensor back.  The switch is per Parameter, not per process: two models with different optimizers coexist.
 def _grad_target(param, like):
     """(buffer to accumulate into, value to return to autograd) for one parameter."""
     if param is None:
         return None, None
-    if (ACCUMULATE_INTO_GRAD and isinstance(param, torch.nn.Parameter) and param.grad is not None
+    if (getattr(param, '_nr_fused_grad', False) and isinstance(param, torch.nn.Parameter) and param.grad is not None
             and param.grad.is_contiguous() and param.grad.dtype == torch.float32
             and param.grad.shape == param.shape and param.grad.is_cuda):
         return param.grad, None
