@@ -4,7 +4,6 @@
 // UserEncoder (NRMS.py:55-62) as one pipeline of tcgen05 GEMMs (nr_tc_gemm.cuh, nr_tc_gemm_tn.cuh)
 // with fused epilogues and fp32 SIMT tails (nr_enc_kernels.cuh).  Gradient math: SURVEY Appendix C.
 #include <string.h>
-#include <mutex>
 #include "nr_enc_kernels.cuh"
 #include "nr_attn_mma.cuh"
 #include "nr_tc_gemm.cuh"
@@ -29,19 +28,9 @@ __device__ __forceinline__ float tanh_fast(float x) {      // MUFU.TANH, rel. er
     return y;
 }
 
-// 16 epilogue warps for the named GEMM?  NR_TC_EW16 = comma-separated kernel names (or "all"/"none"); default below.
-#ifndef NR_TC_EW16_DEFAULT
-#define NR_TC_EW16_DEFAULT "enc.pool_dx"   // measured: pool_dx 0.163 -> 0.139 ms; dx (L2 reductions) and qkv (operand delivery) do not gain
-#endif
-static bool tc_ew16(const char* what) {
-    const char* e = getenv("NR_TC_EW16");
-    if (!e) e = NR_TC_EW16_DEFAULT;
-    if (!strcmp(e, "all")) return true;
-    const char* hit = strstr(e, what);
-    if (!hit) return false;
-    const char c = hit[strlen(what)];
-    return c == 0 || c == ',';
-}
+// 16 epilogue warps (two groups per accumulator) pay only for enc.pool_dx, whose epilogue is the heaviest (measured:
+// pool_dx 0.163 -> 0.139 ms; dx (L2 reductions) and qkv (operand delivery) do not gain, fc1 loses: DESIGN.md section 4)
+static bool tc_ew16(const char* what) { return !strcmp(what, "enc.pool_dx"); }
 template <class Epi>
 int gemm_tc_pick(const bf16* A, int64_t a_rows, int Kt_real, int64_t lda, const bf16* B, int N, int64_t ldb, int taps,
                  const int* shifts, int64_t M, const Epi& epi, cudaStream_t st, const char* what) {
@@ -60,10 +49,9 @@ static bool fused_enabled() {
 
 // Head-major qkv columns ([head][q|k|v], see nr_attn_mma.cuh) whenever one of the warp-MMA kernels runs the
 // attention; the SIMT fall-back kernels keep the canonical q | k | v blocks.  The weight packers, the dW epilogue
-// and the attention launchers all ask this one predicate.  NR_QKV_CANONICAL=1 forces the old order (A/B runs).
+// and the attention launchers all ask this one predicate.
 static bool qkv_head_major(int SP, int dk) {
-    static const bool off = [] { const char* e = getenv("NR_QKV_CANONICAL"); return e && e[0] == '1'; }();
-    return !off && (SP == 32 || SP == 64) && (dk == 8 || dk == 16 || dk == 20 || dk == 32);
+    return (SP == 32 || SP == 64) && (dk == 8 || dk == 16 || dk == 20 || dk == 32);
 }
 
 // AttentionPooling fc1 + tanh + fc2 (model_utils.py:21-23): e (bf16) = tanh(acc + b1);
@@ -346,8 +334,7 @@ int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n
     // adjacent heads of a title share 32-byte sectors (40-byte head slices of a 2400-byte row), and the four warps of a
     // CTA fetch them at slightly different times: the L1 has to keep them, so the carve-out leaves it room (measured:
     // max-shared carve-out = 1.5x slower)
-    int cap = 3, carve = 70;
-    if (const char* e = getenv("NR_ATTN_FWD_CFG")) sscanf(e, "%d,%d", &cap, &carve);
+    const int cap = 3, carve = 70;      // resident CTAs, shared-memory carve-out (%): measured best
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     const int64_t items = n * heads;
     NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
@@ -372,8 +359,7 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     // adjacent heads of a title share 32-byte sectors (40-byte head slices of a 2400-byte row), and the four warps of a
     // CTA fetch them at slightly different times: the L1 has to keep them, so the carve-out leaves it room (measured:
     // max-shared carve-out = 1.5x slower)
-    int cap = 2, carve = 50;
-    if (const char* e = getenv("NR_ATTN_BWD_CFG")) sscanf(e, "%d,%d", &cap, &carve);
+    const int cap = 2, carve = 50;      // resident CTAs, shared-memory carve-out (%): measured best
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, carve));
     const int64_t items = n * heads;
     NR_REQUIRE(items < (int64_t)1 << 30, "attention: n*heads = %lld too large for one launch", (long long)items);
@@ -491,55 +477,6 @@ int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv,
     NR_ENC_DISPATCH_DK(dk, launch_attn_bwd<DK>(qkv, mask, dctx, dqkv, n, S, SP, heads, st));
 }
 
-}  // namespace
-
-// ---- optional fork of the weight-gradient GEMMs (NR_BWD_FORK=1; OFF by default: one run, no gain beyond noise) ------
-// The small launches of a backward (the user encoder: 128 x 50 rows) are latency-bound and serial, yet dW1 and
-// dW_QKV / dW_conv feed nothing downstream.  With the fork they run on a side stream, ordered by events after the
-// kernel that produces their input and joined before the call returns (workspace reuse stays safe, and the pattern
-// is capturable: the side stream joins the capture through the event wait and is joined back before the end).
-namespace {
-struct BwdFork {
-    cudaStream_t side = nullptr;
-    cudaEvent_t ev[3] = {nullptr, nullptr, nullptr};
-};
-BwdFork* bwd_fork_for_device() {
-    static const bool on = [] { const char* e = getenv("NR_BWD_FORK"); return e && e[0] == '1'; }();
-    if (!on) return nullptr;
-    static std::mutex mu;
-    static BwdFork forks[64];
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-    std::lock_guard<std::mutex> lk(mu);
-    BwdFork& f = forks[dev];
-    if (!f.side) {
-        cudaStream_t s = nullptr;
-        if (cudaStreamCreateWithFlags(&s, cudaStreamNonBlocking) != cudaSuccess) return nullptr;
-        for (auto& e : f.ev)
-            if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return nullptr;
-        f.side = s;
-    }
-    return &f;
-}
-struct ForkScope {
-    BwdFork* f;
-    cudaStream_t main;
-    bool used = false;
-    // the side stream may start after everything enqueued on `main` so far
-    cudaStream_t after_main(int slot) {
-        if (!f) return main;
-        cudaEventRecord(f->ev[slot], main);
-        cudaStreamWaitEvent(f->side, f->ev[slot], 0);
-        used = true;
-        return f->side;
-    }
-    ~ForkScope() {
-        if (f && used) {
-            cudaEventRecord(f->ev[2], f->side);
-            cudaStreamWaitEvent(main, f->ev[2], 0);
-        }
-    }
-};
 }  // namespace
 
 extern "C" {
@@ -698,7 +635,9 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         fp.thr = enc->out_drop_p > 0.f ? drop_threshold(enc->out_drop_p) : 0u;
         fp.dscale = enc->out_drop_p > 0.f ? 1.f / (1.f - enc->out_drop_p) : 1.f;
         fp.seed = rows->seed;
-        if (const char* e = getenv("NR_FE_DBG")) fp.dbg = atoi(e);
+#ifdef NR_FE_PROBES
+        if (const char* e = getenv("NR_FE_DBG")) fp.dbg = atoi(e);      // timing probes: development builds only
+#endif
         if (H / enc->heads == 20) return fe::launch_fused<20, true>(fa, fp, st);
         return fe::launch_fused<16, true>(fa, fp, st);
     }
@@ -773,8 +712,6 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     const bool pool = enc->kind == NR_ENC_POOL;
     const bool want_dx = gr->dtable || gr->dx_dense;
     const int one = 0;
-    // small launches only: a backward that fills the GPU gains nothing from a second stream
-    ForkScope fork{p.R <= 16384 ? bwd_fork_for_device() : nullptr, st};
 
     // 1. pooling tail backward: dz, dw2, db2, db1
     {
@@ -802,7 +739,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         if (int e = check_last("enc.pool_bwd")) return e;
     }
     // 2. dW1 (Q,H) += dz^T . y
-    if (int e = gemm_tc_tn(dz, Q, Q, y, H, H, p.R, 1, &one, TnEpiPlain{gr->dp_w1, H, 0}, fork.after_main(0), "enc.dw1")) return e;
+    if (int e = gemm_tc_tn(dz, Q, Q, y, H, H, p.R, 1, &one, TnEpiPlain{gr->dp_w1, H, 0}, st, "enc.dw1")) return e;
     // 3. dY = dz . W1 + alpha g   (output-dropout mask re-applied for MHSA)
     if (!pool || want_dx) {
         EpiPoolDx ep{dy, pool ? gr->dx_dense : nullptr, H, alpha, g, S, p.SP, H,
@@ -816,7 +753,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st)) return e;
         if (int e = gemm_tc_tn(dqkv, 3 * H, 3 * H, xb, Dm + 1, p.ldx, p.R, 1, &one,
                                TnEpiQkv{gr->dw[0], gr->dw[1], gr->dw[2], gr->db[0], gr->db[1], gr->db[2], H, Dm,
-                                        qkv_head_major(p.SP, H / enc->heads) ? H / enc->heads : 0}, fork.after_main(1),
+                                        qkv_head_major(p.SP, H / enc->heads) ? H / enc->heads : 0}, st,
                                "enc.dwqkv"))
             return e;
         if (want_dx)
@@ -825,7 +762,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
                 return e;
     } else {
         const int sh[3] = {-1, 0, 1};
-        if (int e = gemm_tc_tn(dy, H, H, xb, Dm + 1, p.ldx, p.R, 3, sh, TnEpiConv{gr->dw[0], gr->db[0], Dm}, fork.after_main(1),
+        if (int e = gemm_tc_tn(dy, H, H, xb, Dm + 1, p.ldx, p.R, 3, sh, TnEpiConv{gr->dw[0], gr->db[0], Dm}, st,
                                "enc.dwconv"))
             return e;
         if (want_dx) {

@@ -13,9 +13,8 @@
 // drained by epilogue group a, so two tile epilogues and the MMAs of a third tile overlap (the
 // epilogue of these K <= 1200 GEMMs costs more cycles than their MMAs).
 // Persistent: grid = #SMs, tiles assigned round-robin with n fastest (A tile reuse through L2).
-// Optional "B-resident" mode (NR_TC_BRES=1; short-K GEMMs whose (BN x K) weight slice fits shared
-// memory): every CTA loads its n tile's slice of B ONCE and streams only A tiles.  It cuts the L2 -> SM
-// traffic of the QKV GEMM from 2.1 GB to 0.7 GB per launch but was not faster on B200 (see tc_disable_bres).
+// Two variants that cut L2 reads of the weight operand (a B-resident slice in shared memory; TMA-multicast CTA pairs)
+// were built, parity-tested and measured no faster on B200; they are not in the tree.
 #pragma once
 #include <stdlib.h>
 #include "nr_common.cuh"
@@ -36,10 +35,6 @@ struct TcGemmParams {
     int shift[3];     // A row shift per tap
     int stages;
     int m_tiles, n_tiles;
-    int b_res;        // 1: the whole (BN x K) slice of B stays in shared memory, CTA c owns n tile c % n_tiles
-    int groups;       // b_res: CTAs per n tile (grid = groups * n_tiles); CTA c takes m tiles c / n_tiles + i * groups
-    int mc;           // 1: clusters of 2 CTAs on adjacent m tiles of the same n tile; each loads HALF of the B box
-                      //    and multicasts it to both (halves the L2 -> SM traffic of the weight operand)
 };
 
 inline size_t tc_stage_bytes(int BN) { return (size_t)TC_BM * TC_BK * 2 + (size_t)BN * TC_BK * 2; }
@@ -48,24 +43,6 @@ inline bool tc_debug() {
     static const bool on = [] { const char* e = getenv("NR_TC_DEBUG"); return e && e[0] == '1'; }();
     return on;
 }
-// The B-resident mode is OFF unless NR_TC_BRES=1: measured on B200 it does not pay (QKV 0.228 ms resident
-// vs 0.206 ms streaming) — once the epilogue was thinned the kernels were no longer L2-feed bound, and the
-// resident slice costs one pipeline stage and 3 CTAs of the grid.  Kept for A/B measurements.
-inline bool tc_disable_bres() {
-    static const bool on = [] { const char* e = getenv("NR_TC_BRES"); return e && e[0] == '1'; }();
-    return !on;
-}
-
-// TMA-multicast pairs (NR_TC_MC=1, read per call so a test can toggle it): correct, but measured identical to
-// unicast on every shape of the step (qkv 229.2 vs 228.9 us, dx 203.7 vs 200.8 us): B200's L2 already serves a
-// line requested by two SMs within its dedup window from one read, and the limit these GEMMs sit at is bytes
-// DELIVERED per SM (~12 TB/s chip wide), which multicast does not reduce.  cta_group::2 (each SM ingests half of
-// B) is the variant that would; see DESIGN.md.
-inline bool tc_disable_mc() {
-    const char* e = getenv("NR_TC_MC");
-    return !(e && e[0] == '1');
-}
-
 // Epilogue functor protocol (one thread owns one output row of the tile; ALL 32 lanes of the warp call
 // every hook, `cx.live` says whether this lane's row exists):
 //   begin(cx, row) ; chunk(cx, row, col0, v[32], ncols) for col0 = n0, n0+32, ... ; end(cx, row)
@@ -125,7 +102,7 @@ __device__ __forceinline__ void flush_rows_bf16(const EpiCtx& cx, __nv_bfloat16*
 template <class Epi, int EW>
 __global__ void __launch_bounds__(64 + 32 * EW, 1)   // EW = 8: 10 warps, 3 on one SM sub-partition -> 168 registers is the ceiling
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const __grid_constant__ CUtensorMap tmBh, const TcGemmParams p, const Epi epi_in) {
+               const TcGemmParams p, const Epi epi_in) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     // 1024-B alignment for SWIZZLE_128B atoms
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -135,36 +112,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int total_tiles = p.m_tiles * p.n_tiles;
     const int kc = p.Kt / TC_BK;
     const int k_iters = p.taps * kc;
-    const bool bres = p.b_res != 0;
-    const bool mc = p.mc != 0;
-    const uint32_t crank = mc ? tc::cluster_ctarank() : 0u;
-    const uint32_t stage_bytes = bres ? a_bytes : a_bytes + b_bytes;
-    uint8_t* sB = smem;                                            // resident B: k_iters tiles of b_bytes
-    uint8_t* ring = smem + (bres ? (size_t)k_iters * b_bytes : 0); // operand ring
+    const uint32_t stage_bytes = a_bytes + b_bytes;
+    uint8_t* ring = smem;                                           // operand ring
     uint64_t* bars = (uint64_t*)(ring + (size_t)stages * stage_bytes);
     uint64_t* full = bars;                  // [stages]   TMA -> MMA
     uint64_t* empty = bars + stages;        // [stages]   MMA -> TMA
     uint64_t* tfull = bars + 2 * stages;    // [2]        MMA -> epilogue
     uint64_t* tempty = tfull + 2;           // [2]        epilogue -> MMA
-    uint64_t* bfull = tempty + 2;           // [1]        resident B landed
-    uint32_t* tmem_slot = (uint32_t*)(bfull + 1);
+    uint32_t* tmem_slot = (uint32_t*)(tempty + 2);
     __nv_bfloat16* epi_stage = (__nv_bfloat16*)((uint8_t*)bars + 256);      // 8 x [32][TC_STAGE_PITCH]
     // tile sequence of this CTA: it-th tile -> (m tile, n tile)
-    const int my_nt = bres ? (int)blockIdx.x % p.n_tiles : 0;
-    const int my_j = bres ? (int)blockIdx.x / p.n_tiles : 0;
     auto tile_of = [&](int it, int& mt, int& nt) -> bool {
-        if (bres) {
-            nt = my_nt;
-            mt = my_j + it * p.groups;
-            return mt < p.m_tiles;
-        }
-        if (mc) {       // the two CTAs of a cluster walk the same sequence of (m-tile pair, n tile)
-            const int64_t pair = (int64_t)(blockIdx.x >> 1) + (int64_t)it * (gridDim.x >> 1);
-            if (pair >= (int64_t)((p.m_tiles + 1) >> 1) * p.n_tiles) return false;
-            mt = 2 * (int)(pair / p.n_tiles) + (int)crank;      // may be == m_tiles (odd count): all rows dead
-            nt = (int)(pair % p.n_tiles);
-            return true;
-        }
         const int64_t tile = (int64_t)blockIdx.x + (int64_t)it * gridDim.x;
         if (tile >= total_tiles) return false;
         mt = (int)(tile / p.n_tiles);
@@ -175,16 +133,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 0 && lane == 0) {
         tc::prefetch_tmap(&tmA);
         tc::prefetch_tmap(&tmB);
-        // multicast mode: a stage is free only when BOTH CTAs' MMAs have retired it (the peer writes half of it)
-        for (int s = 0; s < stages; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, mc ? 2 : 1); }
+        for (int s = 0; s < stages; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); }
         for (int a = 0; a < 2; ++a) { tc::mbar_init(tfull + a, 1); tc::mbar_init(tempty + a, EW / 2); }
-        tc::mbar_init(bfull, 1);
         tc::fence_barrier_init();
     }
     if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
     tc::tc_fence_before();
     __syncthreads();
-    if (mc) tc::cluster_sync_all();      // the peer's barriers exist before anything is multicast to them
     tc::tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
@@ -193,11 +148,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (lane == 0) {
             int s = 0; uint32_t ph = 0;
             int mt, nt;
-            if (bres && tile_of(0, mt, nt)) {
-                tc::mbar_arrive_expect_tx(bfull, (uint32_t)k_iters * b_bytes);
-                for (int i = 0; i < k_iters; ++i)
-                    tc::tma_load_2d(sB + (size_t)i * b_bytes, &tmB, bfull, i * TC_BK, nt * p.BN);
-            }
             for (int it = 0; tile_of(it, mt, nt); ++it) {
                 const int m0 = mt * TC_BM, n0 = nt * p.BN;
                 for (int i = 0; i < k_iters; ++i) {
@@ -206,13 +156,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                     uint8_t* sa = ring + (size_t)s * stage_bytes;
                     tc::mbar_arrive_expect_tx(full + s, stage_bytes);
                     tc::tma_load_2d(sa, &tmA, full + s, kk, m0 + p.shift[tap]);
-                    if (mc) {
-                        const uint32_t half = b_bytes >> 1;          // BN % 16 == 0: half a box is whole swizzle atoms
-                        tc::tma_load_2d_mc(sa + a_bytes + crank * half, &tmBh, full + s, i * TC_BK,
-                                           n0 + (int)crank * (p.BN >> 1), (uint16_t)3);
-                    } else if (!bres) {
-                        tc::tma_load_2d(sa + a_bytes, &tmB, full + s, i * TC_BK, n0);
-                    }
+                    tc::tma_load_2d(sa + a_bytes, &tmB, full + s, i * TC_BK, n0);
                     if (++s == stages) { s = 0; ph ^= 1; }
                 }
             }
@@ -223,7 +167,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         int s = 0; uint32_t ph = 0;
         int acc = 0; uint32_t aph = 0;
         int mt, nt;
-        if (bres && tile_of(0, mt, nt)) tc::mbar_wait(bfull, 0);
         for (int it = 0; tile_of(it, mt, nt); ++it) {
             tc::mbar_wait(tempty + acc, aph ^ 1);
             tc::tc_fence_after();
@@ -234,12 +177,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (lane == 0) {
                     const uint32_t sa = tc::smem_u32(ring + (size_t)s * stage_bytes);
                     const uint64_t da = tc::umma_desc_sw128(sa, 16, 1024);
-                    const uint64_t db = tc::umma_desc_sw128(bres ? tc::smem_u32(sB + (size_t)i * b_bytes) : sa + a_bytes, 16, 1024);
+                    const uint64_t db = tc::umma_desc_sw128(sa + a_bytes, 16, 1024);
 #pragma unroll
                     for (int k = 0; k < TC_BK / 16; ++k)   // +32 B per 16-element k step (>>4 => +2)
                         tc::umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc, (i | k) ? 1u : 0u);
-                    if (mc) tc::umma_commit_mc(empty + s, (uint16_t)3);  // frees the slot in both CTAs
-                    else tc::umma_commit(empty + s);                 // smem slot free when MMAs retire
+                    tc::umma_commit(empty + s);                      // smem slot free when MMAs retire
                     if (i == k_iters - 1) tc::umma_commit(tfull + acc);   // accumulator ready
                 }
                 __syncwarp();
@@ -312,7 +254,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     tc::tc_fence_before();
     __syncthreads();
-    if (mc) tc::cluster_sync_all();      // the peer may still multicast into this CTA / arrive on its barriers
     if (warp == 1) {
         tc::tc_fence_after();
         tc::tmem_dealloc(tmem_base, 512);
@@ -345,55 +286,21 @@ int gemm_tc(const __nv_bfloat16* A, int64_t a_rows, int Kt_real, int64_t lda, co
     int stages = (int)(budget / tc_stage_bytes(p.BN));
     if (stages > 8) stages = 8;
     NR_REQUIRE(stages >= 2, "%s: tile does not fit shared memory", what);
-    // B-resident mode: the (BN x taps*Kt) slice of B + at least 3 A stages fit, and there are enough CTAs
-    const size_t b_slice = (size_t)taps * (p.Kt / TC_BK) * p.BN * TC_BK * 2;
-    const size_t a_stage = (size_t)TC_BM * TC_BK * 2;
-    p.b_res = 0; p.groups = 0;
     int grid = sm_count();
     const int tiles = p.m_tiles * p.n_tiles;
-    if (!tc_disable_bres() && b_slice + 2 * a_stage <= budget && p.n_tiles <= grid && p.m_tiles >= 2 * (grid / p.n_tiles)) {
-        p.b_res = 1;
-        p.groups = grid / p.n_tiles;
-        grid = p.groups * p.n_tiles;
-        stages = (int)((budget - b_slice) / a_stage);
-        if (stages > 8) stages = 8;
-    } else if (grid > tiles) {
-        grid = tiles;
-    }
-    // multicast mode (opt-in, see tc_disable_mc): pairs of CTAs on adjacent m tiles share the B box, each fetches half
-    p.mc = 0;
-    if (!p.b_res && !tc_disable_mc() && p.m_tiles >= 4) p.mc = 1;
+    if (grid > tiles) grid = tiles;
     p.stages = stages;
-    CUtensorMap tmA, tmB, tmBh;
+    CUtensorMap tmA, tmB;
     if (int e = make_tmap_bf16_2d(&tmA, A, (uint64_t)a_rows, (uint64_t)Kt_real, (uint64_t)lda, TC_BM, TC_BK)) return e;
     if (int e = make_tmap_bf16_2d(&tmB, B, (uint64_t)N, (uint64_t)taps * p.Kt, (uint64_t)ldb, (uint32_t)p.BN, TC_BK))
         return e;
-    if (int e = make_tmap_bf16_2d(&tmBh, B, (uint64_t)N, (uint64_t)taps * p.Kt, (uint64_t)ldb, (uint32_t)(p.BN / 2), TC_BK))
-        return e;
-    const size_t smem = p.b_res ? 1024 + b_slice + stages * a_stage + 256 + TC_STAGE_BYTES * (EW / 8) : tc_smem_bytes(p.BN, stages, EW);
+    const size_t smem = tc_smem_bytes(p.BN, stages, EW);
     NR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<Epi, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     if (tc_debug())
-        fprintf(stderr, "[nr] %s M=%lld N=%d K=%d taps=%d BN=%d tiles=%dx%d b_res=%d groups=%d stages=%d grid=%d smem=%zu\n", what,
-                (long long)M, N, Kt_real, taps, p.BN, p.m_tiles, p.n_tiles, p.b_res, p.groups, stages, grid, smem);
+        fprintf(stderr, "[nr] %s M=%lld N=%d K=%d taps=%d BN=%d tiles=%dx%d stages=%d grid=%d smem=%zu\n", what,
+                (long long)M, N, Kt_real, taps, p.BN, p.m_tiles, p.n_tiles, stages, grid, smem);
     ProfScope ps(what, st);
-    if (p.mc) {
-        cudaLaunchConfig_t cfg = {};
-        cudaLaunchAttribute at[1];
-        at[0].id = cudaLaunchAttributeClusterDimension;
-        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-        cfg.blockDim = dim3(64 + 32 * EW); cfg.dynamicSmemBytes = smem; cfg.stream = st; cfg.attrs = at; cfg.numAttrs = 1;
-        cfg.gridDim = dim3(2);
-        int clusters = 0;
-        NR_CUDA(cudaOccupancyMaxActiveClusters(&clusters, gemm_tc_kernel<Epi, EW>, &cfg));
-        const int64_t pairs = (int64_t)((p.m_tiles + 1) / 2) * p.n_tiles;
-        if (clusters < 1) clusters = 1;
-        if (clusters > pairs) clusters = (int)pairs;
-        cfg.gridDim = dim3(2 * clusters);
-        if (tc_debug()) fprintf(stderr, "[nr] %s multicast pairs: %d clusters\n", what, clusters);
-        NR_CUDA(cudaLaunchKernelEx(&cfg, gemm_tc_kernel<Epi, EW>, tmA, tmB, tmBh, p, epi));
-        return check_last(what);
-    }
-    gemm_tc_kernel<Epi, EW><<<grid, 64 + 32 * EW, smem, st>>>(tmA, tmB, tmBh, p, epi);
+    gemm_tc_kernel<Epi, EW><<<grid, 64 + 32 * EW, smem, st>>>(tmA, tmB, p, epi);
     return check_last(what);
 }
 
