@@ -76,6 +76,14 @@ size_t nr_prof_report(char* buf, size_t cap);
  * replay: bump the value from inside the graph.  nr_dropout_keep_mask applies the salt too. */
 int nr_set_seed_salt(const void* salt_dev);
 
+/* *salt_dev += 1 on `stream` (the first node of a captured train step: every replay draws fresh masks) */
+int nr_seed_salt_bump(void* salt_dev, void* stream);
+/* stream-ordered memset / two-piece concatenation (memset / memcpy nodes when captured): the host code uses them so
+ * that a captured step holds no ATen kernels (zero_grad of the flat gradient bucket; the candidate|history id
+ * concatenation of NRMS.py:87,90 / NAML.py:122,125 fused into one encoder call) */
+int nr_zero_bytes(void* dst, size_t bytes, void* stream);
+int nr_concat2(const void* a, size_t bytes_a, const void* b, size_t bytes_b, void* out, void* stream);
+
 /* keep[i] = 1 if element i of dropout stream (seed, stream_id) is kept at rate p */
 int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed,
                          int32_t stream_id, void* stream);

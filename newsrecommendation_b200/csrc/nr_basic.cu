@@ -521,3 +521,26 @@ extern "C" int nr_score_ce_fwd_noalloc(const float* cand, const float* user, con
     nr::score_ce_reduce_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(per_sample, loss, hits, B);
     return nr::check_last("nr_score_ce_fwd_noalloc(reduce)");
 }
+
+// ---- small stream-ordered utilities so that a captured train step contains no ATen kernels ---------------------
+namespace nr {
+__global__ void salt_bump_kernel(unsigned long long* salt) { *salt += 1ull; }
+}  // namespace nr
+extern "C" int nr_seed_salt_bump(void* salt_dev, void* stream) {
+    NR_REQUIRE(salt_dev, "nr_seed_salt_bump: NULL pointer");
+    nr::ProfScope ps("salt_bump", (cudaStream_t)stream);
+    nr::salt_bump_kernel<<<1, 1, 0, (cudaStream_t)stream>>>((unsigned long long*)salt_dev);
+    return nr::check_last("nr_seed_salt_bump");
+}
+extern "C" int nr_zero_bytes(void* dst, size_t bytes, void* stream) {
+    if (bytes == 0) return 0;
+    NR_REQUIRE(dst, "nr_zero_bytes: NULL pointer");
+    NR_CUDA(cudaMemsetAsync(dst, 0, bytes, (cudaStream_t)stream));
+    return 0;
+}
+extern "C" int nr_concat2(const void* a, size_t bytes_a, const void* b, size_t bytes_b, void* out, void* stream) {
+    NR_REQUIRE(out && (a || !bytes_a) && (b || !bytes_b), "nr_concat2: NULL pointer");
+    if (bytes_a) NR_CUDA(cudaMemcpyAsync(out, a, bytes_a, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    if (bytes_b) NR_CUDA(cudaMemcpyAsync((char*)out + bytes_a, b, bytes_b, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    return 0;
+}

@@ -72,6 +72,7 @@ class FlatAdam:
             p._nr_fused_grad = True          # backward kernels add straight into the flat gradient bucket (ops._grad_target)
         self.lr, self.betas, self.eps = lr, betas, eps
         self.step_count = 0
+        self.one = torch.ones((), dtype=torch.float32, device=dev)      # d(loss)/d(loss), see train_step
 
     def release(self):
         """Hand the Parameters back to ordinary autograd (another optimizer may take the model over)."""
@@ -79,7 +80,7 @@ class FlatAdam:
             p._nr_fused_grad = False
 
     def zero_grad(self):
-        self.flat_g.zero_()
+        L.call('nr_zero_bytes', L.ptr(self.flat_g), self.flat_g.numel() * 4, L.stream())
         for p, off in zip(self.params, self.offsets):      # re-attach in case autograd replaced .grad
             g = self.flat_g[off:off + p.numel()].view(p.shape)
             if p.grad is None or p.grad.data_ptr() != g.data_ptr():
@@ -101,7 +102,7 @@ def train_step(model, opt, history, history_mask, candidate, label):
     """One iteration of src/main.py:105-110.  Returns (loss, hits) device scalars."""
     opt.zero_grad()
     loss, _score = model(history, history_mask, candidate, label)
-    loss.backward()
+    loss.backward(opt.one)              # preallocated seed gradient: autograd's own ones_like would be an ATen fill
     opt.step()
     return loss.detach(), model.last_hits
 
@@ -120,13 +121,17 @@ class GraphedTrainStep:
     forward and backward kernels of one replay read the same value.
 
     The batch shape is fixed at capture; feed a ragged last batch through engine.train_step instead."""
+    _live = None          # the instance whose salt the library currently points at
 
     def __init__(self, model, opt, example_batch, warmup=2):
         self.model, self.opt = model, opt
         self.static = [t.clone() for t in example_batch]
         dev = self.static[0].device
+        if GraphedTrainStep._live is not None:
+            raise RuntimeError('GraphedTrainStep: another instance still owns the library seed salt; close() it first')
         self.salt = torch.zeros(1, dtype=torch.int64, device=dev)
         L.call('nr_set_seed_salt', L.ptr(self.salt))
+        GraphedTrainStep._live = self
         cur = torch.cuda.current_stream()
         side = torch.cuda.Stream()
         side.wait_stream(cur)
@@ -142,10 +147,10 @@ class GraphedTrainStep:
         self.launches_per_replay = L.lib.nr_launch_count() - n0
 
     def _fwd_bwd(self):
-        self.salt.add_(1)
+        L.call('nr_seed_salt_bump', L.ptr(self.salt), L.stream())
         self.opt.zero_grad()
         loss, score = self.model(*self.static)
-        loss.backward()
+        loss.backward(self.opt.one)
         self.loss, self.score, self.hits = loss.detach(), score.detach(), self.model.last_hits
 
     def __call__(self, history, history_mask, candidate, label):
@@ -158,7 +163,17 @@ class GraphedTrainStep:
         return self.loss, self.hits
 
     def close(self):
-        L.call('nr_set_seed_salt', None)
+        """Unregister the device salt (the library keeps a raw pointer to it).  Idempotent; also runs from __del__ so
+        that a step dropped without close() — an exception, a test — never leaves the library reading freed memory."""
+        if GraphedTrainStep._live is self:
+            GraphedTrainStep._live = None
+            L.call('nr_set_seed_salt', None)
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 # --------------------------------------------------------------------------------------

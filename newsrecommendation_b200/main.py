@@ -62,6 +62,11 @@ def _init_rank(rank, args):
     if distributed and not dist.is_initialized():
         setuplogger()
         dist.init_process_group('nccl', world_size=world, rank=rank, init_method='env://')
+    if distributed:
+        # spawned ranks do not inherit the parent's seeding (main.py:284-285 seeds only the launcher): without this
+        # every rank would draw the same dropout masks and label positions and --seed would have no effect
+        random.seed(args.seed + rank)
+        torch.manual_seed(args.seed + rank)
     return rank, world, distributed
 
 
@@ -210,8 +215,18 @@ def train(rank, args):
         t = torch.tensor([n_batches], device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MIN)
         n_batches = int(t.item())
-    graphed = None
     logging.info('Training...')
+    try:
+        _train_epochs(args, rank, dev, model, opt, loader, n_batches, category_dict, subcategory_dict)
+    finally:
+        if engine.GraphedTrainStep._live is not None:              # the library holds a raw pointer to its salt
+            engine.GraphedTrainStep._live.close()
+    _finish(distributed)
+    return model
+
+
+def _train_epochs(args, rank, dev, model, opt, loader, n_batches, category_dict, subcategory_dict):
+    graphed = None
     for ep in range(args.start_epoch, args.epochs):
         loss_sum = torch.zeros((), device=dev)
         hit_sum = torch.zeros((), device=dev)
@@ -247,10 +262,6 @@ def train(rank, args):
             ckpt_path = os.path.join(args.model_dir, f'epoch-{ep + 1}.pt')
             torch.save(_checkpoint_dict(model, args, category_dict, subcategory_dict), ckpt_path)
             logging.info(f'Model saved to {ckpt_path}.')
-    if graphed is not None:
-        graphed.close()
-    _finish(distributed)
-    return model
 
 
 @torch.no_grad()

@@ -92,8 +92,18 @@ def encode_both(news_encoder, cand_rows, hist_rows):
     """The reference encodes candidates and history in two calls (NRMS.py:87,90 / NAML.py:122,125);
     one call over the concatenated rows gives the same vectors with half the launches."""
     nc = cand_rows.shape[0]
-    v = news_encoder(torch.cat([cand_rows, hist_rows], dim=0))
-    return _SplitRows.apply(v, nc)
+    return _SplitRows.apply(news_encoder(_concat_rows(cand_rows, hist_rows)), nc)
+
+
+def _concat_rows(a, b):
+    """torch.cat([a, b], 0) as two stream-ordered device copies (memcpy nodes in a captured step, no ATen kernel)."""
+    a, b = a.contiguous(), b.contiguous()
+    if not (a.is_cuda and a.dtype == b.dtype and a.shape[1:] == b.shape[1:]):
+        return torch.cat([a, b], dim=0)
+    out = torch.empty((a.shape[0] + b.shape[0],) + tuple(a.shape[1:]), dtype=a.dtype, device=a.device)
+    L.call('nr_concat2', L.ptr(a), a.numel() * a.element_size(), L.ptr(b), b.numel() * b.element_size(), L.ptr(out),
+           L.stream())
+    return out
 
 
 class _SplitRows(torch.autograd.Function):
@@ -113,4 +123,4 @@ class _SplitRows(torch.autograd.Function):
             ga = torch.zeros((ctx.k,) + tuple(ctx.tail), dtype=dt, device=dev)
         if gb is None:
             gb = torch.zeros((ctx.n - ctx.k,) + tuple(ctx.tail), dtype=dt, device=dev)
-        return torch.cat([ga, gb], dim=0), None
+        return _concat_rows(ga, gb), None
