@@ -189,6 +189,17 @@ int nr_score_ce_bwd(const float* cand, const float* user, const int64_t* label, 
 int nr_adam_step(float* p, const float* g, float* m, float* v, int64_t count, float lr, float beta1,
                  float beta2, float eps, int32_t step, float grad_scale, void* stream);
 
+/* A12 at N > 1 — gradient exchange fused with the optimizer (src/main.py:82,109-110: DDP gradient mean + Adam.step):
+ * Adam over the slice [lo, hi) of the flat buckets with the step count read from DEVICE memory (*step_dev, int64, so
+ * that the launch can be replayed from a CUDA graph).  With the multicast pointers given (both buckets in symmetric
+ * memory mapped through an NVLink multicast object), g is read with multimem.ld_reduce (summed over the ranks in the
+ * NVSwitch) and the updated parameters are written with multimem.st into every rank's copy: reduce-scatter + Adam +
+ * all-gather in ONE kernel.  p / m / v are this rank's local buffers (m, v are only touched inside the slice).  The
+ * caller brackets the launch with cross-rank barriers.  g_mc == p_mc == NULL: plain local Adam on g. */
+int nr_adam_step_dev(const float* g, const float* g_mc, float* p, float* p_mc, float* m, float* v, int64_t lo,
+                     int64_t hi, float lr, float beta1, float beta2, float eps, const void* step_dev,
+                     float grad_scale, void* stream);
+
 /* ---- A14: eval impression scoring (src/dataset.py:64-74, src/main.py:253) ---------
  * scores[j] = table[cand_idx[j],:] . user_vecs[imp(j),:], impressions as CSR offsets (I+1). */
 int nr_eval_score(const float* table, int64_t table_rows, const float* user_vecs,

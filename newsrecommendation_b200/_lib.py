@@ -81,6 +81,7 @@ _SIGS = {
     'nr_score_ce_fwd_noalloc': (C.c_int, [_P] * 6 + [_I64, _I32, _I32, _P]),
     'nr_score_ce_bwd': (C.c_int, [_P] * 7 + [_I64, _I32, _I32, _P]),
     'nr_adam_step': (C.c_int, [_P, _P, _P, _P, _I64, _F, _F, _F, _F, _I32, _F, _P]),
+    'nr_adam_step_dev': (C.c_int, [_P, _P, _P, _P, _P, _P, _I64, _I64, _F, _F, _F, _F, _P, _F, _P]),
     'nr_tc_gemm_nt': (C.c_int, [_P, _I64, _I32, _I64, _P, _I32, _I64, _P, _P, _I64, _I32, _I64, _I32, _P, _P]),
     'nr_tc_gemm_tn': (C.c_int, [_P, _I32, _I64, _P, _I32, _I64, _I64, _I32, _P, _P, _I64, _I64, _P]),
     'nr_title_encoder_save_bytes': (_SZ, [_E, _I64]),

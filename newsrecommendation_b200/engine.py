@@ -12,6 +12,8 @@ everything, main.py:190-196); impressions as CSR, scored by gather+dot from the 
 table; AUC/MRR/nDCG@5/10 per impression on device; 5-scalar all-reduce.
 """
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -44,8 +46,39 @@ def allreduce_gradients(flat_g):
     return 1.0
 
 
+def _symmetric_buckets(count, dev):
+    """(flat_p, flat_g, handle_p, handle_g) in NVLink symmetric memory with a multicast mapping, or None when the
+    process group / fabric cannot provide one (then NCCL all-reduce + local Adam is the path)."""
+    if not _dist_on() or os.environ.get('NR_FUSED_ALLREDUCE', '1') == '0':
+        return None
+    try:
+        import torch.distributed._symmetric_memory as symm_mem
+        p = symm_mem.empty(count, dtype=torch.float32, device=dev)
+        g = symm_mem.empty(count, dtype=torch.float32, device=dev)
+        hp = symm_mem.rendezvous(p, dist.group.WORLD)
+        hg = symm_mem.rendezvous(g, dist.group.WORLD)
+        ok = bool(hp.multicast_ptr) and bool(hg.multicast_ptr)
+    except Exception as e:        # noqa: BLE001  (private torch API: any failure means "not available")
+        import logging
+        logging.getLogger(__name__).warning(f'symmetric-memory gradient exchange unavailable ({e!r}); using NCCL all-reduce')
+        ok = False
+    # every rank must take the same path
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if not int(flag.item()):
+        return None
+    p.zero_(); g.zero_()
+    return p, g, hp, hg
+
+
 class FlatAdam:
-    """Flat-bucket Adam == torch.optim.Adam(params, lr) (betas .9/.999, eps 1e-8, wd 0)."""
+    """Flat-bucket Adam == torch.optim.Adam(params, lr) (betas .9/.999, eps 1e-8, wd 0).
+
+    With a process group on an NVSwitch fabric the buckets live in symmetric memory and step() is barrier ->
+    ONE kernel (multimem reduce-scatter + Adam on the rank's slice + multimem all-gather of the updated parameters,
+    csrc/nr_collective.cu) -> barrier; Adam moments exist only for the rank's slice.  Everything in it is
+    stream-ordered and capturable (`capturable` is True): GraphedTrainStep then replays the whole optimisation step.
+    Otherwise: one NCCL all-reduce of the bucket + the local fused Adam."""
 
     def __init__(self, model, lr, betas=(0.9, 0.999), eps=1e-8):
         self.params = [p for p in model.parameters() if p.requires_grad]
@@ -60,8 +93,16 @@ class FlatAdam:
             self.offsets.append(off)
             off += (p.numel() + 63) // 64 * 64
         self.count = off
-        self.flat_p = torch.zeros(self.count, dtype=torch.float32, device=dev)
-        self.flat_g = torch.zeros(self.count, dtype=torch.float32, device=dev)
+        self.symm = _symmetric_buckets(self.count, dev)
+        if self.symm is not None:
+            self.flat_p, self.flat_g, self.hdl_p, self.hdl_g = self.symm
+            W, r = dist.get_world_size(), dist.get_rank()
+            per = (self.count // 4 + W - 1) // W * 4                 # 4-float aligned slices
+            self.lo, self.hi = min(self.count, r * per), min(self.count, (r + 1) * per)
+        else:
+            self.flat_p = torch.zeros(self.count, dtype=torch.float32, device=dev)
+            self.flat_g = torch.zeros(self.count, dtype=torch.float32, device=dev)
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)       # Adam's t, on the device for graph replay
         self.m = torch.zeros_like(self.flat_p)
         self.v = torch.zeros_like(self.flat_p)
         for p, off in zip(self.params, self.offsets):
@@ -91,7 +132,29 @@ class FlatAdam:
         if _dist_on():
             dist.broadcast(self.flat_p, src=0)
 
+    @property
+    def capturable(self):
+        return self.symm is not None or not _dist_on()
+
+    def step_on_stream(self):
+        """The whole update as stream-ordered launches (no host-side state): capturable in a CUDA graph."""
+        L.call('nr_seed_salt_bump', L.ptr(self.step_dev), L.stream())           # t += 1
+        b1, b2 = self.betas
+        if self.symm is None:
+            L.call('nr_adam_step_dev', L.ptr(self.flat_g), None, L.ptr(self.flat_p), None, L.ptr(self.m), L.ptr(self.v),
+                   0, self.count, self.lr, b1, b2, self.eps, L.ptr(self.step_dev), 1.0, L.stream())
+            return
+        self.hdl_g.barrier(channel=0)            # every rank's backward has written its gradient bucket
+        L.call('nr_adam_step_dev', None, self.hdl_g.multicast_ptr, L.ptr(self.flat_p), self.hdl_p.multicast_ptr,
+               L.ptr(self.m), L.ptr(self.v), self.lo, self.hi, self.lr, b1, b2, self.eps, L.ptr(self.step_dev),
+               1.0 / dist.get_world_size(), L.stream())
+        self.hdl_p.barrier(channel=1)            # every rank's slice has landed in every copy of the parameters
+
     def step(self):
+        if self.symm is not None:
+            self.step_count += 1
+            self.step_on_stream()
+            return
         scale = allreduce_gradients(self.flat_g)
         self.step_count += 1
         L.call('nr_adam_step', L.ptr(self.flat_p), L.ptr(self.flat_g), L.ptr(self.m), L.ptr(self.v), self.count,
@@ -125,6 +188,8 @@ class GraphedTrainStep:
 
     def __init__(self, model, opt, example_batch, warmup=2):
         self.model, self.opt = model, opt
+        # the update joins the graph when it has no host-side state: single GPU, or the symmetric-memory exchange
+        self.tail_in_graph = bool(getattr(opt, 'capturable', False)) and os.environ.get('NR_GRAPH_TAIL', '1') != '0'
         self.static = [t.clone() for t in example_batch]
         dev = self.static[0].device
         if GraphedTrainStep._live is not None:
@@ -137,7 +202,21 @@ class GraphedTrainStep:
         side.wait_stream(cur)
         with torch.cuda.stream(side):          # warm-up off the capture stream (lazy kernel loading, allocator)
             for _ in range(warmup):
-                self._fwd_bwd()
+                self._fwd_bwd(tail=False)
+            if self.tail_in_graph:
+                # load the update's kernels before the capture without changing the optimiser state: one real
+                # update, then everything it touched is put back (peers write into this rank's parameter copy, so
+                # the restore is fenced by host barriers)
+                keep = [t.clone() for t in (opt.flat_p, opt.m, opt.v, opt.step_dev)]
+                opt.step_on_stream()
+                torch.cuda.synchronize()
+                if _dist_on():
+                    dist.barrier()
+                for t, k in zip((opt.flat_p, opt.m, opt.v, opt.step_dev), keep):
+                    t.copy_(k)
+                torch.cuda.synchronize()
+                if _dist_on():
+                    dist.barrier()
         cur.wait_stream(side)
         torch.cuda.synchronize()
         self.graph = torch.cuda.CUDAGraph()
@@ -146,12 +225,14 @@ class GraphedTrainStep:
             self._fwd_bwd()
         self.launches_per_replay = L.lib.nr_launch_count() - n0
 
-    def _fwd_bwd(self):
+    def _fwd_bwd(self, tail=True):
         L.call('nr_seed_salt_bump', L.ptr(self.salt), L.stream())
         self.opt.zero_grad()
         loss, score = self.model(*self.static)
         loss.backward(self.opt.one)
         self.loss, self.score, self.hits = loss.detach(), score.detach(), self.model.last_hits
+        if tail and self.tail_in_graph:
+            self.opt.step_on_stream()
 
     def __call__(self, history, history_mask, candidate, label):
         for s, t in zip(self.static, (history, history_mask, candidate, label)):
@@ -159,7 +240,10 @@ class GraphedTrainStep:
                 raise ValueError(f'GraphedTrainStep captured batch shape {tuple(s.shape)}, got {tuple(t.shape)}')
             s.copy_(t, non_blocking=True)
         self.graph.replay()
-        self.opt.step()
+        if self.tail_in_graph:
+            self.opt.step_count += 1
+        else:
+            self.opt.step()
         return self.loss, self.hits
 
     def close(self):

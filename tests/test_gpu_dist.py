@@ -40,6 +40,9 @@ def _batch(kind, B):
 def _worker(rank, world, port, kind, prec, mode, out_dir):
     import torch.distributed as dist
     os.environ['MASTER_ADDR'], os.environ['MASTER_PORT'] = '127.0.0.1', str(port)
+    if mode.endswith('_nccl'):          # force the NCCL all-reduce + local Adam path
+        os.environ['NR_FUSED_ALLREDUCE'] = '0'
+        mode = mode[:-5]
     torch.cuda.set_device(rank)
     dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
     try:
@@ -140,3 +143,35 @@ def test_two_ranks_match_one_rank(kind, prec, mode, tmp_path):
                                        err_msg=n)
         checked += 1
     assert checked >= 10
+
+
+@pytest.mark.parametrize('mode', ['engine_eager', 'engine_graph'])
+def test_fused_exchange_matches_nccl_allreduce(mode, tmp_path):
+    """The one-kernel gradient exchange (multimem reduce-scatter + Adam + all-gather over symmetric memory,
+    csrc/nr_collective.cu) against NCCL all-reduce + local Adam (DDP semantics, src/main.py:82,109-110): with two
+    ranks a + b is order-free, so the parameters after 3 steps must agree bit for bit (eager) / to fp32 rounding of
+    the differently ordered dropout-free graph step."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip('needs two GPUs (gpurun --gpus 2)')
+    import torch.multiprocessing as mp
+    res = {}
+    for tag in (mode, mode + '_nccl'):
+        d = tmp_path / tag
+        d.mkdir()
+        mp.spawn(_worker, args=(2, _free_port(), 'nrms', 'bf16', tag, str(d)), nprocs=2, join=True)
+        res[tag] = torch.load(os.path.join(d, 'rank0.pt'))['params']
+        assert all(torch.equal(res[tag][n], torch.load(os.path.join(d, 'rank1.pt'))['params'][n]) for n in res[tag])
+    moved = 0
+    for n in res[mode]:
+        if n.endswith('W_K.bias') or n.endswith('att_fc2.bias'):
+            continue      # analytically zero gradients (key shift / logit shift cancel): Adam turns rounding noise into +-lr steps
+        a, b = res[mode][n], res[mode + '_nccl'][n]
+        # bf16 weight-gradient kernels reduce with atomics (run-to-run order noise ~1e-7 of the gradient); Adam's
+        # first steps move every weight by ~lr, so the two runs agree to a small fraction of lr
+        d = (a - b).abs()
+        # elements whose gradient is at rounding-noise level take +-lr steps of either sign under Adam's normalisation:
+        # allow a small fraction of such outliers, all bounded by the 3-step displacement 3 * lr
+        assert float((d > 3e-5).float().mean()) < 5e-3, (n, float((d > 3e-5).float().mean()))
+        assert float(d.max()) <= 3 * 3e-4 + 1e-6, (n, float(d.max()))
+        moved += int((a - T(synth.case_inputs('nrms_ulm0')[2][n])).abs().max() > 1e-4) if n in synth.case_inputs('nrms_ulm0')[2] else 0
+    assert moved >= 10
