@@ -80,7 +80,7 @@ struct FusedParams {
 };
 
 inline size_t fused_smem_bytes(int HKB) {
-    return 1024 + (size_t)FE_STAGES * FE_STAGE_BYTES + (size_t)HKB * FE_YBLK + 256 + 2048;
+    return 1024 + (size_t)FE_STAGES * FE_STAGE_BYTES + (size_t)HKB * FE_YBLK + 256 + 2048 + 2048;
 }
 
 __device__ __forceinline__ float tanh_fast(float x) {      // MUFU.TANH, rel. error ~2^-11 (< bf16 rounding)
@@ -123,6 +123,20 @@ __device__ __forceinline__ void title_sync(int id) { asm volatile("bar.sync %0, 
 __device__ __forceinline__ uint32_t y_off(int row, int col) {
     return (uint32_t)((col >> 6) * FE_YBLK + row * 128 + ((((col & 63) >> 3) ^ (row & 7)) << 4) + (col & 7) * 2);
 }
+// 32 fp32 accumulator values of this lane's row -> 64 contiguous bytes of bf16 as two 256-bit stores (sm_100:
+// STG.E.ENL2.256; one L1 wavefront per 32-byte sector and row instead of two half-sector 128-bit stores).  dst must be
+// 32-byte aligned (qkv rows: pitch 3H * 2 bytes, H % 16 == 0; column chunks of 32).
+__device__ __forceinline__ void store_row32_bf16_v8(bf16* dst, const float* v, int nc) {
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+        if (16 * j < nc) {    // nc % 16 == 0
+            uint32_t w[8];
+#pragma unroll
+            for (int t = 0; t < 8; ++t) w[t] = tc::pack_bf16(v[16 * j + 2 * t], v[16 * j + 2 * t + 1]);
+            asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(dst + 16 * j), "r"(w[0]), "r"(w[1]), "r"(w[2]),
+                         "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7]) : "memory");
+        }
+}
 // 32 fp32 accumulator values of this lane's row -> 64 contiguous bytes of bf16 (row-major global matrix)
 __device__ __forceinline__ void store_row32_bf16(bf16* dst, const float* v, int nc) {
 #pragma unroll
@@ -151,6 +165,8 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     uint64_t* yfull = bars + 8;             // [1]  compute -> MMA (Y tile complete; FE_CW warps)
     uint32_t* tmem_slot = (uint32_t*)(bars + 9);
     float* plog = (float*)((uint8_t*)bars + 256);                       // [4][128] partial pooling logits
+    float* sb1 = plog + 512;                                            // [256] att_fc1.bias  (zero beyond Q)
+    float* sw2 = sb1 + 256;                                             // [256] att_fc2.weight (zero beyond Q)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     // All CTAs walk the SAME weight blocks; in lockstep they all ask the L2 for the same lines at the same moment
     // (measured on the first version: 0.57 ms in lockstep vs 0.25 ms staggered for the bare GEMM pipeline).  CTA c
@@ -167,6 +183,10 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         for (int a = 0; a < 2; ++a) { tc::mbar_init(tfull + a, 1); tc::mbar_init(tempty + a, FE_CW); }
         tc::mbar_init(yfull, FE_CW);
         tc::fence_barrier_init();
+    }
+    for (int i = threadIdx.x; i < 256; i += FE_THREADS) {
+        sb1[i] = i < p.Q ? __ldg(p.b1 + i) : 0.f;
+        sw2[i] = i < p.Q ? __ldg(p.w2 + i) : 0.f;
     }
     if (warp == FE_MMA_WARP) tc::tmem_alloc(tmem_slot, 512);
     tc::tc_fence_before();
@@ -316,7 +336,7 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                         float v[32];
                         tc::tmem_ld32(t_quad + (uint32_t)c, v);
                         tc::tmem_ld_wait();
-                        if (row < p.R) store_row32_bf16(p.qkv + row * 3 * (int64_t)H + g * BN + c, v, BN - c < 32 ? BN - c : 32);
+                        if (row < p.R) store_row32_bf16_v8(p.qkv + row * 3 * (int64_t)H + g * BN + c, v, BN - c < 32 ? BN - c : 32);
                     }
                 }
                 if (FE_DBG(p, 16)) {       // probe: a pure delay of (dbg >> 8) x 256 cycles per pass, nothing touched
@@ -462,15 +482,16 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 float part = 0.f;
                 for (int c = 32 * sub; c < Q; c += 128) {
                     const int nc = (Q - c < 32) ? Q - c : 32;
-                    float v[32], b[32], w[32];
+                    float v[32];
                     tc::tmem_ld32(t_row + (uint32_t)c, v);
-                    load_bias32(p.b1, c, nc, b);
-                    load_bias32(p.w2, c, nc, w);
                     tc::tmem_ld_wait();
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        v[j] = j < nc ? tanh_fast(v[j] + b[j]) : 0.f;
-                        part = fmaf(v[j], w[j], part);
+                    for (int j = 0; j < 32; j += 4) {      // b1 / w2 from shared memory (broadcast reads; zero beyond Q)
+                        const float4 b = *(const float4*)(sb1 + c + j), w = *(const float4*)(sw2 + c + j);
+                        v[j] = tanh_fast(v[j] + b.x); v[j + 1] = tanh_fast(v[j + 1] + b.y);
+                        v[j + 2] = tanh_fast(v[j + 2] + b.z); v[j + 3] = tanh_fast(v[j + 3] + b.w);
+                        part = fmaf(v[j], w.x, part); part = fmaf(v[j + 1], w.y, part);
+                        part = fmaf(v[j + 2], w.z, part); part = fmaf(v[j + 3], w.w, part);
                     }
                     if (TRAIN && row < p.R && !FE_DBG(p, 2)) store_row32_bf16(p.E + row * (int64_t)Q + c, v, nc);
                 }

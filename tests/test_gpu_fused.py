@@ -4,7 +4,7 @@ pooling in one persistent tcgen05 kernel) against the separate-launch bf16 pipel
 
   * inference variant (save == NULL; what the news-vector cache runs, main.py:190-196): vs oracle at the bf16
     tolerance (rel 1e-2 of the output scale) and vs the separate launches (same rounding points: 2e-3)
-  * training variant (NR_ENC_FUSED=1): loss / score / every gradient vs the separate launches, with and without
+  * training variant (the default; NR_ENC_FUSED=0 selects the separate launches): loss / score / every gradient vs the separate launches, with and without
     dropout (both paths draw the same Philox stream), and vs the oracle at drop_rate 0."""
 import os
 
@@ -22,6 +22,7 @@ pytestmark = pytest.mark.gpu
 
 @pytest.fixture
 def fused_training():
+    """fused training is the default; the test toggles NR_ENC_FUSED (read per call) to get the separate launches"""
     old = os.environ.get('NR_ENC_FUSED')
     os.environ['NR_ENC_FUSED'] = '1'
     yield
@@ -53,7 +54,11 @@ def test_fused_inference_vs_oracle_and_separate_launches(n):
     with torch.no_grad():
         model.news_encoder(x)
     assert L.lib.nr_launch_count() - n0 == 3                  # pack + stage + ONE encoder kernel
-    v_sep = model.news_encoder(x).detach()                    # grad mode -> saving path, separate launches
+    os.environ['NR_ENC_FUSED'] = '0'
+    try:
+        v_sep = model.news_encoder(x).detach()                # grad mode + switch -> saving path, separate launches
+    finally:
+        del os.environ['NR_ENC_FUSED']
     P = {k: T(v) for k, v in Pn.items()}
     v_or = O.nrms_news_encoder(T(ids), P, 20).numpy()
     scale = float(np.abs(v_or).max())
