@@ -22,7 +22,7 @@
  *   mode NR_ROWS_NEWS  : X[i,s,:] = table[ids[i*ids_stride], s*D:(s+1)*D] (A2:
  *                        per-news title row, src/model/NAML.py:47-50)
  * followed, when training with drop_p > 0, by inverted dropout whose keep mask
- * is the counter-based stream (seed, stream id, element index i*S*D + s*D + d)
+ * is the counter-based stream (seed, stream id, element (row i*S + s, column d))
  * exported by nr_dropout_keep_mask (F.dropout at NRMS.py:28-30, NAML.py:51-53).
  */
 #ifndef NR_SM100_H
@@ -84,9 +84,14 @@ int nr_seed_salt_bump(void* salt_dev, void* stream);
 int nr_zero_bytes(void* dst, size_t bytes, void* stream);
 int nr_concat2(const void* a, size_t bytes_a, const void* b, size_t bytes_b, void* out, void* stream);
 
-/* keep[i] = 1 if element i of dropout stream (seed, stream_id) is kept at rate p */
-int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed,
-                         int32_t stream_id, void* stream);
+/* The keep mask of a dropout stream in the plain (rows x row_width) layout of the activation it is applied to:
+ * keep[i] = 1 if element i = (row i / row_width, column i % row_width) is kept at rate p.  Streams are counter based
+ * (Philox4x32-7, one call = eight 16-bit uniforms; csrc/nr_common.cuh): the input stream NR_STREAM_IN indexes
+ * (row, column) of the gathered (n*S x D) rows (seg_width = row_width = D); the output stream NR_STREAM_OUT indexes
+ * (row, head, d) of the (n*S x heads*dk) context (row_width = H, seg_width = dk).  Used by the tests to replay the
+ * kernels' own masks through the oracle (F.dropout, src/model/NRMS.py:28-34, NAML.py:51-53). */
+int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed, int32_t stream_id,
+                         int32_t row_width, int32_t seg_width, void* stream);
 
 /* ---- A1/A2: embedding row gather (bit exact) ---------------------------------
  * out[i,:] = table[ids[i],:], width fp32 elements per row (width % 4 == 0).

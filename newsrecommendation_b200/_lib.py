@@ -61,7 +61,7 @@ _SIGS = {
     'nr_seed_salt_bump': (C.c_int, [_P, _P]),
     'nr_zero_bytes': (C.c_int, [_P, _SZ, _P]),
     'nr_concat2': (C.c_int, [_P, _SZ, _P, _SZ, _P, _P]),
-    'nr_dropout_keep_mask': (C.c_int, [_P, _I64, _F, _U64, _I32, _P]),
+    'nr_dropout_keep_mask': (C.c_int, [_P, _I64, _F, _U64, _I32, _I32, _I32, _P]),
     'nr_gather_rows': (C.c_int, [_P, _I64, _P, _I64, _I32, _P, _P]),
     'nr_attention_pooling_workspace': (_SZ, [_I64, _I32, _I32, _I32, _I32]),
     'nr_attention_pooling_fwd': (C.c_int, [_P] * 9 + [_I64, _I32, _I32, _I32, _I32, _P, _SZ, _P]),

@@ -385,7 +385,6 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         __syncwarp();
         // per-item bases once; per-slot offsets (s*H + c) come precomputed from sl.g1
         const int64_t obase = seq * 32 * H + head * DK;              // ctx / keep-bit element index (padded rows)
-        const uint64_t ebase = (uint64_t)(seq * S * H + head * DK);  // dropout element index (real rows)
         bf16* dst = ctx + obase;
 #pragma unroll
         for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
@@ -396,7 +395,7 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
                 if (thr) {
                     // the 4 keep bits are saved (one byte per 4 elements, padded-row indexing) so that the
                     // backward epilogue reads a byte instead of re-running Philox
-                    const uint32_t bits = dropout4_bits_key(ebase + (uint32_t)sl.g1[i], key, NR_STREAM_OUT, thr);
+                    const uint32_t bits = dropout4_bits_key(out_stream_index(seq * S + s, head, sl.c[i], heads, DK), key, NR_STREAM_OUT, thr);
                     v.x &= ((bits & 1u) ? 0x0000ffffu : 0u) | ((bits & 2u) ? 0xffff0000u : 0u);
                     v.y &= ((bits & 4u) ? 0x0000ffffu : 0u) | ((bits & 8u) ? 0xffff0000u : 0u);
                     if (keep) keep[(obase + sl.g1[i]) >> 2] = (uint8_t)bits;
@@ -657,7 +656,6 @@ attn_fwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             stage_out<NT, DK>(o, Os, lane, inv[0][0], inv[0][1], inv[1][0], inv[1][1]);
             __syncwarp();
             const int64_t obase = (seq * SPB + qb * 32) * H + head * DK;
-            const uint64_t ebase = (uint64_t)((seq * S + qb * 32) * H + head * DK);
             bf16* dst = ctx + obase;
 #pragma unroll
             for (int i = 0; i < Cfg<DK>::SLOTS; ++i) {
@@ -666,7 +664,7 @@ attn_fwd_blk_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
                 if (sa < S) {
                     v = *(const float4*)(Os + s * DK + sl.c[i]);
                     if (thr) {
-                        const uint32_t bits = dropout4_bits_key(ebase + (uint32_t)sl.g1[i], key, NR_STREAM_OUT, thr);
+                        const uint32_t bits = dropout4_bits_key(out_stream_index(seq * S + sa, head, sl.c[i], heads, DK), key, NR_STREAM_OUT, thr);
                         v = apply_keep4(v, bits, dscale);
                         if (keep) keep[(obase + sl.g1[i]) >> 2] = (uint8_t)bits;
                     }

@@ -97,13 +97,18 @@ __global__ void gather_rows_kernel(const float* __restrict__ table, const int32_
     }
 }
 
-__global__ void keep_mask_kernel(uint8_t* keep, int64_t count, uint32_t thr, uint64_t seed, uint32_t sid) {
-    for (int64_t q = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; q * 4 < count;
-         q += (int64_t)gridDim.x * blockDim.x) {
-        const uint4 r = philox4(salted(seed), sid, (uint64_t)q);
-        const uint32_t w[4] = {r.x, r.y, r.z, r.w};
-        for (int j = 0; j < 4; ++j)
-            if (q * 4 + j < count) keep[q * 4 + j] = w[j] >= thr ? 1 : 0;
+// keep[i] for the plain (rows x row_width) layout of a dropout stream: element i = (row, col); the stream index of
+// (row, col) follows nr_common.cuh (rows padded to 8 elements; with seg_width = head width for the output stream)
+__global__ void keep_mask_kernel(uint8_t* keep, int64_t count, uint32_t thr, uint64_t seed, uint32_t sid, int row_width,
+                                 int seg_width) {
+    const uint64_t key = salted(seed);
+    const int nseg = row_width / seg_width;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t row = i / row_width;
+        const int col = (int)(i - row * row_width);
+        const int seg = col / seg_width, d = col - seg * seg_width;
+        const uint64_t e = (uint64_t)((row * nseg + seg) * up8(seg_width) + d);
+        keep[i] = (dropout8_bits_key(e >> 3, key, sid, thr) >> (e & 7)) & 1u;
     }
 }
 
@@ -387,12 +392,15 @@ int nr_set_seed_salt(const void* salt_dev) {
     return 0;
 }
 
-int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed, int32_t sid, void* stream) {
+int nr_dropout_keep_mask(uint8_t* keep, int64_t count, float p, uint64_t seed, int32_t sid, int32_t row_width,
+                         int32_t seg_width, void* stream) {
     NR_REQUIRE(keep && count >= 0 && p >= 0.f && p < 1.f, "nr_dropout_keep_mask: bad arguments");
+    NR_REQUIRE(row_width >= 1 && seg_width >= 1 && row_width % seg_width == 0,
+               "nr_dropout_keep_mask: row_width %d must be a positive multiple of seg_width %d", row_width, seg_width);
     if (count == 0) return 0;
     ProfScope ps_keep_mask("keep_mask", (cudaStream_t)stream);
-    keep_mask_kernel<<<grid_for((count + 3) / 4, 256), 256, 0, (cudaStream_t)stream>>>(
-        keep, count, drop_threshold(p), seed, (uint32_t)sid);
+    keep_mask_kernel<<<grid_for(count, 256), 256, 0, (cudaStream_t)stream>>>(
+        keep, count, drop_threshold(p), seed, (uint32_t)sid, row_width, seg_width);
     return check_last("nr_dropout_keep_mask");
 }
 

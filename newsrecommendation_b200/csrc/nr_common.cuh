@@ -116,27 +116,35 @@ __device__ __forceinline__ uint64_t salted(uint64_t seed) {
     return p ? seed + __ldg(p) : seed;
 }
 
-// Applies inverted dropout to 4 consecutive elements starting at element index e0 (e0 % 4 == 0).
-__device__ __forceinline__ float4 dropout4(float4 v, uint64_t e0, uint64_t seed, uint32_t sid,
-                                           uint32_t thr, float scale) {
-    const uint4 r = philox4(salted(seed), sid, e0 >> 2);
-    v.x = (r.x >= thr) ? v.x * scale : 0.f;
-    v.y = (r.y >= thr) ? v.y * scale : 0.f;
-    v.z = (r.z >= thr) ? v.z * scale : 0.f;
-    v.w = (r.w >= thr) ? v.w * scale : 0.f;
-    return v;
+// ---- dropout streams ---------------------------------------------------------------------------------------------
+// One Philox4x32-7 call yields 128 bits = EIGHT 16-bit uniforms: stream element e uses 16-bit field (e & 7) of
+// philox(counter = e >> 3) and is kept when field >= thr16 = floor(p * 65536) (p = 0.2: keep probability 0.800003).
+// The 32-bit-per-element version of round 1 spent a third of the staging / attention-epilogue instructions on Philox.
+// Stream element indices are laid out so that the 8-element groups line up with what one thread handles:
+//   input dropout  (NR_STREAM_IN,  element (row r, column c) of an (R x D) activation):   e = r * up8(D) + c
+//   output dropout (NR_STREAM_OUT, element (row r, head h, d) of an (R x heads*dk) one):  e = (r * heads + h) * up8(dk) + d
+// (nr_dropout_keep_mask exports either stream in the plain (R x width) layout for the tests.)
+__host__ __device__ __forceinline__ int64_t up8(int64_t v) { return (v + 7) & ~(int64_t)7; }
+__host__ __device__ __forceinline__ uint64_t in_stream_index(int64_t r, int c, int D) { return (uint64_t)(r * up8(D) + c); }
+__host__ __device__ __forceinline__ uint64_t out_stream_index(int64_t r, int h, int d, int heads, int dk) {
+    return (uint64_t)((r * heads + h) * up8(dk) + d);
 }
+__host__ __device__ __forceinline__ uint32_t thr16_of(uint32_t thr32) { return thr32 >> 16; }
 
-// Same stream as dropout4, returned as 4 keep bits (bit j = element e0 + j kept).
-__device__ __forceinline__ uint32_t dropout4_bits(uint64_t e0, uint64_t seed, uint32_t sid, uint32_t thr) {
-    const uint4 r = philox4(salted(seed), sid, e0 >> 2);
-    return (r.x >= thr ? 1u : 0u) | (r.y >= thr ? 2u : 0u) | (r.z >= thr ? 4u : 0u) | (r.w >= thr ? 8u : 0u);
+// 8 keep bits of group G (elements 8G .. 8G+7): bit j = element 8G + j kept
+__host__ __device__ __forceinline__ uint32_t dropout8_bits_key(uint64_t G, uint64_t key, uint32_t sid, uint32_t thr32) {
+    const uint4 r = philox4(key, sid, G);
+    const uint32_t t = thr16_of(thr32);
+    return ((r.x & 0xFFFFu) >= t ? 1u : 0u) | ((r.x >> 16) >= t ? 2u : 0u) | ((r.y & 0xFFFFu) >= t ? 4u : 0u) |
+           ((r.y >> 16) >= t ? 8u : 0u) | ((r.z & 0xFFFFu) >= t ? 16u : 0u) | ((r.z >> 16) >= t ? 32u : 0u) |
+           ((r.w & 0xFFFFu) >= t ? 64u : 0u) | ((r.w >> 16) >= t ? 128u : 0u);
 }
-// same bits with the salted key hoisted by the caller (key = salted(seed) once per kernel: inside a loop that also
-// stores to global memory the compiler has to re-load the salt for every call)
-__device__ __forceinline__ uint32_t dropout4_bits_key(uint64_t e0, uint64_t key, uint32_t sid, uint32_t thr) {
-    const uint4 r = philox4(key, sid, e0 >> 2);
-    return (r.x >= thr ? 1u : 0u) | (r.y >= thr ? 2u : 0u) | (r.z >= thr ? 4u : 0u) | (r.w >= thr ? 8u : 0u);
+// 4 keep bits of the quad starting at element e0 (e0 % 4 == 0): bit j = element e0 + j kept
+__host__ __device__ __forceinline__ uint32_t dropout4_bits_key(uint64_t e0, uint64_t key, uint32_t sid, uint32_t thr32) {
+    return (dropout8_bits_key(e0 >> 3, key, sid, thr32) >> (e0 & 4)) & 0xFu;
+}
+__device__ __forceinline__ uint32_t dropout4_bits(uint64_t e0, uint64_t seed, uint32_t sid, uint32_t thr) {
+    return dropout4_bits_key(e0, salted(seed), sid, thr);
 }
 __device__ __forceinline__ float4 apply_keep4(float4 v, uint32_t bits, float scale) {
     v.x = (bits & 1u) ? v.x * scale : 0.f;
@@ -144,6 +152,10 @@ __device__ __forceinline__ float4 apply_keep4(float4 v, uint32_t bits, float sca
     v.z = (bits & 4u) ? v.z * scale : 0.f;
     v.w = (bits & 8u) ? v.w * scale : 0.f;
     return v;
+}
+// Applies inverted dropout to 4 consecutive elements starting at stream element e0 (e0 % 4 == 0).
+__device__ __forceinline__ float4 dropout4(float4 v, uint64_t e0, uint64_t seed, uint32_t sid, uint32_t thr, float scale) {
+    return apply_keep4(v, dropout4_bits(e0, seed, sid, thr), scale);
 }
 
 // ---- warp / block reductions -------------------------------------------------------
@@ -224,7 +236,7 @@ struct RowsView {
             v = mode == NR_ROWS_TOKEN ? ldg4(table + id * D + c)
                                       : ldg4(table + id * ((int64_t)S * D) + (int64_t)s * D + c);
         }
-        if (thr) v = dropout4(v, (uint64_t)(r * D + c), seed, NR_STREAM_IN, thr, scale);
+        if (thr) v = dropout4(v, in_stream_index(r, c, D), seed, NR_STREAM_IN, thr, scale);
         return v;
     }
 };

@@ -53,9 +53,10 @@ stage_rows_kernel(RowsView x, bf16* __restrict__ xb, int R, int SP, int ldx, uin
             if (x.thr) {
                 // the 8 keep bits of this thread's columns are saved (1 byte, padded-row indexing) so that the
                 // enc.dx epilogue re-applies the mask from a 4-byte load instead of eight Philox calls per chunk
+                // this thread's 8 columns are exactly one 8-element group of the input stream: ONE Philox call
                 uint32_t bits = 0;
-                if (c < x.D) bits = dropout4_bits_key((uint64_t)(r * x.D + c), key, NR_STREAM_IN, x.thr);
-                if (c + 4 < x.D) bits |= dropout4_bits_key((uint64_t)(r * x.D + c + 4), key, NR_STREAM_IN, x.thr) << 4;
+                if (c < x.D) bits = dropout8_bits_key(in_stream_index(r, c, x.D) >> 3, key, NR_STREAM_IN, x.thr);
+                if (c + 4 >= x.D) bits &= 0xFu;
                 a = apply_keep4(a, bits & 0xFu, x.scale);
                 b = apply_keep4(b, bits >> 4, x.scale);
                 if (keep_in) keep_in[(int64_t)row * (ldx >> 3) + threadIdx.x] = (uint8_t)bits;
@@ -191,7 +192,7 @@ attn_fwd_bf16_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key
         for (int d = 0; d < DK; d += 4) {
             float4 t = make_float4(o[d] * inv, o[d + 1] * inv, o[d + 2] * inv, o[d + 3] * inv);
             if (thr) {
-                const uint32_t bits = dropout4_bits((uint64_t)((seq * S + i) * H + head * DK + d), seed, NR_STREAM_OUT, thr);
+                const uint32_t bits = dropout4_bits(out_stream_index(seq * S + i, head, d, heads, DK), seed, NR_STREAM_OUT, thr);
                 t = apply_keep4(t, bits, dscale);
                 if (keep) keep[((seq * SP + i) * H + head * DK + d) >> 2] = (uint8_t)bits;
             }

@@ -154,7 +154,7 @@ struct EpiDx {
         float* dst = (x.mode == NR_ROWS_DENSE ? dx_dense + r * x.D
                    : (x.mode == NR_ROWS_TOKEN ? dtable + id * x.D : dtable + id * ((int64_t)x.S * x.D) + (int64_t)s * x.D))
                      + col0;
-        const uint64_t e0 = (uint64_t)(r * x.D + col0);
+        const uint64_t e0 = in_stream_index(r, col0, x.D);
         uint32_t kb = 0xFFFFFFFFu;
         if (x.thr && keep_in) {        // col0 is a multiple of 16 (BN % 16 == 0): 2-byte aligned, not always 4
             const uint16_t* kp = (const uint16_t*)(keep_in + (seq * SP + s) * kpitch + (col0 >> 3));

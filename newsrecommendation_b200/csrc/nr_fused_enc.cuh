@@ -428,28 +428,50 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                             }
                         amma::mm_32xn<NB>(o, ap, bv);
                     }
-                    // ---- normalise, output dropout (NRMS.py:32-34), bf16, into the swizzled Y tile
-                    const int64_t ebase = (title * S) * H + head * DK;      // dropout element index (real rows)
+                    // ---- normalise, output dropout (NRMS.py:32-34), bf16, into the swizzled Y tile.
+                    // Keep bits: the head's (32 rows x 8-column block) groups of the output stream are drawn ONE Philox
+                    // call per lane for a PAIR of (16-row half mt, block b) tiles — lane l draws row (l & 15) of tile
+                    // 2j + (l >> 4) — and handed to the lanes that hold those elements by shuffles.
                     const int64_t kbase = (title * 32) * H + head * DK;     // keep-byte index (padded rows)
+                    uint32_t kb[2][NB][2];                                  // [mt][b][row half]: 2 keep bits (cols 2t, 2t+1)
+#pragma unroll
+                    for (int mt = 0; mt < 2; ++mt)
+#pragma unroll
+                        for (int b = 0; b < NB; ++b) { kb[mt][b][0] = 3u; kb[mt][b][1] = 3u; }
+                    if (TRAIN && p.thr && !FE_DBG(p, 4)) {
+                        constexpr int NT2 = 2 * NB;                         // (mt, b) tiles of the head, tile index = mt * NB + b
+#pragma unroll
+                        for (int j = 0; j < (NT2 + 1) / 2; ++j) {
+                            const int tile = 2 * j + (lane >> 4);
+                            const int tmt = tile / NB, tb = tile - tmt * NB;
+                            const int prow = 16 * tmt + (lane & 15);
+                            uint32_t bits = 0u;
+                            if (tile < NT2 && prow < S && live) {
+                                bits = dropout8_bits_key(out_stream_index(title * S + prow, head, 8 * tb, p.heads, DK) >> 3, key,
+                                                         NR_STREAM_OUT, p.thr);
+                                if (8 * tb + 4 >= DK) bits &= 0xFu;
+                                uint8_t* kp = p.keep + ((kbase + (int64_t)prow * H + 8 * tb) >> 2);
+                                kp[0] = (uint8_t)(bits & 0xFu);
+                                if (8 * tb + 4 < DK) kp[1] = (uint8_t)(bits >> 4);
+                            }
+#pragma unroll
+                            for (int u = 0; u < 2; ++u) {                   // the two tiles of the pair
+                                const int t2 = 2 * j + u;
+                                if (t2 < NT2) {
+                                    const int mt = t2 / NB, b = t2 - mt * NB;       // compile-time after unrolling
+                                    const uint32_t lo = __shfl_sync(0xffffffffu, bits, 16 * u + g8);
+                                    const uint32_t hi = __shfl_sync(0xffffffffu, bits, 16 * u + g8 + 8);
+                                    kb[mt][b][0] = (lo >> (2 * t4)) & 3u;
+                                    kb[mt][b][1] = (hi >> (2 * t4)) & 3u;
+                                }
+                            }
+                        }
+                    }
 #pragma unroll
                     for (int mt = 0; mt < 2; ++mt)
 #pragma unroll
                         for (int b = 0; b < NB; ++b) {
-                            uint32_t klo = 3u, khi = 3u;
-                            if (TRAIN && p.thr && !FE_DBG(p, 4)) {
-                                // this lane draws ONE quad of the 16 x 8 block: row g + 8 (t >> 1), columns 4 (t & 1) .. +3
-                                const int prow = 16 * mt + g8 + 8 * (t4 >> 1);
-                                const int d4 = 8 * b + 4 * (t4 & 1);
-                                uint32_t bits = 0u;
-                                if (d4 < DK && prow < S && live) {
-                                    bits = dropout4_bits_key((uint64_t)(ebase + (int64_t)prow * H + d4), key, NR_STREAM_OUT, p.thr);
-                                    p.keep[(kbase + (int64_t)prow * H + d4) >> 2] = (uint8_t)bits;
-                                }
-                                const uint32_t blo = __shfl_sync(0xffffffffu, bits, (lane & ~3) | (t4 >> 1));
-                                const uint32_t bhi = __shfl_sync(0xffffffffu, bits, (lane & ~3) | 2 | (t4 >> 1));
-                                klo = (blo >> (2 * (t4 & 1))) & 3u;
-                                khi = (bhi >> (2 * (t4 & 1))) & 3u;
-                            }
+                            const uint32_t klo = kb[mt][b][0], khi = kb[mt][b][1];
                             const int d0 = 8 * b + 2 * t4;
                             if (d0 < DK) {
                                 const int r0 = 16 * mt + g8, r1 = r0 + 8;

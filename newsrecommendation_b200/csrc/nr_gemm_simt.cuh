@@ -82,7 +82,7 @@ struct EpiScatterTok {
         const int64_t seq = r / x.S; const int s = (int)(r - seq * x.S);
         const int64_t id = x.id_of(seq, s);
         if (id == 0) return;
-        if (x.thr) a = dropout4(a, (uint64_t)(r * x.D + c), x.seed, NR_STREAM_IN, x.thr, x.scale);
+        if (x.thr) a = dropout4(a, in_stream_index(r, c, x.D), x.seed, NR_STREAM_IN, x.thr, x.scale);
         float* p = x.mode == NR_ROWS_TOKEN ? dtable + id * x.D + c
                                            : dtable + id * ((int64_t)x.S * x.D) + (int64_t)s * x.D + c;
         atomicAdd(p, a.x); atomicAdd(p + 1, a.y); atomicAdd(p + 2, a.z); atomicAdd(p + 3, a.w);
@@ -101,7 +101,7 @@ struct EpiScatterEmb {
 struct EpiDropStore {     // dense dX with the input-dropout mask re-applied
     float* C; RowsView x;
     __device__ __forceinline__ void operator()(int64_t r, int c, float4 a) const {
-        if (x.thr) a = dropout4(a, (uint64_t)(r * x.D + c), x.seed, NR_STREAM_IN, x.thr, x.scale);
+        if (x.thr) a = dropout4(a, in_stream_index(r, c, x.D), x.seed, NR_STREAM_IN, x.thr, x.scale);
         *(float4*)(C + r * x.D + c) = a;
     }
 };

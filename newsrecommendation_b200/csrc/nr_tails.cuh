@@ -192,7 +192,7 @@ attn_fwd_kernel(const float* __restrict__ qkv, const float* __restrict__ key_mas
 #pragma unroll
         for (int d = 0; d < DK; d += 4) {
             float4 t = make_float4(o[d] * inv, o[d + 1] * inv, o[d + 2] * inv, o[d + 3] * inv);
-            if (thr) t = dropout4(t, (uint64_t)((seq * S + i) * H + head * DK + d), seed, NR_STREAM_OUT, thr, dscale);
+            if (thr) t = dropout4(t, out_stream_index(seq * S + i, head, d, heads, DK), seed, NR_STREAM_OUT, thr, dscale);
             *(float4*)(out + d) = t;
         }
     }
@@ -228,7 +228,7 @@ attn_bwd_kernel(const float* __restrict__ qkv, const float* __restrict__ key_mas
         *(float4*)(Vs + s * DK + q4 * 4) = ldg4(row + 2 * H);
         const int64_t e0 = (seq * S + s) * H + head * DK + q4 * 4;
         float4 gv = ldg4(dctx + e0);
-        if (thr) gv = dropout4(gv, (uint64_t)e0, seed, NR_STREAM_OUT, thr, dscale);
+        if (thr) gv = dropout4(gv, out_stream_index(seq * S + s, head, q4 * 4, heads, DK), seed, NR_STREAM_OUT, thr, dscale);
         *(float4*)(Gs + s * DK + q4 * 4) = gv;
     }
     __syncwarp();

@@ -55,9 +55,12 @@ def gather_rows(table, ids):
     return out
 
 
-def dropout_keep_mask(count, p, seed, stream_id, device):
+def dropout_keep_mask(count, p, seed, stream_id, device, row_width, seg_width=None):
+    """Keep mask of a dropout stream in the (rows, row_width) layout of the activation (seg_width = head width for the
+    output stream of the MHSA; include/nr_sm100.h)."""
     keep = torch.empty(count, dtype=torch.uint8, device=device)
-    L.call('nr_dropout_keep_mask', L.ptr(keep), count, float(p), C.c_uint64(seed), stream_id, L.stream())
+    L.call('nr_dropout_keep_mask', L.ptr(keep), count, float(p), C.c_uint64(seed), stream_id, int(row_width),
+           int(seg_width or row_width), L.stream())
     return keep
 
 

@@ -136,8 +136,8 @@ def test_mhsa_token_rows_with_dropout_replay(ops):
     wd = [t.cuda().requires_grad_(True) for t in w]
     out = ops.mhsa(td, ids.cuda(), None, *wd, mode=L.ROWS_TOKEN, S=S, Dm=D, heads=20, in_drop=p, out_drop=p,
                    seed=seed)
-    k1 = ops.dropout_keep_mask(n * S * D, p, seed, L.STREAM_IN, 'cuda').cpu().view(n, S, D)
-    k2 = ops.dropout_keep_mask(n * S * H, p, seed, L.STREAM_OUT, 'cuda').cpu().view(n, S, H)
+    k1 = ops.dropout_keep_mask(n * S * D, p, seed, L.STREAM_IN, 'cuda', D).cpu().view(n, S, D)
+    k2 = ops.dropout_keep_mask(n * S * H, p, seed, L.STREAM_OUT, 'cuda', H, H // 20).cpu().view(n, S, H)
     assert 0.75 < k1.float().mean() < 0.85 and 0.75 < k2.float().mean() < 0.85
     to = table.clone().requires_grad_(True)
     wo = [t.clone().requires_grad_(True) for t in w]
@@ -179,7 +179,7 @@ def test_conv_news_rows_dropout_and_table_grad(ops):
     td = table.cuda().requires_grad_(True)
     wd, bd = cw.cuda().requires_grad_(True), cb.cuda().requires_grad_(True)
     y = ops.conv1d_k3(td, ids.cuda(), wd, bd, mode=L.ROWS_NEWS, L_=Lw, D=D, in_drop=p, seed=seed)
-    k1 = ops.dropout_keep_mask(n * Lw * D, p, seed, L.STREAM_IN, 'cuda').cpu().view(n, Lw, D)
+    k1 = ops.dropout_keep_mask(n * Lw * D, p, seed, L.STREAM_IN, 'cuda', D).cpu().view(n, Lw, D)
     to, wo, bo = table.clone().requires_grad_(True), cw.clone().requires_grad_(True), cb.clone().requires_grad_(True)
     x = O.dropout(O.embedding_lookup(to, ids[:, 0]).reshape(n, Lw, D), k1, p)
     ref = O.conv1d_k3(x, wo, bo)
@@ -225,3 +225,34 @@ def test_out_of_range_ids_read_the_padding_row():
         L.call('nr_eval_score', L.ptr(cache), V, L.ptr(user), L.ptr(off), L.ptr(cand), L.ptr(s), 2, 7, 400, L.stream())
         sc.append(s)
     assert torch.equal(sc[0], sc[1])
+
+
+def test_dropout_stream_statistics():
+    """16-bit-threshold Philox streams (one call = 8 elements): keep rate, serial correlations at the lags the layout
+    could expose (inside a Philox call: 1..7; across calls: 8, 16; across rows / heads: 300, 304, 400, 24) and
+    independence between the input and output streams and between seeds.  5-sigma bounds on 4 M elements."""
+    from newsrecommendation_b200 import _lib as L, ops
+    N, p = 1 << 22, 0.2
+    a = ops.dropout_keep_mask(N, p, 1234, L.STREAM_IN, 'cuda', 304).float()
+    b = ops.dropout_keep_mask(N, p, 1234, L.STREAM_OUT, 'cuda', 400, 20).float()
+    c = ops.dropout_keep_mask(N, p, 1235, L.STREAM_IN, 'cuda', 304).float()
+    d = ops.dropout_keep_mask(N, p, 1234, L.STREAM_IN, 'cuda', 300).float()     # the real MIND width: rows padded to 304 in stream space
+    sig = (0.8 * 0.2 / N) ** 0.5
+    for m in (a, b, c, d):
+        assert abs(m.mean().item() - (1 - 13107 / 65536)) < 5 * sig          # thr16 = floor(0.2 * 65536)
+    def corr(x, y):
+        x, y = x - x.mean(), y - y.mean()
+        return (x * y).mean().item() / (x.std().item() * y.std().item())
+    lim = 5 / N ** 0.5
+    for m in (a, b, d):
+        for lag in (1, 2, 3, 4, 5, 6, 7, 8, 16, 24, 300, 304, 400):
+            assert abs(corr(m[:-lag], m[lag:])) < lim, lag
+    assert abs(corr(a, b)) < lim and abs(corr(a, c)) < lim
+    # 8-element groups: the 256 keep patterns of a group follow the product law (chi-square over patterns by popcount)
+    g = a.view(-1, 8).sum(1).long()
+    cnt = torch.bincount(g, minlength=9).double().cpu().numpy()
+    from math import comb
+    q = 1 - 13107 / 65536
+    exp = np.array([comb(8, k) * q ** k * (1 - q) ** (8 - k) for k in range(9)]) * (N // 8)
+    chi2 = float(((cnt - exp) ** 2 / exp).sum())
+    assert chi2 < 40.0, chi2                                                  # 8 dof: P(chi2 > 40) ~ 3e-6
