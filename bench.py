@@ -93,7 +93,7 @@ def make_workload(a, rank):
     return args, ctor, news
 
 
-def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20):
+def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20, fused=True):
     """Algorithmic FLOPs per step for each named kernel of the step."""
     n = B * (T + 1 + K_NEG)
     M, Mu = n * L, B * T
@@ -120,13 +120,20 @@ def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20):
         f['enc.attn_fwd'] = f['attn_fwd']
         f['enc.attn_bwd'] = f['attn_bwd']
         f['enc.fc1'] = f['enc.pool_dx'] = f['enc.dw1'] = 2.0 * (M + Mu) * H * Q
+        if fused:
+            # titles: QKV projection + attention + fc1 (+ pooling) in ONE kernel; the separate launches only see the
+            # 128 x 50 history rows of the user encoder
+            f['enc.fused_fwd'] = 2.0 * M * D * 3 * H + 4.0 * n * L * L * H + 2.0 * M * H * Q + 2.0 * M * H
+            f['enc.qkv'] = 2.0 * Mu * H * 3 * H
+            f['enc.attn_fwd'] = 4.0 * B * T * T * H
+            f['enc.fc1'] = 2.0 * Mu * H * Q
     else:
         f['enc.conv'] = f['enc.dwconv'] = 2.0 * M * 3 * D * H
         f['enc.fc1'] = f['enc.pool_dx'] = f['enc.dw1'] = 2.0 * M * H * Q
     return f
 
 
-def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200):
+def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, fused=True):
     """Algorithmic HBM bytes per step for each named kernel of the bf16 step: what the kernel has to read and
     write once, on real (unpadded) tokens.  M title tokens, Mu history tokens."""
     n = B * (T + 1 + K_NEG)
@@ -147,8 +154,16 @@ def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200):
         b['enc.conv'] = M * (D + 1) * 2 + M * H * 2
         b['enc.dwconv'] = M * H * 2 + M * (D + 1) * 2
         b['enc.dx'] = M * H * 2 + M * D * 4
-    b['enc.fc1'] = tok * (H + Q) * 2 + tok * 4                                         # y in, tanh(e) + logit out
-    b['enc.pool_fwd'] = tok * (H * 2 + 4 + 4) + (tok // L) * H * 4
+    if model == 'NRMS' and fused:
+        # fused forward over the M title tokens: Xb in; qkv, Y, E (bf16), alpha, keep bits and the (n, H) vectors out
+        b['enc.fused_fwd'] = M * ((D + 1) * 2 + 3 * H * 2 + H * 2 + Q * 2 + 4) + M * H // 4 + (M // L) * H * 4
+        b['enc.qkv'] = Mu * (H + 1) * 2 + Mu * 3 * H * 2
+        b['enc.attn_fwd'] = Mu * (3 * H + H) * 2
+        tok_sep = Mu
+    else:
+        tok_sep = tok
+    b['enc.fc1'] = tok_sep * (H + Q) * 2 + tok_sep * 4                                 # y in, tanh(e) + logit out
+    b['enc.pool_fwd'] = tok_sep * (H * 2 + 4 + 4) + (tok_sep // L) * H * 4
     b['enc.pool_bwd'] = tok * (H * 2 + Q * 2 + 4 + Q * 2)                              # y, e, alpha in; dz out
     b['enc.dw1'] = tok * (Q + H) * 2
     b['enc.pool_dx'] = tok * (Q * 2 + H * 2 + 4) + (M * H // 4 if model == 'NRMS' else 0)
@@ -371,8 +386,9 @@ def train_leg(a, model_name, rank, world, sampler_idx=None, keep_load=False):
     pk = peaks()
     # with the abstract view every news contributes L_TITLE + L_ABSTRACT token rows to the conv / pooling kernels
     Ltok = L_TITLE + (L_ABSTRACT if (model_name == 'NAML' and a.abstract) else 0)
-    ft = flops_table(model_name, a.batch, L=Ltok)
-    bt = bytes_table(model_name, a.batch, L=Ltok) if a.precision == 'bf16' else {}
+    fused = os.environ.get('NR_ENC_FUSED', '1') != '0'
+    ft = flops_table(model_name, a.batch, L=Ltok, fused=fused)
+    bt = bytes_table(model_name, a.batch, L=Ltok, fused=fused) if a.precision == 'bf16' else {}
     tot = sum(v[1] for v in prof.values()) or 1.0
     kern = {k: {'ms_per_step': v[1] / a.steps, 'launches_per_step': v[0] / a.steps, 'share': v[1] / tot}
             for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}

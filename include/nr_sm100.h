@@ -195,8 +195,9 @@ int nr_adam_step(float* p, const float* g, float* m, float* v, int64_t count, fl
                  float beta2, float eps, int32_t step, float grad_scale, void* stream);
 
 /* A12 at N > 1 — gradient exchange fused with the optimizer (src/main.py:82,109-110: DDP gradient mean + Adam.step):
- * Adam over the slice [lo, hi) of the flat buckets with the step count read from DEVICE memory (*step_dev, int64, so
- * that the launch can be replayed from a CUDA graph).  With the multicast pointers given (both buckets in symmetric
+ * Adam over the slice [lo, hi) of the flat buckets with the step count read from DEVICE memory (t = *step_dev + 1,
+ * int64 count of completed steps, bumped by the caller afterwards with nr_seed_salt_bump: the launch can be replayed
+ * from a CUDA graph and several slices of one step can be updated by separate launches).  With the multicast pointers given (both buckets in symmetric
  * memory mapped through an NVLink multicast object), g is read with multimem.ld_reduce (summed over the ranks in the
  * NVSwitch) and the updated parameters are written with multimem.st into every rank's copy: reduce-scatter + Adam +
  * all-gather in ONE kernel.  p / m / v are this rank's local buffers (m, v are only touched inside the slice).  The
@@ -264,6 +265,9 @@ typedef struct nr_title_encoder_grads {   /* all ACCUMULATED (+=); any pointer m
     float* dp_w1; float* dp_b1; float* dp_w2; float* dp_b2;
     float* dtable;          /* token / news rows: dense embedding-table gradient (row 0 skipped) */
     float* dx_dense;        /* dense rows: (n,S,Dm) gradient, WRITTEN */
+    void* dtable_ready;     /* optional cudaEvent_t recorded on `stream` as soon as dtable / dx_dense is final (MHSA kind:
+                             * before the weight-gradient GEMM), so a caller can overlap the exchange of that part of
+                             * its gradient bucket with the rest of the backward; NULL = not wanted */
 } nr_title_encoder_grads_t;
 size_t nr_title_encoder_save_bytes(const nr_title_encoder_t* enc, int64_t n);
 size_t nr_title_encoder_workspace(const nr_title_encoder_t* enc, int64_t n);

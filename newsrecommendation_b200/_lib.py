@@ -40,7 +40,7 @@ class NrTitleEncoder(C.Structure):
 
 class NrTitleEncoderGrads(C.Structure):
     _fields_ = [('dw', C.c_void_p * 3), ('db', C.c_void_p * 3), ('dp_w1', C.c_void_p), ('dp_b1', C.c_void_p),
-                ('dp_w2', C.c_void_p), ('dp_b2', C.c_void_p), ('dtable', C.c_void_p), ('dx_dense', C.c_void_p)]
+                ('dp_w2', C.c_void_p), ('dp_b2', C.c_void_p), ('dtable', C.c_void_p), ('dx_dense', C.c_void_p), ('dtable_ready', C.c_void_p)]
 
 
 ENC_MHSA, ENC_CONV, ENC_POOL = 0, 1, 2

@@ -13,7 +13,8 @@
 // them).  The launch is bracketed by two cross-rank barriers issued by the host code (torch symmetric-memory signal
 // pads): gradients complete everywhere before, updated parameters visible everywhere after.  All of it is plain
 // stream-ordered launches, so the whole optimisation step replays from one CUDA graph; the Adam step count is read
-// from device memory for that reason.
+// from device memory for that reason (*step_dev = number of COMPLETED steps; bumped by the caller after the update, so
+// that a part of the bucket can be exchanged early, on a side stream, with the same count).
 #include "nr_common.cuh"
 
 namespace nr {
@@ -47,7 +48,7 @@ adam_dev_kernel(const float* __restrict__ g_src, float* p_dst, const float* p_lo
     // bias corrections from the device-resident step count, in double like the host path (nr_adam_step), once per block
     __shared__ float s_bc[2];
     if (threadIdx.x == 0) {
-        const double t = (double)__ldg(step_dev);
+        const double t = (double)(__ldg(step_dev) + 1);      // *step_dev = completed steps; the caller bumps it afterwards
         s_bc[0] = (float)((double)lr / (1.0 - pow((double)b1, t)));
         s_bc[1] = (float)(1.0 / sqrt(1.0 - pow((double)b2, t)));
     }

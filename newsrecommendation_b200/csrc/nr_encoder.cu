@@ -751,15 +751,18 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     const RowsView xv = make_rows_view(rows, n, S, Dm);
     if (enc->kind == NR_ENC_MHSA) {
         if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st)) return e;
+        // dX (the embedding-table gradient: 15 of the 19 MB of the NRMS gradient bucket) BEFORE the weight gradient:
+        // the caller can start exchanging that part of the bucket while enc.dwqkv still runs (gr->dtable_ready)
+        if (want_dx)
+            if (int e = gemm_tc_pick(dqkv, p.R, 3 * H, 3 * H, wt, Dm, p.K3, 1, &one, p.R,
+                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0}, st, "enc.dx"))
+                return e;
+        if (gr->dtable_ready) NR_CUDA(cudaEventRecord((cudaEvent_t)gr->dtable_ready, st));
         if (int e = gemm_tc_tn(dqkv, 3 * H, 3 * H, xb, Dm + 1, p.ldx, p.R, 1, &one,
                                TnEpiQkv{gr->dw[0], gr->dw[1], gr->dw[2], gr->db[0], gr->db[1], gr->db[2], H, Dm,
                                         qkv_head_major(p.SP, H / enc->heads) ? H / enc->heads : 0}, st,
                                "enc.dwqkv"))
             return e;
-        if (want_dx)
-            if (int e = gemm_tc_pick(dqkv, p.R, 3 * H, 3 * H, wt, Dm, p.K3, 1, &one, p.R,
-                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0}, st, "enc.dx"))
-                return e;
     } else {
         const int sh[3] = {-1, 0, 1};
         if (int e = gemm_tc_tn(dy, H, H, xb, Dm + 1, p.ldx, p.R, 3, sh, TnEpiConv{gr->dw[0], gr->db[0], Dm}, st,

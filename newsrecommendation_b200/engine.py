@@ -102,7 +102,27 @@ class FlatAdam:
         else:
             self.flat_p = torch.zeros(self.count, dtype=torch.float32, device=dev)
             self.flat_g = torch.zeros(self.count, dtype=torch.float32, device=dev)
-        self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)       # Adam's t, on the device for graph replay
+        self.step_dev = torch.zeros(1, dtype=torch.int64, device=dev)       # completed Adam steps, on the device (graph replay)
+        # Early exchange: when one parameter dominates the bucket (NRMS: the dense (V,300) embedding gradient, 15 of
+        # 19 MB) and sits at one end of it, its slice of the bucket is exchanged on a side stream as soon as the
+        # backward has finished it (ops.TitleEncoderFn records `_nr_grad_ready_event` after enc.dx, before the
+        # weight-gradient GEMM), overlapping the NVLink traffic with the rest of the backward.
+        self.early = None
+        if self.symm is not None and os.environ.get('NR_EXCHANGE_OVERLAP', '1') != '0':
+            i = max(range(len(self.params)), key=lambda k: self.params[k].numel())
+            big = self.params[i].numel() * 3 >= self.count or os.environ.get('NR_EXCHANGE_OVERLAP') == 'always'   # 'always': tests
+            if big and i in (0, len(self.params) - 1):
+                a = self.offsets[i]
+                b = self.offsets[i + 1] if i + 1 < len(self.params) else self.count
+                W, r = dist.get_world_size(), dist.get_rank()
+
+                def sl(lo, hi):
+                    per = ((hi - lo) // 4 + W - 1) // W * 4
+                    return min(hi, lo + r * per), min(hi, lo + (r + 1) * per)
+                self.early = {'param': self.params[i], 'slice': sl(a, b), 'rest': sl(b, self.count) if i == 0 else sl(0, a),
+                              'side': torch.cuda.Stream(), 'ready': torch.cuda.Event(), 'join': torch.cuda.Event()}
+                self.early['ready'].record()                      # materialise the CUDA event handle
+                self.params[i]._nr_grad_ready_event = self.early['ready']
         self.m = torch.zeros_like(self.flat_p)
         self.v = torch.zeros_like(self.flat_p)
         for p, off in zip(self.params, self.offsets):
@@ -136,19 +156,33 @@ class FlatAdam:
     def capturable(self):
         return self.symm is not None or not _dist_on()
 
+    def _exchange(self, lo, hi, ch):
+        b1, b2 = self.betas
+        self.hdl_g.barrier(channel=ch)           # every rank's backward has written this part of its gradient bucket
+        L.call('nr_adam_step_dev', None, self.hdl_g.multicast_ptr, L.ptr(self.flat_p), self.hdl_p.multicast_ptr,
+               L.ptr(self.m), L.ptr(self.v), lo, hi, self.lr, b1, b2, self.eps, L.ptr(self.step_dev),
+               1.0 / dist.get_world_size(), L.stream())
+        self.hdl_p.barrier(channel=ch + 1)       # every rank's slice has landed in every copy of the parameters
+
     def step_on_stream(self):
         """The whole update as stream-ordered launches (no host-side state): capturable in a CUDA graph."""
-        L.call('nr_seed_salt_bump', L.ptr(self.step_dev), L.stream())           # t += 1
         b1, b2 = self.betas
         if self.symm is None:
             L.call('nr_adam_step_dev', L.ptr(self.flat_g), None, L.ptr(self.flat_p), None, L.ptr(self.m), L.ptr(self.v),
                    0, self.count, self.lr, b1, b2, self.eps, L.ptr(self.step_dev), 1.0, L.stream())
-            return
-        self.hdl_g.barrier(channel=0)            # every rank's backward has written its gradient bucket
-        L.call('nr_adam_step_dev', None, self.hdl_g.multicast_ptr, L.ptr(self.flat_p), self.hdl_p.multicast_ptr,
-               L.ptr(self.m), L.ptr(self.v), self.lo, self.hi, self.lr, b1, b2, self.eps, L.ptr(self.step_dev),
-               1.0 / dist.get_world_size(), L.stream())
-        self.hdl_p.barrier(channel=1)            # every rank's slice has landed in every copy of the parameters
+        elif self.early is not None and getattr(self.early['param'], '_nr_grad_ready_recorded', False):
+            e = self.early
+            e['param']._nr_grad_ready_recorded = False
+            main = torch.cuda.current_stream()
+            e['side'].wait_event(e['ready'])     # recorded by the backward right after the dominant gradient was final
+            with torch.cuda.stream(e['side']):
+                self._exchange(*e['slice'], 2)
+                e['join'].record()
+            self._exchange(*e['rest'], 0)        # behind the whole backward, on the main stream
+            main.wait_event(e['join'])
+        else:
+            self._exchange(self.lo, self.hi, 0)
+        L.call('nr_seed_salt_bump', L.ptr(self.step_dev), L.stream())           # completed steps += 1
 
     def step(self):
         if self.symm is not None:

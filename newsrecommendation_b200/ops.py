@@ -412,6 +412,10 @@ class TitleEncoderFn(torch.autograd.Function):
             else:
                 buf, dsrc = _grad_target(psrc, rows.table)
                 gr.dtable = L.ptr(buf)
+                ev = getattr(psrc, '_nr_grad_ready_event', None)      # engine.FlatAdam: overlap the exchange of this slice
+                if ev is not None:
+                    gr.dtable_ready = ev.cuda_event
+                    psrc._nr_grad_ready_recorded = True
         ws = L.workspace(L.lib.nr_title_encoder_workspace(C.byref(enc), n), dev)
         r = rows.c()
         L.call('nr_title_encoder_bwd', C.byref(enc), C.byref(r), n, L.ptr(g), L.ptr(save), save.numel(), C.byref(gr),

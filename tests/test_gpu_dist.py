@@ -43,6 +43,9 @@ def _worker(rank, world, port, kind, prec, mode, out_dir):
     if mode.endswith('_nccl'):          # force the NCCL all-reduce + local Adam path
         os.environ['NR_FUSED_ALLREDUCE'] = '0'
         mode = mode[:-5]
+    if mode.endswith('_early'):         # early side-stream exchange of the largest parameter even for this tiny vocabulary
+        os.environ['NR_EXCHANGE_OVERLAP'] = 'always'
+        mode = mode[:-6]
     torch.cuda.set_device(rank)
     dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
     try:
@@ -145,17 +148,19 @@ def test_two_ranks_match_one_rank(kind, prec, mode, tmp_path):
     assert checked >= 10
 
 
-@pytest.mark.parametrize('mode', ['engine_eager', 'engine_graph'])
+@pytest.mark.parametrize('mode', ['engine_eager', 'engine_graph', 'engine_eager_early', 'engine_graph_early'])
 def test_fused_exchange_matches_nccl_allreduce(mode, tmp_path):
     """The one-kernel gradient exchange (multimem reduce-scatter + Adam + all-gather over symmetric memory,
-    csrc/nr_collective.cu) against NCCL all-reduce + local Adam (DDP semantics, src/main.py:82,109-110): with two
+    csrc/nr_collective.cu; `_early`: the largest parameter's slice exchanged on a side stream from inside the backward)
+    against NCCL all-reduce + local Adam (DDP semantics, src/main.py:82,109-110): with two
     ranks a + b is order-free, so the parameters after 3 steps must agree bit for bit (eager) / to fp32 rounding of
     the differently ordered dropout-free graph step."""
     if torch.cuda.device_count() < 2:
         pytest.skip('needs two GPUs (gpurun --gpus 2)')
     import torch.multiprocessing as mp
     res = {}
-    for tag in (mode, mode + '_nccl'):
+    base = mode.replace('_early', '')
+    for tag in (mode, base + '_nccl'):
         d = tmp_path / tag
         d.mkdir()
         mp.spawn(_worker, args=(2, _free_port(), 'nrms', 'bf16', tag, str(d)), nprocs=2, join=True)
@@ -165,7 +170,7 @@ def test_fused_exchange_matches_nccl_allreduce(mode, tmp_path):
     for n in res[mode]:
         if n.endswith('W_K.bias') or n.endswith('att_fc2.bias'):
             continue      # analytically zero gradients (key shift / logit shift cancel): Adam turns rounding noise into +-lr steps
-        a, b = res[mode][n], res[mode + '_nccl'][n]
+        a, b = res[mode][n], res[base + '_nccl'][n]
         # bf16 weight-gradient kernels reduce with atomics (run-to-run order noise ~1e-7 of the gradient); Adam's
         # first steps move every weight by ~lr, so the two runs agree to a small fraction of lr
         d = (a - b).abs()
