@@ -491,9 +491,11 @@ size_t nr_title_encoder_workspace(const nr_title_encoder_t* enc, int64_t n) {
 }
 
 static bool infer_supported(const nr_title_encoder_t* e) {
-    if (e->kind != NR_ENC_MHSA || e->heads < 1 || e->H % e->heads) return false;
     const int SP = round_up(e->S + 1, 32), Kp = round_up(e->Dm + 1, 64);
-    return e->S <= 31 && e->out_drop_p == 0.f && fe::fused_supported(SP, e->H / e->heads, e->heads, e->H, e->Q, Kp);
+    if (e->S > 31 || e->out_drop_p != 0.f) return false;
+    if (e->kind == NR_ENC_CONV) return fe::fused_conv_supported(SP, e->H, e->Q, Kp);
+    if (e->kind != NR_ENC_MHSA || e->heads < 1 || e->H % e->heads) return false;
+    return fe::fused_supported(SP, e->H / e->heads, e->heads, e->H, e->Q, Kp);
 }
 struct InferPlan { int SP, ldx, Kp, HK; int64_t R; size_t o_wb, o_w1b, o_xb, bytes; };
 static InferPlan make_infer_plan(const nr_title_encoder_t* e, int64_t n) {
@@ -502,7 +504,7 @@ static InferPlan make_infer_plan(const nr_title_encoder_t* e, int64_t n) {
     p.R = n * p.SP;
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t r = o; o += (bytes + 1023) & ~size_t(1023); return r; };
-    p.o_wb = take((size_t)3 * e->H * p.Kp * 2);
+    p.o_wb = take((size_t)3 * e->H * p.Kp * 2);            // MHSA: (3H x Kp); CONV: (H x 3 Kp)
     p.o_w1b = take((size_t)e->Q * p.HK * 2);
     p.o_xb = take((size_t)p.R * p.ldx * 2);
     p.bytes = o;
@@ -517,14 +519,15 @@ size_t nr_title_encoder_infer_bytes(const nr_title_encoder_t* enc, int64_t n) {
 static int title_encoder_infer(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, float* out, void* ws,
                                size_t ws_bytes, cudaStream_t st) {
     const char* who = "nr_title_encoder_fwd(inference)";
-    NR_REQUIRE(infer_supported(enc), "%s: save == NULL needs an MHSA title encoder inside the fused envelope (S <= 31, "
-               "head width 16 or 20, heads %% 4 == 0, no output dropout); pass a save buffer otherwise", who);
+    NR_REQUIRE(infer_supported(enc), "%s: save == NULL needs an MHSA or CONV title encoder inside the fused envelope (S <= 31; "
+               "MHSA: head width 16 or 20, heads %% 4 == 0, no output dropout); pass a save buffer otherwise", who);
     NR_REQUIRE(rows->drop_p == 0.f, "%s: input dropout in inference mode", who);
     NR_REQUIRE(ws, "%s: workspace is NULL", who);
     const InferPlan p = make_infer_plan(enc, n);
     char* w = (char*)(((uintptr_t)ws + 1023) & ~(uintptr_t)1023);
     NR_REQUIRE((size_t)(w - (char*)ws) + p.bytes <= ws_bytes, "%s: workspace too small (%zu < %zu)", who, ws_bytes, p.bytes + 1024);
-    const int S = enc->S, Dm = enc->Dm, H = enc->H, Q = enc->Q, dk = H / enc->heads;
+    const bool conv = enc->kind == NR_ENC_CONV;
+    const int S = enc->S, Dm = enc->Dm, H = enc->H, Q = enc->Q, dk = conv ? 20 : H / enc->heads;
     bf16* wb = (bf16*)(w + p.o_wb);
     bf16* w1b = (bf16*)(w + p.o_w1b);
     bf16* xb = (bf16*)(w + p.o_xb);
@@ -532,7 +535,8 @@ static int title_encoder_infer(const nr_title_encoder_t* enc, const nr_rows_t* r
         PackArgs ja[2];
         bf16* jo[2];
         ja[0] = PackArgs{enc->p_w1, nullptr, nullptr, 0, Q, H, 0, Q, p.HK, 1}; jo[0] = w1b;
-        ja[1] = PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3, enc->b[0], enc->b[1], enc->b[2], dk};
+        if (conv) ja[1] = PackArgs{enc->w[0], nullptr, nullptr, 2, H, Dm, p.Kp, H, 3 * p.Kp, 1, enc->b[0], nullptr, nullptr};
+        else ja[1] = PackArgs{enc->w[0], enc->w[1], enc->w[2], 0, H, Dm, 0, 3 * H, p.Kp, 3, enc->b[0], enc->b[1], enc->b[2], dk};
         jo[1] = wb;
         if (int e = pack_multi(ja, jo, 2, st)) return e;
     }
@@ -550,12 +554,13 @@ static int title_encoder_infer(const nr_title_encoder_t* enc, const nr_rows_t* r
     }
     fe::FusedArgs fa{xb, p.R, p.ldx, Dm + 1, wb, p.Kp, w1b, p.HK, nullptr};
     fe::FusedParams fp{};
-    fp.R = p.R; fp.n = n; fp.S = S; fp.H = H; fp.Q = Q; fp.heads = enc->heads;
+    fp.R = p.R; fp.n = n; fp.S = S; fp.H = H; fp.Q = Q; fp.heads = conv ? 4 : enc->heads;
     fp.out = out; fp.mask = enc->mask; fp.b1 = enc->p_b1; fp.w2 = enc->p_w2; fp.b2 = enc->p_b2;
     fp.scale = 1.0f / sqrtf((float)dk);
     fp.dscale = 1.f;
-    if (dk == 20) return fe::launch_fused<20, false>(fa, fp, st);
-    return fe::launch_fused<16, false>(fa, fp, st);
+    if (conv) return fe::launch_fused<20, false, true>(fa, fp, st);
+    if (dk == 20) return fe::launch_fused<20, false, false>(fa, fp, st);
+    return fe::launch_fused<16, false, false>(fa, fp, st);
 }
 
 int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, float* out, void* save,
@@ -638,8 +643,17 @@ int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
 #ifdef NR_FE_PROBES
         if (const char* e = getenv("NR_FE_DBG")) fp.dbg = atoi(e);      // timing probes: development builds only
 #endif
-        if (H / enc->heads == 20) return fe::launch_fused<20, true>(fa, fp, st);
-        return fe::launch_fused<16, true>(fa, fp, st);
+        if (H / enc->heads == 20) return fe::launch_fused<20, true, false>(fa, fp, st);
+        return fe::launch_fused<16, true, false>(fa, fp, st);
+    }
+    if (enc->kind == NR_ENC_CONV && fused_enabled() && fe::fused_conv_supported(p.SP, H, Q, p.Kp)) {
+        // NAML titles: Conv1d(k=3) passes write the Y tile in shared memory, then fc1 + pooling — one kernel
+        fe::FusedArgs fa{xb, p.R, p.ldx, Dm + 1, wb, p.Kp, w1b, p.HK, y};
+        fe::FusedParams fp{};
+        fp.R = p.R; fp.n = n; fp.S = S; fp.H = H; fp.Q = Q; fp.heads = 4;
+        fp.out = out; fp.mask = enc->mask; fp.b1 = enc->p_b1; fp.w2 = enc->p_w2; fp.b2 = enc->p_b2;
+        fp.E = eb; fp.alpha = alpha; fp.dscale = 1.f;
+        return fe::launch_fused<20, true, true>(fa, fp, st);
     }
     if (pool) {
     } else if (enc->kind == NR_ENC_MHSA) {

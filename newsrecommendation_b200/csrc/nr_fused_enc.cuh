@@ -61,7 +61,10 @@ struct FCfg {
 struct FusedParams {
     int64_t R, n;            // padded rows (n * 32), titles
     int S, H, Q, heads;
-    int G;                   // passes per tile = heads / HG
+    int G;                   // passes per tile: heads / HG (MHSA) or the n chunks of the Conv1d output (CONV)
+    int BN;                  // accumulator columns per pass (MHSA: 4 heads x 3 dk; CONV: H split into G chunks, % 16 == 0)
+    int taps;                // CONV: 3 (A row shifts -1, 0, +1 = Conv1d(k=3, pad=1), NAML.py:27-32); MHSA: 1
+    int Kp;                  // CONV: k pitch of one tap in the packed weights
     int KB;                  // 64-column k blocks of Xb / the packed QKV weights
     int HKB;                 // 64-column blocks of the Y tile = ceil(H / 64)
     int NQ;                  // fc1 accumulator columns = round_up(Q, 16) (weight rows >= Q are zero filled by TMA)
@@ -146,13 +149,14 @@ __device__ __forceinline__ void store_row32_bf16(bf16* dst, const float* v, int 
                                                 tc::pack_bf16(v[8 * j + 4], v[8 * j + 5]), tc::pack_bf16(v[8 * j + 6], v[8 * j + 7]));
 }
 
-template <int DK, bool TRAIN>
+template <int DK, bool TRAIN, bool CONV>
 __global__ void __launch_bounds__(FE_THREADS, 1)
 fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                      const __grid_constant__ CUtensorMap tmW1, const __grid_constant__ CUtensorMap tmY,
                      const FusedParams p) {
     using C = FCfg<DK>;
     constexpr int KF = C::KF, KH = C::KH, NB = C::NB, HG = C::HG, BN = C::BN;
+    const int kpp = p.taps * p.KB;                  // ring stages per pass (CONV: 3 taps x KB k blocks)
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
     uint8_t* ring = smem;
@@ -175,7 +179,7 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
     // computes it (fp32 accumulation order; tests/test_gpu_fullsize.py checks scores bit for bit under batch
     // permutation).
     const int g_rot = (int)blockIdx.x % p.G;
-    constexpr int k_rot = 0, y_rot = 0;
+    constexpr int y_rot = 0;
     if (warp == FE_TMA_WARP && lane == 0) {
         tc::prefetch_tmap(&tmA); tc::prefetch_tmap(&tmB); tc::prefetch_tmap(&tmW1);
         if (TRAIN) tc::prefetch_tmap(&tmY);
@@ -202,13 +206,14 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 const int m0 = tile * TC_BM;
                 for (int gi = 0; gi < p.G; ++gi) {
                     const int g = (gi + g_rot) % p.G;
-                    for (int ki = 0; ki < p.KB; ++ki) {
-                        const int kb = (ki + k_rot) % p.KB;
+                    for (int ki = 0; ki < kpp; ++ki) {
+                        const int tap = ki / p.KB, kb = ki - tap * p.KB;
                         tc::mbar_wait(empty + s, ph ^ 1);
                         uint8_t* sa = ring + (size_t)s * FE_STAGE_BYTES;
-                        tc::mbar_arrive_expect_tx(full + s, FE_A_BYTES + BN * TC_BK * 2);
-                        tc::tma_load_2d(sa, &tmA, full + s, kb * TC_BK, m0);
-                        tc::tma_load_2d(sa + FE_A_BYTES, &tmB, full + s, kb * TC_BK, g * BN);
+                        tc::mbar_arrive_expect_tx(full + s, FE_A_BYTES + (uint32_t)p.BN * TC_BK * 2);
+                        // CONV: tap t reads the rows shifted by t - 1 (zero rows between titles, TMA zero fill off the ends)
+                        tc::tma_load_2d(sa, &tmA, full + s, kb * TC_BK, CONV ? m0 + tap - 1 : m0);
+                        tc::tma_load_2d(sa + FE_A_BYTES, &tmB, full + s, tap * p.Kp + kb * TC_BK, g * p.BN);
                         if (++s == FE_STAGES) { s = 0; ph ^= 1; }
                     }
                 }
@@ -224,7 +229,7 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         }
     } else if (warp == FE_MMA_WARP) {
         // ===== MMA issuer =====
-        const uint32_t idesc_qkv = tc::umma_idesc_bf16(TC_BM, BN, 0, 0);
+        const uint32_t idesc_qkv = tc::umma_idesc_bf16(TC_BM, p.BN, 0, 0);
         const uint32_t idesc_fc1 = tc::umma_idesc_bf16(TC_BM, p.NQ, 0, 0);
         int s = 0; uint32_t ph = 0;
         uint32_t pc = 0;                                // pass counter: accumulator pc & 1, use number pc >> 1
@@ -241,7 +246,7 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                     __syncwarp();
                     continue;
                 }
-                for (int kb = 0; kb < p.KB; ++kb) {
+                for (int kb = 0; kb < kpp; ++kb) {
                     tc::mbar_wait(full + s, ph);
                     tc::tc_fence_after();
                     if (lane == 0) {
@@ -252,7 +257,7 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                         for (int k = 0; k < TC_BK / 16; ++k)
                             tc::umma_bf16(d_tmem, da + 2 * k, db + 2 * k, idesc_qkv, (kb | k) ? 1u : 0u);
                         tc::umma_commit(empty + s);
-                        if (kb == p.KB - 1) {
+                        if (kb == kpp - 1) {
                             // the previous tile's Y tile is still being read by its TMA store: the compute warps start
                             // overwriting it when this pass is signalled
                             if (TRAIN && g == 0 && it > 0) bulk_wait_read0();
@@ -330,7 +335,25 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                 tc::mbar_wait(tfull + acc, (pc >> 1) & 1u);
                 tc::tc_fence_after();
                 const uint32_t t_quad = tmem_base + ((uint32_t)(q * 32) << 16) + acc * 256u;
-                if (TRAIN && !FE_DBG(p, 2)) {
+                if (CONV) {
+                    // Conv1d output chunk (bias already inside the product) -> bf16 -> the swizzled Y tile; thread = row,
+                    // the title's four warps take every fourth 32-column chunk
+                    const int ncols = (H - g * p.BN < p.BN) ? H - g * p.BN : p.BN;
+                    for (int c = 32 * sub; c < ncols; c += 128) {
+                        float v[32];
+                        tc::tmem_ld32(t_quad + (uint32_t)c, v);
+                        tc::tmem_ld_wait();
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (c + 8 * j < ncols) {      // H % 8 == 0
+                                const uint32_t a = ybase + y_off(q * 32 + lane, g * p.BN + c + 8 * j);
+                                asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(tc::pack_bf16(v[8 * j], v[8 * j + 1])),
+                                             "r"(tc::pack_bf16(v[8 * j + 2], v[8 * j + 3])), "r"(tc::pack_bf16(v[8 * j + 4], v[8 * j + 5])),
+                                             "r"(tc::pack_bf16(v[8 * j + 6], v[8 * j + 7])) : "memory");
+                            }
+                    }
+                }
+                if (!CONV && TRAIN && !FE_DBG(p, 2)) {
                     // qkv (bf16, head-major columns g*BN + c) -> HBM: thread = row, 64 contiguous bytes per chunk
                     for (int c = 32 * sub; c < BN; c += 128) {
                         float v[32];
@@ -343,7 +366,7 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
                     const long long t0 = clock64();
                     while (clock64() - t0 < (long long)(p.dbg >> 8) * 256) {}
                 }
-                if (sub < HG && !FE_DBG(p, 1)) {
+                if (!CONV && sub < HG && !FE_DBG(p, 1)) {
                     const int head = g * HG + sub;
                     const uint32_t cb = (uint32_t)(sub * 3 * DK);
                     uint32_t rq[2][4 * NB], rk[2][4 * NB], rv[2][4 * NB];
@@ -579,7 +602,7 @@ fused_enc_fwd_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 // host side ------------------------------------------------------------------------------------------------------
 struct FusedArgs {
     const bf16* xb; int64_t R; int ldx; int Kx;      // staged rows (R x ldx), Kx = Dm + 1 real columns
-    const bf16* wb; int Kp;                         // packed head-major QKV weights (3H x Kp)
+    const bf16* wb; int Kp;                         // MHSA: packed head-major QKV weights (3H x Kp); CONV: (H x 3 Kp), tap-major
     const bf16* w1b; int HK;                        // packed W1 (Q x HK)
     bf16* y;                                        // (R x H) training save, NULL in inference
 };
@@ -590,18 +613,35 @@ inline bool fused_supported(int SP, int dk, int heads, int H, int Q, int Kp) {
     if (H % 16 || H > 448 || Q % 8 || Q > 240 || Q < 8) return false;
     return Kp % 64 == 0;
 }
+inline bool fused_conv_supported(int SP, int H, int Q, int Kp) {
+    return SP == 32 && H % 16 == 0 && H >= 16 && H <= 448 && Q % 8 == 0 && Q >= 8 && Q <= 240 && Kp % 64 == 0;
+}
 
-template <int DK, bool TRAIN>
+template <int DK, bool TRAIN, bool CONV>
 int launch_fused(const FusedArgs& a, FusedParams p, cudaStream_t st) {
     using C = FCfg<DK>;
-    p.G = p.heads / C::HG;
+    if (CONV) {
+        const int n16 = (p.H + 15) / 16 * 16;
+        p.G = (n16 + 239) / 240;
+        p.BN = ((n16 + p.G - 1) / p.G + 15) / 16 * 16;
+        p.taps = 3;
+    } else {
+        p.G = p.heads / C::HG;
+        p.BN = C::BN;
+        p.taps = 1;
+    }
+    p.Kp = a.Kp;
     p.KB = a.Kp / 64;
     p.HKB = (p.H + 63) / 64;
     p.NQ = (p.Q + 15) / 16 * 16;
     p.tiles = (int)((a.R + TC_BM - 1) / TC_BM);
     CUtensorMap tmA, tmB, tmW1, tmY;
     if (int e = make_tmap_bf16_2d(&tmA, a.xb, (uint64_t)a.R, (uint64_t)a.Kx, (uint64_t)a.ldx, TC_BM, TC_BK)) return e;
-    if (int e = make_tmap_bf16_2d(&tmB, a.wb, (uint64_t)3 * p.H, (uint64_t)a.Kp, (uint64_t)a.Kp, (uint32_t)C::BN, TC_BK)) return e;
+    if (CONV) {
+        if (int e = make_tmap_bf16_2d(&tmB, a.wb, (uint64_t)p.H, (uint64_t)3 * a.Kp, (uint64_t)3 * a.Kp, (uint32_t)p.BN, TC_BK)) return e;
+    } else {
+        if (int e = make_tmap_bf16_2d(&tmB, a.wb, (uint64_t)3 * p.H, (uint64_t)a.Kp, (uint64_t)a.Kp, (uint32_t)p.BN, TC_BK)) return e;
+    }
     if (int e = make_tmap_bf16_2d(&tmW1, a.w1b, (uint64_t)p.Q, (uint64_t)a.HK, (uint64_t)a.HK, (uint32_t)p.NQ, TC_BK)) return e;
     if (TRAIN) {
         if (int e = make_tmap_bf16_2d(&tmY, a.y, (uint64_t)a.R, (uint64_t)p.H, (uint64_t)p.H, TC_BM, TC_BK)) return e;
@@ -610,7 +650,7 @@ int launch_fused(const FusedArgs& a, FusedParams p, cudaStream_t st) {
     }
     const size_t smem = fused_smem_bytes(p.HKB);
     NR_REQUIRE(smem <= 227 * 1024, "fused title encoder: %zu bytes of shared memory do not fit", smem);
-    auto kern = fused_enc_fwd_kernel<DK, TRAIN>;
+    auto kern = fused_enc_fwd_kernel<DK, TRAIN, CONV>;
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int grid = sm_count();
     if (grid > p.tiles) grid = p.tiles;

@@ -107,3 +107,47 @@ def test_fused_training_vs_separate_launches(tag, drop, fused_training):
         lo, so = O.nrms_forward(hist, mask, cand, label, P, 20, kw['user_log_mask'])
         assert abs(l_f - lo.item()) <= 1e-2 * abs(lo.item())
         np.testing.assert_allclose(s_f, so.numpy(), rtol=1e-2, atol=1e-2 * float(so.abs().max()))
+
+
+@pytest.mark.parametrize('tag', ['naml_ulm0_c00', 'naml_ulm0_c11'])
+def test_fused_conv_encoder_vs_oracle_and_separate_launches(tag):
+    """NAML title path (gather -> Conv1d(k=3) -> AttentionPooling, NAML.py:47-56) through the fused kernel's CONV mode:
+    inference and training variants vs the oracle and vs the separate conv / fc1 / pooling launches, incl. gradients."""
+    kind, kw, Pn, bt, model = build_model(tag, precision='bf16')
+    rs = np.random.RandomState(3)
+    N = kw['N']
+    F = 1 + int(kw['use_cat']) + int(kw['use_sub'])
+    x = np.zeros((N + 1, F), np.int32)
+    x[:, 0] = np.arange(N + 1)
+    if kw['use_cat']:
+        x[1:, 1] = rs.randint(1, synth.NCAT + 1, size=N)
+    if kw['use_sub']:
+        x[1:, F - 1] = rs.randint(1, synth.NSUB + 1, size=N)
+    xd = T(x).cuda()
+    P = {k: T(v) for k, v in Pn.items()}
+    v_or = O.naml_news_encoder(T(x), P, kw['L'], synth.D, kw['use_cat'], kw['use_sub']).numpy()
+    scale = float(np.abs(v_or).max())
+    model.eval()
+    with torch.no_grad():
+        v_inf = model.news_encoder(xd)
+    os.environ['NR_ENC_FUSED'] = '0'
+    try:
+        v_sep = model.news_encoder(xd).detach()
+    finally:
+        del os.environ['NR_ENC_FUSED']
+    np.testing.assert_allclose(v_inf.cpu().numpy(), v_or, rtol=1e-2, atol=1e-2 * scale)
+    np.testing.assert_allclose(v_inf.cpu().numpy(), v_sep.cpu().numpy(), rtol=2e-3, atol=2e-3 * scale)
+    # training variant: whole model step, fused vs separate launches
+    model.train()
+    l_f, s_f, g_f = _run(model, bt, seed=7)
+    os.environ['NR_ENC_FUSED'] = '0'
+    try:
+        l_s, s_s, g_s = _run(model, bt, seed=7)
+    finally:
+        del os.environ['NR_ENC_FUSED']
+    assert abs(l_f - l_s) <= 2e-3 * abs(l_s)
+    np.testing.assert_allclose(s_f, s_s, rtol=0, atol=3e-3 * float(np.abs(s_s).max()))
+    gmax = max(float(np.abs(g).max()) for g in g_s.values())
+    for k in g_s:
+        m = float(np.abs(g_s[k]).max())
+        np.testing.assert_allclose(g_f[k], g_s[k], rtol=0, atol=2e-2 * m + 1e-5 * gmax, err_msg=k)
