@@ -44,13 +44,21 @@ stage_rows_kernel(RowsView x, bf16* __restrict__ xb, int R, int SP, int ldx, uin
         if (s < x.S) {
             const int64_t r = (int64_t)seq * x.S + s;
             const float* src;
+            bool pad_token = false;
             if (x.mode == NR_ROWS_DENSE) src = x.dense + r * x.D;
-            else if (x.mode == NR_ROWS_TOKEN) src = x.table + x.id_of(seq, s) * x.D;
+            else if (x.mode == NR_ROWS_TOKEN) { const int64_t id = x.id_of(seq, s); pad_token = id == 0; src = x.table + id * x.D; }
             else src = x.table + x.id_of(seq, s) * ((int64_t)x.S * x.D) + (int64_t)s * x.D;
             float4 a = make_float4(0.f, 0.f, 0.f, 0.f), b = a;
             if (c < x.D) a = ldg4(src + c);
             if (c + 4 < x.D) b = ldg4(src + c + 4);
-            if (x.thr) {
+            // Pad tokens (id 0 = padding_idx: 62 % of MIND title positions): their embedding row is zero, dropout(0) = 0
+            // whatever the mask, and their gradient is dropped (NRMS.py:73), so the Philox draw is skipped when the
+            // loaded values really are all zero (a non-zero row 0 takes the ordinary path).
+            const bool skip_draw = pad_token && a.x == 0.f && a.y == 0.f && a.z == 0.f && a.w == 0.f &&
+                                   b.x == 0.f && b.y == 0.f && b.z == 0.f && b.w == 0.f;
+            if (x.thr && skip_draw) {
+                if (keep_in) keep_in[(int64_t)row * (ldx >> 3) + threadIdx.x] = 0;
+            } else if (x.thr) {
                 // the 8 keep bits of this thread's columns are saved (1 byte, padded-row indexing) so that the
                 // enc.dx epilogue re-applies the mask from a 4-byte load instead of eight Philox calls per chunk
                 // this thread's 8 columns are exactly one 8-element group of the input stream: ONE Philox call
