@@ -75,16 +75,38 @@ class UserEncoder(nn.Module):
         return self.attn(self.multi_head_self_attn(v))
 
 
+    SHORT = 31          # longest history the fused title-encoder kernel takes (one 32-row TMEM quadrant)
+
     def forward_gathered(self, table, idx, log_mask):
         """Eval (src/dataset.py:67-68 + main.py:247): user vectors straight from the cached news-vector table and the
         padded click indices — the (b,50,400) fp32 gather of the reference is never materialised, the staging kernel
         of the encoder reads the table rows itself.  Returns None when this mode needs the materialised rows
-        (pad_doc blend, fp32 parity mode): the caller then gathers and calls forward()."""
+        (pad_doc blend, fp32 parity mode): the caller then gathers and calls forward().
+
+        With `user_log_mask=True` a masked slot contributes nothing as a key (model_utils.py:50-51) and is dropped as a
+        query by the masked pooling (:26-27), and histories are FRONT padded (dataset.py:17-24): a history with at most
+        31 real clicks is therefore exactly a 31-slot sequence (its last 31 slots).  Those — two thirds of MIND-shaped
+        histories — go through the fused inference kernel (one launch after the staging), the longer ones through the
+        separate launches over all 50 slots."""
         if self.prec != L.PREC_BF16 or not self.args.user_log_mask:
             return None
         m = self.multi_head_self_attn
-        return ops.title_encoder(L.ENC_MHSA, table, idx, log_mask, m._w(), self.attn._p(), mode=L.ROWS_TOKEN,
-                                 S=idx.shape[1], Dm=m.d_model, heads=m.n_heads)
+        T = idx.shape[1]
+
+        def run(ids, mask):
+            return ops.title_encoder(L.ENC_MHSA, table, ids, mask, m._w(), self.attn._p(), mode=L.ROWS_TOKEN,
+                                     S=ids.shape[1], Dm=m.d_model, heads=m.n_heads)
+        if T <= self.SHORT or self.SHORT <= 0 or torch.is_grad_enabled():
+            return run(idx, log_mask)
+        short = log_mask[:, :T - self.SHORT].sum(1) == 0          # nothing real before the last 31 slots
+        si = short.nonzero(as_tuple=True)[0]
+        li = (~short).nonzero(as_tuple=True)[0]
+        out = torch.empty(idx.shape[0], table.shape[1], dtype=torch.float32, device=table.device)
+        if si.numel():
+            out[si] = run(idx[si][:, T - self.SHORT:].contiguous(), log_mask[si][:, T - self.SHORT:].contiguous())
+        if li.numel():
+            out[li] = run(idx[li].contiguous(), log_mask[li].contiguous())
+        return out
 
 
 class Model(nn.Module):

@@ -194,3 +194,32 @@ def test_eval_pipeline_bf16_vs_oracle(tag):
     sel = valid_o & (gap > 2.0 * err + 1e-7)
     assert sel.sum() >= 20, int(sel.sum())
     np.testing.assert_allclose(md[sel], mets_o[sel], rtol=0, atol=1e-12)
+
+
+def test_short_histories_through_fused_kernel_equal_the_full_route():
+    """user_log_mask=True: a front-padded history with <= 31 real clicks scored as a 31-slot sequence by the fused
+    inference kernel == the same history through the separate launches over all 50 slots (masked keys contribute
+    nothing, masked queries are dropped by the masked pooling; model_utils.py:26-27,50-51, dataset.py:17-24)."""
+    kind, kw, Pn, bt, model = build_model('nrms_ulm1', precision='bf16')
+    model.eval()
+    rs = np.random.RandomState(12)
+    N, I, Tn = 500, 700, 50
+    table = T((rs.standard_normal((N + 1, 400)) * 0.2).astype(np.float32)).cuda()
+    hist = np.zeros((I, Tn), np.int32); hmask = np.zeros((I, Tn), np.float32)
+    lens = rs.randint(0, 51, size=I); lens[:4] = (0, 1, 31, 32)
+    for i in range(I):
+        hist[i], hmask[i] = O.pad_history(rs.randint(1, N + 1, size=int(lens[i])).tolist(), Tn)
+    ue = model.user_encoder
+    with torch.no_grad():
+        mixed = ue.forward_gathered(table, T(hist).cuda(), T(hmask).cuda())              # short -> fused, long -> separate
+        old = ue.SHORT
+        try:
+            ue.SHORT = 0                                                                  # everything over all 50 slots
+            full = ue.forward_gathered(table, T(hist).cuda(), T(hmask).cuda())
+        finally:
+            ue.SHORT = old
+    assert (mixed[0] == 0).all() and (full[0] == 0).all()                                 # empty history -> exact zero (B1)
+    scale = float(full.abs().max())
+    close(mixed, full, rtol=0, atol=4e-3 * scale)
+    long_rows = torch.from_numpy(lens > 31).cuda()
+    close(mixed[long_rows], full[long_rows], rtol=0, atol=1e-5 * scale)                   # same route (batch size picks the pooling-tail variant)
