@@ -130,6 +130,8 @@ def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20, fu
     else:
         f['enc.conv'] = f['enc.dwconv'] = 2.0 * M * 3 * D * H
         f['enc.fc1'] = f['enc.pool_dx'] = f['enc.dw1'] = 2.0 * M * H * Q
+        if fused:       # titles: Conv1d passes + fc1 + pooling in one kernel (CONV mode of the fused encoder)
+            f['enc.fused_fwd'] = 2.0 * M * 3 * D * H + 2.0 * M * H * Q + 2.0 * M * H
     return f
 
 
@@ -154,6 +156,9 @@ def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, fused=True):
         b['enc.conv'] = M * (D + 1) * 2 + M * H * 2
         b['enc.dwconv'] = M * H * 2 + M * (D + 1) * 2
         b['enc.dx'] = M * H * 2 + M * D * 4
+    if model == 'NAML' and fused:
+        # fused forward over the M title tokens: Xb in; Y, E (bf16), alpha and the (n, H) vectors out
+        b['enc.fused_fwd'] = M * ((D + 1) * 2 + H * 2 + Q * 2 + 4) + (M // L) * H * 4
     if model == 'NRMS' and fused:
         # fused forward over the M title tokens: Xb in; qkv, Y, E (bf16), alpha, keep bits and the (n, H) vectors out
         b['enc.fused_fwd'] = M * ((D + 1) * 2 + 3 * H * 2 + H * 2 + Q * 2 + 4) + M * H // 4 + (M // L) * H * 4
