@@ -122,7 +122,8 @@ def _embedding_table(data_dir, args, field='title'):
         return np.load(os.path.join(data_dir, 'word_embeddings.npy'))
     table = mind_io.read_news_embeddings(data_dir, field=field)
     raw = os.path.join(data_dir, mind_io.TITLE_TABLE_RAW.replace('title_', field + '_'))
-    if args.precision == 'fp32' and mind_io.raw_table_dtype(raw) == 'bf16' and not isinstance(table, np.memmap):
+    if (args.precision == 'fp32' and mind_io.news_embeddings_source(data_dir, field) == 'raw'
+            and mind_io.raw_table_dtype(raw) == 'bf16'):      # only when the bf16 file is the one actually read
         logging.warning(f'{raw} holds a bf16 payload: --precision fp32 will not match a run on the fp32 table')
     want = (args.num_words_title if field == 'title' else args.num_words_abstract) * args.word_embedding_dim
     if table.shape[1] != want:

@@ -152,13 +152,23 @@ def raw_table_dtype(path):
     return {v: k for k, v in TABLE_DTYPES.items()}.get(code)
 
 
+def news_embeddings_source(data_dir, field='title'):
+    """Which file read_news_embeddings takes: 'raw' (the memory-mappable table, when at least as new as the .npy.gz)
+    or 'gz'."""
+    gz = os.path.join(data_dir, TITLE_TABLE_GZ.replace('title_', field + '_'))
+    raw = os.path.join(data_dir, TITLE_TABLE_RAW.replace('title_', field + '_'))
+    if os.path.exists(raw) and (not os.path.exists(gz) or os.path.getmtime(raw) >= os.path.getmtime(gz)):
+        return 'raw'
+    return 'gz'
+
+
 def read_news_embeddings(data_dir, cache=False, field='title', cache_dtype='fp32'):
     """preprocess.py:227-232.  Prefers the raw table next to the .npy.gz when it is at least as new;
     `cache=True` writes it (as `cache_dtype`) after a gzip read so the next start-up skips the gunzip.  `field='abstract'` reads the
     second table of the abstract view (same format, `abstract_embeddings.bpemb.*`)."""
     gz = os.path.join(data_dir, TITLE_TABLE_GZ.replace('title_', field + '_'))
     raw = os.path.join(data_dir, TITLE_TABLE_RAW.replace('title_', field + '_'))
-    if os.path.exists(raw) and (not os.path.exists(gz) or os.path.getmtime(raw) >= os.path.getmtime(gz)):
+    if news_embeddings_source(data_dir, field) == 'raw':
         return read_title_table(raw)
     with gzip.GzipFile(gz, 'r') as f:
         table = np.load(f)
