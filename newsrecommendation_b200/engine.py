@@ -193,6 +193,8 @@ class FlatAdam:
         self.step_count += 1
         L.call('nr_adam_step', L.ptr(self.flat_p), L.ptr(self.flat_g), L.ptr(self.m), L.ptr(self.v), self.count,
                self.lr, self.betas[0], self.betas[1], self.eps, self.step_count, scale, L.stream())
+        # keep the device-resident count (read by graph-replayed updates) in step with eager updates
+        L.call('nr_seed_salt_bump', L.ptr(self.step_dev), L.stream())
 
 
 def train_step(model, opt, history, history_mask, candidate, label):

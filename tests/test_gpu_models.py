@@ -320,3 +320,33 @@ def test_masked_slots_and_batch_composition_do_not_matter(prec):
             tol = 2e-6 if prec == 'fp32' else 1e-2
             torch.testing.assert_close(both[:n_c], cv, rtol=tol, atol=tol * float(cv.abs().max()))
             torch.testing.assert_close(both[n_c:], nv.reshape(-1, nv.shape[-1]), rtol=tol, atol=tol * float(nv.abs().max()))
+
+
+def test_graph_replays_and_eager_steps_share_the_adam_step_count():
+    """A ragged last batch goes through engine.train_step between graph replays (no drop_last, main.py:92): the update
+    inside the graph reads Adam's step count from device memory, the eager update from the host — both must advance
+    the same count.  Adam's bias correction makes the FIRST steps sensitive to t (1 / (1 - 0.9^t)), so a count that is
+    off by one moves every weight by a visibly different amount."""
+    from newsrecommendation_b200 import engine
+    kind, kw, Pn, bt, model = build_model('nrms_ulm0')
+    model.train()
+    opt = engine.FlatAdam(model, lr=3e-4)
+    batch = [T(a).cuda() for a in bt]
+    ragged = [t[:2].contiguous() for t in batch]
+    step = engine.GraphedTrainStep(model, opt, batch)
+    step(*batch)                                   # t = 1 (graph)
+    engine.train_step(model, opt, *ragged)         # t = 2 (eager)
+    step(*batch)                                   # t = 3 (graph)
+    step.close()
+    torch.cuda.synchronize()
+    assert int(opt.step_dev.item()) == 3 and opt.step_count == 3
+    # reference: the same three steps all eager
+    kind, kw, Pn, bt, ref = build_model('nrms_ulm0')
+    ref.train()
+    ropt = engine.FlatAdam(ref, lr=3e-4)
+    for b in (batch, ragged, batch):
+        engine.train_step(ref, ropt, *b)
+    torch.cuda.synchronize()
+    a, b = opt.flat_p.cpu().numpy(), ropt.flat_p.cpu().numpy()
+    d = np.abs(a - b)
+    assert (d > 2e-5).mean() < 0.02 and d.max() <= 3 * 3e-4 + 1e-6, (float((d > 2e-5).mean()), float(d.max()))
