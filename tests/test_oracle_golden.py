@@ -129,3 +129,39 @@ def test_pad_history():
     assert idx.tolist() == [0, 0, 5, 6, 7] and m.tolist() == [0, 0, 1, 1, 1]
     idx, m = O.pad_history(list(range(1, 9)), 5)
     assert idx.tolist() == [4, 5, 6, 7, 8] and m.tolist() == [1] * 5
+
+
+def test_oracle_ref_recipe_is_the_unmodified_reference():
+    """oracle/make_ref.py: the files under oracle/_ref (what bench.py times as the CPU baseline, `kind: "reference"`) are
+    byte-identical copies of the reference's modules (checked against /root/reference when it is present, against the
+    recipe's own manifest otherwise), and the loaded modules agree with the oracle port on a golden case."""
+    import hashlib
+    import json
+    import os
+    from oracle import make_ref
+    if not make_ref.available():
+        if not os.path.isdir(make_ref.REF_SRC):
+            pytest.skip('oracle/_ref absent and /root/reference not present')
+        assert make_ref.make(verbose=False)
+    man = json.load(open(os.path.join(make_ref.OUT, 'MANIFEST.json')))['sha256']
+    for rel in make_ref.FILES:
+        h = hashlib.sha256(open(os.path.join(make_ref.OUT, rel), 'rb').read()).hexdigest()
+        assert h == man[rel], rel
+        src = os.path.join(make_ref.REF_SRC, rel)
+        if os.path.exists(src):
+            assert h == hashlib.sha256(open(src, 'rb').read()).hexdigest(), rel
+    NRMS, NAML, M = make_ref.load()
+    import argparse
+    kind, kw, P, bt = synth.case_inputs('nrms_ulm1')
+    a = argparse.Namespace(drop_rate=0.0, news_dim=400, num_attention_heads=20, word_embedding_dim=300,
+                           news_query_vector_dim=200, user_query_vector_dim=200, user_log_mask=True, user_log_length=50,
+                           num_words_title=kw['L'], npratio=4, freeze_embedding=False)
+    m = NRMS.Model(a, P['news_encoder.embedding_matrix.weight'])
+    m.load_state_dict({k: torch.from_numpy(v) for k, v in P.items()})
+    m.eval()
+    hist, mask, cand, label = [torch.from_numpy(x) for x in bt]
+    with torch.no_grad():
+        loss, score = m(hist, mask, cand, label)
+    lo, so = O.nrms_forward(hist, mask, cand, label, {k: torch.from_numpy(v) for k, v in P.items()}, 20, True)
+    np.testing.assert_allclose(score.numpy(), so.numpy(), rtol=1e-5, atol=5e-6)
+    np.testing.assert_allclose(loss.item(), lo.item(), rtol=1e-5)
