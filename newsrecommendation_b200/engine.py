@@ -225,7 +225,7 @@ class GraphedTrainStep:
     def __init__(self, model, opt, example_batch, warmup=2):
         self.model, self.opt = model, opt
         # the update joins the graph when it has no host-side state: single GPU, or the symmetric-memory exchange
-        self.tail_in_graph = bool(getattr(opt, 'capturable', False)) and os.environ.get('NR_GRAPH_TAIL', '1') != '0'
+        self.tail_in_graph = bool(getattr(opt, 'capturable', False))
         self.static = [t.clone() for t in example_batch]
         dev = self.static[0].device
         if GraphedTrainStep._live is not None:
