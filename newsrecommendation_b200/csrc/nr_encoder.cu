@@ -136,45 +136,108 @@ struct EpiPoolDx {
 
 // dX of the encoder input: input-dropout mask re-applied, then either a dense fp32 store (n,S,Dm) or a
 // scatter-add into the embedding-table gradient (id 0 = padding_idx skipped; NRMS.py:73, B7).
+// A thread owns one row of the accumulator, so a direct scatter would issue 32 separate 16-byte reductions per warp
+// instruction (32 LSU wavefronts, half-filled sectors).  Each 32-column chunk is transposed through the warp's
+// staging tile instead: one instruction then covers 4 rows x 128 contiguous bytes.
 struct EpiDx {
+    static constexpr int kRowPitch = 36;                                 // floats: conflict-free 16-byte accesses both ways
+    static constexpr int kStagePerWarp = 32 * kRowPitch * 4 + 32 * 8;    // [32][36] fp32 + the 32 row pointers
     float* dx_dense; float* dtable; RowsView x; int SP;
     const uint8_t* keep_in; int kpitch;     // input-dropout keep bits saved by enc.stage: 1 byte per 8 columns
     int64_t seq; int s; int64_t id;
+    const int32_t* rowlist;                 // row-gather mode: output row i is padded row rowlist[i] (dx_rowlist_kernel)
     __device__ __forceinline__ void begin(const EpiCtx& cx, int64_t row) {
+        if (rowlist) row = cx.live ? (int64_t)__ldg(rowlist + row) : 0;
         seq = row / SP; s = (int)(row - seq * SP);
         id = -1;
         if (!cx.live) s = x.S;          // rows past the end behave like pad rows
         if (s < x.S && x.mode != NR_ROWS_DENSE) id = x.id_of(seq, s);
+        float* dst = nullptr;           // where this lane's row goes (NULL: pad slot, pad token or past the end)
+        if (s < x.S && !(x.mode != NR_ROWS_DENSE && id == 0)) {
+            const int64_t r = seq * x.S + s;
+            dst = x.mode == NR_ROWS_DENSE ? dx_dense + r * x.D
+                : (x.mode == NR_ROWS_TOKEN ? dtable + id * x.D : dtable + id * ((int64_t)x.S * x.D) + (int64_t)s * x.D);
+        }
+        __syncwarp();
+        ((float**)((float*)cx.stage + 32 * kRowPitch))[cx.lane] = dst;
+        __syncwarp();
     }
     __device__ __forceinline__ void end(const EpiCtx&, int64_t) {}
-    __device__ __forceinline__ void chunk(const EpiCtx&, int64_t, int col0, const float* v, int nc) {
-        if (s >= x.S) return;
-        if (x.mode != NR_ROWS_DENSE && id == 0) return;
+    __device__ __forceinline__ void chunk(const EpiCtx& cx, int64_t, int col0, const float* v, int nc) {
+        float* tile = (float*)cx.stage;
+        float* const* rowp = (float* const*)(tile + 32 * kRowPitch);
         const int64_t r = seq * x.S + s;
-        float* dst = (x.mode == NR_ROWS_DENSE ? dx_dense + r * x.D
-                   : (x.mode == NR_ROWS_TOKEN ? dtable + id * x.D : dtable + id * ((int64_t)x.S * x.D) + (int64_t)s * x.D))
-                     + col0;
-        const uint64_t e0 = in_stream_index(r, col0, x.D);
         uint32_t kb = 0xFFFFFFFFu;
-        if (x.thr && keep_in) {        // col0 is a multiple of 16 (BN % 16 == 0): 2-byte aligned, not always 4
+        const bool mine = s < x.S && !(x.mode != NR_ROWS_DENSE && id == 0);
+        if (mine && x.thr && keep_in) {        // col0 is a multiple of 16 (BN % 16 == 0): 2-byte aligned, not always 4
             const uint16_t* kp = (const uint16_t*)(keep_in + (seq * SP + s) * kpitch + (col0 >> 3));
             kb = (uint32_t)__ldg(kp);
             if (nc > 16) kb |= (uint32_t)__ldg(kp + 1) << 16;
         }
+        float4* srow = (float4*)(tile + cx.lane * kRowPitch);
 #pragma unroll
         for (int j = 0; j < 8; ++j) {      // nc % 4 == 0 (Dm % 4 == 0)
-            if (4 * j < nc) {
-                float4 t = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                if (x.thr) {
-                    if (keep_in) t = apply_keep4(t, (kb >> (4 * j)) & 0xFu, x.scale);
-                    else t = dropout4(t, e0 + 4 * j, x.seed, NR_STREAM_IN, x.thr, x.scale);
-                }
-                if (x.mode == NR_ROWS_DENSE) *(float4*)(dst + 4 * j) = t;
-                else atomicAdd((float4*)(dst + 4 * j), t);
+            float4 t = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+            if (mine && x.thr && 4 * j < nc) {
+                if (keep_in) t = apply_keep4(t, (kb >> (4 * j)) & 0xFu, x.scale);
+                else t = dropout4(t, in_stream_index(r, col0, x.D) + 4 * j, x.seed, NR_STREAM_IN, x.thr, x.scale);
+            }
+            srow[j] = t;
+        }
+        __syncwarp();
+        const int c = (cx.lane & 7) * 4;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int rr = (cx.lane >> 3) + 4 * j;
+            float* dst = rowp[rr];
+            if (dst && c < nc) {
+                const float4 t = *(const float4*)(tile + rr * kRowPitch + c);
+                if (x.mode == NR_ROWS_DENSE) *(float4*)(dst + col0 + c) = t;
+                else atomicAdd((float4*)(dst + col0 + c), t);
             }
         }
+        __syncwarp();
     }
 };
+
+// Rows of the padded (n, SP) row space that carry a real token (s < S and id != padding_idx 0): the only rows whose
+// dX is kept (NRMS.py:73).  62 % of the rows of a MIND step are pad tokens, so enc.dx runs over this list instead of
+// all R rows (gemm_tc row-gather mode).  Order inside the list does not matter: every output row is independent and
+// the scatter into the table gradient is a reduction.  One atomic per block of 1024 rows; *count zeroed by the caller.
+__global__ void __launch_bounds__(1024) dx_rowlist_kernel(const RowsView x, const int SP, const int64_t R,
+                                                          int32_t* __restrict__ list, int32_t* __restrict__ count) {
+    __shared__ int wsum[32];
+    __shared__ int base;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool real = false;
+    if (row < R) {
+        const int64_t seq = row / SP;
+        const int s = (int)(row - seq * SP);
+        real = s < x.S && x.id_of(seq, s) != 0;
+    }
+    const unsigned b = __ballot_sync(0xFFFFFFFFu, real);
+    if (lane == 0) wsum[warp] = __popc(b);
+    __syncthreads();
+    if (warp == 0) {
+        const int c = wsum[lane];
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        wsum[lane] = incl - c;                       // exclusive offset of each warp
+        if (lane == 31) base = incl ? atomicAdd(count, incl) : 0;
+    }
+    __syncthreads();
+    if (real) list[base + wsum[warp] + __popc(b & ((1u << lane) - 1u))] = (int32_t)row;
+}
+// NR_DX_GATHER=0 (read per call) keeps enc.dx on all R rows: the A/B switch of bench.py and tests/test_gpu_fused.py
+static bool dx_gather_enabled() {
+    const char* e = getenv("NR_DX_GATHER");
+    return !(e && e[0] == '0');
+}
 
 // ---- TN epilogues ----------------------------------------------------------------------------------------
 // rows i of [dW_Q; dW_K; dW_V] (3H x Dm); column Dm of the product (ones column of Xb) = bias gradient
@@ -227,7 +290,7 @@ struct Plan {
     // save
     size_t o_wb, o_w1b, o_w1t, o_wt, o_bias, o_keep, o_keep_in, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
     // backward workspace
-    size_t o_dz, o_dy, o_dqkv, ws_bytes;
+    size_t o_dz, o_dy, o_dqkv, o_rowlist, ws_bytes;
 };
 
 Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
@@ -263,6 +326,7 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     p.o_dz = take((size_t)p.R * e->Q * 2);
     p.o_dy = take(pool ? 0 : (size_t)p.R * e->H * 2);
     p.o_dqkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
+    p.o_rowlist = take(e->kind == NR_ENC_MHSA ? 64 + (size_t)p.R * 4 : 0);     // [count, pad to 64 bytes, list of real-token rows]
     p.ws_bytes = o;
     return p;
 }
@@ -767,10 +831,22 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st)) return e;
         // dX (the embedding-table gradient: 15 of the 19 MB of the NRMS gradient bucket) BEFORE the weight gradient:
         // the caller can start exchanging that part of the bucket while enc.dwqkv still runs (gr->dtable_ready)
-        if (want_dx)
-            if (int e = gemm_tc_pick(dqkv, p.R, 3 * H, 3 * H, wt, Dm, p.K3, 1, &one, p.R,
-                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0}, st, "enc.dx"))
+        if (want_dx) {
+            // token rows: only the rows of real tokens (dx_rowlist_kernel); dense / per-title rows keep every row
+            const bool gather = rows->mode == NR_ROWS_TOKEN && p.R <= INT32_MAX && dx_gather_enabled();
+            int32_t* cnt = (int32_t*)(wsb + p.o_rowlist);
+            int32_t* list = cnt + 16;
+            if (gather) {
+                ProfScope ps("enc.dx_rows", st);
+                NR_CUDA(cudaMemsetAsync(cnt, 0, 4, st));
+                dx_rowlist_kernel<<<(unsigned)((p.R + 1023) / 1024), 1024, 0, st>>>(xv, p.SP, p.R, list, cnt);
+                if (int e = check_last("enc.dx_rows")) return e;
+            }
+            if (int e = gemm_tc<EpiDx, 8>(dqkv, p.R, 3 * H, 3 * H, wt, Dm, p.K3, 1, &one, p.R,
+                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0,
+                                      gather ? list : nullptr}, st, "enc.dx", gather ? list : nullptr, gather ? cnt : nullptr))
                 return e;
+        }
         if (gr->dtable_ready) NR_CUDA(cudaEventRecord((cudaEvent_t)gr->dtable_ready, st));
         if (int e = gemm_tc_tn(dqkv, 3 * H, 3 * H, xb, Dm + 1, p.ldx, p.R, 1, &one,
                                TnEpiQkv{gr->dw[0], gr->dw[1], gr->dw[2], gr->db[0], gr->db[1], gr->db[2], H, Dm,
@@ -785,7 +861,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         if (want_dx) {
             const int shx[3] = {1, 0, -1};
             if (int e = gemm_tc_pick(dy, p.R, H, H, wt, Dm, 3 * p.HK, 3, shx, p.R,
-                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0}, st, "enc.dx"))
+                                EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0, nullptr}, st, "enc.dx"))
                 return e;
         }
     }

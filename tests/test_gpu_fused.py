@@ -151,3 +151,36 @@ def test_fused_conv_encoder_vs_oracle_and_separate_launches(tag):
     for k in g_s:
         m = float(np.abs(g_s[k]).max())
         np.testing.assert_allclose(g_f[k], g_s[k], rtol=0, atol=2e-2 * m + 1e-5 * gmax, err_msg=k)
+
+
+@pytest.mark.parametrize('drop', [0.0, 0.2])
+def test_dx_over_real_token_rows_vs_all_rows(drop):
+    """enc.dx runs over the list of real-token rows (gemm_tc row-gather mode: TMA gather4 loads of the dqkv rows,
+    csrc/nr_tc_gemm.cuh) instead of all padded rows; NR_DX_GATHER=0 (read per call) keeps every row.  Each output
+    row is the same dot product in both modes, so the embedding gradient (NRMS.py:73, padding_idx row stays zero)
+    differs only by the order of the fp32 reductions into the table."""
+    kind, kw, Pn, bt, model = build_model('nrms_ulm0', precision='bf16', drop_rate=drop)
+    model.train()
+    ids = np.concatenate([bt[0].reshape(-1, kw['L']), bt[2].reshape(-1, kw['L'])])
+    assert 0.05 < (ids == 0).mean() < 0.95                    # the case has pad tokens AND real ones
+    old = os.environ.pop('NR_DX_GATHER', None)
+    try:
+        l_g, s_g, g_g = _run(model, bt, seed=7)
+        os.environ['NR_DX_GATHER'] = '0'
+        l_a, s_a, g_a = _run(model, bt, seed=7)
+    finally:
+        os.environ.pop('NR_DX_GATHER', None)
+        if old is not None:
+            os.environ['NR_DX_GATHER'] = old
+    assert l_g == l_a and np.array_equal(s_g, s_a)            # the forward is untouched
+    k = 'news_encoder.embedding_matrix.weight'
+    gmax = float(np.abs(g_a[k]).max())
+    assert gmax > 0 and not g_g[k][0].any() and not g_a[k][0].any()
+    np.testing.assert_allclose(g_g[k], g_a[k], rtol=0, atol=2e-6 * gmax)
+    touched = np.unique(ids[ids != 0])
+    assert np.abs(g_g[k][touched]).sum(1).min() > 0           # every real token received its gradient
+    untouched = np.setdiff1d(np.arange(g_g[k].shape[0]), touched)
+    assert not g_g[k][untouched].any()
+    for name in g_a:                                          # nothing else moves
+        m = float(np.abs(g_a[name]).max())
+        np.testing.assert_allclose(g_g[name], g_a[name], rtol=0, atol=1e-5 * m + 1e-9, err_msg=name)
