@@ -292,6 +292,24 @@ __device__ __forceinline__ void store_tile_bf(bf16* dst, const int (&off)[Cfg<DK
     }
 }
 
+// compact variant: row s of the tile goes to row cm[slot] of a matrix of pitch ld3 that holds real-token rows only
+// (cm < 0: pad token or pad slot, nothing is written)
+template <int DK>
+__device__ __forceinline__ void store_tile_bf_rows(bf16* base, const int (&cm)[Cfg<DK>::SLOTS], int64_t ld3, const bf16* os,
+                                                   const Slots<DK>& sl) {
+#pragma unroll
+    for (int i = 0; i < Cfg<DK>::SLOTS; ++i)
+        if (cm[i] >= 0) *(uint2*)(base + (int64_t)cm[i] * ld3 + sl.c[i]) = *(const uint2*)(os + sl.s[i] * DK + sl.c[i]);
+}
+// per-thread partial column sums of a (32 x 8NT) accumulator: b[nt][e] covers column nt*8 + 2t + e, this lane's 4 rows
+template <int NT>
+__device__ __forceinline__ void add_colsum(float (&b)[NT][2], const float (&c)[2][NT][4]) {
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+        for (int e = 0; e < 2; ++e) b[nt][e] += (c[0][nt][e] + c[0][nt][e + 2]) + (c[1][nt][e] + c[1][nt][e + 2]);
+}
+
 __host__ __device__ constexpr int pitch_of(int DK) { return DK == 32 ? 40 : (DK == 8 ? 8 : 24); }
 __host__ __device__ constexpr size_t fwd_smem_per_warp(int DK) {
     return (size_t)2 * 3 * 32 * pitch_of(DK) * 2 + (size_t)32 * DK * 2;
@@ -407,10 +425,16 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     }
 }
 
-template <int DK, bool MASK>
+// COMPACT: dqkv holds the rows of real tokens only (rowmap: padded row -> compact row or -1; dx_rowlist_kernel), the
+// layout enc.dx and enc.dwqkv then contract over; the bias gradients (column sums over ALL rows, which the ones column
+// of Xb used to deliver through enc.dwqkv) are accumulated here from the fp32 fragments.  The host sizes the grid so
+// that 4 * gridDim.x is a multiple of heads: a warp then sees ONE head and keeps its 6 NT partial sums in registers.
+template <int DK, bool MASK, bool COMPACT = false>
 static __global__ void __launch_bounds__(128)
 attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
-                    bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale, int hs, int ms) {
+                    bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale, int hs, int ms,
+                    const int32_t* __restrict__ rowmap = nullptr, float* __restrict__ dbq = nullptr,
+                    float* __restrict__ dbk = nullptr, float* __restrict__ dbv = nullptr) {
     constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -437,10 +461,20 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         prefetch_tile<DK>(b + 3 * TILE, dctx + (int64_t)sq * 32 * H + hd * DK, sl.g1, sl);
         cp_async_commit();
     };
+    float bq[NT][2], bk2[NT][2], bv[NT][2];        // COMPACT: column sums of dQ, dK, dV over this warp's items
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) bq[nt][0] = bq[nt][1] = bk2[nt][0] = bk2[nt][1] = bv[nt][0] = bv[nt][1] = 0.f;
+    const int my_head = item % heads;
+    const bool any_item = item < items;
     if (item < items) issue(item, 0);
     for (int stage = 0; item < items; item += stride, stage ^= 1) {
         const int64_t seq = item / heads;
         const int head = item - (int)seq * heads;
+        int cm[Cfg<DK>::SLOTS];
+        if (COMPACT) {
+#pragma unroll
+            for (int i = 0; i < Cfg<DK>::SLOTS; ++i) cm[i] = __ldg(rowmap + seq * 32 + sl.s[i]);
+        }
         if ((int64_t)item + stride < items) issue(item + stride, stage ^ 1); else cp_async_commit();
         const bf16* Qs = buf + stage * 4 * TILE;
         const bf16* Ks = Qs + TILE;
@@ -456,7 +490,7 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             }
         cp_async_wait<1>();
         __syncwarp();
-        bf16* dst = dqkv + seq * 32 * 3 * H + head * hs;
+        bf16* dst = COMPACT ? dqkv + head * hs : dqkv + seq * 32 * 3 * H + head * hs;
         // ---- A = P/Z, dA = dO V^T, dS = A (dA - rd); dQ = dS K / sqrt(dk).  The key-major operands
         //      A^T and dS^T of dV = A^T dO and dK = dS^T Q are NOT recomputed (that was a second S^T = K Q^T,
         //      dA^T = V dO^T and exp pass): every 8 x 8 bf16 block of the packed fragments is transposed in
@@ -518,27 +552,51 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             load_b_cols<DK>(Ks, lane, bk);
             float dq[2][NT][4];
             mm_32xn<NT>(dq, ads, bk);
+            if (COMPACT) add_colsum<NT>(bq, dq);
             stage_out_bf<NT, DK>(dq, Os, lane, scale);
         }
         __syncwarp();
-        store_tile_bf<DK>(dst, sl.g3, Os, S, sl);
+        if (COMPACT) store_tile_bf_rows<DK>(dst, cm, 3 * H, Os, sl); else store_tile_bf<DK>(dst, sl.g3, Os, S, sl);
         __syncwarp();
         {
             uint32_t bf[NT][2][2];
             float out[2][NT][4];
             load_b_cols<DK>(Qs, lane, bf);
             mm_32xn<NT>(out, dst_t, bf);                          // dK = dS^T Q / sqrt(dk)
+            if (COMPACT) add_colsum<NT>(bk2, out);
             stage_out_bf<NT, DK>(out, Os, lane, scale);
             __syncwarp();
-            store_tile_bf<DK>(dst + ms, sl.g3, Os, S, sl);
+            if (COMPACT) store_tile_bf_rows<DK>(dst + ms, cm, 3 * H, Os, sl); else store_tile_bf<DK>(dst + ms, sl.g3, Os, S, sl);
             __syncwarp();
             load_b_cols<DK>(Gs, lane, bf);
             mm_32xn<NT>(out, at, bf);                             // dV = A^T dO
+            if (COMPACT) add_colsum<NT>(bv, out);
             stage_out_bf<NT, DK>(out, Os, lane, 1.f);
         }
         __syncwarp();
-        store_tile_bf<DK>(dst + 2 * ms, sl.g3, Os, S, sl);
+        if (COMPACT) store_tile_bf_rows<DK>(dst + 2 * ms, cm, 3 * H, Os, sl); else store_tile_bf<DK>(dst + 2 * ms, sl.g3, Os, S, sl);
         __syncwarp();
+    }
+    if (COMPACT) {
+        // rows 4 lanes apart hold the same columns: fold the 8 row groups, then lanes 0..3 add their 2 NT columns
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                float a = bq[nt][e], b = bk2[nt][e], c = bv[nt][e];
+#pragma unroll
+                for (int o = 4; o < 32; o <<= 1) {
+                    a += __shfl_xor_sync(0xFFFFFFFFu, a, o);
+                    b += __shfl_xor_sync(0xFFFFFFFFu, b, o);
+                    c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
+                }
+                const int col = nt * 8 + 2 * t + e;
+                if (any_item && g == 0 && col < DK) {
+                    if (dbq) atomicAdd(dbq + my_head * DK + col, a * scale);
+                    if (dbk) atomicAdd(dbk + my_head * DK + col, b * scale);
+                    if (dbv) atomicAdd(dbv + my_head * DK + col, c);
+                }
+            }
     }
 }
 

@@ -201,11 +201,14 @@ struct EpiDx {
 };
 
 // Rows of the padded (n, SP) row space that carry a real token (s < S and id != padding_idx 0): the only rows whose
-// dX is kept (NRMS.py:73).  62 % of the rows of a MIND step are pad tokens, so enc.dx runs over this list instead of
-// all R rows (gemm_tc row-gather mode).  Order inside the list does not matter: every output row is independent and
-// the scatter into the table gradient is a reduction.  One atomic per block of 1024 rows; *count zeroed by the caller.
+// dX is kept (NRMS.py:73) and the only ones with a non-zero input row in dW = dqkv^T Xb.  62 % of the rows of a MIND
+// step are pad tokens, so the backward keeps dqkv COMPACT: list[c] = padded row of compact row c, rowmap[row] = c or
+// -1.  A block covers 1024 consecutive rows in order (a title's real rows stay adjacent); blocks land in the order
+// of one atomic each, which does not matter: every output row is independent and the consumers are reductions.
+// *count is zeroed by the caller.
 __global__ void __launch_bounds__(1024) dx_rowlist_kernel(const RowsView x, const int SP, const int64_t R,
-                                                          int32_t* __restrict__ list, int32_t* __restrict__ count) {
+                                                          int32_t* __restrict__ list, int32_t* __restrict__ rowmap,
+                                                          int32_t* __restrict__ count) {
     __shared__ int wsum[32];
     __shared__ int base;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -231,9 +234,18 @@ __global__ void __launch_bounds__(1024) dx_rowlist_kernel(const RowsView x, cons
         if (lane == 31) base = incl ? atomicAdd(count, incl) : 0;
     }
     __syncthreads();
-    if (real) list[base + wsum[warp] + __popc(b & ((1u << lane) - 1u))] = (int32_t)row;
+    const int c = base + wsum[warp] + __popc(b & ((1u << lane) - 1u));
+    if (real) list[c] = (int32_t)row;
+    if (row < R) rowmap[row] = real ? c : -1;
 }
-// NR_DX_GATHER=0 (read per call) keeps enc.dx on all R rows: the A/B switch of bench.py and tests/test_gpu_fused.py
+// rows [count, count + 64) of the compact dqkv are read by the last k chunk of enc.dwqkv: they must be finite zeros
+__global__ void zero_tail_rows_kernel(bf16* __restrict__ a, const int32_t* __restrict__ count, int64_t rows, int ld) {
+    const int64_t r = (int64_t)__ldg(count) + blockIdx.x;
+    if (r >= rows) return;
+    uint4* p = (uint4*)(a + r * ld);
+    for (int i = threadIdx.x; i < ld / 8; i += blockDim.x) p[i] = make_uint4(0u, 0u, 0u, 0u);
+}
+// NR_DX_GATHER=0 (read per call) keeps the backward on all R rows: the A/B switch of bench.py and tests/test_gpu_fused.py
 static bool dx_gather_enabled() {
     const char* e = getenv("NR_DX_GATHER");
     return !(e && e[0] == '0');
@@ -326,7 +338,7 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     p.o_dz = take((size_t)p.R * e->Q * 2);
     p.o_dy = take(pool ? 0 : (size_t)p.R * e->H * 2);
     p.o_dqkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
-    p.o_rowlist = take(e->kind == NR_ENC_MHSA ? 64 + (size_t)p.R * 4 : 0);     // [count, pad to 64 bytes, list of real-token rows]
+    p.o_rowlist = take(e->kind == NR_ENC_MHSA ? 64 + (size_t)p.R * 8 : 0);     // [count, pad to 64 bytes, list (R), rowmap (R)]
     p.ws_bytes = o;
     return p;
 }
@@ -414,11 +426,12 @@ int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n
                                             hm ? 3 * DK : DK, hm ? DK : heads * DK);
     return check_last("enc.attn_fwd");
 }
-template <int DK, bool MASK>
+// rowmap != NULL: compact dqkv rows + bias gradients db[0..2] from the kernel (amma::attn_bwd_mma_kernel COMPACT)
+template <int DK, bool MASK, bool COMPACT = false>
 int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
-                        bool hm, cudaStream_t st) {
+                        bool hm, cudaStream_t st, const int32_t* rowmap = nullptr, float* const* db = nullptr) {
     const size_t smem = 4 * amma::bwd_smem_per_warp(DK);
-    auto kern = amma::attn_bwd_mma_kernel<DK, MASK>;
+    auto kern = amma::attn_bwd_mma_kernel<DK, MASK, COMPACT>;
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // adjacent heads of a title share 32-byte sectors (40-byte head slices of a 2400-byte row), and the four warps of a
     // CTA fetch them at slightly different times: the L1 has to keep them, so the carve-out leaves it room (measured:
@@ -433,9 +446,19 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     if (per_sm < 1) per_sm = 1;
     if (per_sm > cap) per_sm = cap;
     if (grid > (int64_t)sm_count() * per_sm) grid = (int64_t)sm_count() * per_sm;
+    if (COMPACT) {
+        // a warp's items are 4 * grid apart: a multiple of heads keeps every warp on one head (its bias sums stay in
+        // registers); surplus CTAs of a tiny launch simply find no item
+        int g4 = heads, a = 4;
+        while (a) { const int t = g4 % a; g4 = a; a = t; }            // gcd(heads, 4)
+        const int m = heads / g4;
+        grid = grid / m * m;
+        if (grid < m) grid = m;
+    }
     ProfScope ps("enc.attn_bwd", st);
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK),
-                                            hm ? 3 * DK : DK, hm ? DK : heads * DK);
+                                            hm ? 3 * DK : DK, hm ? DK : heads * DK, rowmap, db ? db[0] : nullptr,
+                                            db ? db[1] : nullptr, db ? db[2] : nullptr);
     return check_last("enc.attn_bwd");
 }
 // blocked variant: 32 < pitch <= 64 (the user encoder's 50 clicked titles)
@@ -482,8 +505,10 @@ int launch_attn_bwd_blk(const bf16* qkv, const float* mask, const bf16* dctx, bf
                               : launch_attn_bwd_blk<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, hm, st))
 #define NR_MMA_FWD(DKV) (mask ? launch_attn_fwd_mma<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, hm, st) \
                               : launch_attn_fwd_mma<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, hm, st))
-#define NR_MMA_BWD(DKV) (mask ? launch_attn_bwd_mma<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st) \
-                              : launch_attn_bwd_mma<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, hm, st))
+#define NR_MMA_BWD(DKV) (rowmap ? (mask ? launch_attn_bwd_mma<DKV, true, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st, rowmap, db) \
+                                        : launch_attn_bwd_mma<DKV, false, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st, rowmap, db)) \
+                                : (mask ? launch_attn_bwd_mma<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st) \
+                                        : launch_attn_bwd_mma<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, hm, st)))
 
 #define NR_ENC_DISPATCH_DK(dk, CALL)                                                   \
     switch (dk) {                                                                      \
@@ -517,9 +542,12 @@ int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, 
     }
     NR_ENC_DISPATCH_DK(dk, launch_attn_fwd<DK>(qkv, mask, ctx, n, S, SP, heads, p, seed, keep, st));
 }
+// rowmap (pitch 32 with a warp-MMA head width only, see compact_supported): dqkv rows of real tokens only, db filled here
+static bool compact_supported(int SP, int dk) { return SP == 32 && (dk == 8 || dk == 16 || dk == 20 || dk == 32); }
 int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int SP, int heads,
-               int dk, cudaStream_t st) {
+               int dk, cudaStream_t st, const int32_t* rowmap = nullptr, float* const* db = nullptr) {
     const bool hm = qkv_head_major(SP, dk);
+    NR_REQUIRE(!rowmap || compact_supported(SP, dk), "attention backward: compact rows need pitch 32 and a warp-MMA head width");
     if (SP == 32) {
         switch (dk) {
             case 8: return NR_MMA_BWD(8);
@@ -828,30 +856,37 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
     if (pool) return 0;
     const RowsView xv = make_rows_view(rows, n, S, Dm);
     if (enc->kind == NR_ENC_MHSA) {
-        if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st)) return e;
+        // token rows: dqkv is kept COMPACT (rows of real tokens only; dx_rowlist_kernel).  attn_bwd writes it and sums the
+        // bias gradients itself, enc.dx and enc.dwqkv contract over the compact rows.  Dense / per-title rows keep every row.
+        const bool gather = rows->mode == NR_ROWS_TOKEN && p.R <= INT32_MAX && compact_supported(p.SP, H / enc->heads) &&
+                            dx_gather_enabled();
+        int32_t* cnt = (int32_t*)(wsb + p.o_rowlist);
+        int32_t* list = cnt + 16;
+        int32_t* rowmap = list + p.R;
+        if (gather) {
+            ProfScope ps("enc.dx_rows", st);
+            NR_CUDA(cudaMemsetAsync(cnt, 0, 4, st));
+            dx_rowlist_kernel<<<(unsigned)((p.R + 1023) / 1024), 1024, 0, st>>>(xv, p.SP, p.R, list, rowmap, cnt);
+            zero_tail_rows_kernel<<<TN_BK, 128, 0, st>>>(dqkv, cnt, p.R, 3 * H);
+            if (int e = check_last("enc.dx_rows")) return e;
+        }
+        float* const db[3] = {gr->db[0], gr->db[1], gr->db[2]};
+        if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st, gather ? rowmap : nullptr,
+                               gather ? db : nullptr))
+            return e;
         // dX (the embedding-table gradient: 15 of the 19 MB of the NRMS gradient bucket) BEFORE the weight gradient:
         // the caller can start exchanging that part of the bucket while enc.dwqkv still runs (gr->dtable_ready)
-        if (want_dx) {
-            // token rows: only the rows of real tokens (dx_rowlist_kernel); dense / per-title rows keep every row
-            const bool gather = rows->mode == NR_ROWS_TOKEN && p.R <= INT32_MAX && dx_gather_enabled();
-            int32_t* cnt = (int32_t*)(wsb + p.o_rowlist);
-            int32_t* list = cnt + 16;
-            if (gather) {
-                ProfScope ps("enc.dx_rows", st);
-                NR_CUDA(cudaMemsetAsync(cnt, 0, 4, st));
-                dx_rowlist_kernel<<<(unsigned)((p.R + 1023) / 1024), 1024, 0, st>>>(xv, p.SP, p.R, list, cnt);
-                if (int e = check_last("enc.dx_rows")) return e;
-            }
+        if (want_dx)
             if (int e = gemm_tc<EpiDx, 8>(dqkv, p.R, 3 * H, 3 * H, wt, Dm, p.K3, 1, &one, p.R,
                                 EpiDx{gr->dx_dense, gr->dtable, xv, p.SP, (const uint8_t*)(sv + p.o_keep_in), p.ldx / 8, 0, 0, 0,
-                                      gather ? list : nullptr}, st, "enc.dx", gather ? list : nullptr, gather ? cnt : nullptr))
+                                      gather ? list : nullptr}, st, "enc.dx", gather ? cnt : nullptr))
                 return e;
-        }
         if (gr->dtable_ready) NR_CUDA(cudaEventRecord((cudaEvent_t)gr->dtable_ready, st));
         if (int e = gemm_tc_tn(dqkv, 3 * H, 3 * H, xb, Dm + 1, p.ldx, p.R, 1, &one,
-                               TnEpiQkv{gr->dw[0], gr->dw[1], gr->dw[2], gr->db[0], gr->db[1], gr->db[2], H, Dm,
+                               TnEpiQkv{gr->dw[0], gr->dw[1], gr->dw[2], gather ? nullptr : gr->db[0], gather ? nullptr : gr->db[1],
+                                        gather ? nullptr : gr->db[2], H, Dm,
                                         qkv_head_major(p.SP, H / enc->heads) ? H / enc->heads : 0}, st,
-                               "enc.dwqkv"))
+                               "enc.dwqkv", gather ? list : nullptr, gather ? cnt : nullptr))
             return e;
     } else {
         const int sh[3] = {-1, 0, 1};

@@ -35,16 +35,10 @@ struct TcGemmParams {
     int shift[3];     // A row shift per tap
     int stages;
     int m_tiles, n_tiles;
-    // row-gather mode (GATHER kernels, taps == 1): output row i is A row rowlist[i], i < *m_count <= M.  Four extra
-    // producer warps copy the 128 gathered rows of a stage with 16-byte cp.async into the SWIZZLE_128B layout a TMA
-    // tile load would have produced; B still arrives by TMA.
-    const int32_t* rowlist;
+    // DYNM kernels: the number of rows that exist is read from device memory (*m_count <= M), e.g. the count of
+    // real-token rows of a step; tiles past it are never scheduled
     const int32_t* m_count;
-    const __nv_bfloat16* a_ptr;
-    int64_t lda;
-    int k_real;
 };
-constexpr int TC_GATHER_WARPS = 4;
 
 // per-warp epilogue staging: 32 x TC_STAGE_PITCH bf16 unless the functor asks for more (Epi::kStagePerWarp bytes)
 template <class E, class = void> struct EpiStage { static constexpr int bytes = 32 * TC_STAGE_PITCH * 2; };
@@ -111,8 +105,8 @@ __device__ __forceinline__ void flush_rows_bf16(const EpiCtx& cx, __nv_bfloat16*
 // EW = epilogue warps: 8 (two groups of 4, one per accumulator) or 16 (two groups per accumulator, each draining
 // half of the tile's 32-column chunks; 18 warps -> at most 112 registers per thread).  Functors that carry per-row
 // state across chunks (Epi::kRowState) need the whole row in one thread and stay at EW = 8.
-template <class Epi, int EW, bool GATHER = false>
-__global__ void __launch_bounds__(64 + 32 * EW + (GATHER ? 32 * TC_GATHER_WARPS : 0), 1)   // EW = 8: 10 warps, 3 on one SM sub-partition -> 168 registers is the ceiling
+template <class Epi, int EW, bool DYNM = false>
+__global__ void __launch_bounds__(64 + 32 * EW, 1)   // EW = 8: 10 warps, 3 on one SM sub-partition -> 168 registers is the ceiling
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const TcGemmParams p, const Epi epi_in) {
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -121,8 +115,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int stages = p.stages;
     const uint32_t a_bytes = TC_BM * TC_BK * 2, b_bytes = (uint32_t)p.BN * TC_BK * 2;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int64_t M = GATHER ? (int64_t)__ldg(p.m_count) : p.M;
-    const int total_tiles = (GATHER ? (int)((M + TC_BM - 1) / TC_BM) : p.m_tiles) * p.n_tiles;
+    const int64_t M = DYNM ? (int64_t)__ldg(p.m_count) : p.M;
+    const int total_tiles = (DYNM ? (int)((M + TC_BM - 1) / TC_BM) : p.m_tiles) * p.n_tiles;
     const int kc = p.Kt / TC_BK;
     const int k_iters = p.taps * kc;
     const uint32_t stage_bytes = a_bytes + b_bytes;
@@ -146,8 +140,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 0 && lane == 0) {
         tc::prefetch_tmap(&tmA);
         tc::prefetch_tmap(&tmB);
-        // full: one arrive (+ tx bytes) from the TMA lane; GATHER adds one cp.async-completion arrive per producer thread
-        for (int s = 0; s < stages; ++s) { tc::mbar_init(full + s, GATHER ? 1 + 32 * TC_GATHER_WARPS : 1); tc::mbar_init(empty + s, 1); }
+        for (int s = 0; s < stages; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); }
         for (int a = 0; a < 2; ++a) { tc::mbar_init(tfull + a, 1); tc::mbar_init(tempty + a, EW / 2); }
         tc::fence_barrier_init();
     }
@@ -159,21 +152,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
     if (warp == 0) {
         // ===== TMA producer =====
-        if (GATHER) {
-            if (lane == 0) {            // B only; the A rows come from the cp.async warps below
-                int s = 0; uint32_t ph = 0;
-                int mt, nt;
-                for (int it = 0; tile_of(it, mt, nt); ++it) {
-                    const int n0 = nt * p.BN;
-                    for (int i = 0; i < kc; ++i) {
-                        tc::mbar_wait(empty + s, ph ^ 1);
-                        tc::mbar_arrive_expect_tx(full + s, b_bytes);
-                        tc::tma_load_2d(ring + (size_t)s * stage_bytes + a_bytes, &tmB, full + s, i * TC_BK, n0);
-                        if (++s == stages) { s = 0; ph ^= 1; }
-                    }
-                }
-            }
-        } else if (lane == 0) {
+        if (lane == 0) {
             int s = 0; uint32_t ph = 0;
             int mt, nt;
             for (int it = 0; tile_of(it, mt, nt); ++it) {
@@ -201,7 +180,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const uint32_t d_tmem = tmem_base + (uint32_t)acc * TC_MAX_BN;
             for (int i = 0; i < k_iters; ++i) {
                 tc::mbar_wait(full + s, ph);
-                if (GATHER) tc::fence_proxy_async_smem();        // cp.async wrote A through the generic proxy
                 tc::tc_fence_after();
                 if (lane == 0) {
                     const uint32_t sa = tc::smem_u32(ring + (size_t)s * stage_bytes);
@@ -217,36 +195,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (++s == stages) { s = 0; ph ^= 1; }
             }
             if (++acc == 2) { acc = 0; aph ^= 1; }
-        }
-    } else if (GATHER && warp >= 2 + EW) {
-        // ===== A-row gather producers: warp g copies rows 32g..32g+31 of every stage; lane l moves the 16-byte
-        // chunk (l & 7) of rows 32g + 4j + (l >> 3), j = 0..7 (a warp instruction reads 4 rows x 128 contiguous bytes).
-        // Slots past the end of the list read row 0 (their accumulator rows are never drained); chunks past the real
-        // K extent are zero filled (src-size 0), as the TMA tile load does.
-        const int g = warp - (2 + EW);
-        const int c = lane & 7, r4 = lane >> 3;
-        int s = 0; uint32_t ph = 0;
-        int mt, nt;
-        for (int it = 0; tile_of(it, mt, nt); ++it) {
-            const __nv_bfloat16* src[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const int64_t i = (int64_t)mt * TC_BM + 32 * g + 4 * j + r4;
-                const int64_t rr = i < M ? (int64_t)__ldg(p.rowlist + i) : 0;
-                src[j] = p.a_ptr + rr * p.lda + c * 8;
-            }
-            for (int i = 0; i < kc; ++i) {
-                const uint32_t sa = tc::smem_u32(ring + (size_t)s * stage_bytes);
-                const uint32_t nbytes = (i * TC_BK + c * 8 < p.k_real) ? 16u : 0u;
-                tc::mbar_wait(empty + s, ph ^ 1);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const int row = 32 * g + 4 * j + r4;
-                    tc::cp_async16_zfill(sa + row * 128 + ((c ^ (row & 7)) << 4), src[j] + i * TC_BK, nbytes);
-                }
-                tc::cp_async_mbar_arrive_noinc(full + s);
-                if (++s == stages) { s = 0; ph ^= 1; }
-            }
         }
     } else {
         // ===== epilogue: group g = warps 2+4g .. 5+4g drains accumulator g; warp w may touch TMEM
@@ -326,17 +274,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 template <class Epi, int EW = 8>
 int gemm_tc(const __nv_bfloat16* A, int64_t a_rows, int Kt_real, int64_t lda, const __nv_bfloat16* B, int N,
             int64_t ldb, int taps, const int* shifts, int64_t M, const Epi& epi, cudaStream_t st,
-            const char* what, const int32_t* rowlist = nullptr, const int32_t* m_count = nullptr) {
+            const char* what, const int32_t* m_count = nullptr) {
     if (M == 0 || N == 0) return 0;
-    NR_REQUIRE(!rowlist || (taps == 1 && m_count && (Kt_real & 7) == 0 && a_rows <= INT32_MAX),
-               "%s: row-gather mode needs taps == 1, a count pointer and K %% 8 == 0", what);
     NR_REQUIRE(taps >= 1 && taps <= 3, "%s: taps %d outside [1,3]", what, taps);
     NR_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0, "%s: leading dimensions must be multiples of 8 elements", what);
     NR_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0, "%s: operands must be 16-byte aligned", what);
     TcGemmParams p;
     p.M = M; p.N = N; p.taps = taps;
-    p.rowlist = rowlist; p.m_count = m_count;
-    p.a_ptr = A; p.lda = lda; p.k_real = Kt_real;
+    p.m_count = m_count;
     p.Kt = (Kt_real + TC_BK - 1) / TC_BK * TC_BK;
     for (int t = 0; t < 3; ++t) p.shift[t] = t < taps ? shifts[t] : 0;
     // n tile: the widest multiple of 16 <= 256 that splits N evenly enough
@@ -358,10 +303,10 @@ int gemm_tc(const __nv_bfloat16* A, int64_t a_rows, int Kt_real, int64_t lda, co
     if (int e = make_tmap_bf16_2d(&tmB, B, (uint64_t)N, (uint64_t)taps * p.Kt, (uint64_t)ldb, (uint32_t)p.BN, TC_BK))
         return e;
     const size_t smem = tc_smem_bytes(p.BN, stages, EW * EpiStage<Epi>::bytes);
-    if (rowlist) {
+    if (m_count) {
         NR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<Epi, EW, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         ProfScope ps(what, st);
-        gemm_tc_kernel<Epi, EW, true><<<grid, 64 + 32 * EW + 32 * TC_GATHER_WARPS, smem, st>>>(tmA, tmB, p, epi);
+        gemm_tc_kernel<Epi, EW, true><<<grid, 64 + 32 * EW, smem, st>>>(tmA, tmB, p, epi);
         return check_last(what);
     }
     NR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<Epi, EW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -30,15 +30,30 @@ struct TnParams {
     int shift[3];
     int total_chunks, chunks_per_split;
     int stages;
+    // GATHER kernels (taps == 1, one n tile): A holds *k_count compact rows; compact row r pairs with B row list[r].
+    // Four extra producer warps copy the 64 gathered B rows of a stage with 16-byte cp.async into the MN-major
+    // SWIZZLE_128B boxes a TMA load would have produced (rows past the count are zero filled); A still arrives by TMA.
+    const int32_t* list;
+    const int32_t* k_count;
+    const __nv_bfloat16* b_ptr;
+    int64_t ldb;
 };
+constexpr int TN_GATHER_WARPS = 4;
 
-template <class Epi>
-__global__ void __launch_bounds__(TN_THREADS, 1)
+template <class Epi, bool GATHER = false>
+__global__ void __launch_bounds__(TN_THREADS + (GATHER ? 32 * TN_GATHER_WARPS : 0), 1)
 gemm_tn_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                   const TnParams p, const Epi epi_in) {
-    const int c_begin = blockIdx.y * p.chunks_per_split;
-    int c_end = c_begin + p.chunks_per_split;
-    if (c_end > p.total_chunks) c_end = p.total_chunks;
+    int total_chunks = p.total_chunks, per_split = p.chunks_per_split;
+    int64_t k_rows = 0;
+    if (GATHER) {           // the contraction length is a device-side count: split it evenly over blockIdx.y
+        k_rows = (int64_t)__ldg(p.k_count);
+        total_chunks = (int)((k_rows + TN_BK - 1) / TN_BK);
+        per_split = (total_chunks + (int)gridDim.y - 1) / (int)gridDim.y;
+    }
+    const int c_begin = blockIdx.y * per_split;
+    int c_end = c_begin + per_split;
+    if (c_end > total_chunks) c_end = total_chunks;
     if (c_begin >= c_end) return;
 
     extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -63,7 +78,8 @@ gemm_tn_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
     if (warp == 0 && lane == 0) {
         tc::prefetch_tmap(&tmA);
         tc::prefetch_tmap(&tmB);
-        for (int s = 0; s < stages; ++s) { tc::mbar_init(full + s, 1); tc::mbar_init(empty + s, 1); }
+        // full: one arrive (+ tx bytes) from the TMA lane; GATHER adds one cp.async-completion arrive per producer thread
+        for (int s = 0; s < stages; ++s) { tc::mbar_init(full + s, GATHER ? 1 + 32 * TN_GATHER_WARPS : 1); tc::mbar_init(empty + s, 1); }
         tc::mbar_init(tfull, 1);
         tc::fence_barrier_init();
     }
@@ -80,11 +96,12 @@ gemm_tn_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 const int r = c * TN_BK;
                 tc::mbar_wait(empty + s, ph ^ 1);
                 uint8_t* sa = smem + (size_t)s * stage_bytes;
-                tc::mbar_arrive_expect_tx(full + s, stage_bytes);
+                tc::mbar_arrive_expect_tx(full + s, GATHER ? a_bytes : stage_bytes);
                 tc::tma_load_2d(sa, &tmA, full + s, i0, r);
                 tc::tma_load_2d(sa + TN_BOX_BYTES, &tmA, full + s, i0 + 64, r);
-                for (int b = 0; b < p.nb; ++b)
-                    tc::tma_load_2d(sa + a_bytes + (size_t)b * TN_BOX_BYTES, &tmB, full + s, j0 + 64 * b, r + shift);
+                if (!GATHER)
+                    for (int b = 0; b < p.nb; ++b)
+                        tc::tma_load_2d(sa + a_bytes + (size_t)b * TN_BOX_BYTES, &tmB, full + s, j0 + 64 * b, r + shift);
                 if (++s == stages) { s = 0; ph ^= 1; }
             }
         }
@@ -94,6 +111,7 @@ gemm_tn_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
         int s = 0; uint32_t ph = 0;
         for (int c = c_begin; c < c_end; ++c) {
             tc::mbar_wait(full + s, ph);
+            if (GATHER) tc::fence_proxy_async_smem();        // cp.async wrote B through the generic proxy
             tc::tc_fence_after();
             if (lane == 0) {
                 const uint32_t sa = tc::smem_u32(smem + (size_t)s * stage_bytes);
@@ -110,6 +128,40 @@ gemm_tn_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
                 if (c == c_end - 1) tc::umma_commit(tfull);
             }
             __syncwarp();
+            if (++s == stages) { s = 0; ph ^= 1; }
+        }
+    } else if (GATHER && warp >= 6) {
+        // ===== B-row gather producers: warp g copies k-rows 16g..16g+15 of every stage; lane l moves the 16-byte chunk
+        // (l & 7) of rows 16g + 4j + (l >> 3), j = 0..3, in each of the nb 64-column boxes (a warp instruction reads
+        // 4 rows x 128 contiguous bytes).  The row indices of the next stage are fetched while this one is issued.
+        const int g = warp - 6;
+        const int c = lane & 7, r4 = lane >> 3;
+        const __nv_bfloat16* bcol = p.b_ptr + j0 + c * 8;
+        auto rows_of = [&](int chunk, int32_t (&rr)[4]) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int64_t i = (int64_t)chunk * TN_BK + 16 * g + 4 * j + r4;
+                rr[j] = i < k_rows ? __ldg(p.list + i) : -1;
+            }
+        };
+        int32_t cur[4], nxt[4];
+        rows_of(c_begin, cur);
+        int s = 0; uint32_t ph = 0;
+        for (int ch = c_begin; ch < c_end; ++ch) {
+            if (ch + 1 < c_end) rows_of(ch + 1, nxt);
+            const uint32_t sb = tc::smem_u32(smem + (size_t)s * stage_bytes) + a_bytes;
+            tc::mbar_wait(empty + s, ph ^ 1);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int row = 16 * g + 4 * j + r4;
+                const uint32_t d = sb + row * 128 + ((c ^ (row & 7)) << 4);
+                const __nv_bfloat16* src = bcol + (int64_t)(cur[j] < 0 ? 0 : cur[j]) * p.ldb;
+                const uint32_t nbytes = cur[j] < 0 ? 0u : 16u;
+                for (int b = 0; b < p.nb; ++b) tc::cp_async16_zfill(d + b * TN_BOX_BYTES, src + 64 * b, nbytes);
+            }
+            tc::cp_async_mbar_arrive_noinc(full + s);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) cur[j] = nxt[j];
             if (++s == stages) { s = 0; ph ^= 1; }
         }
     } else {
@@ -138,7 +190,8 @@ gemm_tn_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant
 // A: (rows x Mo) bf16, leading dimension lda; B: (rows x No) bf16, leading dimension ldb.
 template <class Epi>
 int gemm_tc_tn(const __nv_bfloat16* A, int Mo, int64_t lda, const __nv_bfloat16* B, int No, int64_t ldb,
-               int64_t rows, int taps, const int* shifts, const Epi& epi, cudaStream_t st, const char* what) {
+               int64_t rows, int taps, const int* shifts, const Epi& epi, cudaStream_t st, const char* what,
+               const int32_t* list = nullptr, const int32_t* k_count = nullptr) {
     if (rows == 0 || Mo == 0 || No == 0) return 0;
     NR_REQUIRE(taps >= 1 && taps <= 3, "%s: taps %d outside [1,3]", what, taps);
     NR_REQUIRE((lda % 8) == 0 && (ldb % 8) == 0, "%s: leading dimensions must be multiples of 8 elements", what);
@@ -167,10 +220,20 @@ int gemm_tc_tn(const __nv_bfloat16* A, int Mo, int64_t lda, const __nv_bfloat16*
     if (stages > 6) stages = 6;
     NR_REQUIRE(stages >= 2, "%s: tile does not fit shared memory", what);
     p.stages = stages;
+    p.list = list; p.k_count = k_count; p.b_ptr = B; p.ldb = ldb;
+    NR_REQUIRE(!list || (k_count && taps == 1 && p.n_tiles == 1 && ldb >= (int64_t)p.nb * 64),
+               "%s: row-gather mode needs a count pointer, taps == 1, one n tile and ldb >= %d", what, p.nb * 64);
     CUtensorMap tmA, tmB;
     if (int e = make_tmap_bf16_2d(&tmA, A, (uint64_t)rows, (uint64_t)Mo, (uint64_t)lda, TN_BK, 64)) return e;
     if (int e = make_tmap_bf16_2d(&tmB, B, (uint64_t)rows, (uint64_t)No, (uint64_t)ldb, TN_BK, 64)) return e;
     const size_t smem = 1024 + stages * stage_bytes + 256;
+    if (list) {
+        NR_CUDA(cudaFuncSetAttribute(gemm_tn_tc_kernel<Epi, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ProfScope ps(what, st);
+        gemm_tn_tc_kernel<Epi, true><<<dim3((unsigned)tiles, (unsigned)splits), TN_THREADS + 32 * TN_GATHER_WARPS, smem, st>>>(
+            tmA, tmB, p, epi);
+        return check_last(what);
+    }
     NR_CUDA(cudaFuncSetAttribute(gemm_tn_tc_kernel<Epi>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     ProfScope ps(what, st);
     gemm_tn_tc_kernel<Epi><<<dim3((unsigned)tiles, (unsigned)splits), TN_THREADS, smem, st>>>(tmA, tmB, p, epi);

@@ -155,10 +155,13 @@ def test_fused_conv_encoder_vs_oracle_and_separate_launches(tag):
 
 @pytest.mark.parametrize('drop', [0.0, 0.2])
 def test_dx_over_real_token_rows_vs_all_rows(drop):
-    """enc.dx runs over the list of real-token rows (gemm_tc row-gather mode: TMA gather4 loads of the dqkv rows,
-    csrc/nr_tc_gemm.cuh) instead of all padded rows; NR_DX_GATHER=0 (read per call) keeps every row.  Each output
-    row is the same dot product in both modes, so the embedding gradient (NRMS.py:73, padding_idx row stays zero)
-    differs only by the order of the fp32 reductions into the table."""
+    """The title-encoder backward keeps dqkv COMPACT (rows of real tokens only: attn_bwd writes them through a row map,
+    enc.dx and enc.dwqkv contract over them, csrc/nr_encoder.cu); NR_DX_GATHER=0 (read per call) keeps every padded
+    row.  Each dX row is the same dot product in both modes, so the embedding gradient (NRMS.py:73, padding_idx row
+    stays zero) differs only by the order of the fp32 reductions into the table; the W_Q/W_K/W_V weight gradients lose
+    only all-zero input rows.  Their BIAS gradients are summed inside attn_bwd from the fp32 fragments instead of from
+    the bf16-rounded dqkv (the ones column of enc.dwqkv): equal to bf16 rounding (these sums cancel heavily: both routes sit
+    3-4 % of max|g| from the fp32 oracle for W_V.bias, the compact one closer; profiles/r2/bias_check.py)."""
     kind, kw, Pn, bt, model = build_model('nrms_ulm0', precision='bf16', drop_rate=drop)
     model.train()
     ids = np.concatenate([bt[0].reshape(-1, kw['L']), bt[2].reshape(-1, kw['L'])])
@@ -181,6 +184,9 @@ def test_dx_over_real_token_rows_vs_all_rows(drop):
     assert np.abs(g_g[k][touched]).sum(1).min() > 0           # every real token received its gradient
     untouched = np.setdiff1d(np.arange(g_g[k].shape[0]), touched)
     assert not g_g[k][untouched].any()
+    gall = max(float(np.abs(v).max()) for v in g_a.values())
     for name in g_a:                                          # nothing else moves
         m = float(np.abs(g_a[name]).max())
-        np.testing.assert_allclose(g_g[name], g_a[name], rtol=0, atol=1e-5 * m + 1e-9, err_msg=name)
+        bias = name.endswith(('W_Q.bias', 'W_K.bias', 'W_V.bias')) and name.startswith('news_encoder')
+        atol = 2.5e-2 * m + 1e-4 * gall if bias else 1e-5 * m + 1e-9       # W_K.bias is analytically zero: rounding noise
+        np.testing.assert_allclose(g_g[name], g_a[name], rtol=0, atol=atol, err_msg=name)
