@@ -93,10 +93,13 @@ def make_workload(a, rank):
     return args, ctor, news
 
 
-def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20, fused=True):
-    """Algorithmic FLOPs per step for each named kernel of the step."""
+def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20, fused=True, real_frac=1.0):
+    """Algorithmic FLOPs per step for each named kernel of the step.  real_frac = share of the
+    title tokens that are not the padding id: the NRMS backward contracts enc.dx / enc.dwqkv over those rows only (a pad
+    token's embedding row is zero and its gradient is dropped, NRMS.py:73), so only they are algorithmic work."""
     n = B * (T + 1 + K_NEG)
     M, Mu = n * L, B * T
+    Mr = M * real_frac
     f = {}
     if model == 'NRMS':
         f['mhsa.qkv'] = 2.0 * M * D * 3 * H + 2.0 * Mu * H * 3 * H
@@ -116,7 +119,8 @@ def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20, fu
     f['pool.dw1'] = f['pool.fc1']
     # bf16 tensor-core title encoder (nr_encoder.cu)
     if model == 'NRMS':
-        f['enc.qkv'] = f['enc.dwqkv'] = f['enc.dx'] = 2.0 * M * D * 3 * H + 2.0 * Mu * H * 3 * H
+        f['enc.qkv'] = 2.0 * M * D * 3 * H + 2.0 * Mu * H * 3 * H
+        f['enc.dwqkv'] = f['enc.dx'] = 2.0 * Mr * D * 3 * H + 2.0 * Mu * H * 3 * H
         f['enc.attn_fwd'] = f['attn_fwd']
         f['enc.attn_bwd'] = f['attn_bwd']
         f['enc.fc1'] = f['enc.pool_dx'] = f['enc.dw1'] = 2.0 * (M + Mu) * H * Q
@@ -135,7 +139,7 @@ def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20, fu
     return f
 
 
-def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, fused=True):
+def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, fused=True, real_frac=1.0):
     """Algorithmic HBM bytes per step for each named kernel of the bf16 step: what the kernel has to read and
     write once, on real (unpadded) tokens.  M title tokens, Mu history tokens."""
     n = B * (T + 1 + K_NEG)
@@ -147,9 +151,10 @@ def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, fused=True):
         b['enc.stage'] = M * (4 + (D + 1) * 2) + tab + Mu * (H * 4 + (H + 1) * 2)     # ids + table + fp32 rows in, bf16 out
         b['enc.qkv'] = M * (D + 1) * 2 + Mu * (H + 1) * 2 + tok * 3 * H * 2
         b['enc.attn_fwd'] = tok * (3 * H + H) * 2 + M * H // 4                         # qkv in, ctx out, keep bits
-        b['enc.attn_bwd'] = tok * (3 * H + H + 3 * H) * 2                              # qkv + dctx in, dqkv out
-        b['enc.dwqkv'] = tok * 3 * H * 2 + M * (D + 1) * 2 + Mu * (H + 1) * 2
-        b['enc.dx'] = tok * 3 * H * 2 + tab + Mu * H * 4                               # dqkv in, table gradient / fp32 dx out
+        Mr = M * real_frac                     # title rows that carry a real token: the only dqkv rows that are kept
+        b['enc.attn_bwd'] = tok * (3 * H + H) * 2 + (Mr + Mu) * 3 * H * 2              # qkv + dctx in, compact dqkv out
+        b['enc.dwqkv'] = (Mr + Mu) * 3 * H * 2 + Mr * (D + 1) * 2 + Mu * (H + 1) * 2
+        b['enc.dx'] = (Mr + Mu) * 3 * H * 2 + tab + Mu * H * 4                         # dqkv in, table gradient / fp32 dx out
     else:
         tok = M
         b['enc.stage'] = M * (4 + D * 4 + (D + 1) * 2)
@@ -392,8 +397,13 @@ def train_leg(a, model_name, rank, world, sampler_idx=None, keep_load=False):
     # with the abstract view every news contributes L_TITLE + L_ABSTRACT token rows to the conv / pooling kernels
     Ltok = L_TITLE + (L_ABSTRACT if (model_name == 'NAML' and a.abstract) else 0)
     fused = os.environ.get('NR_ENC_FUSED', '1') != '0'
-    ft = flops_table(model_name, a.batch, L=Ltok, fused=fused)
-    bt = bytes_table(model_name, a.batch, L=Ltok, fused=fused) if a.precision == 'bf16' else {}
+    # NRMS batches carry token ids (B, T|C, L): the share of non-pad tokens sizes the compact backward (NR_DX_GATHER=0:
+    # every padded row is computed and counted)
+    real_frac = 1.0
+    if model_name == 'NRMS' and os.environ.get('NR_DX_GATHER', '1') != '0':
+        real_frac = float(np.mean([np.concatenate([(b[0] != 0).ravel(), (b[2] != 0).ravel()]).mean() for b in host]))
+    ft = flops_table(model_name, a.batch, L=Ltok, fused=fused, real_frac=real_frac)
+    bt = bytes_table(model_name, a.batch, L=Ltok, fused=fused, real_frac=real_frac) if a.precision == 'bf16' else {}
     tot = sum(v[1] for v in prof.values()) or 1.0
     kern = {k: {'ms_per_step': v[1] / a.steps, 'launches_per_step': v[0] / a.steps, 'share': v[1] / tot}
             for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
@@ -424,6 +434,7 @@ def train_leg(a, model_name, rank, world, sampler_idx=None, keep_load=False):
            'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roof, 'kernels': kern,
            'step_tensor_frac': (gf_sample * 1e9 * B * a.steps / (ms * 1e-3) / 1e12) / pk['tensor'],
            'final_loss': losses[-1] if losses else None, 'params_identical_across_ranks': params_identical,
+           'real_token_frac': real_frac,
            'workload': f'{model_name} train step (fwd+bwd+allreduce+Adam), MIND-small shape: batch {B}/GPU, '
                        f'title len {L_TITLE}, history {T_HIST}, npratio {K_NEG}, 300-d emb, 20x20 heads, '
                        f'drop 0.2, V={V_SMALL}, N={N_SMALL}' + (f', + abstract view ({L_ABSTRACT} tokens)' if (model_name == 'NAML' and a.abstract) else '')}

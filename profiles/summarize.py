@@ -91,7 +91,8 @@ NAMES = (('fused_enc_fwd_kernel', 'enc.fused_fwd'), ('adam_dev_kernel', 'adam'),
          ('stage_rows_kernel', 'enc.stage'), ('pack_weights_kernel', 'enc.pack_w'), ('EpiTanhLogit', 'enc.fc1'),
          ('EpiPoolDx', 'enc.pool_dx'), ('EpiDx', 'enc.dx'), ('TnEpiPlain', 'enc.dw1'), ('TnEpiQkv', 'enc.dwqkv'),
          ('TnEpiConv', 'enc.dwconv'), ('attn_fwd', 'enc.attn_fwd'), ('attn_bwd', 'enc.attn_bwd'),
-         ('pool_tail_fwd', 'enc.pool_fwd'), ('pool_tail_bwd', 'enc.pool_bwd'))
+         ('pool_tail_fwd', 'enc.pool_fwd'), ('pool_tail_bwd', 'enc.pool_bwd'), ('dx_rowlist_kernel', 'enc.dx_rows'),
+         ('zero_tail_rows_kernel', 'enc.dx_rows'))
 
 
 def traffic(src, model, dst):
