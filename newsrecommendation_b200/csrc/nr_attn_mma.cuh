@@ -428,13 +428,13 @@ attn_fwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
 // COMPACT: dqkv holds the rows of real tokens only (rowmap: padded row -> compact row or -1; dx_rowlist_kernel), the
 // layout enc.dx and enc.dwqkv then contract over; the bias gradients (column sums over ALL rows, which the ones column
 // of Xb used to deliver through enc.dwqkv) are accumulated here from the fp32 fragments.  The host sizes the grid so
-// that 4 * gridDim.x is a multiple of heads: a warp then sees ONE head and keeps its 6 NT partial sums in registers.
+// that 4 * gridDim.x is a multiple of heads: a warp then sees ONE head, keeps its 6 NT partial sums in registers and
+// leaves them in the dbpart scratch (4 * gridDim.x x 3 x DK floats) for db_reduce_kernel.
 template <int DK, bool MASK, bool COMPACT = false>
 static __global__ void __launch_bounds__(128)
 attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
                     bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale, int hs, int ms,
-                    const int32_t* __restrict__ rowmap = nullptr, float* __restrict__ dbq = nullptr,
-                    float* __restrict__ dbk = nullptr, float* __restrict__ dbv = nullptr) {
+                    const int32_t* __restrict__ rowmap = nullptr, float* __restrict__ dbq = nullptr) {   // dbq: dbpart scratch
     constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -464,8 +464,6 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     float bq[NT][2], bk2[NT][2], bv[NT][2];        // COMPACT: column sums of dQ, dK, dV over this warp's items
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) bq[nt][0] = bq[nt][1] = bk2[nt][0] = bk2[nt][1] = bv[nt][0] = bv[nt][1] = 0.f;
-    const int my_head = item % heads;
-    const bool any_item = item < items;
     if (item < items) issue(item, 0);
     for (int stage = 0; item < items; item += stride, stage ^= 1) {
         const int64_t seq = item / heads;
@@ -578,7 +576,10 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
         __syncwarp();
     }
     if (COMPACT) {
-        // rows 4 lanes apart hold the same columns: fold the 8 row groups, then lanes 0..3 add their 2 NT columns
+        // rows 4 lanes apart hold the same columns: fold the 8 row groups, then lanes 0..3 write their 2 NT columns of
+        // this warp's partial sums, dbpart[warp][q | k | v][DK] (zeros for a warp without items); db_reduce_kernel adds
+        // the partials of each head in warp order, so the bias gradients do not depend on the order atomics land in
+        float* mine = dbq + (int64_t)((int)blockIdx.x * 4 + warp) * 3 * DK;
 #pragma unroll
         for (int nt = 0; nt < NT; ++nt)
 #pragma unroll
@@ -591,15 +592,35 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
                     c += __shfl_xor_sync(0xFFFFFFFFu, c, o);
                 }
                 const int col = nt * 8 + 2 * t + e;
-                if (any_item && g == 0 && col < DK) {
-                    if (dbq) atomicAdd(dbq + my_head * DK + col, a * scale);
-                    if (dbk) atomicAdd(dbk + my_head * DK + col, b * scale);
-                    if (dbv) atomicAdd(dbv + my_head * DK + col, c);
+                if (g == 0 && col < DK) {
+                    mine[col] = a * scale;
+                    mine[DK + col] = b * scale;
+                    mine[2 * DK + col] = c;
                 }
             }
     }
 }
 
+// bias gradients of the COMPACT backward: db[m][head*DK + col] += sum over the warps w = head (mod heads) of
+// part[w][m][col], in increasing w (a fixed order: run-to-run identical).  One thread per output element.
+static __global__ void db_reduce_kernel(const float* __restrict__ part, int nwarps, int heads, int DK,
+                                        float* __restrict__ dbq, float* __restrict__ dbk, float* __restrict__ dbv) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int H = heads * DK;
+    if (i >= 3 * H) return;
+    const int m = i / H, hc = i - m * H, head = hc / DK, col = hc - head * DK;
+    float s = 0.f;
+    const float* src = part + (int64_t)m * DK + col;
+    for (int w = head; w < nwarps; w += 16 * heads) {        // 16 loads in flight, added in warp order
+        float v[16];
+#pragma unroll
+        for (int u = 0; u < 16; ++u) v[u] = w + u * heads < nwarps ? __ldg(src + (int64_t)(w + u * heads) * 3 * DK) : 0.f;
+#pragma unroll
+        for (int u = 0; u < 16; ++u) s += v[u];
+    }
+    float* db = m == 0 ? dbq : (m == 1 ? dbk : dbv);
+    if (db) db[hc] += s;
+}
 
 // ---------------------------------------------------------------------------------------------------------------
 // Blocked variant for sequences of up to 32*NB positions (the user encoder: 50 clicked titles, pitch 64).

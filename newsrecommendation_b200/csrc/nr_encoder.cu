@@ -302,9 +302,11 @@ struct Plan {
     // save
     size_t o_wb, o_w1b, o_w1t, o_wt, o_bias, o_keep, o_keep_in, o_xb, o_qkv, o_y, o_e, o_alpha, o_logits, save_bytes;
     // backward workspace
-    size_t o_dz, o_dy, o_dqkv, o_rowlist, ws_bytes;
+    size_t o_dz, o_dy, o_dqkv, o_rowlist, o_dbpart, ws_bytes;
 };
 
+// scratch of the compact attention backward: one 3 x dk slot of partial bias sums per warp of the largest grid
+static size_t dbpart_bytes(int heads, int dk) { return (size_t)4 * (2 * sm_count() + heads) * 3 * dk * sizeof(float); }
 Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     Plan p;
     const bool pool = e->kind == NR_ENC_POOL;
@@ -339,6 +341,7 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     p.o_dy = take(pool ? 0 : (size_t)p.R * e->H * 2);
     p.o_dqkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
     p.o_rowlist = take(e->kind == NR_ENC_MHSA ? 64 + (size_t)p.R * 8 : 0);     // [count, pad to 64 bytes, list (R), rowmap (R)]
+    p.o_dbpart = take(e->kind == NR_ENC_MHSA ? dbpart_bytes(e->heads, e->H / e->heads) : 0);
     p.ws_bytes = o;
     return p;
 }
@@ -457,8 +460,9 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     }
     ProfScope ps("enc.attn_bwd", st);
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK),
-                                            hm ? 3 * DK : DK, hm ? DK : heads * DK, rowmap, db ? db[0] : nullptr,
-                                            db ? db[1] : nullptr, db ? db[2] : nullptr);
+                                            hm ? 3 * DK : DK, hm ? DK : heads * DK, rowmap, COMPACT ? db[3] : nullptr);
+    if (COMPACT)        // db[3] = per-warp partial sums (dbpart_bytes), folded in a fixed order
+        amma::db_reduce_kernel<<<(3 * heads * DK + 127) / 128, 128, 0, st>>>(db[3], (int)grid * 4, heads, DK, db[0], db[1], db[2]);
     return check_last("enc.attn_bwd");
 }
 // blocked variant: 32 < pitch <= 64 (the user encoder's 50 clicked titles)
@@ -542,7 +546,8 @@ int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, 
     }
     NR_ENC_DISPATCH_DK(dk, launch_attn_fwd<DK>(qkv, mask, ctx, n, S, SP, heads, p, seed, keep, st));
 }
-// rowmap (pitch 32 with a warp-MMA head width only, see compact_supported): dqkv rows of real tokens only, db filled here
+// rowmap (pitch 32 with a warp-MMA head width only, see compact_supported): dqkv rows of real tokens only, db[0..2] filled
+// here through the scratch db[3] (dbpart_bytes)
 static bool compact_supported(int SP, int dk) { return SP == 32 && (dk == 8 || dk == 16 || dk == 20 || dk == 32); }
 int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int SP, int heads,
                int dk, cudaStream_t st, const int32_t* rowmap = nullptr, float* const* db = nullptr) {
@@ -870,7 +875,7 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
             zero_tail_rows_kernel<<<TN_BK, 128, 0, st>>>(dqkv, cnt, p.R, 3 * H);
             if (int e = check_last("enc.dx_rows")) return e;
         }
-        float* const db[3] = {gr->db[0], gr->db[1], gr->db[2]};
+        float* const db[4] = {gr->db[0], gr->db[1], gr->db[2], (float*)(wsb + p.o_dbpart)};
         if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st, gather ? rowmap : nullptr,
                                gather ? db : nullptr))
             return e;
