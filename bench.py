@@ -435,6 +435,9 @@ def train_leg(a, model_name, rank, world, sampler_idx=None, keep_load=False):
            'step_tensor_frac': (gf_sample * 1e9 * B * a.steps / (ms * 1e-3) / 1e12) / pk['tensor'],
            'final_loss': losses[-1] if losses else None, 'params_identical_across_ranks': params_identical,
            'real_token_frac': real_frac,
+           'launch': ('eager' if graphed is None else
+                      'fwd + bwd + gradient exchange + Adam replayed from ONE CUDA graph' if graphed.tail_in_graph else
+                      'fwd + bwd replayed from one CUDA graph, gradient exchange + Adam eager'),
            'workload': f'{model_name} train step (fwd+bwd+allreduce+Adam), MIND-small shape: batch {B}/GPU, '
                        f'title len {L_TITLE}, history {T_HIST}, npratio {K_NEG}, 300-d emb, 20x20 heads, '
                        f'drop 0.2, V={V_SMALL}, N={N_SMALL}' + (f', + abstract view ({L_ABSTRACT} tokens)' if (model_name == 'NAML' and a.abstract) else '')}
@@ -553,13 +556,13 @@ def run_ours(a):
             'data': 'synthetic',
             'config': {'workload': main['workload'], 'model_family': legs[0], 'per_gpu_batch': B,
                        'global_batch': B * world, 'precision': a.precision, 'parallelism': f'dp{world}',
-                       'launch': 'eager' if a.no_graph else 'fwd+bwd replayed from one CUDA graph, all-reduce + Adam eager',
+                       'launch': main['launch'],
                        'l2_policy': '8 distinct resident batches rotated; per-step activations '
                                     '(>1 GB) exceed the 126 MB L2',
                        'legs': legs},
             'e2e': main['e2e'], 'gpu_launches': main['gpu_launches'], 'clocks': main['clocks'],
             'roofline': main['roofline'], 'kernels': main['kernels'], 'step_tensor_frac': main['step_tensor_frac'],
-            'final_loss': main['final_loss'],
+            'real_token_frac': main['real_token_frac'], 'final_loss': main['final_loss'],
         }
         if world > 1:
             line['params_identical_across_ranks'] = main['params_identical_across_ranks']

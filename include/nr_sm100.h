@@ -279,7 +279,10 @@ size_t nr_title_encoder_infer_bytes(const nr_title_encoder_t* enc, int64_t n);
 /* out (n,H) fp32 */
 int nr_title_encoder_fwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, float* out,
                          void* save, size_t save_bytes, void* ws, size_t ws_bytes, void* stream);
-/* g (n,H) fp32 = dL/dout */
+/* g (n,H) fp32 = dL/dout.  MHSA kind over NR_ROWS_TOKEN rows (the NRMS title encoder, NRMS.py:28,73): dqkv is kept only
+ * for the rows of real tokens (id != 0 = padding_idx); dtable, dw[] contract over those rows, db[] is summed over all
+ * rows inside the attention backward in a fixed order.  NR_DX_GATHER=0 in the environment (read per call) keeps every
+ * padded row; results agree to the order of fp32 reductions (db: to bf16 rounding of dqkv). */
 int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, int64_t n, const float* g,
                          const void* save, size_t save_bytes, const nr_title_encoder_grads_t* grads,
                          void* ws, size_t ws_bytes, void* stream);
