@@ -190,3 +190,63 @@ def test_dx_over_real_token_rows_vs_all_rows(drop):
         bias = name.endswith(('W_Q.bias', 'W_K.bias', 'W_V.bias')) and name.startswith('news_encoder')
         atol = 2.5e-2 * m + 1e-4 * gall if bias else 1e-5 * m + 1e-9       # W_K.bias is analytically zero: rounding noise
         np.testing.assert_allclose(g_g[name], g_a[name], rtol=0, atol=atol, err_msg=name)
+
+
+@pytest.mark.parametrize('case', ['all_pad', 'no_pad', 'one_title', 'one_real_token', 'ragged_517'])
+def test_compact_backward_edge_cases(case):
+    """The compact title-encoder backward at the edges of its row list: no real token at all (count 0: enc.dx and
+    enc.dwqkv schedule no tile, the bias gradients still come out of attn_bwd), no pad token, a single title (fewer
+    items than the attention grid has warps), a single real token (one compact row, 63 zero-filled gather rows), and a
+    ragged count that is a multiple of neither 64 nor 128 — each against the all-rows backward (NR_DX_GATHER=0)."""
+    kind, kw, Pn, bt, model = build_model('nrms_ulm0', precision='bf16', drop_rate=0.0)
+    model.train()
+    L, V = kw['L'], kw['V']
+    rs = np.random.RandomState(11)
+    n = {'all_pad': 37, 'no_pad': 37, 'one_title': 1, 'one_real_token': 9, 'ragged_517': 64}[case]
+    ids = rs.randint(1, V, size=(n, L)).astype(np.int32)
+    if case == 'all_pad':
+        ids[:] = 0
+    elif case == 'one_real_token':
+        ids[:] = 0
+        ids[5, 3] = 7
+    elif case == 'ragged_517':
+        ids[:] = 0
+        flat = ids.reshape(-1)
+        flat[rs.permutation(flat.size)[:517]] = rs.randint(1, V, size=517)      # holes inside titles too
+    elif case == 'one_title':
+        ids[0, 20:] = 0
+    x = T(ids).cuda()
+    w = torch.from_numpy(rs.randn(n, 400).astype(np.float32)).cuda()
+
+    def grads(gather):
+        old = os.environ.pop('NR_DX_GATHER', None)
+        if not gather:
+            os.environ['NR_DX_GATHER'] = '0'
+        try:
+            model.zero_grad(set_to_none=True)
+            out = model.news_encoder(x)
+            (out * w).sum().backward()
+            return out.detach().cpu().numpy(), {k: p.grad.detach().cpu().numpy().copy()
+                                                for k, p in model.news_encoder.named_parameters() if p.grad is not None}
+        finally:
+            os.environ.pop('NR_DX_GATHER', None)
+            if old is not None:
+                os.environ['NR_DX_GATHER'] = old
+    o_c, g_c = grads(True)
+    o_a, g_a = grads(False)
+    assert np.array_equal(o_c, o_a) and g_c.keys() == g_a.keys() and len(g_c) >= 10
+    gall = max(float(np.abs(v).max()) for v in g_a.values())
+    emb = 'embedding_matrix.weight'
+    real = np.unique(ids[ids != 0])
+    assert not g_c[emb][0].any()
+    assert not np.delete(g_c[emb], real, axis=0).any()
+    if real.size:
+        assert np.abs(g_c[emb][real]).sum(1).min() > 0
+    for k in g_a:
+        m = float(np.abs(g_a[k]).max())
+        bias = k.endswith(('W_Q.bias', 'W_K.bias', 'W_V.bias'))
+        atol = 2.5e-2 * m + 1e-4 * gall if bias else 1e-5 * m + 1e-7 * gall
+        np.testing.assert_allclose(g_c[k], g_a[k], rtol=0, atol=atol, err_msg=k)
+    if case == 'all_pad':      # zero input rows: no weight gradient in either mode, the biases do get one
+        assert not g_c['multi_head_self_attn.W_Q.weight'].any() and not g_c['multi_head_self_attn.W_V.weight'].any()
+        assert np.abs(g_c['multi_head_self_attn.W_V.bias']).max() > 0
