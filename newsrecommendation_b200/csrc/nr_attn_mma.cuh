@@ -434,7 +434,8 @@ template <int DK, bool MASK, bool COMPACT = false>
 static __global__ void __launch_bounds__(128)
 attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_mask, const bf16* __restrict__ dctx,
                     bf16* __restrict__ dqkv, int64_t items, int S, int heads, float scale, int hs, int ms,
-                    const int32_t* __restrict__ rowmap = nullptr, float* __restrict__ dbq = nullptr) {   // dbq: dbpart scratch
+                    const int32_t* __restrict__ rowmap = nullptr, float* __restrict__ dbq = nullptr,    // dbq: dbpart scratch
+                    const uint8_t* __restrict__ allpad = nullptr) {
     constexpr int NT = Cfg<DK>::NT, TILE = Cfg<DK>::TILE;
     extern __shared__ __align__(16) uint8_t smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -450,14 +451,21 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
     sl.init(lane, H);
     const int stride = (int)gridDim.x * 4;          // items = n * heads < 2^31 (host checked)
     int item = (int)blockIdx.x * 4 + warp;
+    // COMPACT without a key mask: a title whose 32 rows are all pad tokens (allpad[title], dx_rowlist_kernel) has
+    // q = k = v = the biases in every row, so A is uniform, dA is constant along the keys, dS = A (dA - rd) = 0,
+    // dQ = dK = 0 and sum_j dV_j = sum_i dO_i: such an item only needs its dO tile, for the V-bias column sums
+    // (half of the titles of a MIND step are the padding news of short histories).
+    auto skip_item = [&](int sq) -> bool { return COMPACT && !MASK && __ldg(allpad + sq) != 0; };
     auto issue = [&](int it, int stage) {
         const int sq = it / heads;
         const int hd = it - sq * heads;
         const bf16* src = qkv + (int64_t)sq * 32 * 3 * H + hd * hs;
         bf16* b = buf + stage * 4 * TILE;
-        prefetch_tile<DK>(b, src, sl.g3, sl);
-        prefetch_tile<DK>(b + TILE, src + ms, sl.g3, sl);
-        prefetch_tile<DK>(b + 2 * TILE, src + 2 * ms, sl.g3, sl);
+        if (!skip_item(sq)) {
+            prefetch_tile<DK>(b, src, sl.g3, sl);
+            prefetch_tile<DK>(b + TILE, src + ms, sl.g3, sl);
+            prefetch_tile<DK>(b + 2 * TILE, src + 2 * ms, sl.g3, sl);
+        }
         prefetch_tile<DK>(b + 3 * TILE, dctx + (int64_t)sq * 32 * H + hd * DK, sl.g1, sl);
         cp_async_commit();
     };
@@ -488,6 +496,25 @@ attn_bwd_mma_kernel(const bf16* __restrict__ qkv, const float* __restrict__ key_
             }
         cp_async_wait<1>();
         __syncwarp();
+        if (skip_item((int)seq)) {
+            // V-bias column sums straight from the dO tile: lane (g, t) adds rows g, g+8, g+16, g+24 of its 2 NT columns
+#pragma unroll
+            for (int h = 0; h < 4; ++h) {
+                const int r = g + 8 * h;
+                if (r < S) {
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) {
+                        const int col = nt * 8 + 2 * t;
+                        if (col < DK) {
+                            const float2 v2 = __bfloat1622float2(*(const __nv_bfloat162*)(Gs + r * Cfg<DK>::PITCH + col));
+                            bv[nt][0] += v2.x; bv[nt][1] += v2.y;
+                        }
+                    }
+                }
+            }
+            __syncwarp();
+            continue;
+        }
         bf16* dst = COMPACT ? dqkv + head * hs : dqkv + seq * 32 * 3 * H + head * hs;
         // ---- A = P/Z, dA = dO V^T, dS = A (dA - rd); dQ = dS K / sqrt(dk).  The key-major operands
         //      A^T and dS^T of dV = A^T dO and dK = dS^T Q are NOT recomputed (that was a second S^T = K Q^T,

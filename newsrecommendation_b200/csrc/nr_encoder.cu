@@ -145,7 +145,7 @@ struct EpiDx {
     float* dx_dense; float* dtable; RowsView x; int SP;
     const uint8_t* keep_in; int kpitch;     // input-dropout keep bits saved by enc.stage: 1 byte per 8 columns
     int64_t seq; int s; int64_t id;
-    const int32_t* rowlist;                 // row-gather mode: output row i is padded row rowlist[i] (dx_rowlist_kernel)
+    const int32_t* rowlist;                 // compact backward: output row i is padded row rowlist[i] (dx_rowlist_kernel)
     __device__ __forceinline__ void begin(const EpiCtx& cx, int64_t row) {
         if (rowlist) row = cx.live ? (int64_t)__ldg(rowlist + row) : 0;
         seq = row / SP; s = (int)(row - seq * SP);
@@ -208,19 +208,30 @@ struct EpiDx {
 // *count is zeroed by the caller.
 __global__ void __launch_bounds__(1024) dx_rowlist_kernel(const RowsView x, const int SP, const int64_t R,
                                                           int32_t* __restrict__ list, int32_t* __restrict__ rowmap,
-                                                          int32_t* __restrict__ count) {
+                                                          uint8_t* __restrict__ allpad, int32_t* __restrict__ count) {
     __shared__ int wsum[32];
     __shared__ int base;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // nn.Embedding.from_pretrained(..., padding_idx=0) keeps whatever row 0 of the pretrained matrix holds and only
+    // drops its gradient (NRMS.py:71-73).  A pad token's input row is zero only if that row is: when it is not, every
+    // position s < S stays in the list (dW needs it; enc.dx still skips id 0), and nothing is lost but the saving.
+    bool nz = false;
+    for (int c = threadIdx.x * 4; c < x.D; c += blockDim.x * 4) {
+        const float4 v = ldg4(x.table + c);
+        nz = nz || v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f;
+    }
+    const bool row0_live = __syncthreads_or(nz) != 0;
     const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     bool real = false;
     if (row < R) {
         const int64_t seq = row / SP;
         const int s = (int)(row - seq * SP);
-        real = s < x.S && x.id_of(seq, s) != 0;
+        real = s < x.S && (row0_live || x.id_of(seq, s) != 0);
     }
     const unsigned b = __ballot_sync(0xFFFFFFFFu, real);
     if (lane == 0) wsum[warp] = __popc(b);
+    // SP == 32 (compact_supported): a warp is exactly one title; a title without any listed row is ALL PAD
+    if (lane == 0 && row < R) allpad[row / SP] = b == 0u;
     __syncthreads();
     if (warp == 0) {
         const int c = wsum[lane];
@@ -340,7 +351,7 @@ Plan make_plan(const nr_title_encoder_t* e, int64_t n) {
     p.o_dz = take((size_t)p.R * e->Q * 2);
     p.o_dy = take(pool ? 0 : (size_t)p.R * e->H * 2);
     p.o_dqkv = take(e->kind == NR_ENC_MHSA ? (size_t)p.R * 3 * e->H * 2 : 0);
-    p.o_rowlist = take(e->kind == NR_ENC_MHSA ? 64 + (size_t)p.R * 8 : 0);     // [count, pad to 64 bytes, list (R), rowmap (R)]
+    p.o_rowlist = take(e->kind == NR_ENC_MHSA ? 64 + (size_t)p.R * 8 + (size_t)n : 0);     // [count, pad to 64 bytes, list (R), rowmap (R), allpad (n bytes)]
     p.o_dbpart = take(e->kind == NR_ENC_MHSA ? dbpart_bytes(e->heads, e->H / e->heads) : 0);
     p.ws_bytes = o;
     return p;
@@ -432,7 +443,8 @@ int launch_attn_fwd_mma(const bf16* qkv, const float* mask, bf16* ctx, int64_t n
 // rowmap != NULL: compact dqkv rows + bias gradients db[0..2] from the kernel (amma::attn_bwd_mma_kernel COMPACT)
 template <int DK, bool MASK, bool COMPACT = false>
 int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int heads,
-                        bool hm, cudaStream_t st, const int32_t* rowmap = nullptr, float* const* db = nullptr) {
+                        bool hm, cudaStream_t st, const int32_t* rowmap = nullptr, float* const* db = nullptr,
+                        const uint8_t* allpad = nullptr) {
     const size_t smem = 4 * amma::bwd_smem_per_warp(DK);
     auto kern = amma::attn_bwd_mma_kernel<DK, MASK, COMPACT>;
     NR_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -460,7 +472,7 @@ int launch_attn_bwd_mma(const bf16* qkv, const float* mask, const bf16* dctx, bf
     }
     ProfScope ps("enc.attn_bwd", st);
     kern<<<(unsigned)grid, 128, smem, st>>>(qkv, mask, dctx, dqkv, items, S, heads, 1.0f / sqrtf((float)DK),
-                                            hm ? 3 * DK : DK, hm ? DK : heads * DK, rowmap, COMPACT ? db[3] : nullptr);
+                                            hm ? 3 * DK : DK, hm ? DK : heads * DK, rowmap, COMPACT ? db[3] : nullptr, allpad);
     if (COMPACT)        // db[3] = per-warp partial sums (dbpart_bytes), folded in a fixed order
         amma::db_reduce_kernel<<<(3 * heads * DK + 127) / 128, 128, 0, st>>>(db[3], (int)grid * 4, heads, DK, db[0], db[1], db[2]);
     return check_last("enc.attn_bwd");
@@ -509,8 +521,8 @@ int launch_attn_bwd_blk(const bf16* qkv, const float* mask, const bf16* dctx, bf
                               : launch_attn_bwd_blk<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, hm, st))
 #define NR_MMA_FWD(DKV) (mask ? launch_attn_fwd_mma<DKV, true>(qkv, mask, ctx, n, S, heads, p, seed, keep, hm, st) \
                               : launch_attn_fwd_mma<DKV, false>(qkv, mask, ctx, n, S, heads, p, seed, keep, hm, st))
-#define NR_MMA_BWD(DKV) (rowmap ? (mask ? launch_attn_bwd_mma<DKV, true, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st, rowmap, db) \
-                                        : launch_attn_bwd_mma<DKV, false, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st, rowmap, db)) \
+#define NR_MMA_BWD(DKV) (rowmap ? (mask ? launch_attn_bwd_mma<DKV, true, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st, rowmap, db, allpad) \
+                                        : launch_attn_bwd_mma<DKV, false, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st, rowmap, db, allpad)) \
                                 : (mask ? launch_attn_bwd_mma<DKV, true>(qkv, mask, dctx, dqkv, n, S, heads, hm, st) \
                                         : launch_attn_bwd_mma<DKV, false>(qkv, mask, dctx, dqkv, n, S, heads, hm, st)))
 
@@ -550,7 +562,8 @@ int attn_fwd_b(const bf16* qkv, const float* mask, bf16* ctx, int64_t n, int S, 
 // here through the scratch db[3] (dbpart_bytes)
 static bool compact_supported(int SP, int dk) { return SP == 32 && (dk == 8 || dk == 16 || dk == 20 || dk == 32); }
 int attn_bwd_b(const bf16* qkv, const float* mask, const bf16* dctx, bf16* dqkv, int64_t n, int S, int SP, int heads,
-               int dk, cudaStream_t st, const int32_t* rowmap = nullptr, float* const* db = nullptr) {
+               int dk, cudaStream_t st, const int32_t* rowmap = nullptr, float* const* db = nullptr,
+               const uint8_t* allpad = nullptr) {
     const bool hm = qkv_head_major(SP, dk);
     NR_REQUIRE(!rowmap || compact_supported(SP, dk), "attention backward: compact rows need pitch 32 and a warp-MMA head width");
     if (SP == 32) {
@@ -868,16 +881,17 @@ int nr_title_encoder_bwd(const nr_title_encoder_t* enc, const nr_rows_t* rows, i
         int32_t* cnt = (int32_t*)(wsb + p.o_rowlist);
         int32_t* list = cnt + 16;
         int32_t* rowmap = list + p.R;
+        uint8_t* allpad = (uint8_t*)(rowmap + p.R);
         if (gather) {
             ProfScope ps("enc.dx_rows", st);
             NR_CUDA(cudaMemsetAsync(cnt, 0, 4, st));
-            dx_rowlist_kernel<<<(unsigned)((p.R + 1023) / 1024), 1024, 0, st>>>(xv, p.SP, p.R, list, rowmap, cnt);
+            dx_rowlist_kernel<<<(unsigned)((p.R + 1023) / 1024), 1024, 0, st>>>(xv, p.SP, p.R, list, rowmap, allpad, cnt);
             zero_tail_rows_kernel<<<TN_BK, 128, 0, st>>>(dqkv, cnt, p.R, 3 * H);
             if (int e = check_last("enc.dx_rows")) return e;
         }
         float* const db[4] = {gr->db[0], gr->db[1], gr->db[2], (float*)(wsb + p.o_dbpart)};
         if (int e = attn_bwd_b(qkv, enc->mask, dy, dqkv, n, S, p.SP, enc->heads, H / enc->heads, st, gather ? rowmap : nullptr,
-                               gather ? db : nullptr))
+                               gather ? db : nullptr, gather ? allpad : nullptr))
             return e;
         // dX (the embedding-table gradient: 15 of the 19 MB of the NRMS gradient bucket) BEFORE the weight gradient:
         // the caller can start exchanging that part of the bucket while enc.dwqkv still runs (gr->dtable_ready)

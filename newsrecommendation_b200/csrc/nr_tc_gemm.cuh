@@ -13,6 +13,7 @@
 // drained by epilogue group a, so two tile epilogues and the MMAs of a third tile overlap (the
 // epilogue of these K <= 1200 GEMMs costs more cycles than their MMAs).
 // Persistent: grid = #SMs, tiles assigned round-robin with n fastest (A tile reuse through L2).
+// DYNM instantiations read the number of rows that exist from device memory (the compact backward).
 // Two variants that cut L2 reads of the weight operand (a B-resident slice in shared memory; TMA-multicast CTA pairs)
 // were built, parity-tested and measured no faster on B200; they are not in the tree.
 #pragma once

@@ -192,17 +192,20 @@ def test_dx_over_real_token_rows_vs_all_rows(drop):
         np.testing.assert_allclose(g_g[name], g_a[name], rtol=0, atol=atol, err_msg=name)
 
 
-@pytest.mark.parametrize('case', ['all_pad', 'no_pad', 'one_title', 'one_real_token', 'ragged_517'])
+@pytest.mark.parametrize('case', ['all_pad', 'no_pad', 'one_title', 'one_real_token', 'ragged_517', 'row0_nonzero'])
 def test_compact_backward_edge_cases(case):
     """The compact title-encoder backward at the edges of its row list: no real token at all (count 0: enc.dx and
     enc.dwqkv schedule no tile, the bias gradients still come out of attn_bwd), no pad token, a single title (fewer
     items than the attention grid has warps), a single real token (one compact row, 63 zero-filled gather rows), and a
-    ragged count that is a multiple of neither 64 nor 128 — each against the all-rows backward (NR_DX_GATHER=0)."""
+    ragged count that is a multiple of neither 64 nor 128 — each against the all-rows backward (NR_DX_GATHER=0).
+    `row0_nonzero`: `from_pretrained(..., padding_idx=0)` (NRMS.py:71-73) keeps a non-zero pretrained row 0, so a pad
+    token's input is NOT zero and the W_Q/W_K/W_V gradients need its rows: the row list then keeps every position.
+    Titles that are all padding take the attention-backward shortcut (dQ = dK = 0, sum dV = sum dO) in the other cases."""
     kind, kw, Pn, bt, model = build_model('nrms_ulm0', precision='bf16', drop_rate=0.0)
     model.train()
     L, V = kw['L'], kw['V']
     rs = np.random.RandomState(11)
-    n = {'all_pad': 37, 'no_pad': 37, 'one_title': 1, 'one_real_token': 9, 'ragged_517': 64}[case]
+    n = {'all_pad': 37, 'no_pad': 37, 'one_title': 1, 'one_real_token': 9, 'ragged_517': 64, 'row0_nonzero': 21}[case]
     ids = rs.randint(1, V, size=(n, L)).astype(np.int32)
     if case == 'all_pad':
         ids[:] = 0
@@ -215,6 +218,11 @@ def test_compact_backward_edge_cases(case):
         flat[rs.permutation(flat.size)[:517]] = rs.randint(1, V, size=517)      # holes inside titles too
     elif case == 'one_title':
         ids[0, 20:] = 0
+    elif case == 'row0_nonzero':
+        ids[:, 9:] = 0
+        ids[3] = 0                                               # an all-pad title that is NOT a shortcut case here
+        with torch.no_grad():
+            model.news_encoder.embedding_matrix.weight[0] = torch.from_numpy(rs.randn(300).astype(np.float32) * 0.1).cuda()
     x = T(ids).cuda()
     w = torch.from_numpy(rs.randn(n, 400).astype(np.float32)).cuda()
 
@@ -242,6 +250,8 @@ def test_compact_backward_edge_cases(case):
     assert not np.delete(g_c[emb], real, axis=0).any()
     if real.size:
         assert np.abs(g_c[emb][real]).sum(1).min() > 0
+    if case == 'row0_nonzero':      # pad rows feed dW: a backward that dropped them would be off by far more than 1e-5
+        assert np.abs(g_c['multi_head_self_attn.W_V.weight']).max() > 0
     for k in g_a:
         m = float(np.abs(g_a[k]).max())
         bias = k.endswith(('W_Q.bias', 'W_K.bias', 'W_V.bias'))
