@@ -139,7 +139,7 @@ def flops_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, heads=20, fu
     return f
 
 
-def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, fused=True, real_frac=1.0):
+def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, fused=True, real_frac=1.0, allpad_frac=0.0):
     """Algorithmic HBM bytes per step for each named kernel of the bf16 step: what the kernel has to read and
     write once, on real (unpadded) tokens.  M title tokens, Mu history tokens."""
     n = B * (T + 1 + K_NEG)
@@ -152,7 +152,9 @@ def bytes_table(model, B, L=L_TITLE, T=T_HIST, D=300, H=400, Q=200, fused=True, 
         b['enc.qkv'] = M * (D + 1) * 2 + Mu * (H + 1) * 2 + tok * 3 * H * 2
         b['enc.attn_fwd'] = tok * (3 * H + H) * 2 + M * H // 4                         # qkv in, ctx out, keep bits
         Mr = M * real_frac                     # title rows that carry a real token: the only dqkv rows that are kept
-        b['enc.attn_bwd'] = tok * (3 * H + H) * 2 + (Mr + Mu) * 3 * H * 2              # qkv + dctx in, compact dqkv out
+        # qkv + dctx in, compact dqkv out; a title of pad tokens only (allpad_frac of them) has dQ = dK = 0 and needs
+        # just its dctx tile for the V-bias sums
+        b['enc.attn_bwd'] = (M * (1 - allpad_frac) + Mu) * (3 * H + H) * 2 + M * allpad_frac * H * 2 + (Mr + Mu) * 3 * H * 2
         b['enc.dwqkv'] = (Mr + Mu) * 3 * H * 2 + Mr * (D + 1) * 2 + Mu * (H + 1) * 2
         b['enc.dx'] = (Mr + Mu) * 3 * H * 2 + tab + Mu * H * 4                         # dqkv in, table gradient / fp32 dx out
     else:
@@ -399,11 +401,14 @@ def train_leg(a, model_name, rank, world, sampler_idx=None, keep_load=False):
     fused = os.environ.get('NR_ENC_FUSED', '1') != '0'
     # NRMS batches carry token ids (B, T|C, L): the share of non-pad tokens sizes the compact backward (NR_DX_GATHER=0:
     # every padded row is computed and counted)
-    real_frac = 1.0
+    real_frac, allpad_frac = 1.0, 0.0
     if model_name == 'NRMS' and os.environ.get('NR_DX_GATHER', '1') != '0':
         real_frac = float(np.mean([np.concatenate([(b[0] != 0).ravel(), (b[2] != 0).ravel()]).mean() for b in host]))
+        allpad_frac = float(np.mean([np.concatenate([(b[0] == 0).all(-1).ravel(), (b[2] == 0).all(-1).ravel()]).mean()
+                                     for b in host]))
     ft = flops_table(model_name, a.batch, L=Ltok, fused=fused, real_frac=real_frac)
-    bt = bytes_table(model_name, a.batch, L=Ltok, fused=fused, real_frac=real_frac) if a.precision == 'bf16' else {}
+    bt = (bytes_table(model_name, a.batch, L=Ltok, fused=fused, real_frac=real_frac, allpad_frac=allpad_frac)
+          if a.precision == 'bf16' else {})
     tot = sum(v[1] for v in prof.values()) or 1.0
     kern = {k: {'ms_per_step': v[1] / a.steps, 'launches_per_step': v[0] / a.steps, 'share': v[1] / tot}
             for k, v in sorted(prof.items(), key=lambda kv: -kv[1][1])}
@@ -434,7 +439,7 @@ def train_leg(a, model_name, rank, world, sampler_idx=None, keep_load=False):
            'gpu_launches': int(launches), 'clocks': clocks, 'roofline': roof, 'kernels': kern,
            'step_tensor_frac': (gf_sample * 1e9 * B * a.steps / (ms * 1e-3) / 1e12) / pk['tensor'],
            'final_loss': losses[-1] if losses else None, 'params_identical_across_ranks': params_identical,
-           'real_token_frac': real_frac,
+           'real_token_frac': real_frac, 'allpad_title_frac': allpad_frac,
            'launch': ('eager' if graphed is None else
                       'fwd + bwd + gradient exchange + Adam replayed from ONE CUDA graph' if graphed.tail_in_graph else
                       'fwd + bwd replayed from one CUDA graph, gradient exchange + Adam eager'),
@@ -562,7 +567,8 @@ def run_ours(a):
                        'legs': legs},
             'e2e': main['e2e'], 'gpu_launches': main['gpu_launches'], 'clocks': main['clocks'],
             'roofline': main['roofline'], 'kernels': main['kernels'], 'step_tensor_frac': main['step_tensor_frac'],
-            'real_token_frac': main['real_token_frac'], 'final_loss': main['final_loss'],
+            'real_token_frac': main['real_token_frac'], 'allpad_title_frac': main['allpad_title_frac'],
+            'final_loss': main['final_loss'],
         }
         if world > 1:
             line['params_identical_across_ranks'] = main['params_identical_across_ranks']
